@@ -1,0 +1,268 @@
+"""ctypes binding of libabub_cuda.so (include/abub_cuda.h) -- harness plumbing only.
+
+The product is the shared library; this module exists so that tests and bench.py can
+call the C ABI with numpy buffers.  There is no CPU fallback: a missing library or a
+failing call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libabub_cuda.so")
+
+ABUB_MAX_TRACK = 10
+
+EXPORTS = [
+    "abub_ctx_create", "abub_ctx_destroy", "abub_last_error", "abub_sync", "abub_stream",
+    "abub_set_background", "abub_set_background_from_training",
+    "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_device_ptr",
+    "abub_event_set_nframes",
+    "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_scan", "abub_trigger_results", "abub_trigger",
+    "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_finish",
+    "abub_train_partials", "abub_train_allreduce", "abub_train_finish_partials",
+    "abub_localize", "abub_localize_binary", "abub_process_frame",
+]
+
+
+class Blob(C.Structure):
+    """struct abub_blob."""
+    _fields_ = [("k", C.c_int32), ("x", C.c_int32), ("y", C.c_int32), ("w", C.c_int32), ("h", C.c_int32),
+                ("npts", C.c_int32), ("first_px", C.c_int32), ("reserved", C.c_int32),
+                ("sum_x", C.c_int64), ("sum_y", C.c_int64),
+                ("area", C.c_double), ("m00", C.c_double), ("m10", C.c_double), ("m01", C.c_double)]
+
+
+class AbubError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """dlopen the in-tree library; raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise AbubError(f"{LIB_PATH} is missing: run `python -m autobub3hs_b200.build` (no CPU fallback exists)")
+    lib = C.CDLL(LIB_PATH)
+    vp, ip, u8p = C.c_void_p, C.POINTER(C.c_int), C.c_void_p
+    lib.abub_ctx_create.argtypes = [C.c_int] * 6 + [C.POINTER(vp)]
+    lib.abub_ctx_destroy.argtypes = [vp]
+    lib.abub_ctx_destroy.restype = None
+    lib.abub_last_error.argtypes = [vp]
+    lib.abub_last_error.restype = C.c_char_p
+    lib.abub_sync.argtypes = [vp]
+    lib.abub_stream.argtypes = [vp]
+    lib.abub_stream.restype = vp
+    lib.abub_set_background.argtypes = [vp, C.c_int, u8p, u8p, C.c_int]
+    lib.abub_set_background_from_training.argtypes = [vp, C.c_int]
+    lib.abub_pinned_acquire.argtypes = [vp, C.c_int, C.POINTER(vp)]
+    lib.abub_event_submit.argtypes = [vp, C.c_int, ip]
+    lib.abub_event_upload.argtypes = [vp, C.c_int, C.c_int, u8p, C.c_int]
+    lib.abub_event_device_ptr.argtypes = [vp, C.c_int, C.POINTER(vp)]
+    lib.abub_event_set_nframes.argtypes = [vp, C.c_int, ip]
+    lib.abub_trigger_hist.argtypes = [vp, C.c_int, C.c_int]
+    lib.abub_trigger_hist_read.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.abub_trigger_scan.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.abub_trigger_results.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp]
+    lib.abub_trigger.argtypes = [vp, C.c_int, C.c_int, C.c_int, ip, ip, ip, vp]
+    lib.abub_train_begin.argtypes = [vp, C.c_int]
+    lib.abub_train_add_event.argtypes = [vp, C.c_int, u8p, C.POINTER(C.c_float), ip]
+    lib.abub_train_add_slot.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float), ip]
+    lib.abub_train_finish.argtypes = [vp, C.c_int, u8p, u8p, ip, ip]
+    lib.abub_train_partials.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    lib.abub_train_allreduce.argtypes = [vp, C.c_int, vp]
+    lib.abub_train_finish_partials.argtypes = [vp, C.c_int, u8p, u8p, ip, ip, ip]
+    lib.abub_localize.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(Blob), C.c_int, ip]
+    lib.abub_localize_binary.argtypes = [vp, C.c_int, u8p]
+    lib.abub_process_frame.argtypes = [vp, C.c_int, u8p, u8p, u8p, vp]
+    for name in EXPORTS:
+        fn = getattr(lib, name)
+        if name not in ("abub_ctx_destroy", "abub_last_error", "abub_stream"):
+            fn.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def _p(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _u8(a: np.ndarray) -> np.ndarray:
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    return a
+
+
+class Context:
+    """Thin RAII wrapper around abub_ctx*."""
+
+    def __init__(self, rows: int, cols: int, ncams: int = 4, max_frames: int = 40, max_slots: int = 1,
+                 device: int = 0):
+        self.lib = load()
+        self.rows, self.cols, self.ncams, self.max_frames, self.max_slots = rows, cols, ncams, max_frames, max_slots
+        self.npix = rows * cols
+        h = C.c_void_p()
+        rc = self.lib.abub_ctx_create(device, rows, cols, ncams, max_frames, max_slots, C.byref(h))
+        self.h = h
+        if rc != 0:
+            msg = self.lib.abub_last_error(h).decode() if h else "abub_ctx_create failed"
+            if h:
+                self.lib.abub_ctx_destroy(h)
+                self.h = None
+            raise AbubError(f"abub_ctx_create rc={rc}: {msg}")
+
+    def close(self) -> None:
+        if getattr(self, "h", None):
+            self.lib.abub_ctx_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc: int, what: str) -> None:
+        if rc != 0:
+            raise AbubError(f"{what} rc={rc}: {self.lib.abub_last_error(self.h).decode()}")
+
+    # ---- plumbing ----
+    def sync(self) -> None:
+        self._ck(self.lib.abub_sync(self.h), "abub_sync")
+
+    def stream(self) -> int:
+        return int(self.lib.abub_stream(self.h) or 0)
+
+    def set_background(self, cam: int, mean: np.ndarray, sigma: np.ndarray, training_set_size: int) -> None:
+        m, s = _u8(mean), _u8(sigma)
+        assert m.size == self.npix and s.size == self.npix
+        self._ck(self.lib.abub_set_background(self.h, cam, _p(m), _p(s), training_set_size), "abub_set_background")
+
+    def set_background_from_training(self, cam: int) -> None:
+        self._ck(self.lib.abub_set_background_from_training(self.h, cam), "abub_set_background_from_training")
+
+    def pinned(self, slot: int) -> np.ndarray:
+        """numpy view [ncams, max_frames, rows, cols] of the slot's pinned staging buffer."""
+        p = C.c_void_p()
+        self._ck(self.lib.abub_pinned_acquire(self.h, slot, C.byref(p)), "abub_pinned_acquire")
+        n = self.ncams * self.max_frames * self.npix
+        buf = (C.c_uint8 * n).from_address(p.value)
+        return np.frombuffer(buf, dtype=np.uint8).reshape(self.ncams, self.max_frames, self.rows, self.cols)
+
+    def event_submit(self, slot: int, nframes: Sequence[int]) -> None:
+        nf = (C.c_int * self.ncams)(*nframes)
+        self._ck(self.lib.abub_event_submit(self.h, slot, nf), "abub_event_submit")
+
+    def event_upload(self, slot: int, cam: int, frames: np.ndarray) -> None:
+        f = _u8(frames)
+        n = 0 if f.size == 0 else f.shape[0]
+        self._ck(self.lib.abub_event_upload(self.h, slot, cam, _p(f) if n else None, n), "abub_event_upload")
+
+    def event_device_ptr(self, slot: int) -> int:
+        p = C.c_void_p()
+        self._ck(self.lib.abub_event_device_ptr(self.h, slot, C.byref(p)), "abub_event_device_ptr")
+        return int(p.value)
+
+    def event_set_nframes(self, slot: int, nframes: Sequence[int]) -> None:
+        nf = (C.c_int * self.ncams)(*nframes)
+        self._ck(self.lib.abub_event_set_nframes(self.h, slot, nf), "abub_event_set_nframes")
+
+    # ---- trigger ----
+    def trigger_hist(self, slot_first: int = 0, nslots: int = 1) -> None:
+        self._ck(self.lib.abub_trigger_hist(self.h, slot_first, nslots), "abub_trigger_hist")
+
+    def trigger_hist_read(self, slot: int, cam: int) -> np.ndarray:
+        out = np.zeros((self.max_frames, 256), np.uint32)
+        self._ck(self.lib.abub_trigger_hist_read(self.h, slot, cam, _p(out)), "abub_trigger_hist_read")
+        return out
+
+    def trigger_scan(self, slot_first: int = 0, nslots: int = 1, start_frames: Optional[np.ndarray] = None) -> None:
+        st = None if start_frames is None else np.ascontiguousarray(start_frames, dtype=np.int32)
+        self._ck(self.lib.abub_trigger_scan(self.h, slot_first, nslots, _p(st)), "abub_trigger_scan")
+
+    def trigger_results(self, slot_first: int = 0, nslots: int = 1, want_sig: bool = True):
+        n = nslots * self.ncams
+        trig, status, lt = (np.zeros(n, np.int32) for _ in range(3))
+        sig = np.zeros((n, self.max_frames), np.float64) if want_sig else None
+        self._ck(self.lib.abub_trigger_results(self.h, slot_first, nslots, _p(trig), _p(status), _p(lt), _p(sig)),
+                 "abub_trigger_results")
+        sh = (nslots, self.ncams)
+        return trig.reshape(sh), status.reshape(sh), lt.reshape(sh), (None if sig is None else sig.reshape(sh + (-1,)))
+
+    def trigger(self, slot: int, cam: int, start_frame: int = 1):
+        t, s, l = C.c_int(), C.c_int(), C.c_int()
+        sig = np.zeros(self.max_frames, np.float64)
+        self._ck(self.lib.abub_trigger(self.h, slot, cam, start_frame, C.byref(t), C.byref(s), C.byref(l), _p(sig)),
+                 "abub_trigger")
+        return t.value, s.value, l.value, sig
+
+    # ---- training ----
+    def train_begin(self, cam: int) -> None:
+        self._ck(self.lib.abub_train_begin(self.h, cam), "abub_train_begin")
+
+    def train_add_event(self, cam: int, frame0: np.ndarray, frame1: np.ndarray) -> Tuple[float, bool]:
+        f = np.ascontiguousarray(np.stack([_u8(frame0), _u8(frame1)]))
+        e, k = C.c_float(), C.c_int()
+        self._ck(self.lib.abub_train_add_event(self.h, cam, _p(f), C.byref(e), C.byref(k)), "abub_train_add_event")
+        return e.value, bool(k.value)
+
+    def train_add_slot(self, cam: int, slot: int) -> Tuple[float, bool]:
+        e, k = C.c_float(), C.c_int()
+        self._ck(self.lib.abub_train_add_slot(self.h, cam, slot, C.byref(e), C.byref(k)), "abub_train_add_slot")
+        return e.value, bool(k.value)
+
+    def train_finish(self, cam: int):
+        mean = np.zeros((self.rows, self.cols), np.uint8)
+        sigma = np.zeros((self.rows, self.cols), np.uint8)
+        n, st = C.c_int(), C.c_int()
+        self._ck(self.lib.abub_train_finish(self.h, cam, _p(mean), _p(sigma), C.byref(n), C.byref(st)),
+                 "abub_train_finish")
+        return mean, sigma, n.value, st.value
+
+    def train_partials(self, cam: int) -> Tuple[int, int, int]:
+        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self._ck(self.lib.abub_train_partials(self.h, cam, C.byref(a), C.byref(b), C.byref(c)), "abub_train_partials")
+        return int(a.value), int(b.value), int(c.value)
+
+    def train_finish_partials(self, cam: int):
+        mean = np.zeros((self.rows, self.cols), np.uint8)
+        sigma = np.zeros((self.rows, self.cols), np.uint8)
+        n, st, nf = C.c_int(), C.c_int(), C.c_int()
+        self._ck(self.lib.abub_train_finish_partials(self.h, cam, _p(mean), _p(sigma), C.byref(n), C.byref(st),
+                                                     C.byref(nf)), "abub_train_finish_partials")
+        return mean, sigma, n.value, st.value, nf.value
+
+    # ---- localizer ----
+    def localize(self, slot: int, cam: int, trig: int, pre_trig: int, loc_thres: int, n_post: int, cap: int = 4096):
+        blobs = (Blob * cap)()
+        npf = (C.c_int * (ABUB_MAX_TRACK + 1))()
+        self._ck(self.lib.abub_localize(self.h, slot, cam, trig, pre_trig, loc_thres, n_post, blobs, cap, npf),
+                 "abub_localize")
+        counts = [npf[k] for k in range(n_post + 1)]
+        return [blobs[i] for i in range(sum(counts))], counts
+
+    def localize_binary(self, k: int) -> np.ndarray:
+        out = np.zeros((self.rows, self.cols), np.uint8)
+        self._ck(self.lib.abub_localize_binary(self.h, k, _p(out)), "abub_localize_binary")
+        return out
+
+    # ---- parity taps ----
+    def process_frame(self, cam: int, work: np.ndarray, prev: np.ndarray):
+        w, p = _u8(work), _u8(prev)
+        diff = np.zeros((self.rows, self.cols), np.uint8)
+        hist = np.zeros(256, np.uint32)
+        self._ck(self.lib.abub_process_frame(self.h, cam, _p(w), _p(p), _p(diff), _p(hist)), "abub_process_frame")
+        return diff, hist

@@ -1,0 +1,102 @@
+// Internal declarations shared by the kernels of libabub_cuda.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+#include "../../include/abub_cuda.h"
+
+#define ABUB_MAX_CAMS 8
+#define ABUB_K1_TILE_W 120          // output columns per warp (30 lanes x 4 px; lanes 0,31 = halo)
+#define ABUB_MAX_POST (ABUB_MAX_TRACK + 1)
+
+struct abub_cam_state {
+    uint8_t*  d_mean = nullptr;     // TrainedAvgImage
+    uint8_t*  d_sigma = nullptr;    // TrainedSigmaImage
+    uint32_t* d_k32 = nullptr;      // per pixel (255-t)|(765-t)<<16, t=min(6*sigma,255)  (K1 stage A)
+    uint8_t*  d_t8 = nullptr;       // t = min(6*sigma,255)
+    int training_set_size = 0;
+    bool has_background = false;
+    // training: kept frames live in device chunks until abub_train_finish
+    std::vector<uint8_t*> chunks;   // each holds TRAIN_CHUNK frames
+    std::vector<const uint8_t*> kept;   // device pointers in push order (Trainer.cpp:291-292)
+    const uint8_t** d_table = nullptr;  // device copy of `kept`
+    int table_cap = 0;
+    int n_stored = 0;               // frames written into chunks (kept only)
+    uint32_t* d_sum = nullptr;      // exact integer partials (multi-GPU)
+    uint64_t* d_sumsq = nullptr;
+    int*      d_count = nullptr;    // [0]=kept frames (this rank, then reduced), [1]=flag count
+    uint8_t*  d_flag = nullptr;
+    bool training = false;
+};
+
+#define ABUB_TRAIN_CHUNK 32
+
+struct abub_slot_state {
+    uint8_t* d_frames = nullptr;    // [cam][frame][rows*cols]
+    uint8_t* h_pinned = nullptr;    // lazily allocated staging
+    int nframes[ABUB_MAX_CAMS] = {0};
+    bool hist_valid = false;
+};
+
+struct abub_ctx {
+    int device = 0, rows = 0, cols = 0, ncams = 0, max_frames = 0, max_slots = 0;
+    size_t npix = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    abub_cam_state cam[ABUB_MAX_CAMS];
+    std::vector<abub_slot_state> slots;
+    // trigger tables
+    uint32_t* d_hist = nullptr;     // [slot][cam][frame][256]
+    int*      d_nframes = nullptr;  // [slot][cam]
+    int*      d_start = nullptr;    // [slot][cam]
+    int*      d_trig = nullptr;     // [slot][cam] x {trig,status,loc_thres,scanned}
+    double*   d_sig = nullptr;      // [slot][cam][frame]
+    int*      d_tss = nullptr;      // [cam] TrainingSetSize
+    uint32_t** d_k32_ptrs = nullptr;  // [cam] device array of K32 plane pointers
+    uint8_t**  d_slot_ptrs = nullptr; // [slot] device array of slot base pointers
+    // scratch for single-frame ops / training
+    uint8_t*  d_tmp8[4] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t* d_hist_tmp = nullptr; // 16 x 256
+    void*     loc = nullptr;        // localizer arena (k5_localize.cu)
+};
+
+#define ABUB_CHECK_CUDA(ctx, call)                                                        \
+    do {                                                                                  \
+        cudaError_t e__ = (call);                                                         \
+        if (e__ != cudaSuccess) {                                                         \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);             \
+            return ABUB_E_CUDA;                                                           \
+        }                                                                                 \
+    } while (0)
+
+#define ABUB_REQUIRE(ctx, cond, msg)                                                      \
+    do {                                                                                  \
+        if (!(cond)) {                                                                    \
+            (ctx)->err = std::string("invalid argument: ") + (msg);                       \
+            return ABUB_E_INVALID;                                                        \
+        }                                                                                 \
+    } while (0)
+
+// ---- kernel launchers (one per .cu) ------------------------------------------------
+// K1 (k1_processframe.cu)
+int abub_k1_build_k32(abub_ctx* ctx, int cam);
+int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots);
+int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b, const uint32_t* d_k32,
+                          uint8_t* d_out, uint32_t* d_hist, int tozero_thres);
+// K2 (k2_trigger_scan.cu)
+int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots);
+// K3/K4 (k34_trainer.cu)
+int abub_k3_gate_hist16(abub_ctx* ctx, const uint8_t* d_f0, const uint8_t* d_f1, uint32_t* d_hist16);
+int abub_k4_welford(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint8_t* d_mean, uint8_t* d_sigma);
+int abub_k4_partials(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint32_t* d_sum, uint64_t* d_sumsq);
+int abub_k4_finish_from_partials(abub_ctx* ctx, const uint32_t* d_sum, const uint64_t* d_sumsq, int n, uint8_t* d_mean,
+                                 uint8_t* d_sigma, int* d_nflag, uint8_t* d_flag);
+int abub_k4_fixup(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, const uint8_t* d_flag, uint8_t* d_mean,
+                  uint8_t* d_sigma);
+// K5-K7 (k5_localize.cu)
+int abub_loc_init(abub_ctx* ctx);
+void abub_loc_free(abub_ctx* ctx);

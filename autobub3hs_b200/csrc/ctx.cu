@@ -1,0 +1,316 @@
+// Context management and the C-ABI entry points that are not a kernel by themselves
+// (include/abub_cuda.h).  No CPU fallback anywhere: every arithmetic entry point launches
+// the sm_100a kernels or fails with ABUB_E_CUDA.
+#include <dlfcn.h>
+#include <math.h>
+
+#include "abub_internal.cuh"
+
+static const char* kNoErr = "";
+
+extern "C" const char* abub_last_error(const abub_ctx* ctx) { return ctx ? ctx->err.c_str() : kNoErr; }
+
+extern "C" int abub_ctx_create(int device, int rows, int cols, int ncams, int max_frames, int max_slots,
+                               abub_ctx** out) {
+    if (!out) return ABUB_E_INVALID;
+    *out = nullptr;
+    if (rows < 5 || cols < 5 || ncams < 1 || ncams > ABUB_MAX_CAMS || max_frames < 2 || max_slots < 1)
+        return ABUB_E_INVALID;
+    if (cudaSetDevice(device) != cudaSuccess) return ABUB_E_CUDA;
+    abub_ctx* ctx = new abub_ctx();
+    ctx->device = device; ctx->rows = rows; ctx->cols = cols; ctx->ncams = ncams;
+    ctx->max_frames = max_frames; ctx->max_slots = max_slots;
+    ctx->npix = (size_t)rows * cols;
+    ctx->slots.resize(max_slots);
+    *out = ctx;     // returned even on failure so that abub_last_error works; caller destroys
+    ABUB_CHECK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    const size_t n = ctx->npix;
+    for (int c = 0; c < ncams; c++) {
+        abub_cam_state& cs = ctx->cam[c];
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_mean, n));
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_sigma, n));
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_t8, n));
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_k32, n * sizeof(uint32_t)));
+    }
+    const size_t frames_per_slot = (size_t)ncams * max_frames;
+    std::vector<uint8_t*> sp(max_slots);
+    for (int s = 0; s < max_slots; s++) {
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->slots[s].d_frames, frames_per_slot * n));
+        sp[s] = ctx->slots[s].d_frames;
+    }
+    const size_t sc = (size_t)max_slots * ncams;
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_hist, sc * max_frames * 256 * sizeof(uint32_t)));
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_nframes, sc * sizeof(int)));
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_start, sc * sizeof(int)));
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_trig, sc * 4 * sizeof(int)));
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_sig, sc * max_frames * sizeof(double)));
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_tss, ABUB_MAX_CAMS * sizeof(int)));
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_k32_ptrs, ABUB_MAX_CAMS * sizeof(uint32_t*)));
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_slot_ptrs, max_slots * sizeof(uint8_t*)));
+    ABUB_CHECK_CUDA(ctx, cudaMemset(ctx->d_nframes, 0, sc * sizeof(int)));
+    ABUB_CHECK_CUDA(ctx, cudaMemset(ctx->d_tss, 0, ABUB_MAX_CAMS * sizeof(int)));
+    ABUB_CHECK_CUDA(ctx, cudaMemset(ctx->d_hist, 0, sc * max_frames * 256 * sizeof(uint32_t)));
+    ABUB_CHECK_CUDA(ctx, cudaMemcpy(ctx->d_slot_ptrs, sp.data(), max_slots * sizeof(uint8_t*), cudaMemcpyHostToDevice));
+    uint32_t* kp[ABUB_MAX_CAMS] = {nullptr};
+    for (int c = 0; c < ncams; c++) kp[c] = ctx->cam[c].d_k32;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpy(ctx->d_k32_ptrs, kp, sizeof(kp), cudaMemcpyHostToDevice));
+    for (int i = 0; i < 4; i++) ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_tmp8[i], n));
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_hist_tmp, 16 * 256 * sizeof(uint32_t)));
+    int rc = abub_loc_init(ctx);
+    if (rc != ABUB_OK) return rc;
+    return ABUB_OK;
+}
+
+static void train_release(abub_cam_state& cs) {
+    for (uint8_t* p : cs.chunks) cudaFree(p);
+    cs.chunks.clear();
+    cs.kept.clear();
+    cs.n_stored = 0;
+}
+
+extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    abub_loc_free(ctx);
+    for (int c = 0; c < ABUB_MAX_CAMS; c++) {
+        abub_cam_state& cs = ctx->cam[c];
+        cudaFree(cs.d_mean); cudaFree(cs.d_sigma); cudaFree(cs.d_t8); cudaFree(cs.d_k32);
+        cudaFree(cs.d_sum); cudaFree(cs.d_sumsq); cudaFree(cs.d_count); cudaFree(cs.d_flag);
+        cudaFree((void*)cs.d_table);
+        train_release(cs);
+    }
+    for (auto& s : ctx->slots) {
+        cudaFree(s.d_frames);
+        if (s.h_pinned) cudaFreeHost(s.h_pinned);
+    }
+    cudaFree(ctx->d_hist); cudaFree(ctx->d_nframes); cudaFree(ctx->d_start); cudaFree(ctx->d_trig);
+    cudaFree(ctx->d_sig); cudaFree(ctx->d_tss); cudaFree(ctx->d_k32_ptrs); cudaFree(ctx->d_slot_ptrs);
+    for (int i = 0; i < 4; i++) cudaFree(ctx->d_tmp8[i]);
+    cudaFree(ctx->d_hist_tmp);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" int abub_sync(abub_ctx* ctx) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ABUB_OK;
+}
+
+extern "C" void* abub_stream(abub_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+// ---- background -------------------------------------------------------------------
+static int install_background(abub_ctx* ctx, int cam, int tss) {
+    abub_cam_state& cs = ctx->cam[cam];
+    cs.training_set_size = tss;
+    cs.has_background = true;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_tss + cam, &cs.training_set_size, sizeof(int), cudaMemcpyHostToDevice,
+                                         ctx->stream));
+    int rc = abub_k1_build_k32(ctx, cam);
+    if (rc) return rc;
+    for (auto& s : ctx->slots) s.hist_valid = false;
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // &training_set_size must outlive the copy
+    return ABUB_OK;
+}
+
+extern "C" int abub_set_background(abub_ctx* ctx, int cam, const uint8_t* mean, const uint8_t* sigma,
+                                   int training_set_size) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, cam >= 0 && cam < ctx->ncams && mean && sigma, "abub_set_background");
+    cudaSetDevice(ctx->device);
+    abub_cam_state& cs = ctx->cam[cam];
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(cs.d_mean, mean, ctx->npix, cudaMemcpyHostToDevice, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(cs.d_sigma, sigma, ctx->npix, cudaMemcpyHostToDevice, ctx->stream));
+    return install_background(ctx, cam, training_set_size);
+}
+
+extern "C" int abub_set_background_from_training(abub_ctx* ctx, int cam) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, cam >= 0 && cam < ctx->ncams, "cam");
+    ABUB_REQUIRE(ctx, ctx->cam[cam].has_background, "no trained planes for this camera");
+    cudaSetDevice(ctx->device);
+    return install_background(ctx, cam, ctx->cam[cam].training_set_size);
+}
+
+// ---- event frames -----------------------------------------------------------------
+static size_t slot_bytes(const abub_ctx* ctx) { return (size_t)ctx->ncams * ctx->max_frames * ctx->npix; }
+
+static int push_nframes(abub_ctx* ctx, int slot) {
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_nframes + (size_t)slot * ctx->ncams, ctx->slots[slot].nframes,
+                                         ctx->ncams * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    ctx->slots[slot].hist_valid = false;
+    return ABUB_OK;
+}
+
+extern "C" int abub_pinned_acquire(abub_ctx* ctx, int slot, uint8_t** host_ptr) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && host_ptr, "abub_pinned_acquire");
+    cudaSetDevice(ctx->device);
+    abub_slot_state& s = ctx->slots[slot];
+    if (!s.h_pinned) ABUB_CHECK_CUDA(ctx, cudaHostAlloc(&s.h_pinned, slot_bytes(ctx), cudaHostAllocDefault));
+    *host_ptr = s.h_pinned;
+    return ABUB_OK;
+}
+
+extern "C" int abub_event_submit(abub_ctx* ctx, int slot, const int* nframes) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && nframes, "abub_event_submit");
+    abub_slot_state& s = ctx->slots[slot];
+    ABUB_REQUIRE(ctx, s.h_pinned != nullptr, "slot has no pinned buffer (call abub_pinned_acquire)");
+    cudaSetDevice(ctx->device);
+    for (int c = 0; c < ctx->ncams; c++) {
+        ABUB_REQUIRE(ctx, nframes[c] >= 0 && nframes[c] <= ctx->max_frames, "nframes out of range");
+        s.nframes[c] = nframes[c];
+        const size_t off = (size_t)c * ctx->max_frames * ctx->npix;
+        if (nframes[c] > 0)
+            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(s.d_frames + off, s.h_pinned + off, (size_t)nframes[c] * ctx->npix,
+                                                 cudaMemcpyHostToDevice, ctx->stream));
+    }
+    return push_nframes(ctx, slot);
+}
+
+extern "C" int abub_event_upload(abub_ctx* ctx, int slot, int cam, const uint8_t* frames, int nframes) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && cam >= 0 && cam < ctx->ncams, "slot/cam");
+    ABUB_REQUIRE(ctx, nframes >= 0 && nframes <= ctx->max_frames && (frames || nframes == 0), "frames");
+    cudaSetDevice(ctx->device);
+    abub_slot_state& s = ctx->slots[slot];
+    s.nframes[cam] = nframes;
+    if (nframes > 0) {
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(s.d_frames + (size_t)cam * ctx->max_frames * ctx->npix, frames,
+                                             (size_t)nframes * ctx->npix, cudaMemcpyHostToDevice, ctx->stream));
+        ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // pageable source may be reused by the caller
+    }
+    return push_nframes(ctx, slot);
+}
+
+extern "C" int abub_event_device_ptr(abub_ctx* ctx, int slot, uint8_t** dev_ptr) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && dev_ptr, "abub_event_device_ptr");
+    *dev_ptr = ctx->slots[slot].d_frames;
+    return ABUB_OK;
+}
+
+extern "C" int abub_event_set_nframes(abub_ctx* ctx, int slot, const int* nframes) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && nframes, "abub_event_set_nframes");
+    cudaSetDevice(ctx->device);
+    for (int c = 0; c < ctx->ncams; c++) {
+        ABUB_REQUIRE(ctx, nframes[c] >= 0 && nframes[c] <= ctx->max_frames, "nframes out of range");
+        ctx->slots[slot].nframes[c] = nframes[c];
+    }
+    int rc = push_nframes(ctx, slot);
+    if (rc) return rc;
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ABUB_OK;
+}
+
+// ---- trigger ------------------------------------------------------------------------
+static int require_backgrounds(abub_ctx* ctx) {
+    for (int c = 0; c < ctx->ncams; c++)
+        ABUB_REQUIRE(ctx, ctx->cam[c].has_background, "background not installed for every camera");
+    return ABUB_OK;
+}
+
+extern "C" int abub_trigger_hist(abub_ctx* ctx, int slot_first, int nslots) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot_first >= 0 && nslots >= 1 && slot_first + nslots <= ctx->max_slots, "slot range");
+    int rc = require_backgrounds(ctx);
+    if (rc) return rc;
+    cudaSetDevice(ctx->device);
+    rc = abub_k1_launch_trigger(ctx, slot_first, nslots);
+    if (rc) return rc;
+    for (int s = slot_first; s < slot_first + nslots; s++) ctx->slots[s].hist_valid = true;
+    return ABUB_OK;
+}
+
+extern "C" int abub_trigger_hist_read(abub_ctx* ctx, int slot, int cam, uint32_t* hist) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && cam >= 0 && cam < ctx->ncams && hist, "args");
+    cudaSetDevice(ctx->device);
+    const size_t n = (size_t)ctx->max_frames * 256;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(hist, ctx->d_hist + ((size_t)slot * ctx->ncams + cam) * n, n * sizeof(uint32_t),
+                                         cudaMemcpyDeviceToHost, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ABUB_OK;
+}
+
+extern "C" int abub_trigger_scan(abub_ctx* ctx, int slot_first, int nslots, const int* start_frames) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot_first >= 0 && nslots >= 1 && slot_first + nslots <= ctx->max_slots, "slot range");
+    cudaSetDevice(ctx->device);
+    const size_t n = (size_t)nslots * ctx->ncams;
+    std::vector<int> st(n, 1);
+    if (start_frames) st.assign(start_frames, start_frames + n);
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_start + (size_t)slot_first * ctx->ncams, st.data(), n * sizeof(int),
+                                         cudaMemcpyHostToDevice, ctx->stream));
+    int rc = abub_k2_launch(ctx, slot_first, nslots);
+    // the start vector is a local: make sure the copy has been consumed
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return rc;
+}
+
+extern "C" int abub_trigger_results(abub_ctx* ctx, int slot_first, int nslots, int* trig, int* status, int* loc_thres,
+                                    double* sig) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot_first >= 0 && nslots >= 1 && slot_first + nslots <= ctx->max_slots, "slot range");
+    cudaSetDevice(ctx->device);
+    const size_t n = (size_t)nslots * ctx->ncams;
+    std::vector<int> r(n * 4);
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(r.data(), ctx->d_trig + (size_t)slot_first * ctx->ncams * 4, n * 4 * sizeof(int),
+                                         cudaMemcpyDeviceToHost, ctx->stream));
+    if (sig)
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(sig, ctx->d_sig + (size_t)slot_first * ctx->ncams * ctx->max_frames,
+                                             n * ctx->max_frames * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (size_t i = 0; i < n; i++) {
+        if (trig) trig[i] = r[i * 4 + 0];
+        if (status) status[i] = r[i * 4 + 1];
+        if (loc_thres) loc_thres[i] = r[i * 4 + 2];
+    }
+    return ABUB_OK;
+}
+
+extern "C" int abub_trigger(abub_ctx* ctx, int slot, int cam, int start_frame, int* trig, int* status, int* loc_thres,
+                            double* sig) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && cam >= 0 && cam < ctx->ncams, "slot/cam");
+    int rc;
+    if (!ctx->slots[slot].hist_valid) {
+        rc = abub_trigger_hist(ctx, slot, 1);
+        if (rc) return rc;
+    }
+    std::vector<int> st(ctx->ncams, 1), t(ctx->ncams), s(ctx->ncams), l(ctx->ncams);
+    st[cam] = start_frame;
+    rc = abub_trigger_scan(ctx, slot, 1, st.data());
+    if (rc) return rc;
+    std::vector<double> sg(sig ? (size_t)ctx->ncams * ctx->max_frames : 0);
+    rc = abub_trigger_results(ctx, slot, 1, t.data(), s.data(), l.data(), sig ? sg.data() : nullptr);
+    if (rc) return rc;
+    if (trig) *trig = t[cam];
+    if (status) *status = s[cam];
+    if (loc_thres) *loc_thres = l[cam];
+    if (sig) memcpy(sig, sg.data() + (size_t)cam * ctx->max_frames, ctx->max_frames * sizeof(double));
+    return ABUB_OK;
+}
+
+// ---- single-frame parity tap --------------------------------------------------------
+extern "C" int abub_process_frame(abub_ctx* ctx, int cam, const uint8_t* work, const uint8_t* prev, uint8_t* diff,
+                                  uint32_t* hist) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, cam >= 0 && cam < ctx->ncams && work && prev && diff, "abub_process_frame");
+    ABUB_REQUIRE(ctx, ctx->cam[cam].has_background, "background not installed");
+    cudaSetDevice(ctx->device);
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_tmp8[0], work, ctx->npix, cudaMemcpyHostToDevice, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_tmp8[1], prev, ctx->npix, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = abub_k1_launch_single(ctx, ctx->d_tmp8[0], ctx->d_tmp8[1], ctx->cam[cam].d_k32, ctx->d_tmp8[2],
+                                   ctx->d_hist_tmp, -1);
+    if (rc) return rc;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(diff, ctx->d_tmp8[2], ctx->npix, cudaMemcpyDeviceToHost, ctx->stream));
+    if (hist)
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(hist, ctx->d_hist_tmp, 256 * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                             ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ABUB_OK;
+}

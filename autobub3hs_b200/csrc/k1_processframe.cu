@@ -1,0 +1,303 @@
+// K1 -- AnalyzerUnit::ProcessFrame fused with the 256-bin calcHist
+// (reference: AnalyzerUnit.cpp:346-377 and :441-456).
+//
+//   pos = sat_u8(a - b - 6*sigma), neg = sat_u8(b - a - 6*sigma)        (:351-352)
+//   P = GaussianBlur5x5(pos), N = GaussianBlur5x5(neg)                  (:359-360)
+//       = (sum_ij k_i k_j p + 128) >> 8, k = [1 4 6 4 1], BORDER_REFLECT_101
+//   out = |P - N|                                                        (:370)
+//   H[out] += 1 over the whole frame, no mask                            (:456)
+//
+// Layout of the computation (HBM-bound by design, integer-issue-bound in practice):
+//   * one warp owns a strip of 120 output columns x TH rows; lane l holds the 4 pixels
+//     x0-4+4l .. x0-1+4l (lanes 0 and 31 are the 2-px halo, rounded up to a word);
+//   * every pixel is one 32-bit word  pos | neg<<16 : the binomial sums of both planes
+//     stay below 2^16 (255*256 + 128), so plain IADD/IMAD blur both planes at once;
+//   * stage A (a,b,6sigma -> word) uses dp4a on [a_i,b_i,a_j,b_j] byte pairs and one IMAD
+//     against a per-pixel constant plane K32 = (255-t) | (765-t)<<16, t = min(6 sigma,255):
+//        y = (a-b+255) * 0xFFFF0001 + K32  ->  lanes [a-b-t+510 , b-a-t+510]
+//        word = max.u16x2(y, 510) - 510
+//   * vertical 5-tap pass in registers (5-row sliding window), horizontal pass after a
+//     conflict-free 8-byte neighbour exchange through shared memory (one __syncwarp);
+//   * only non-zero outputs touch the shared-memory histogram; bin 0 is recovered as
+//     rows*cols - sum(other bins) by a finalize kernel.
+#include "abub_internal.cuh"
+
+namespace {
+
+constexpr uint32_t BIAS2 = 0x01FE01FEu;   // 510 | 510<<16
+constexpr uint32_t RND2  = 0x00800080u;   // 128 | 128<<16
+
+__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+__device__ __forceinline__ int reflect101(int p, int n) {
+    if (p < 0) p = -p;
+    if (p >= n) p = 2 * (n - 1) - p;
+    return min(max(p, 0), n - 1);
+}
+
+__device__ __forceinline__ uint32_t stageA1(int s255, uint32_t k) {
+    uint32_t y = (uint32_t)s255 * 0xFFFF0001u + k;
+    return __vmaxu2(y, BIAS2) - BIAS2;
+}
+
+// words of 4 neighbouring pixels from packed bytes a4,b4 and their K32 constants
+__device__ __forceinline__ void stageA(uint32_t a4, uint32_t b4, const uint4 k, uint32_t w[4]) {
+    const uint32_t p01 = __byte_perm(a4, b4, 0x5140);   // [a0,b0,a1,b1]
+    const uint32_t p23 = __byte_perm(a4, b4, 0x7362);   // [a2,b2,a3,b3]
+    w[0] = stageA1(dp4a_us(p01, 0x0000FF01, 255), k.x);
+    w[1] = stageA1(dp4a_us(p01, (int)0xFF010000, 255), k.y);
+    w[2] = stageA1(dp4a_us(p23, 0x0000FF01, 255), k.z);
+    w[3] = stageA1(dp4a_us(p23, (int)0xFF010000, 255), k.w);
+}
+
+struct RowIn { uint32_t a4, b4; uint4 k; };
+
+__device__ __forceinline__ RowIn load_row(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B,
+                                          const uint32_t* __restrict__ K, int y, int gx, int cols, bool fast) {
+    RowIn r;
+    const size_t ro = (size_t)y * cols;
+    if (fast) {
+        r.a4 = __ldg(reinterpret_cast<const uint32_t*>(A + ro + gx));
+        r.b4 = __ldg(reinterpret_cast<const uint32_t*>(B + ro + gx));
+        r.k  = __ldg(reinterpret_cast<const uint4*>(K + ro + gx));
+    } else {
+        uint32_t a = 0, b = 0, kk[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const int x = reflect101(gx + c, cols);
+            a |= (uint32_t)A[ro + x] << (8 * c);
+            b |= (uint32_t)B[ro + x] << (8 * c);
+            kk[c] = K[ro + x];
+        }
+        r.a4 = a; r.b4 = b; r.k = make_uint4(kk[0], kk[1], kk[2], kk[3]);
+    }
+    return r;
+}
+
+// One warp: strip of ABUB_K1_TILE_W output columns starting at x0, output rows [y0, y0+th).
+// MODE 0: histogram of the outputs only.  MODE 1: also store the (optionally TOZERO'd) output.
+template <int MODE>
+__device__ __forceinline__ void k1_strip(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B,
+                                         const uint32_t* __restrict__ K, int rows, int cols,
+                                         int y0, int th, int x0, uint32_t* sh_hist, uint32_t* xch,
+                                         uint8_t* __restrict__ out, int tozero) {
+    const int lane = threadIdx.x & 31;
+    const int gx = x0 - 4 + lane * 4;
+    const bool fast = ((cols & 3) == 0) && gx >= 0 && gx + 4 <= cols;
+    const bool out_lane = lane >= 1 && lane <= 30 && gx < cols;
+    const int nout = min(th, rows - y0);
+    const int nloc = nout + 4;
+    uint32_t win[5][4];
+    RowIn nxt = load_row(A, B, K, reflect101(y0 - 2, rows), gx, cols, fast);
+
+#pragma unroll 1
+    for (int rb = 0; rb < nloc; rb += 5) {
+#pragma unroll
+        for (int r = 0; r < 5; r++) {
+            const int rl = rb + r;
+            if (rl < nloc) {
+                const RowIn cur = nxt;
+                if (rl + 1 < nloc) nxt = load_row(A, B, K, reflect101(y0 - 2 + rl + 1, rows), gx, cols, fast);
+                stageA(cur.a4, cur.b4, cur.k, win[r]);
+                if (rl >= 4) {
+                    // vertical pass: rows rl-4..rl live in win[(r+1)%5] .. win[r]
+                    uint32_t v[4];
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const uint32_t e = win[(r + 1) % 5][c] + win[r][c];
+                        const uint32_t o = win[(r + 2) % 5][c] + win[(r + 4) % 5][c];
+                        v[c] = e + 4u * o + 6u * win[(r + 3) % 5][c];
+                    }
+                    // neighbour exchange (lo pair = cols 0,1 ; hi pair = cols 2,3)
+                    uint2* xlo = reinterpret_cast<uint2*>(xch + (rl & 1) * 128);
+                    uint2* xhi = xlo + 32;
+                    xlo[lane] = make_uint2(v[0], v[1]);
+                    xhi[lane] = make_uint2(v[2], v[3]);
+                    __syncwarp();
+                    const uint2 L = xhi[(lane + 31) & 31];
+                    const uint2 R = xlo[(lane + 1) & 31];
+                    const uint32_t e0 = L.x, e1 = L.y, e6 = R.x, e7 = R.y;
+                    uint32_t h[4];
+                    h[0] = (e0 + v[2]) + 4u * (e1 + v[1]) + 6u * v[0] + RND2;
+                    h[1] = (e1 + v[3]) + 4u * (v[0] + v[2]) + 6u * v[1] + RND2;
+                    h[2] = (v[0] + e6) + 4u * (v[1] + v[3]) + 6u * v[2] + RND2;
+                    h[3] = (v[1] + e7) + 4u * (v[2] + e6) + 6u * v[3] + RND2;
+                    const int y = y0 + rl - 4;
+                    const uint32_t z = (h[0] | h[1] | h[2] | h[3]) & 0xFF00FF00u;
+                    uint32_t packed = 0;
+                    if (z != 0 && out_lane) {
+#pragma unroll
+                        for (int c = 0; c < 4; c++) {
+                            const uint32_t P = (h[c] >> 8) & 0xFFu, N = h[c] >> 24;
+                            uint32_t o = __usad(P, N, 0u);
+                            if (MODE == 1 && (int)o <= tozero) o = 0;
+                            if (o != 0 && gx + c < cols) {
+                                atomicAdd(&sh_hist[o], 1u);
+                                packed |= o << (8 * c);
+                            }
+                        }
+                    }
+                    if (MODE == 1 && out_lane) {
+                        uint8_t* op = out + (size_t)y * cols + gx;
+                        if (fast) {
+                            *reinterpret_cast<uint32_t*>(op) = packed;
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < 4; c++)
+                                if (gx + c < cols) op[c] = (uint8_t)(packed >> (8 * c));
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+constexpr int K1_TH = 35;     // output rows per strip (1050 = 30 x 35)
+
+// grid: x = strip, y = j-1, z = (slot-slot_first)*ncams + cam ; block = 32 * ceil(cols/120)
+__global__ void k1_trigger_kernel(uint8_t* const* __restrict__ slot_ptrs, const int* __restrict__ nframes,
+                                  const int* __restrict__ tss, uint32_t* const* __restrict__ k32_ptrs,
+                                  uint32_t* __restrict__ hist, int slot_first, int rows, int cols,
+                                  int ncams, int max_frames) {
+    extern __shared__ uint32_t smem[];
+    uint32_t* sh_hist = smem;                       // 256
+    const int warp = threadIdx.x >> 5;
+    uint32_t* xch = smem + 256 + warp * 256;        // 2 x 128 words per warp
+    const int rel = blockIdx.z;
+    const int slot = slot_first + rel / ncams;
+    const int cam = rel % ncams;
+    const int j = blockIdx.y + 1;
+    const int nf = nframes[slot * ncams + cam];
+    if (j >= nf) return;
+    const int d = (tss[cam] < 6) ? 1 : 2;           // twoFrameOffset, AnalyzerUnit.cpp:182-188
+    const int jp = (j - d < 0) ? 0 : j - d;         // j==1 uses frame 0 (:176)
+    const size_t npix = (size_t)rows * cols;
+    const uint8_t* base = slot_ptrs[slot] + (size_t)cam * max_frames * npix;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
+    __syncthreads();
+    const int y0 = blockIdx.x * K1_TH;
+    if (y0 < rows)
+        k1_strip<0>(base + (size_t)j * npix, base + (size_t)jp * npix, k32_ptrs[cam], rows, cols, y0, K1_TH,
+                    warp * ABUB_K1_TILE_W, sh_hist, xch, nullptr, -1);
+    __syncthreads();
+    uint32_t* H = hist + (((size_t)slot * ncams + cam) * max_frames + j) * 256;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        const uint32_t c = sh_hist[i];
+        if (c) atomicAdd(&H[i], c);
+    }
+}
+
+// bin 0 = rows*cols - sum(bins 1..255); one warp per (slot,cam,j)
+__global__ void k1_fill_bin0_kernel(uint32_t* __restrict__ hist, const int* __restrict__ nframes, int slot_first,
+                                    int nslots, int ncams, int max_frames, uint32_t npix) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const int total = nslots * ncams * max_frames;
+    if (w >= total) return;
+    const int j = w % max_frames;
+    const int sc = w / max_frames;
+    const int slot = slot_first + sc / ncams, cam = sc % ncams;
+    if (j < 1 || j >= nframes[slot * ncams + cam]) return;
+    uint32_t* H = hist + (((size_t)slot * ncams + cam) * max_frames + j) * 256;
+    uint32_t s = 0;
+    for (int i = lane; i < 256; i += 32) s += (i == 0) ? 0u : H[i];
+    s = __reduce_add_sync(0xffffffffu, s);
+    if (lane == 0) H[0] = npix - s;
+}
+
+// single frame pair (parity tap + localizer genesis frame)
+__global__ void k1_single_kernel(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B,
+                                 const uint32_t* __restrict__ K, uint8_t* __restrict__ out,
+                                 uint32_t* __restrict__ hist, int rows, int cols, int tozero) {
+    extern __shared__ uint32_t smem[];
+    uint32_t* sh_hist = smem;
+    const int warp = threadIdx.x >> 5;
+    uint32_t* xch = smem + 256 + warp * 256;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
+    __syncthreads();
+    const int y0 = blockIdx.x * K1_TH;
+    if (y0 < rows)
+        k1_strip<1>(A, B, K, rows, cols, y0, K1_TH, warp * ABUB_K1_TILE_W, sh_hist, xch, out, tozero);
+    __syncthreads();
+    if (hist)
+        for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+            const uint32_t c = sh_hist[i];
+            if (c) atomicAdd(&hist[i], c);
+        }
+}
+
+__global__ void k1_fill_bin0_single(uint32_t* hist, uint32_t npix) {
+    const int lane = threadIdx.x;
+    uint32_t s = 0;
+    for (int i = lane; i < 256; i += 32) s += (i == 0) ? 0u : hist[i];
+    s = __reduce_add_sync(0xffffffffu, s);
+    if (lane == 0) hist[0] = npix - s;
+}
+
+// K32 = (255-t) | (765-t)<<16, t = min(6*sigma, 255); also t8
+__global__ void k1_build_k32_kernel(const uint8_t* __restrict__ sigma, uint32_t* __restrict__ k32,
+                                    uint8_t* __restrict__ t8, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t t = min(6u * sigma[i], 255u);
+    k32[i] = (255u - t) | ((765u - t) << 16);
+    t8[i] = (uint8_t)t;
+}
+
+}  // namespace
+
+static inline int k1_block_threads(int cols) { return 32 * ((cols + ABUB_K1_TILE_W - 1) / ABUB_K1_TILE_W); }
+static inline size_t k1_smem_bytes(int threads) { return (256 + (threads / 32) * 256) * sizeof(uint32_t); }
+
+int abub_k1_build_k32(abub_ctx* ctx, int cam) {
+    abub_cam_state& c = ctx->cam[cam];
+    const size_t n = ctx->npix;
+    k1_build_k32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(c.d_sigma, c.d_k32, c.d_t8, n);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    return ABUB_OK;
+}
+
+int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots) {
+    const int threads = k1_block_threads(ctx->cols);
+    ABUB_REQUIRE(ctx, threads <= 1024, "cols too large for K1 (max 3840)");
+    const size_t hist_off = (size_t)slot_first * ctx->ncams * ctx->max_frames * 256;
+    const size_t hist_n = (size_t)nslots * ctx->ncams * ctx->max_frames * 256;
+    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(ctx->d_hist + hist_off, 0, hist_n * sizeof(uint32_t), ctx->stream));
+    const int nstrips = (ctx->rows + K1_TH - 1) / K1_TH;
+    // z is limited to 65535: chunk the (slot,cam) range
+    const int per = 65535 / ctx->ncams;
+    for (int s0 = 0; s0 < nslots; s0 += per) {
+        const int ns = (nslots - s0 < per) ? nslots - s0 : per;
+        dim3 grid(nstrips, ctx->max_frames - 1, ns * ctx->ncams);
+        k1_trigger_kernel<<<grid, threads, k1_smem_bytes(threads), ctx->stream>>>(
+            ctx->d_slot_ptrs, ctx->d_nframes, ctx->d_tss, ctx->d_k32_ptrs, ctx->d_hist, slot_first + s0,
+            ctx->rows, ctx->cols, ctx->ncams, ctx->max_frames);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
+    const int total_w = nslots * ctx->ncams * ctx->max_frames;
+    k1_fill_bin0_kernel<<<(total_w * 32 + 255) / 256, 256, 0, ctx->stream>>>(
+        ctx->d_hist, ctx->d_nframes, slot_first, nslots, ctx->ncams, ctx->max_frames, (uint32_t)ctx->npix);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    return ABUB_OK;
+}
+
+int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b, const uint32_t* d_k32,
+                          uint8_t* d_out, uint32_t* d_hist, int tozero_thres) {
+    const int threads = k1_block_threads(ctx->cols);
+    ABUB_REQUIRE(ctx, threads <= 1024, "cols too large for K1 (max 3840)");
+    if (d_hist) ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_hist, 0, 256 * sizeof(uint32_t), ctx->stream));
+    const int nstrips = (ctx->rows + K1_TH - 1) / K1_TH;
+    k1_single_kernel<<<nstrips, threads, k1_smem_bytes(threads), ctx->stream>>>(d_a, d_b, d_k32, d_out, d_hist,
+                                                                                 ctx->rows, ctx->cols, tozero_thres);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    if (d_hist) {
+        k1_fill_bin0_single<<<1, 32, 0, ctx->stream>>>(d_hist, (uint32_t)ctx->npix);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
+    return ABUB_OK;
+}

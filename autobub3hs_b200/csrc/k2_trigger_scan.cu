@@ -1,0 +1,157 @@
+// K2 -- the significance trigger state machine on the histogram tables produced by K1.
+// Reference: AnalyzerUnit::calculateSignificanceFrame + CalcMean/CalcStdDev
+// (AnalyzerUnit.cpp:435-504, 514-532) and AnalyzerUnit::FindTriggerFrame (:119-324).
+//
+// One warp per (slot, camera).  The reference's pix_counts history (vector<vector<int>>)
+// is the H table itself: frame f contributes H[f][b] to bin b (bins the reference never
+// reaches hold 0, which changes neither sum), and the history length is the number of
+// stored frames, n = i when frame i has just been stored (frames 1..i).  Per frame the 254
+// per-bin z-scores are evaluated in parallel; the clamped running sum over bins
+// (`if (significance < 0) significance = 0`, :479) is order-dependent and is done by lane 0.
+// All fp64 arithmetic uses the _rn intrinsics so that nothing is contracted into FMAs
+// (the reference is built with -O0, CMakeLists.txt:35).
+#include "abub_internal.cuh"
+
+namespace {
+
+constexpr int K2_WARPS = 4;
+
+struct WarpScratch {
+    double s1[256];     // sum of counts per bin over stored frames
+    double s2[256];     // sum of (int)(count*count) per bin (int32 wrap, AnalyzerUnit.cpp:529)
+    double term[256];   // (c-mean)/sd of the frame under evaluation
+    uint32_t use[8];    // bit b: term b is added (`binEntry != mean || sigma > 0`, :478)
+};
+
+__device__ __forceinline__ double wrapsq(uint32_t c) { return (double)(int32_t)(c * c); }
+
+// Evaluates one histogram row against the current history.  Returns the significance on
+// all lanes; first_over / max_adc as the reference tracks them (:483-485).
+__device__ double significance(const uint32_t* __restrict__ Hrow, WarpScratch* ws, int n, int lane,
+                               int* first_over, int* max_adc) {
+    int maxbin = 0;
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+        const int b = q * 32 + lane;
+        const uint32_t cu = Hrow[b];
+        if (cu) maxbin = b;
+        const double c = (double)(float)cu;                       // binEntry is float (:459)
+        const double mean = __ddiv_rn(ws->s1[b], (double)n);      // CalcMean :514-521
+        const double var = __dsub_rn(__ddiv_rn(ws->s2[b], (double)n), __dmul_rn(mean, mean));
+        const double sd = __dsqrt_rn(var);                        // CalcStdDev :523-532
+        const bool use = (c != mean) || (sd > 0.0);               // :478
+        ws->term[b] = __ddiv_rn(__dsub_rn(c, mean), sd);
+        const uint32_t m = __ballot_sync(0xffffffffu, use);
+        if (lane == 0) ws->use[q] = m;
+    }
+    maxbin = __reduce_max_sync(0xffffffffu, maxbin);
+    __syncwarp();
+    double sig = 0.0;
+    int fo = -1;
+    if (lane == 0) {
+        for (int b = 2; b <= maxbin; b++) {                       // bins 0,1 add nothing (:473)
+            if ((ws->use[b >> 5] >> (b & 31)) & 1u) sig = __dadd_rn(sig, ws->term[b]);
+            if (sig < 0.0) sig = 0.0;                             // :479
+            if (sig > 3.5 && fo < 0) fo = b;                      // :483
+        }
+    }
+    sig = __shfl_sync(0xffffffffu, sig, 0);
+    fo = __shfl_sync(0xffffffffu, fo, 0);
+    __syncwarp();
+    *first_over = fo;
+    *max_adc = maxbin;                                            // :485
+    return sig;
+}
+
+__global__ void __launch_bounds__(32 * K2_WARPS)
+k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict__ nframes,
+                       const int* __restrict__ start, const int* __restrict__ tss_cam,
+                       int* __restrict__ result, double* __restrict__ sig_out, int slot_first, int nslots,
+                       int ncams, int max_frames) {
+    __shared__ WarpScratch scratch[K2_WARPS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int item = blockIdx.x * K2_WARPS + warp;
+    if (item >= nslots * ncams) return;
+    const int slot = slot_first + item / ncams, cam = item % ncams;
+    const int sc = slot * ncams + cam;
+    WarpScratch* ws = &scratch[warp];
+    const uint32_t* H = hist + (size_t)sc * max_frames * 256;
+    double* so = sig_out + (size_t)sc * max_frames;
+    int* res = result + sc * 4;
+    const int nf = nframes[sc];
+    const int tss = tss_cam[cam];
+    for (int f = lane; f < max_frames; f += 32) so[f] = 0.0;
+
+    if (nf < 5) {                                                 // :122-126
+        if (lane == 0) { res[0] = 0; res[1] = -9; res[2] = -1; res[3] = 0; }
+        return;
+    }
+    int s = start[sc];
+    if (s < 1) s = 1;                                             // :163
+    float thr = 3.5f;                                             // :142
+    if (tss < 6) thr = (float)((double)thr * (5 / 3.5));          // :185-188
+    // history of frames 1..s-1 (empty when s == 1, :165-169)
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+        const int b = q * 32 + lane;
+        double a1 = 0.0, a2 = 0.0;
+        for (int f = 1; f < s && f < nf; f++) {
+            const uint32_t c = H[(size_t)f * 256 + b];
+            a1 += (double)c;
+            a2 += wrapsq(c);
+        }
+        ws->s1[b] = a1;
+        ws->s2[b] = a2;
+    }
+    __syncwarp();
+
+    int status = -3, trig = 0, loc_thres = -1, scanned = 0;      // :180
+    for (int i = s; i < nf; i++) {                                // :191
+        const uint32_t* Hi = H + (size_t)i * 256;
+#pragma unroll
+        for (int q = 0; q < 8; q++) {                             // store = true (:461)
+            const int b = q * 32 + lane;
+            const uint32_t c = Hi[b];
+            ws->s1[b] += (double)c;
+            ws->s2[b] += wrapsq(c);
+        }
+        __syncwarp();
+        int fo, madc;
+        const double sg = significance(Hi, ws, i, lane, &fo, &madc);   // :228
+        scanned++;
+        if (lane == 0) so[i] = sg;
+        int lt = max(fo - 1, madc - 1);                           // :487-491
+        if (lt < 2) lt = 2;
+        if (lt > 3 || tss < 6) lt = 3;
+        loc_thres = lt;
+        float single = (float)sg;
+        if (single > thr && i >= 2) {                             // :254
+            if (i != nf - 1) {                                    // :261
+                double max_so_far = (double)single;              // :280
+                for (int ii = 1; ii <= 2 && ii + i < nf; ii++) {  // :282
+                    int fo2, madc2;
+                    const double s2v = significance(H + (size_t)(i + ii) * 256, ws, i, lane, &fo2, &madc2);
+                    single = (float)s2v;                          // :292  (store = false)
+                    const double lhs = __dadd_rn(__ddiv_rn((double)single, __dmul_rn(__ddiv_rn((double)thr, 3.5), 5.0)),
+                                                 __ddiv_rn((double)single, max_so_far));
+                    if (lhs <= 3.0) break;                        // :296
+                    else if (ii == 2) { status = 0; trig = i; }   // :297-300
+                    if ((double)single > max_so_far) max_so_far = (double)single;   // :302
+                }
+                if (status == 0) break;
+            }
+        }
+    }
+    if (lane == 0) { res[0] = trig; res[1] = status; res[2] = loc_thres; res[3] = scanned; }
+}
+
+}  // namespace
+
+int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots) {
+    const int items = nslots * ctx->ncams;
+    k2_trigger_scan_kernel<<<(items + K2_WARPS - 1) / K2_WARPS, 32 * K2_WARPS, 0, ctx->stream>>>(
+        ctx->d_hist, ctx->d_nframes, ctx->d_start, ctx->d_tss, ctx->d_trig, ctx->d_sig, slot_first, nslots,
+        ctx->ncams, ctx->max_frames);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    return ABUB_OK;
+}

@@ -1,0 +1,156 @@
+/* abub_cuda.h -- C ABI of libabub_cuda.so, the B200 (sm_100a) implementation of the
+ * AutoBub3hs per-event image hot path.
+ *
+ * The reference (picoexperiment/AutoBub3hs) has no plugin / FFI layer: its seam is the
+ * C++ class surface driven by AnyCamAnalysis()/main() (AutoBubStart3.cpp:67-125,
+ * :295-388).  Every entry point below names the reference call it replaces.  Plain
+ * pointers and sizes only; int return (0 = ok, negative = ABUB_E_*); no exceptions
+ * cross the boundary; buffers are caller-owned unless stated.
+ *
+ * Threading: one abub_ctx (CUDA stream + scratch arena) per host worker thread
+ * (the reference runs one OpenMP thread per event, AutoBubStart3.cpp:342); a ctx is
+ * not internally locked.
+ *
+ * Frame layout everywhere: 8-bit gray, row-major, rows*cols bytes, no padding
+ * (cv::Mat CV_8U continuous, as produced by Parser::GetImage, RawParser.cpp:34-47).
+ */
+#ifndef ABUB_CUDA_H
+#define ABUB_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ABUB_OK            0
+#define ABUB_E_INVALID    -101   /* bad argument                                   */
+#define ABUB_E_CUDA       -102   /* CUDA runtime error (see abub_last_error)       */
+#define ABUB_E_NOMEM      -103
+#define ABUB_E_CAPACITY   -104   /* caller-provided output buffer too small        */
+#define ABUB_E_NCCL       -105
+
+#define ABUB_MAX_TRACK    10     /* NumFramesBubbleTrack, common/CommonParameters.h:5 */
+
+typedef struct abub_ctx abub_ctx;
+
+/* One external contour of one binarised frame, in cv::findContours order
+ * (RETR_EXTERNAL, CHAIN_APPROX_TC89_L1; L3Localizer.cpp:264,793).  Mirrors what
+ * BubbleImageFrame (bubble/bubble.hpp:22-31) is filled from. */
+typedef struct abub_blob {
+    int32_t k;          /* 0 = trigger (genesis) frame, 1..10 = post-trigger frame    */
+    int32_t x, y, w, h; /* cv::boundingRect of the approximated polygon               */
+    int32_t npts;       /* number of polygon vertices                                 */
+    int32_t first_px;   /* raster index (y*cols+x) of the component's first pixel     */
+    int32_t reserved;
+    int64_t sum_x;      /* sum of polygon vertex x / y (centroid fallback,            */
+    int64_t sum_y;      /*   L3Localizer.cpp:409-419)                                 */
+    double  area;       /* cv::contourArea                                            */
+    double  m00, m10, m01; /* cv::moments (spatial, polygon)                          */
+} abub_blob;
+
+/* ---- context ----------------------------------------------------------------- */
+/* Replaces nothing in the reference (no device there).  max_slots = events resident
+ * in HBM at once; each slot holds ncams*max_frames frames. */
+int  abub_ctx_create(int device, int rows, int cols, int ncams, int max_frames,
+                     int max_slots, abub_ctx** out);
+void abub_ctx_destroy(abub_ctx* ctx);
+const char* abub_last_error(const abub_ctx* ctx);   /* never NULL */
+int  abub_sync(abub_ctx* ctx);                      /* cudaStreamSynchronize */
+/* cudaStream_t of the ctx as an opaque pointer (for event timing by the harness). */
+void* abub_stream(abub_ctx* ctx);
+
+/* ---- trained background (Trainer public fields, Trainer.hpp:35-54) ------------- */
+/* Installs TrainedAvgImage / TrainedSigmaImage / TrainingSetSize for one camera;
+ * replaces the per-analyzer deep copy `new Trainer(**TrainedData)`
+ * (AnalyzerUnit.cpp:27).  Host pointers, rows*cols bytes each. */
+int abub_set_background(abub_ctx* ctx, int cam, const uint8_t* mean, const uint8_t* sigma,
+                        int training_set_size);
+/* Same, from planes already in device memory (after abub_train_finish). */
+int abub_set_background_from_training(abub_ctx* ctx, int cam);
+
+/* ---- event frames -------------------------------------------------------------- */
+/* Pinned staging buffer of a slot: ncams*max_frames*rows*cols bytes, camera-major
+ * ([cam][frame][rows*cols]).  The host decodes Parser::GetImage output straight into
+ * it (RawParser.cpp:39 / ZipParser.cpp:222). */
+int abub_pinned_acquire(abub_ctx* ctx, int slot, uint8_t** host_ptr);
+/* Async H2D of the slot's staging buffer (cudaMemcpyAsync on the ctx stream);
+ * nframes[cam] = CameraFrames.size() of that camera (AnalyzerUnit.cpp:33). */
+int abub_event_submit(abub_ctx* ctx, int slot, const int* nframes);
+/* Copy one camera's frames from arbitrary host memory (pageable ok) into a slot. */
+int abub_event_upload(abub_ctx* ctx, int slot, int cam, const uint8_t* frames, int nframes);
+/* Device address of the slot's [cam][frame][rows*cols] stack (for producers that
+ * already live on the device) and the matching frame counts. */
+int abub_event_device_ptr(abub_ctx* ctx, int slot, uint8_t** dev_ptr);
+int abub_event_set_nframes(abub_ctx* ctx, int slot, const int* nframes);
+
+/* ---- trigger: AnalyzerUnit::FindTriggerFrame (AnalyzerUnit.cpp:119-324) --------- */
+/* K1: for every (slot, cam, j>=1) computes the 256-bin histogram of
+ * ProcessFrame(frame[j], frame[j-d]) (AnalyzerUnit.cpp:346-377 + calcHist :441-456),
+ * d = 2 (1 when TrainingSetSize < 6; frame 0 for j == 1).  Async. */
+int abub_trigger_hist(abub_ctx* ctx, int slot_first, int nslots);
+/* D2H of one (slot,cam) histogram table: hist[max_frames][256] (row 0 unused = 0). */
+int abub_trigger_hist_read(abub_ctx* ctx, int slot, int cam, uint32_t* hist);
+/* K2: the significance state machine (calculateSignificanceFrame :435-504 +
+ * FindTriggerFrame :119-324) for every (slot,cam) of the range, from
+ * start_frames[(slot-slot_first)*ncams+cam] (NULL = 1 everywhere).  A start frame > 1
+ * resumes with the history of frames 1..start-1 intact (AnalyzerUnit.cpp:165).  Async. */
+int abub_trigger_scan(abub_ctx* ctx, int slot_first, int nslots, const int* start_frames);
+/* Results of the last scan, D2H (synchronises the stream).  Arrays of nslots*ncams:
+ * trig = MatTrigFrame (valid when status 0), status = TriggerFrameIdentificationStatus
+ * (0, -3, -9), loc_thres = AnalyzerUnit::loc_thres.  sig (may be NULL) =
+ * nslots*ncams*max_frames doubles: stored significance of frame j (NaN-safe bit copy;
+ * untouched frames hold 0). */
+int abub_trigger_results(abub_ctx* ctx, int slot_first, int nslots, int* trig, int* status,
+                         int* loc_thres, double* sig);
+/* Convenience: FindTriggerFrame for one (slot,cam) with host buffers in the slot
+ * (runs K1 for the slot if its table is stale, then K2, then reads back). */
+int abub_trigger(abub_ctx* ctx, int slot, int cam, int start_frame, int* trig, int* status,
+                 int* loc_thres, double* sig);
+
+/* ---- training: Trainer::MakeAvgSigmaImage (Trainer.cpp:221-331) ----------------- */
+int abub_train_begin(abub_ctx* ctx, int cam);
+/* Gate (Trainer.cpp:279-287): 16-bin histogram of frame1-frame0 on the device, entropy
+ * in float on the host; when entropy <= 0.0005 both frames join the statistics.
+ * `frames01` = 2*rows*cols host bytes (frame 0 then frame 1).  *entropy / *kept out. */
+int abub_train_add_event(abub_ctx* ctx, int cam, const uint8_t* frames01, float* entropy, int* kept);
+/* Same with the two frames taken from a resident slot (frames 0 and 1 of `cam`). */
+int abub_train_add_slot(abub_ctx* ctx, int cam, int slot, float* entropy, int* kept);
+/* CalculateMeanSigmaImageVector (Trainer.cpp:144-216): exact sequential float32
+ * Welford in push order.  mean/sigma host out (may be NULL), *set_size =
+ * TrainingSetSize, *status = 0 or -7 (nothing kept, Trainer.cpp:308-313). */
+int abub_train_finish(abub_ctx* ctx, int cam, uint8_t* mean, uint8_t* sigma, int* set_size, int* status);
+/* Multi-GPU: exact integer partial sums (u32 sum x, u64 sum x^2, kept-frame count) of
+ * the frames this rank added; device buffers of rows*cols elements owned by the ctx,
+ * exposed so that the host can all-reduce them (NCCL sum) in place. */
+int abub_train_partials(abub_ctx* ctx, int cam, uint32_t** d_sum, uint64_t** d_sumsq, int** d_count);
+/* ncclAllReduce(sum) of the partials over `nccl_comm` (ncclComm_t passed opaquely;
+ * libnccl is dlopen'ed).  SURVEY.md 8(e): the only collective of the path. */
+int abub_train_allreduce(abub_ctx* ctx, int cam, void* nccl_comm);
+/* mean/sigma from reduced partials in fp64 + flags pixels within eps of a rounding
+ * boundary.  n_flagged out. */
+int abub_train_finish_partials(abub_ctx* ctx, int cam, uint8_t* mean, uint8_t* sigma,
+                               int* set_size, int* status, int* n_flagged);
+
+/* ---- localizer: L3Localizer::LocalizeOMatic (L3Localizer.cpp:881-968) ----------- */
+/* For the trigger frame (k=0: CalculateInitialBubbleParams :215-290, frames `trig` and
+ * `pre_trig`, TOZERO at loc_thres, Otsu, external contours) and the post-trigger
+ * frames k=1..n_post (CalculatePostTriggerFrameParams :764-836) of one (slot,cam):
+ * writes the contour records in findContours order, frame after frame, into `out`
+ * (capacity `cap`), and n_per_frame[k] for k=0..n_post.  Mask tests, BoxArea filters
+ * and tracking stay on the host (L3Localizer.cpp:277-290,392-444,842-863). */
+int abub_localize(abub_ctx* ctx, int slot, int cam, int trig, int pre_trig, int loc_thres,
+                  int n_post, abub_blob* out, int cap, int* n_per_frame);
+/* Debug/parity taps: binary image of frame k of the last abub_localize (rows*cols). */
+int abub_localize_binary(abub_ctx* ctx, int k, uint8_t* out);
+
+/* ---- single-frame ops (parity taps; each is one kernel of the path) ------------- */
+/* ProcessFrame (AnalyzerUnit.cpp:346-377) of two host frames with the installed
+ * sigma of `cam`; diff out (rows*cols), hist out (256, may be NULL). */
+int abub_process_frame(abub_ctx* ctx, int cam, const uint8_t* work, const uint8_t* prev,
+                       uint8_t* diff, uint32_t* hist);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ABUB_CUDA_H */

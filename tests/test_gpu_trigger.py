@@ -1,0 +1,159 @@
+"""GPU parity: K1 (ProcessFrame + 256-bin histogram) and K2 (significance trigger) through
+the C ABI against the cv2 oracle.  Bit-exact for histograms / trigger index / status /
+loc_thres; significance doubles compared exactly too (same IEEE operations, no FMA)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from autobub3hs_b200 import capi
+    capi.load()
+    return capi
+
+
+def _oracle_hists(o, frames, sigma, tss):
+    n = len(frames)
+    H = np.zeros((n, 256), np.uint32)
+    d = 2 if tss >= 6 else 1
+    for j in range(1, n):
+        jp = max(j - d, 0)
+        H[j] = o.hist256(o.process_frame(frames[j], frames[jp], sigma)).astype(np.uint32)
+    return H
+
+
+@pytest.mark.parametrize("shape", [(264, 420), (77, 131), (40, 244), (35, 120), (5, 5), (36, 121)])
+def test_process_frame_single(capi, shape):
+    import oracle.cv2_oracle as o
+    rows, cols = shape
+    rng = np.random.default_rng(rows * 1000 + cols)
+    with capi.Context(rows, cols, ncams=1, max_frames=4, max_slots=1) as ctx:
+        for trial in range(4):
+            base = rng.integers(0, 256, (rows, cols)).astype(np.float32)
+            a = np.clip(base + rng.normal(0, 4 + 20 * trial, (rows, cols)), 0, 255).astype(np.uint8)
+            b = np.clip(base + rng.normal(0, 4 + 20 * trial, (rows, cols)), 0, 255).astype(np.uint8)
+            sigma = rng.integers(0, 3 + trial * 20, (rows, cols)).astype(np.uint8)
+            mean = np.zeros_like(sigma)
+            ctx.set_background(0, mean, sigma, 12)
+            diff, hist = ctx.process_frame(0, a, b)
+            ref = o.process_frame(a, b, sigma)
+            assert np.array_equal(diff, ref)
+            assert np.array_equal(hist, o.hist256(ref).astype(np.uint32))
+            assert int(hist.sum()) == rows * cols
+
+
+def test_process_frame_extremes(capi):
+    import oracle.cv2_oracle as o
+    rows, cols = 64, 248
+    with capi.Context(rows, cols, ncams=1, max_frames=4, max_slots=1) as ctx:
+        cases = [(255, 0, 0), (0, 255, 0), (255, 0, 42), (255, 0, 255), (7, 7, 0)]
+        for av, bv, sv in cases:
+            a = np.full((rows, cols), av, np.uint8)
+            b = np.full((rows, cols), bv, np.uint8)
+            s = np.full((rows, cols), sv, np.uint8)
+            ctx.set_background(0, s, s, 12)
+            diff, hist = ctx.process_frame(0, a, b)
+            ref = o.process_frame(a, b, s)
+            assert np.array_equal(diff, ref), (av, bv, sv)
+            assert np.array_equal(hist, o.hist256(ref).astype(np.uint32))
+        # checkerboard of saturated values: exercises both planes and every rounding carry
+        yy, xx = np.mgrid[0:rows, 0:cols]
+        a = (((yy + xx) & 1) * 255).astype(np.uint8)
+        b = (255 - a).astype(np.uint8)
+        s = np.zeros((rows, cols), np.uint8)
+        ctx.set_background(0, s, s, 12)
+        diff, hist = ctx.process_frame(0, a, b)
+        assert np.array_equal(diff, o.process_frame(a, b, s))
+
+
+def test_trigger_batch_vs_oracle(capi, small_run, small_trained):
+    import oracle.cv2_oracle as o
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    nev = len(run.events)
+    with capi.Context(rows, cols, ncams=4, max_frames=40, max_slots=nev) as ctx:
+        for c in range(4):
+            ctx.set_background(c, trained[c].avg, trained[c].sigma, trained[c].training_set_size)
+        for ev in range(nev):
+            for c in range(4):
+                ctx.event_upload(ev, c, run.events[ev][c])
+        ctx.trigger_hist(0, nev)
+        ctx.trigger_scan(0, nev)
+        trig, status, lt, sig = ctx.trigger_results(0, nev)
+        for ev in range(nev):
+            for c in range(4):
+                fr = run.events[ev][c]
+                H = ctx.trigger_hist_read(ev, c)
+                Href = _oracle_hists(o, fr, trained[c].sigma, trained[c].training_set_size)
+                assert np.array_equal(H[:len(fr)], Href), (ev, c)
+                st = o.SignificanceState()
+                r = o.find_trigger_frame(o.FrameSource(fr), trained[c].sigma, trained[c].training_set_size, 1, st, 0)
+                assert status[ev, c] == r.status, (ev, c, run.specs[ev].klass)
+                if r.status == 0:
+                    assert trig[ev, c] == r.trig
+                if r.status != -9:
+                    assert lt[ev, c] == r.loc_thres
+                for (i, s) in r.sig:
+                    g = sig[ev, c, i]
+                    assert (np.isnan(s) and np.isnan(g)) or s == g, (ev, c, i, s, g)
+
+
+def test_trigger_retrigger_and_small_training_set(capi, small_run, small_trained):
+    """start_frame > 1 resumes with history intact (AnalyzerUnit.cpp:165); TrainingSetSize < 6
+    switches to the one-frame offset and the 5.0 threshold (:182-188)."""
+    import oracle.cv2_oracle as o
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    with capi.Context(rows, cols, ncams=4, max_frames=40, max_slots=1) as ctx:
+        for tss in (12, 4):
+            for c in range(4):
+                ctx.set_background(c, trained[c].avg, trained[c].sigma, tss)
+            for ev in (0, 1, 7):
+                for c in range(4):
+                    ctx.event_upload(0, c, run.events[ev][c])
+                for c in range(4):
+                    fr = run.events[ev][c]
+                    st = o.SignificanceState()
+                    hp = o.HistProvider(o.FrameSource(fr), trained[c].sigma)
+                    mat = 0
+                    for attempt in range(4):
+                        r = o.find_trigger_frame(o.FrameSource(fr), trained[c].sigma, tss, mat + 1, st, mat, hp)
+                        t, s, l, sig = ctx.trigger(0, c, mat + 1)
+                        assert s == r.status, (tss, ev, c, attempt)
+                        if r.status != 0:
+                            break
+                        assert t == r.trig and l == r.loc_thres
+                        for (i, sv) in r.sig:
+                            assert sig[i] == sv or (np.isnan(sv) and np.isnan(sig[i]))
+                        mat = r.trig
+
+
+def test_significance_corner_cases(capi):
+    """Hand-built frames that drive bins >= 2 above 46340 counts (int32 wrap of val*val,
+    AnalyzerUnit.cpp:529), zero-variance histories and NaN/inf propagation."""
+    import oracle.cv2_oracle as o
+    rows, cols = 300, 400      # 120000 px > 46340
+    n = 12
+    rng = np.random.default_rng(5)
+    frames = np.zeros((n, rows, cols), np.uint8)
+    for f in range(n):
+        frames[f] = 100 + (f % 2) * 0
+    # big uniform step at frame 6 and 7 -> whole image in one non-zero bin
+    frames[6:] += 40
+    frames[9:] += 3
+    frames[10, :50] += 90
+    sigma = np.zeros((rows, cols), np.uint8)
+    with capi.Context(rows, cols, ncams=1, max_frames=n, max_slots=1) as ctx:
+        for tss in (12, 2):
+            ctx.set_background(0, sigma, sigma, tss)
+            ctx.event_upload(0, 0, frames)
+            t, s, l, sig = ctx.trigger(0, 0, 1)
+            st = o.SignificanceState()
+            r = o.find_trigger_frame(o.FrameSource(frames), sigma, tss, 1, st, 0)
+            assert s == r.status
+            if r.status == 0:
+                assert t == r.trig and l == r.loc_thres
+            for (i, sv) in r.sig:
+                assert sig[i] == sv or (np.isnan(sv) and np.isnan(sig[i])), (tss, i, sv, sig[i])
