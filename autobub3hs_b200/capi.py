@@ -25,7 +25,7 @@ EXPORTS = [
     "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_scan", "abub_trigger_results", "abub_trigger",
     "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_finish",
     "abub_train_partials", "abub_train_allreduce", "abub_train_finish_partials",
-    "abub_localize", "abub_localize_binary", "abub_process_frame",
+    "abub_localize", "abub_localize_batch", "abub_localize_binary", "abub_process_frame",
 ]
 
 
@@ -35,6 +35,12 @@ class Blob(C.Structure):
                 ("npts", C.c_int32), ("first_px", C.c_int32), ("reserved", C.c_int32),
                 ("sum_x", C.c_int64), ("sum_y", C.c_int64),
                 ("area", C.c_double), ("m00", C.c_double), ("m10", C.c_double), ("m01", C.c_double)]
+
+
+class LocItem(C.Structure):
+    """struct abub_loc_item."""
+    _fields_ = [("slot", C.c_int32), ("cam", C.c_int32), ("trig", C.c_int32), ("pre_trig", C.c_int32),
+                ("loc_thres", C.c_int32), ("n_post", C.c_int32)]
 
 
 class AbubError(RuntimeError):
@@ -81,6 +87,7 @@ def load() -> C.CDLL:
     lib.abub_train_allreduce.argtypes = [vp, C.c_int, vp]
     lib.abub_train_finish_partials.argtypes = [vp, C.c_int, u8p, u8p, ip, ip, ip]
     lib.abub_localize.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(Blob), C.c_int, ip]
+    lib.abub_localize_batch.argtypes = [vp, C.POINTER(LocItem), C.c_int, C.POINTER(Blob), C.c_int, ip, ip]
     lib.abub_localize_binary.argtypes = [vp, C.c_int, u8p]
     lib.abub_process_frame.argtypes = [vp, C.c_int, u8p, u8p, u8p, vp]
     for name in EXPORTS:
@@ -253,6 +260,25 @@ class Context:
                  "abub_localize")
         counts = [npf[k] for k in range(n_post + 1)]
         return [blobs[i] for i in range(sum(counts))], counts
+
+    def localize_batch(self, items: Sequence[Tuple[int, int, int, int, int, int]], cap: int = 65536):
+        """items: (slot, cam, trig, pre_trig, loc_thres, n_post).  Returns per item a list (k=0..n_post) of blob lists."""
+        n = len(items)
+        arr = (LocItem * n)(*[LocItem(*it) for it in items])
+        blobs = (Blob * cap)()
+        npf = (C.c_int * (n * (ABUB_MAX_TRACK + 1)))()
+        tot = C.c_int()
+        self._ck(self.lib.abub_localize_batch(self.h, arr, n, blobs, cap, npf, C.byref(tot)), "abub_localize_batch")
+        out, off = [], 0
+        for i, it in enumerate(items):
+            frames = []
+            for k in range(it[5] + 1):
+                c = npf[i * (ABUB_MAX_TRACK + 1) + k]
+                frames.append([blobs[off + j] for j in range(c)])
+                off += c
+            out.append(frames)
+        assert off == tot.value
+        return out
 
     def localize_binary(self, k: int) -> np.ndarray:
         out = np.zeros((self.rows, self.cols), np.uint8)

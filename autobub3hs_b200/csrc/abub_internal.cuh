@@ -97,6 +97,20 @@ int abub_k4_finish_from_partials(abub_ctx* ctx, const uint32_t* d_sum, const uin
                                  uint8_t* d_sigma, int* d_nflag, uint8_t* d_flag);
 int abub_k4_fixup(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, const uint8_t* d_flag, uint8_t* d_mean,
                   uint8_t* d_sigma);
+// one binarisation job of the localizer (a frame of an item)
+struct abub_loc_job {
+    const uint8_t* a;        // genesis: trigger frame ; post: frame[trig+k]
+    const uint8_t* b;        // genesis: pre-trigger frame ; post: TrainedAvgImage
+    const uint32_t* k32;     // genesis: K32 plane of the camera
+    const uint8_t* t8;       // post: min(6 sigma, 255)
+    uint8_t* tz;             // out: TOZERO'd image (rows*cols)
+    uint32_t* hist;          // out: 256-bin histogram of tz
+    int tozero;              // loc_thres (genesis) or 3 (post)
+    int genesis;
+    int k;                   // 0 = genesis frame, 1.. = post-trigger frame
+    int item;                // index of the abub_loc_item this job belongs to
+};
+int abub_k1_launch_genesis_jobs(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs);
 // K5-K7 (k5_localize.cu)
 int abub_loc_init(abub_ctx* ctx);
 void abub_loc_free(abub_ctx* ctx);

@@ -231,6 +231,28 @@ __global__ void k1_single_kernel(const uint8_t* __restrict__ A, const uint8_t* _
         }
 }
 
+// localizer genesis jobs (CalculateInitialBubbleParams, L3Localizer.cpp:232,252): ProcessFrame,
+// THRESH_TOZERO at loc_thres, histogram of the result; grid.y = job (non-genesis jobs return)
+__global__ void k1_genesis_jobs_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols) {
+    extern __shared__ uint32_t smem[];
+    const abub_loc_job job = jobs[blockIdx.y];
+    if (!job.genesis) return;
+    uint32_t* sh_hist = smem;
+    const int warp = threadIdx.x >> 5;
+    uint32_t* xch = smem + 256 + warp * 256;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
+    __syncthreads();
+    const int y0 = blockIdx.x * K1_TH;
+    if (y0 < rows)
+        k1_strip<1>(job.a, job.b, job.k32, rows, cols, y0, K1_TH, warp * ABUB_K1_TILE_W, sh_hist, xch, job.tz,
+                    job.tozero);
+    __syncthreads();
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        const uint32_t c = sh_hist[i];
+        if (c) atomicAdd(&job.hist[i], c);
+    }
+}
+
 __global__ void k1_fill_bin0_single(uint32_t* hist, uint32_t npix) {
     const int lane = threadIdx.x;
     uint32_t s = 0;
@@ -297,6 +319,19 @@ int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b,
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     if (d_hist) {
         k1_fill_bin0_single<<<1, 32, 0, ctx->stream>>>(d_hist, (uint32_t)ctx->npix);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
+    return ABUB_OK;
+}
+
+int abub_k1_launch_genesis_jobs(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs) {
+    const int threads = k1_block_threads(ctx->cols);
+    ABUB_REQUIRE(ctx, threads <= 1024, "cols too large for K1 (max 3840)");
+    const int nstrips = (ctx->rows + K1_TH - 1) / K1_TH;
+    for (int j0 = 0; j0 < njobs; j0 += 65535) {
+        const int nj = (njobs - j0 < 65535) ? njobs - j0 : 65535;
+        k1_genesis_jobs_kernel<<<dim3(nstrips, nj), threads, k1_smem_bytes(threads), ctx->stream>>>(d_jobs + j0, ctx->rows,
+                                                                                                   ctx->cols);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     return ABUB_OK;

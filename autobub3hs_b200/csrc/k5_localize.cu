@@ -1,16 +1,511 @@
-// K5-K7 -- L3Localizer blob extraction (placeholder until the kernels land in this file).
+// K5-K7 -- L3Localizer blob extraction on the device.
+// Reference: L3Localizer::CalculateInitialBubbleParams (L3Localizer.cpp:215-290),
+// CalculatePostTriggerFrameParams (:764-836), i.e. OpenCV threshold(TOZERO),
+// threshold(BINARY|OTSU), blur 3x3, findContours(RETR_EXTERNAL, CHAIN_APPROX_TC89_L1),
+// boundingRect, contourArea, moments.
+//
+// The binarised frames are almost empty (a few blobs), so nothing here labels the whole
+// image.  Pipeline per chunk of binarisation jobs (one job = one frame of one analyzer):
+//   K5a  genesis jobs : ProcessFrame + TOZERO(loc_thres) + histogram   (k1_processframe.cu)
+//   K5b  post jobs    : absdiff(frame,avg) - 6 sigma, 3x3 box, TOZERO(3) + histogram
+//   K5c  Otsu threshold per job from the histogram (fp64, sequential as OpenCV)
+//   K6   raster-start candidates: foreground pixels with no foreground neighbour earlier in
+//        raster order (W, NW, N, NE).  Every 8-connected component has exactly one
+//        candidate that is the raster-first pixel of the border it starts (its own first
+//        pixel); all other candidates meet an earlier pixel while following their border.
+//   sort candidates by (job, descending raster index)  == findContours output order
+//   K7a  trace pass 1: follow the border (Suzuki outer-border rule), reject on an earlier
+//        pixel, measure the chain length
+//   K7b  trace pass 2 into an exactly-sized arena + TC89_L1 approximation + polygon
+//        boundingRect / area / moments
+//   K7c  RETR_EXTERNAL: a component is dropped when its first pixel lies inside another
+//        component's outer border (= in one of its holes), decided by crack parity on the
+//        stored chain
+//   compaction in order -> abub_blob records
+#include <cub/cub.cuh>
+
 #include "abub_internal.cuh"
 
-int abub_loc_init(abub_ctx*) { return ABUB_OK; }
-void abub_loc_free(abub_ctx*) {}
+namespace {
 
-extern "C" int abub_localize(abub_ctx* ctx, int, int, int, int, int, int, abub_blob*, int, int*) {
-    if (!ctx) return ABUB_E_INVALID;
-    ctx->err = "abub_localize: not built yet";
-    return ABUB_E_INVALID;
+struct Cand {           // one traced border
+    int job;
+    int first_px;       // y*cols + x of the start pixel
+    int len;            // chain length (0: isolated pixel)
+    int accepted;       // start is the raster-first pixel of its border
+    int minx, maxx, miny, maxy;   // bbox of the chain
+    long long arena_off;
+    int external;
+    int pad;
+};
+
+struct LocArena {
+    // job-level
+    abub_loc_job* d_jobs = nullptr;  abub_loc_job* h_jobs = nullptr;  int jobs_cap = 0;
+    uint8_t* d_tz = nullptr;         size_t tz_cap = 0;       // jobs_cap * npix
+    uint32_t* d_hist = nullptr;                                 // jobs_cap * 256
+    int* d_thr = nullptr;                                       // jobs_cap
+    // candidates
+    unsigned long long* d_keys = nullptr; unsigned long long* d_keys_alt = nullptr; int cand_cap = 0;
+    Cand* d_cand = nullptr;
+    int* d_counters = nullptr;       // [0]=n candidates, [1]=n accepted, [2]=n external, [3]=overflow
+    long long* d_scan = nullptr;     // arena offsets (exclusive scan)
+    int* d_iscan = nullptr;
+    void* d_cub_tmp = nullptr; size_t cub_tmp_bytes = 0;
+    // chain arena: per element {x:int16,y:int16} + code/flags byte + S byte + K u16 + removed byte
+    uint8_t* d_chain = nullptr; size_t chain_cap = 0;          // bytes
+    abub_blob* d_blobs = nullptr; int blob_cap = 0;
+    int* d_npf = nullptr;            // per job count of emitted blobs
+    // parity tap of the last call
+    int last_njobs = 0;
+};
+
+
+// ------------------------------------------------------------------------------------
+// K5b: post-trigger frames
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ int refl(int p, int n) {
+    if (p < 0) p = -p;
+    if (p >= n) p = 2 * (n - 1) - p;
+    return min(max(p, 0), n - 1);
 }
-extern "C" int abub_localize_binary(abub_ctx* ctx, int, uint8_t*) {
+
+constexpr int PT_W = 64, PT_H = 16;
+
+__global__ void __launch_bounds__(256)
+k5_post_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols) {
+    __shared__ uint8_t d[(PT_H + 2)][PT_W + 2 + 2];
+    __shared__ uint32_t sh_hist[256];
+    const abub_loc_job job = jobs[blockIdx.z];
+    if (job.genesis) return;
+    const int x0 = blockIdx.x * PT_W, y0 = blockIdx.y * PT_H;
+    sh_hist[threadIdx.x] = 0;
+    for (int i = threadIdx.x; i < (PT_H + 2) * (PT_W + 2); i += 256) {
+        const int ly = i / (PT_W + 2), lx = i % (PT_W + 2);
+        const int y = refl(y0 + ly - 1, rows), x = refl(x0 + lx - 1, cols);
+        const size_t p = (size_t)y * cols + x;
+        const int v = abs((int)job.a[p] - (int)job.b[p]) - (int)job.t8[p];   // L3Localizer.cpp:779-782
+        d[ly][lx] = (uint8_t)max(v, 0);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < PT_H * PT_W; i += 256) {
+        const int ly = i / PT_W, lx = i % PT_W;
+        const int y = y0 + ly, x = x0 + lx;
+        if (y < rows && x < cols) {
+            int s = 0;
+#pragma unroll
+            for (int j = 0; j < 3; j++) s += d[ly + j][lx] + d[ly + j][lx + 1] + d[ly + j][lx + 2];
+            int v = (s + 4) / 9;                     // cv::blur 3x3 (:785)
+            if (v <= job.tozero) v = 0;              // THRESH_TOZERO (:786)
+            job.tz[(size_t)y * cols + x] = (uint8_t)v;
+            if (v) atomicAdd(&sh_hist[v], 1u);
+        }
+    }
+    __syncthreads();
+    const uint32_t c = sh_hist[threadIdx.x];
+    if (c && threadIdx.x) atomicAdd(&job.hist[threadIdx.x], c);
+}
+
+// ------------------------------------------------------------------------------------
+// K5c: Otsu (OpenCV getThreshVal_Otsu_8u), one thread per job; also fills bin 0
+// ------------------------------------------------------------------------------------
+__global__ void k5_otsu_kernel(const abub_loc_job* __restrict__ jobs, int* __restrict__ thr, int njobs, uint32_t npix) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= njobs) return;
+    uint32_t* h = jobs[j].hist;
+    uint32_t s = 0;
+    for (int i = 1; i < 256; i++) s += h[i];
+    h[0] = npix - s;
+    const double scale = __ddiv_rn(1.0, (double)npix);
+    double mu = 0;
+    for (int i = 0; i < 256; i++) mu = __dadd_rn(mu, __dmul_rn((double)i, (double)h[i]));
+    mu = __dmul_rn(mu, scale);
+    double mu1 = 0, q1 = 0, max_sigma = 0;
+    int t = 0;
+    for (int i = 0; i < 256; i++) {
+        const double p_i = __dmul_rn((double)h[i], scale);
+        mu1 = __dmul_rn(mu1, q1);
+        q1 = __dadd_rn(q1, p_i);
+        const double q2 = __dsub_rn(1.0, q1);
+        if (fmin(q1, q2) < 1.1920928955078125e-07 || fmax(q1, q2) > 1. - 1.1920928955078125e-07) continue;
+        mu1 = __ddiv_rn(__dadd_rn(mu1, __dmul_rn((double)i, p_i)), q1);
+        const double mu2 = __ddiv_rn(__dsub_rn(mu, __dmul_rn(q1, mu1)), q2);
+        const double dm = __dsub_rn(mu1, mu2);
+        const double sg = __dmul_rn(__dmul_rn(__dmul_rn(q1, q2), dm), dm);
+        if (sg > max_sigma) { max_sigma = sg; t = i; }
+    }
+    thr[j] = t;
+}
+
+// ------------------------------------------------------------------------------------
+// K6: raster-start candidates
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k6_candidates_kernel(const abub_loc_job* __restrict__ jobs, const int* __restrict__ thr, int rows, int cols,
+                     unsigned long long* __restrict__ keys, int* __restrict__ counters, int cand_cap, int job0) {
+    const int jl = blockIdx.y;
+    const uint8_t* tz = jobs[jl].tz;
+    const int t = thr[jl];
+    const size_t npix = (size_t)rows * cols;
+    for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += (size_t)gridDim.x * blockDim.x) {
+        if (tz[p] <= t) continue;
+        const int y = (int)(p / cols), x = (int)(p % cols);
+        bool earlier = false;
+        if (x > 0 && tz[p - 1] > t) earlier = true;
+        if (y > 0) {
+            const uint8_t* up = tz + p - cols;
+            if (up[0] > t) earlier = true;
+            if (x > 0 && up[-1] > t) earlier = true;
+            if (x + 1 < cols && up[1] > t) earlier = true;
+        }
+        if (!earlier) {
+            const int slot = atomicAdd(&counters[0], 1);
+            if (slot < cand_cap)
+                keys[slot] = ((unsigned long long)(unsigned)(job0 + jl) << 32) | (unsigned)(0xFFFFFFFFu - (unsigned)p);
+            else
+                counters[3] = 1;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// K7: border following / approximation / measurement, one thread per candidate
+// ------------------------------------------------------------------------------------
+}  // namespace
+#include "contour_core.cuh"
+namespace {
+using namespace abub_contour;
+
+__device__ __forceinline__ void decode_key(unsigned long long key, int job0, int* jl, int* px) {
+    *jl = (int)(key >> 32) - job0;
+    *px = (int)(0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull));
+}
+
+__global__ void k7_trace1_kernel(const unsigned long long* __restrict__ keys, int ncand, const abub_loc_job* __restrict__ jobs,
+                                 const int* __restrict__ thr, int rows, int cols, int job0, Cand* __restrict__ cand,
+                                 long long* __restrict__ sizes) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ncand) return;
+    int jl, p;
+    decode_key(keys[i], job0, &jl, &p);
+    const Pix im{jobs[jl].tz, thr[jl], rows, cols};
+    const TraceResult t = trace_border(im, p % cols, p / cols, nullptr, 4 * rows * cols);
+    Cand c;
+    c.job = jl; c.first_px = p; c.len = t.len; c.accepted = t.accepted;
+    c.minx = t.minx; c.maxx = t.maxx; c.miny = t.miny; c.maxy = t.maxy;
+    c.arena_off = 0; c.external = 1; c.pad = 0;
+    cand[i] = c;
+    sizes[i] = t.accepted ? (long long)((ChainView::bytes(t.len) + 15) & ~(size_t)15) : 0;
+}
+
+__global__ void k7_trace2_kernel(int ncand, const abub_loc_job* __restrict__ jobs, const int* __restrict__ thr, int rows,
+                                 int cols, Cand* __restrict__ cand, const long long* __restrict__ offs,
+                                 uint8_t* __restrict__ arena, abub_blob* __restrict__ tmp) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ncand) return;
+    Cand c = cand[i];
+    if (!c.accepted) return;
+    c.arena_off = offs[i];
+    cand[i].arena_off = c.arena_off;
+    const Pix im{jobs[c.job].tz, thr[c.job], rows, cols};
+    ChainView cv(arena + c.arena_off, c.len);
+    int L;
+    if (c.len == 0) {
+        cv.P[0] = make_short2((short)(c.first_px % cols), (short)(c.first_px / cols));
+        cv.removed[0] = 0;
+        L = 1;
+    } else {
+        trace_border(im, c.first_px % cols, c.first_px / cols, &cv, 4 * rows * cols);
+        L = approx_tc89_l1(cv, c.len);
+    }
+    const PolyMeasure m = measure_alive(cv, L);
+    abub_blob b;
+    b.k = jobs[c.job].k; b.x = m.x; b.y = m.y; b.w = m.w; b.h = m.h; b.npts = m.npts; b.first_px = c.first_px;
+    b.reserved = jobs[c.job].item; b.sum_x = m.sum_x; b.sum_y = m.sum_y;
+    b.area = m.area; b.m00 = m.m00; b.m10 = m.m10; b.m01 = m.m01;
+    tmp[i] = b;
+}
+
+// RETR_EXTERNAL: drop components whose first pixel lies inside another component's outer border.
+// Candidates are sorted by job, so the same-job range is found by walking both ways.
+__global__ void k7_external_kernel(int ncand, int cols, Cand* __restrict__ cand, const uint8_t* __restrict__ arena,
+                                   int* __restrict__ flags) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ncand) return;
+    const Cand c = cand[i];
+    int keep = c.accepted;
+    if (keep) {
+        const int qx = c.first_px % cols, qy = c.first_px / cols;
+        for (int dir = -1; dir <= 1 && keep; dir += 2) {
+            for (int j = i + dir; j >= 0 && j < ncand && keep; j += dir) {
+                const Cand o = cand[j];
+                if (o.job != c.job) break;
+                if (!o.accepted || o.len == 0) continue;
+                if (qx <= o.minx || qx >= o.maxx || qy <= o.miny || qy >= o.maxy) continue;
+                const ChainView cv(const_cast<uint8_t*>(arena) + o.arena_off, o.len);
+                if (inside_outer_border(cv, o.len, qx, qy)) keep = 0;
+            }
+        }
+    }
+    flags[i] = keep;
+}
+
+__global__ void k7_emit_kernel(int ncand, const Cand* __restrict__ cand, const int* __restrict__ flags,
+                               const int* __restrict__ pos, const abub_blob* __restrict__ tmp, abub_blob* __restrict__ out,
+                               int out_cap, int* __restrict__ npf, int* __restrict__ counters) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ncand || !flags[i]) return;
+    const int o = pos[i];
+    if (o < out_cap) out[o] = tmp[i];
+    atomicAdd(&npf[cand[i].job], 1);
+    atomicAdd(&counters[2], 1);
+}
+
+__global__ void k5_binary_kernel(const uint8_t* __restrict__ tz, const int* __restrict__ thr, int job, uint8_t* __restrict__ out,
+                                 size_t npix) {
+    const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < npix) out[p] = tz[(size_t)job * npix + p] > thr[job] ? 255 : 0;
+}
+
+template <typename T>
+int grow(abub_ctx* ctx, T** p, size_t n_elems) {
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    ABUB_CHECK_CUDA(ctx, cudaMalloc((void**)p, n_elems * sizeof(T)));
+    return ABUB_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------
+// host orchestration
+// ------------------------------------------------------------------------------------
+static LocArena* arena_of(abub_ctx* ctx) { return reinterpret_cast<LocArena*>(ctx->loc); }
+
+int abub_loc_init(abub_ctx* ctx) {
+    LocArena* a = new LocArena();
+    ctx->loc = a;
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&a->d_counters, 8 * sizeof(int)));
+    return ABUB_OK;
+}
+
+void abub_loc_free(abub_ctx* ctx) {
+    LocArena* a = arena_of(ctx);
+    if (!a) return;
+    cudaFree(a->d_jobs); cudaFree(a->d_tz); cudaFree(a->d_hist); cudaFree(a->d_thr);
+    cudaFree(a->d_keys); cudaFree(a->d_keys_alt); cudaFree(a->d_cand); cudaFree(a->d_counters);
+    cudaFree(a->d_scan); cudaFree(a->d_iscan); cudaFree(a->d_cub_tmp); cudaFree(a->d_chain);
+    cudaFree(a->d_blobs); cudaFree(a->d_npf);
+    free(a->h_jobs);
+    delete a;
+    ctx->loc = nullptr;
+}
+
+static int ensure_jobs(abub_ctx* ctx, LocArena* a, int njobs) {
+    if (njobs <= a->jobs_cap) return ABUB_OK;
+    int rc;
+    if ((rc = grow(ctx, &a->d_jobs, (size_t)njobs))) return rc;
+    if ((rc = grow(ctx, &a->d_tz, (size_t)njobs * ctx->npix))) return rc;
+    if ((rc = grow(ctx, &a->d_hist, (size_t)njobs * 256))) return rc;
+    if ((rc = grow(ctx, &a->d_thr, (size_t)njobs))) return rc;
+    if ((rc = grow(ctx, &a->d_npf, (size_t)njobs))) return rc;
+    free(a->h_jobs);
+    a->h_jobs = (abub_loc_job*)malloc(sizeof(abub_loc_job) * njobs);
+    a->jobs_cap = njobs;
+    return ABUB_OK;
+}
+
+static int ensure_cands(abub_ctx* ctx, LocArena* a, int n) {
+    if (n <= a->cand_cap) return ABUB_OK;
+    int rc;
+    if ((rc = grow(ctx, &a->d_keys, (size_t)n))) return rc;
+    if ((rc = grow(ctx, &a->d_keys_alt, (size_t)n))) return rc;
+    if ((rc = grow(ctx, &a->d_cand, (size_t)n))) return rc;
+    if ((rc = grow(ctx, &a->d_scan, (size_t)n + 1))) return rc;
+    if ((rc = grow(ctx, &a->d_iscan, (size_t)2 * n + 2))) return rc;
+    if ((rc = grow(ctx, &a->d_blobs, (size_t)2 * n))) return rc;      // tmp records [0,n) + ordered output [n,2n)
+    a->blob_cap = n;
+    size_t t1 = 0, t2 = 0, t3 = 0;
+    cub::DeviceRadixSort::SortKeys(nullptr, t1, a->d_keys, a->d_keys_alt, 2 * n + 2);
+    cub::DeviceScan::ExclusiveSum(nullptr, t2, a->d_scan, a->d_scan, 2 * n + 2);
+    cub::DeviceScan::ExclusiveSum(nullptr, t3, a->d_iscan, a->d_iscan, 2 * n + 2);
+    size_t t = t1 > t2 ? t1 : t2;
+    if (t3 > t) t = t3;
+    cudaFree(a->d_cub_tmp);
+    a->d_cub_tmp = nullptr;
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&a->d_cub_tmp, t + 256));
+    a->cub_tmp_bytes = t + 256;
+    a->cand_cap = n;
+    return ABUB_OK;
+}
+
+// one chunk of jobs already described in a->h_jobs[0..njobs)
+static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blob>& blobs_out, std::vector<int>& npf_out) {
+    cudaStream_t st = ctx->stream;
+    const size_t npix = ctx->npix;
+    int rc;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(a->d_jobs, a->h_jobs, sizeof(abub_loc_job) * njobs, cudaMemcpyHostToDevice, st));
+    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_hist, 0, (size_t)njobs * 256 * sizeof(uint32_t), st));
+    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_npf, 0, (size_t)njobs * sizeof(int), st));
+    if ((rc = abub_k1_launch_genesis_jobs(ctx, a->d_jobs, njobs))) return rc;
+    {
+        dim3 grid((ctx->cols + PT_W - 1) / PT_W, (ctx->rows + PT_H - 1) / PT_H, njobs);
+        k5_post_kernel<<<grid, 256, 0, st>>>(a->d_jobs, ctx->rows, ctx->cols);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
+    k5_otsu_kernel<<<(njobs + 63) / 64, 64, 0, st>>>(a->d_jobs, a->d_thr, njobs, (uint32_t)npix);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    a->last_njobs = njobs;
+
+    int counters[8];
+    if (a->cand_cap == 0 && (rc = ensure_cands(ctx, a, 1 << 16))) return rc;
+    for (;;) {
+        ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_counters, 0, 8 * sizeof(int), st));
+        const int gx = (int)((npix + 256 * 16 - 1) / (256 * 16));
+        k6_candidates_kernel<<<dim3(gx, njobs), 256, 0, st>>>(a->d_jobs, a->d_thr, ctx->rows, ctx->cols, a->d_keys,
+                                                             a->d_counters, a->cand_cap, 0);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(counters, a->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
+        ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(st));
+        if (counters[0] <= a->cand_cap) break;
+        if ((rc = ensure_cands(ctx, a, counters[0] + counters[0] / 4 + 1024))) return rc;
+    }
+    const int ncand = counters[0];
+    npf_out.assign(njobs, 0);
+    if (ncand == 0) return ABUB_OK;
+    size_t tmpb = a->cub_tmp_bytes;
+    cub::DeviceRadixSort::SortKeys(a->d_cub_tmp, tmpb, a->d_keys, a->d_keys_alt, ncand, 0, 64, st);
+    const int tb = 64, nb = (ncand + tb - 1) / tb;
+    k7_trace1_kernel<<<nb, tb, 0, st>>>(a->d_keys_alt, ncand, a->d_jobs, a->d_thr, ctx->rows, ctx->cols, 0, a->d_cand,
+                                        a->d_scan);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    // arena offsets: exclusive scan over ncand+1 entries (the extra entry yields the total)
+    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_scan + ncand, 0, sizeof(long long), st));
+    tmpb = a->cub_tmp_bytes;
+    cub::DeviceScan::ExclusiveSum(a->d_cub_tmp, tmpb, a->d_scan, a->d_scan, ncand + 1, st);
+    long long total = 0;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(&total, a->d_scan + ncand, sizeof(long long), cudaMemcpyDeviceToHost, st));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(st));
+    if ((size_t)total + 64 > a->chain_cap) {
+        const size_t want = (size_t)total + (size_t)total / 2 + (1 << 20);
+        if ((rc = grow(ctx, &a->d_chain, want))) return rc;
+        a->chain_cap = want;
+    }
+    abub_blob* tmp = a->d_blobs;
+    abub_blob* ordered = a->d_blobs + a->blob_cap;
+    k7_trace2_kernel<<<nb, tb, 0, st>>>(ncand, a->d_jobs, a->d_thr, ctx->rows, ctx->cols, a->d_cand, a->d_scan, a->d_chain, tmp);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    int* flags = a->d_iscan;
+    int* pos = a->d_iscan + ncand + 1;
+    k7_external_kernel<<<nb, tb, 0, st>>>(ncand, ctx->cols, a->d_cand, a->d_chain, flags);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    tmpb = a->cub_tmp_bytes;
+    cub::DeviceScan::ExclusiveSum(a->d_cub_tmp, tmpb, flags, pos, ncand, st);
+    k7_emit_kernel<<<nb, tb, 0, st>>>(ncand, a->d_cand, flags, pos, tmp, ordered, a->blob_cap, a->d_npf, a->d_counters);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(counters, a->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(npf_out.data(), a->d_npf, njobs * sizeof(int), cudaMemcpyDeviceToHost, st));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(st));
+    const int nblob = counters[2];
+    const size_t base = blobs_out.size();
+    blobs_out.resize(base + nblob);
+    if (nblob)
+        ABUB_CHECK_CUDA(ctx, cudaMemcpy(blobs_out.data() + base, ordered, sizeof(abub_blob) * nblob, cudaMemcpyDeviceToHost));
+    return ABUB_OK;
+}
+
+extern "C" int abub_localize_batch(abub_ctx* ctx, const abub_loc_item* items, int n_items, abub_blob* out, int cap,
+                                   int* n_per_frame, int* n_total) {
     if (!ctx) return ABUB_E_INVALID;
-    ctx->err = "abub_localize_binary: not built yet";
-    return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, items && n_items >= 1 && n_per_frame && (out || cap == 0), "abub_localize_batch");
+    cudaSetDevice(ctx->device);
+    LocArena* a = arena_of(ctx);
+    const size_t npix = ctx->npix;
+    for (int i = 0; i < n_items; i++) {
+        const abub_loc_item& it = items[i];
+        ABUB_REQUIRE(ctx, it.slot >= 0 && it.slot < ctx->max_slots && it.cam >= 0 && it.cam < ctx->ncams, "item slot/cam");
+        ABUB_REQUIRE(ctx, ctx->cam[it.cam].has_background, "background not installed");
+        const int nf = ctx->slots[it.slot].nframes[it.cam];
+        ABUB_REQUIRE(ctx, it.trig >= 0 && it.trig < nf && it.pre_trig >= 0 && it.pre_trig < nf, "trig/pre_trig out of range");
+        ABUB_REQUIRE(ctx, it.n_post >= 0 && it.n_post <= ABUB_MAX_TRACK && it.trig + it.n_post < nf, "n_post out of range");
+    }
+    // chunk so that the TOZERO'd scratch stays around 1 GB
+    size_t max_jobs = ((size_t)1 << 30) / npix;
+    if (max_jobs < ABUB_MAX_TRACK + 1) max_jobs = ABUB_MAX_TRACK + 1;
+    std::vector<abub_blob> blobs;
+    std::vector<int> npf;
+    int written = 0, rc;
+    for (int i0 = 0; i0 < n_items;) {
+        int i1 = i0, njobs = 0;
+        while (i1 < n_items && njobs + items[i1].n_post + 1 <= (int)max_jobs) { njobs += items[i1].n_post + 1; i1++; }
+        if ((rc = ensure_jobs(ctx, a, njobs))) return rc;
+        int j = 0;
+        for (int i = i0; i < i1; i++) {
+            const abub_loc_item& it = items[i];
+            const abub_cam_state& cs = ctx->cam[it.cam];
+            const uint8_t* base = ctx->slots[it.slot].d_frames + (size_t)it.cam * ctx->max_frames * npix;
+            for (int k = 0; k <= it.n_post; k++, j++) {
+                abub_loc_job& jb = a->h_jobs[j];
+                jb.genesis = (k == 0);
+                jb.k = k;
+                jb.item = i;
+                jb.k32 = cs.d_k32;
+                jb.t8 = cs.d_t8;
+                jb.tz = a->d_tz + (size_t)j * npix;
+                jb.hist = a->d_hist + (size_t)j * 256;
+                if (k == 0) {
+                    jb.a = base + (size_t)it.trig * npix;        // L3Localizer.cpp:929
+                    jb.b = base + (size_t)it.pre_trig * npix;    // :932-934
+                    jb.tozero = it.loc_thres;                    // :252
+                } else {
+                    jb.a = base + (size_t)(it.trig + k) * npix;  // :770
+                    jb.b = cs.d_mean;                            // :779
+                    jb.tozero = 3;                               // :786
+                }
+            }
+        }
+        blobs.clear();
+        if ((rc = run_chunk(ctx, a, njobs, blobs, npf))) return rc;
+        j = 0;
+        for (int i = i0; i < i1; i++)
+            for (int k = 0; k <= ABUB_MAX_TRACK; k++)
+                n_per_frame[i * (ABUB_MAX_TRACK + 1) + k] = (k <= items[i].n_post) ? npf[j++] : 0;
+        for (const abub_blob& b : blobs) {
+            if (written < cap) {
+                out[written] = b;
+                out[written].reserved = 0;
+            }
+            written++;
+        }
+        i0 = i1;
+    }
+    if (n_total) *n_total = written;
+    if (written > cap) {
+        ctx->err = "abub_localize_batch: output capacity too small (" + std::to_string(written) + " blobs)";
+        return ABUB_E_CAPACITY;
+    }
+    return ABUB_OK;
+}
+
+extern "C" int abub_localize(abub_ctx* ctx, int slot, int cam, int trig, int pre_trig, int loc_thres, int n_post,
+                             abub_blob* out, int cap, int* n_per_frame) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, n_per_frame != nullptr, "n_per_frame");
+    abub_loc_item it{slot, cam, trig, pre_trig, loc_thres, n_post};
+    int npf[ABUB_MAX_TRACK + 1], total = 0;
+    int rc = abub_localize_batch(ctx, &it, 1, out, cap, npf, &total);
+    for (int k = 0; k <= ABUB_MAX_TRACK; k++) n_per_frame[k] = npf[k];
+    return rc;
+}
+
+extern "C" int abub_localize_binary(abub_ctx* ctx, int k, uint8_t* out) {
+    if (!ctx) return ABUB_E_INVALID;
+    LocArena* a = arena_of(ctx);
+    ABUB_REQUIRE(ctx, out && a && k >= 0 && k < a->last_njobs, "abub_localize_binary: no such frame in the last call");
+    cudaSetDevice(ctx->device);
+    k5_binary_kernel<<<(unsigned)((ctx->npix + 255) / 256), 256, 0, ctx->stream>>>(a->d_tz, a->d_thr, k, ctx->d_tmp8[3], ctx->npix);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(out, ctx->d_tmp8[3], ctx->npix, cudaMemcpyDeviceToHost, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ABUB_OK;
 }

@@ -141,6 +141,14 @@ int abub_train_finish_partials(abub_ctx* ctx, int cam, uint8_t* mean, uint8_t* s
  * and tracking stay on the host (L3Localizer.cpp:277-290,392-444,842-863). */
 int abub_localize(abub_ctx* ctx, int slot, int cam, int trig, int pre_trig, int loc_thres,
                   int n_post, abub_blob* out, int cap, int* n_per_frame);
+/* Batched form (one launch set for many (slot,cam) analyzers -- the shape the GPU wants):
+ * items[i] describes one LocalizeOMatic call; blobs of item i, frame k are contiguous in
+ * `out`, items in order; n_per_frame[i*(ABUB_MAX_TRACK+1)+k]; *n_total = blobs written. */
+typedef struct abub_loc_item {
+    int32_t slot, cam, trig, pre_trig, loc_thres, n_post;
+} abub_loc_item;
+int abub_localize_batch(abub_ctx* ctx, const abub_loc_item* items, int n_items, abub_blob* out,
+                        int cap, int* n_per_frame, int* n_total);
 /* Debug/parity taps: binary image of frame k of the last abub_localize (rows*cols). */
 int abub_localize_binary(abub_ctx* ctx, int k, uint8_t* out);
 

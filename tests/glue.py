@@ -1,0 +1,87 @@
+"""Test-side host glue: drives the C ABI the way the C++ host (AnyCamAnalysis / LocalizeOMatic)
+does and turns abub_blob records into the oracle's BubbleImageFrame / Bubble bookkeeping, so
+that the final abub3hs text can be compared byte for byte with the oracle's."""
+import numpy as np
+
+import oracle.cv2_oracle as o
+
+F32, F64 = np.float32, np.float64
+
+
+def blob_to_frame(b, genesis: bool) -> o.BubbleImageFrame:
+    with np.errstate(all="ignore"):
+        radius = float(np.sqrt(F64(b.area) / F64(3.14159)))
+        if (not genesis) or b.m00 > 0:
+            cx = F32(F64(b.m10) / F64(b.m00))
+            cy = F32(F64(b.m01) / F64(b.m00))
+        else:
+            cx = F32(F64(b.sum_x) / F64(b.npts))
+            cy = F32(F64(b.sum_y) / F64(b.npts))
+    return o.BubbleImageFrame(b.x, b.y, b.w, b.h, b.area, radius, b.m00, b.m10, b.m01, cx, cy)
+
+
+def n_post_frames(trig: int, nframes: int) -> int:
+    """L3Localizer.cpp:944-954."""
+    kmax = o.NUM_FRAMES_BUBBLE_TRACK if trig < 29 else 39 - trig
+    n = 0
+    for k in range(1, kmax + 1):
+        if trig + k >= nframes:
+            break
+        n += 1
+    return n
+
+
+def genesis_from_blobs(blobs, cam_mask, bellows_mask):
+    """CalculateInitialBubbleParams bookkeeping (L3Localizer.cpp:273-290, 392-444)."""
+    kept, largest = [], 0
+    all_in_bellows = len(blobs) > 0
+    for b in blobs:
+        if not o.is_in_mask(b.x, b.y, b.w, b.h, bellows_mask, True):
+            all_in_bellows = False
+            largest = max(largest, b.w * b.h)
+            kept.append(b)
+    if all_in_bellows:
+        raise o.BellowsBranchTaken()
+    out = []
+    for b in kept:
+        if b.w * b.h > 10 or b.w * b.h >= largest:
+            f = blob_to_frame(b, True)
+            if o.is_in_mask(f.x, f.y, f.w, f.h, cam_mask, False):
+                out.append(f)
+    return out
+
+
+def post_from_blobs(blobs, cam_mask):
+    out = []
+    for b in blobs:
+        if b.w * b.h > 10:
+            f = blob_to_frame(b, False)
+            if o.is_in_mask(f.x, f.y, f.w, f.h, cam_mask, False):
+                out.append(f)
+    return out
+
+
+def gpu_any_cam_analysis(ctx, slot, cam, nframes, tss, cam_mask, bellows_mask, event_number):
+    """AnyCamAnalysis (AutoBubStart3.cpp:67-125) with trigger + localizer on the device."""
+    bubbles, mat_trig, loc_thres = [], 0, 3
+    out = o.CameraOutput()
+    while True:
+        t, status, lt, _ = ctx.trigger(slot, cam, mat_trig + 1)
+        if status == 0:
+            mat_trig = t
+        if lt >= 0:
+            loc_thres = lt
+        if status != 0:
+            return o.CameraOutput(status, 0, event_number)
+        if nframes <= 5:
+            return o.CameraOutput(-8, 0, event_number)
+        pre = max(0, mat_trig - (1 if tss < 6 else 2))
+        npost = n_post_frames(mat_trig, nframes)
+        frames = ctx.localize_batch([(slot, cam, mat_trig, pre, loc_thres, npost)])[0]
+        for g in genesis_from_blobs(frames[0], cam_mask, bellows_mask):
+            bubbles.append(o.Bubble(g))
+        for k in range(1, npost + 1):
+            o.track_candidates(bubbles, post_from_blobs(frames[k], cam_mask))
+        out = o.stage_camera_output(bubbles, mat_trig, event_number)
+        if bubbles:
+            return out

@@ -1,0 +1,191 @@
+"""GPU parity: K3/K4 Trainer statistics and K5-K7 localizer through the C ABI vs the oracle."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from autobub3hs_b200 import capi
+    capi.load()
+    return capi
+
+
+def test_trainer_matches_oracle(capi, small_run, small_trained):
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    with capi.Context(rows, cols, 4, 40, max_slots=1) as ctx:
+        for c in range(4):
+            ctx.train_begin(c)
+            for ev in range(len(run.events)):
+                fr = run.events[ev][c]
+                e, kept = ctx.train_add_event(c, fr[0], fr[1])
+                assert abs(e - trained[c].entropies[ev]) <= 1e-6          # float32 entropy, abs tolerance 1e-6
+                assert kept == (ev in trained[c].kept_events)
+            mean, sigma, n, st = ctx.train_finish(c)
+            assert (n, st) == (trained[c].training_set_size, trained[c].status)
+            assert np.array_equal(mean, trained[c].avg)
+            assert np.array_equal(sigma, trained[c].sigma)
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 5, 6, 33])
+def test_welford_sizes(capi, n):
+    import oracle.cv2_oracle as o
+    rng = np.random.default_rng(n)
+    rows, cols = 50, 68
+    base = rng.integers(0, 256, (rows, cols))
+    frames = [np.clip(base + rng.normal(0, 3, (rows, cols)).round(), 0, 255).astype(np.uint8) for _ in range(n + (n & 1))]
+    frames = frames[: n + (n & 1)]
+    with capi.Context(rows, cols, 1, 4, max_slots=1) as ctx:
+        ctx.train_begin(0)
+        kept = []
+        for i in range(0, len(frames), 2):
+            e, k = ctx.train_add_event(0, frames[i], frames[i])      # identical pair: entropy 0 -> always kept
+            assert k and e == 0.0
+            kept += [frames[i], frames[i]]
+        mean, sigma, cnt, st = ctx.train_finish(0)
+        m_ref, s_ref = o.welford_mean_sigma(kept)
+        assert st == 0 and cnt == len(kept)
+        assert np.array_equal(mean, m_ref) and np.array_equal(sigma, s_ref)
+
+
+def test_train_nothing_kept_is_minus7(capi):
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 40, (40, 52)).astype(np.uint8)
+    b = (a + 100).astype(np.uint8)
+    with capi.Context(40, 52, 1, 4, max_slots=1) as ctx:
+        ctx.train_begin(0)
+        e, k = ctx.train_add_event(0, a, b)
+        assert not k and e > 0.0005
+        _, _, n, st = ctx.train_finish(0)
+        assert (n, st) == (0, -7)
+
+
+def test_train_partials_single_rank_equals_sequential(capi, small_run, small_trained):
+    """Exact integer partials + boundary fix-up reproduce the sequential float32 Welford."""
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    with capi.Context(rows, cols, 4, 40, max_slots=1) as ctx:
+        ctx.train_begin(1)
+        for ev in range(len(run.events)):
+            ctx.train_add_event(1, run.events[ev][1][0], run.events[ev][1][1])
+        ctx.train_partials(1)
+        mean, sigma, n, st, nflag = ctx.train_finish_partials(1)
+        assert st == 0 and n == trained[1].training_set_size
+        assert np.array_equal(mean, trained[1].avg) and np.array_equal(sigma, trained[1].sigma)
+        assert nflag < mean.size * 0.2
+
+
+def _check_blobs(o, blobs, binary):
+    import cv2
+    cs, _ = cv2.findContours(binary, cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_TC89_L1)
+    assert len(cs) == len(blobs)
+    for c, b in zip(cs, blobs):
+        assert cv2.boundingRect(c) == (b.x, b.y, b.w, b.h)
+        assert len(c) == b.npts
+        assert cv2.contourArea(c) == b.area
+        m = cv2.moments(c)
+        assert (m["m00"], m["m10"], m["m01"]) == (b.m00, b.m10, b.m01)
+        assert int(c[:, 0, 0].sum()) == b.sum_x and int(c[:, 0, 1].sum()) == b.sum_y
+
+
+def test_localizer_blobs_vs_cv2(capi, small_run, small_trained):
+    import oracle.cv2_oracle as o
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    nev = len(run.events)
+    with capi.Context(rows, cols, 4, 40, max_slots=nev) as ctx:
+        for c in range(4):
+            ctx.set_background(c, trained[c].avg, trained[c].sigma, trained[c].training_set_size)
+        items = []
+        for ev in range(nev):
+            for c in range(4):
+                ctx.event_upload(ev, c, run.events[ev][c])
+                n = len(run.events[ev][c])
+                if n > 12:
+                    for trig, lt in ((n // 2, 3), (n - 3, 2), (2, 3)):
+                        items.append((ev, c, trig, max(0, trig - 2), lt, min(10, n - 1 - trig)))
+        res = ctx.localize_batch(items)
+        nblobs = 0
+        for it, frames in zip(items, res):
+            ev, c, trig, pre, lt, npost = it
+            fr = run.events[ev][c]
+            _check_blobs(o, frames[0], o.genesis_binary(fr[trig], fr[pre], trained[c].sigma, lt))
+            for k in range(1, npost + 1):
+                _check_blobs(o, frames[k], o.post_trigger_binary(fr[trig + k], trained[c].avg, trained[c].sigma))
+                nblobs += len(frames[k])
+        assert nblobs > 50
+        # single-item entry point + binary tap
+        ev, c, trig, pre, lt, npost = items[0]
+        blobs, counts = ctx.localize(ev, c, trig, pre, lt, npost)
+        assert counts == [len(f) for f in res[0]]
+        fr = run.events[ev][c]
+        assert np.array_equal(ctx.localize_binary(0), o.genesis_binary(fr[trig], fr[pre], trained[c].sigma, lt))
+        assert np.array_equal(ctx.localize_binary(1), o.post_trigger_binary(fr[trig + 1], trained[c].avg, trained[c].sigma))
+
+
+def test_contours_fuzz_through_device(capi):
+    """Random binary shapes pushed through the device contour path (as a post-trigger frame with
+    avg = 0, sigma = 0 the binarised image is controlled by the input) vs cv2."""
+    import cv2
+    import oracle.cv2_oracle as o
+    rng = np.random.default_rng(11)
+    rows, cols = 96, 160
+    zero = np.zeros((rows, cols), np.uint8)
+    with capi.Context(rows, cols, 1, 12, max_slots=1) as ctx:
+        ctx.set_background(0, zero, zero, 12)
+        for rep in range(6):
+            frames = np.zeros((12, rows, cols), np.uint8)
+            for f in range(1, 12):
+                img = np.zeros((rows, cols), np.uint8)
+                kind = (f + rep) % 4
+                if kind == 0:
+                    img = ((rng.random((rows, cols)) < rng.uniform(0.02, 0.5)) * 200).astype(np.uint8)
+                elif kind == 1:
+                    for _ in range(rng.integers(1, 9)):
+                        cv2.ellipse(img, (int(rng.integers(0, cols)), int(rng.integers(0, rows))),
+                                    (int(rng.integers(1, 30)), int(rng.integers(1, 30))), float(rng.uniform(0, 180)), 0, 360,
+                                    200, int(rng.choice([-1, 1, 2])))
+                elif kind == 2:
+                    for _ in range(rng.integers(1, 4)):
+                        ctr = (int(rng.integers(0, cols)), int(rng.integers(0, rows)))
+                        for r in range(int(rng.integers(4, 40)), 2, -int(rng.integers(3, 7))):
+                            cv2.circle(img, ctr, r, 200, 1)
+                    img |= ((rng.random((rows, cols)) < 0.02) * 200).astype(np.uint8)
+                else:
+                    g = cv2.GaussianBlur(rng.random((rows, cols)).astype(np.float32), (0, 0), 3)
+                    img = ((g > np.quantile(g, 0.6)) * 200).astype(np.uint8)
+                frames[f] = img
+            ctx.event_upload(0, 0, frames)
+            res = ctx.localize_batch([(0, 0, 1, 0, 3, 10)])[0]
+            for k in range(1, 11):
+                _check_blobs(o, res[k], o.post_trigger_binary(frames[1 + k], zero, zero))
+
+
+def test_end_to_end_text_matches_oracle(capi, small_run, small_trained):
+    """Training + trigger + localizer on the device, host bookkeeping as the reference, output
+    text byte-identical to the oracle's (BASELINE.json: 'bit-exact abub3 recon output')."""
+    import oracle.cv2_oracle as o
+    from tests import glue
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    ref_text, _ = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks)
+    with capi.Context(rows, cols, 4, 40, max_slots=1) as ctx:
+        tss = []
+        for c in range(4):
+            ctx.train_begin(c)
+            for ev in range(len(run.events)):
+                ctx.train_add_event(c, run.events[ev][c][0], run.events[ev][c][1])
+            _, _, n, st = ctx.train_finish(c)
+            assert st == 0
+            tss.append(n)
+            ctx.set_background_from_training(c)
+        text = []
+        for evn, ev in zip(run.event_numbers, run.events):
+            for c in range(4):
+                ctx.event_upload(0, c, ev[c])
+            cams = [glue.gpu_any_cam_analysis(ctx, 0, c, len(ev[c]), tss[c], run.cam_masks[c], run.bellows_masks[c], evn)
+                    for c in range(4)]
+            text.append(o.write_camera_output(run.run_id, cams, run.frame_offset))
+    assert "".join(text) == ref_text
