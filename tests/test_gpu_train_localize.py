@@ -42,7 +42,7 @@ def test_welford_sizes(capi, n):
         kept = []
         for i in range(0, len(frames), 2):
             e, k = ctx.train_add_event(0, frames[i], frames[i])      # identical pair: entropy 0 -> always kept
-            assert k and e == 0.0
+            assert k and abs(e) <= 1e-6
             kept += [frames[i], frames[i]]
         mean, sigma, cnt, st = ctx.train_finish(0)
         m_ref, s_ref = o.welford_mean_sigma(kept)
@@ -53,7 +53,7 @@ def test_welford_sizes(capi, n):
 def test_train_nothing_kept_is_minus7(capi):
     rng = np.random.default_rng(0)
     a = rng.integers(0, 40, (40, 52)).astype(np.uint8)
-    b = (a + 100).astype(np.uint8)
+    b = rng.integers(0, 256, (40, 52)).astype(np.uint8)       # difference spread over many bins
     with capi.Context(40, 52, 1, 4, max_slots=1) as ctx:
         ctx.train_begin(0)
         e, k = ctx.train_add_event(0, a, b)
