@@ -22,7 +22,7 @@ EXPORTS = [
     "abub_set_background", "abub_set_background_from_training",
     "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_device_ptr",
     "abub_event_set_nframes",
-    "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_scan", "abub_trigger_results", "abub_trigger",
+    "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_hist_write", "abub_trigger_scan", "abub_trigger_results", "abub_trigger",
     "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_finish",
     "abub_train_partials", "abub_train_allreduce", "abub_train_finish_partials",
     "abub_localize", "abub_localize_batch", "abub_localize_binary", "abub_process_frame",
@@ -76,6 +76,7 @@ def load() -> C.CDLL:
     lib.abub_event_set_nframes.argtypes = [vp, C.c_int, ip]
     lib.abub_trigger_hist.argtypes = [vp, C.c_int, C.c_int]
     lib.abub_trigger_hist_read.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.abub_trigger_hist_write.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int]
     lib.abub_trigger_scan.argtypes = [vp, C.c_int, C.c_int, vp]
     lib.abub_trigger_results.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp]
     lib.abub_trigger.argtypes = [vp, C.c_int, C.c_int, C.c_int, ip, ip, ip, vp]
@@ -195,6 +196,11 @@ class Context:
         out = np.zeros((self.max_frames, 256), np.uint32)
         self._ck(self.lib.abub_trigger_hist_read(self.h, slot, cam, _p(out)), "abub_trigger_hist_read")
         return out
+
+    def trigger_hist_write(self, slot: int, cam: int, hist: np.ndarray, nframes: int) -> None:
+        h = np.zeros((self.max_frames, 256), np.uint32)
+        h[:hist.shape[0]] = hist
+        self._ck(self.lib.abub_trigger_hist_write(self.h, slot, cam, _p(h), nframes), "abub_trigger_hist_write")
 
     def trigger_scan(self, slot_first: int = 0, nslots: int = 1, start_frames: Optional[np.ndarray] = None) -> None:
         st = None if start_frames is None else np.ascontiguousarray(start_frames, dtype=np.int32)

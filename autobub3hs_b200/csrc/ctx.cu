@@ -236,6 +236,22 @@ extern "C" int abub_trigger_hist_read(abub_ctx* ctx, int slot, int cam, uint32_t
     return ABUB_OK;
 }
 
+extern "C" int abub_trigger_hist_write(abub_ctx* ctx, int slot, int cam, const uint32_t* hist, int nframes) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && cam >= 0 && cam < ctx->ncams && hist, "args");
+    ABUB_REQUIRE(ctx, nframes >= 0 && nframes <= ctx->max_frames, "nframes");
+    cudaSetDevice(ctx->device);
+    const size_t n = (size_t)ctx->max_frames * 256;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_hist + ((size_t)slot * ctx->ncams + cam) * n, hist, n * sizeof(uint32_t),
+                                         cudaMemcpyHostToDevice, ctx->stream));
+    ctx->slots[slot].nframes[cam] = nframes;
+    int rc = push_nframes(ctx, slot);
+    if (rc) return rc;
+    ctx->slots[slot].hist_valid = true;
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ABUB_OK;
+}
+
 extern "C" int abub_trigger_scan(abub_ctx* ctx, int slot_first, int nslots, const int* start_frames) {
     if (!ctx) return ABUB_E_INVALID;
     ABUB_REQUIRE(ctx, slot_first >= 0 && nslots >= 1 && slot_first + nslots <= ctx->max_slots, "slot range");

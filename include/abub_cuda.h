@@ -91,6 +91,9 @@ int abub_event_set_nframes(abub_ctx* ctx, int slot, const int* nframes);
 int abub_trigger_hist(abub_ctx* ctx, int slot_first, int nslots);
 /* D2H of one (slot,cam) histogram table: hist[max_frames][256] (row 0 unused = 0). */
 int abub_trigger_hist_read(abub_ctx* ctx, int slot, int cam, uint32_t* hist);
+/* Parity tap: H2D of one (slot,cam) histogram table (same layout), so that K2 can be driven
+ * with hand-built tables (int32-wrap / NaN / inf corner cases of AnalyzerUnit.cpp:478,529). */
+int abub_trigger_hist_write(abub_ctx* ctx, int slot, int cam, const uint32_t* hist, int nframes);
 /* K2: the significance state machine (calculateSignificanceFrame :435-504 +
  * FindTriggerFrame :119-324) for every (slot,cam) of the range, from
  * start_frames[(slot-slot_first)*ncams+cam] (NULL = 1 everywhere).  A start frame > 1

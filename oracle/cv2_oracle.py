@@ -171,6 +171,24 @@ class HistProvider:
         return self.cache[key]
 
 
+class TableHistProvider:
+    """Histogram rows given up front (golden vectors / corner cases): H[j] for every j."""
+
+    def __init__(self, table: np.ndarray):
+        self.table = np.asarray(table)
+
+    def hist(self, j: int, jprev: int) -> np.ndarray:
+        return self.table[j].astype(np.float32)
+
+
+class TableSource(FrameSource):
+    """A frame source that only knows how many frames there are and the pixel count."""
+
+    def __init__(self, nframes: int, total: int):
+        self.frames = [np.zeros(total, np.uint8)] * nframes
+        self.bad = set()
+
+
 def find_trigger_frame(src: FrameSource, sigma: np.ndarray, training_set_size: int,
                        startframe: int, st: SignificanceState, mat_trig_frame: int,
                        hp: Optional[HistProvider] = None,
