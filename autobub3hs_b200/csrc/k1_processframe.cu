@@ -157,13 +157,132 @@ __device__ __forceinline__ void k1_strip(const uint8_t* __restrict__ A, const ui
     }
 }
 
-constexpr int K1_TH = 35;     // output rows per strip (1050 = 30 x 35)
+
+// ---- fast strip (cols % 4 == 0) -------------------------------------------------------
+// Same arithmetic as k1_strip, restructured for instruction count: word loads only (lanes
+// outside the image load a clamped address and are ignored), column reflection done by
+// register selects on the lanes that touch the image border, row pointers advanced by the
+// pitch (reflection only when EDGE_Y), 10-row unroll so that the 5-row window, the 2-deep
+// load prefetch and the exchange double buffer all have static register names.
+template <int MODE, bool EDGE_Y>
+__device__ __forceinline__ void k1_strip_fast(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B,
+                                              const uint32_t* __restrict__ K, int rows, int cols, int y0, int th,
+                                              int x0, uint32_t* sh_hist, uint32_t* xch, uint8_t* __restrict__ out,
+                                              int tozero) {
+    const int lane = threadIdx.x & 31;
+    const int gx = x0 - 4 + lane * 4;
+    const int gxl = min(max(gx, 0), cols - 4);                 // clamped load column
+    const bool out_lane = lane >= 1 && lane <= 30 && gx < cols;
+    const bool left_edge = (gx == 0), right_edge = (gx + 4 == cols);
+    const int nout = min(th, rows - y0);
+    const int nloc = nout + 4;
+    const size_t pitch = (size_t)cols;
+    const uint8_t* pa = A + gxl;
+    const uint8_t* pb = B + gxl;
+    const uint32_t* pk = K + gxl;
+    if (!EDGE_Y) {
+        const size_t o = (size_t)(y0 - 2) * pitch;
+        pa += o; pb += o; pk += o;
+    }
+    uint8_t* po = (MODE == 1) ? out + (size_t)y0 * pitch + gxl : nullptr;
+    uint2* const xlo = reinterpret_cast<uint2*>(xch) + lane;        // (v0,v1) of this lane, buffer 0
+    uint2* const xhi = xlo + 32;                                    // (v2,v3)
+    const uint2* const xL = reinterpret_cast<const uint2*>(xch) + 32 + ((lane + 31) & 31);
+    const uint2* const xR = reinterpret_cast<const uint2*>(xch) + ((lane + 1) & 31);
+    uint32_t win[5][4];
+    uint32_t ra[2], rb[2];
+    uint4 rk[2];
+    {
+        const size_t o = EDGE_Y ? (size_t)reflect101(y0 - 2, rows) * pitch : 0;
+        ra[0] = __ldg(reinterpret_cast<const uint32_t*>(pa + o));
+        rb[0] = __ldg(reinterpret_cast<const uint32_t*>(pb + o));
+        rk[0] = __ldg(reinterpret_cast<const uint4*>(pk + o));
+    }
+#pragma unroll 1
+    for (int rb0 = 0; rb0 < nloc; rb0 += 10) {
+#pragma unroll
+        for (int r = 0; r < 10; r++) {
+            const int rl = rb0 + r;
+            if (rl < nloc) {
+                if (rl + 1 < nloc) {
+                    size_t o;
+                    if (EDGE_Y) {
+                        o = (size_t)reflect101(y0 - 2 + rl + 1, rows) * pitch;
+                    } else {
+                        pa += pitch; pb += pitch; pk += pitch;
+                        o = 0;
+                    }
+                    ra[(r + 1) & 1] = __ldg(reinterpret_cast<const uint32_t*>(pa + o));
+                    rb[(r + 1) & 1] = __ldg(reinterpret_cast<const uint32_t*>(pb + o));
+                    rk[(r + 1) & 1] = __ldg(reinterpret_cast<const uint4*>(pk + o));
+                }
+                stageA(ra[r & 1], rb[r & 1], rk[r & 1], win[r % 5]);
+                if (rl >= 4) {
+                    uint32_t v[4];
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const uint32_t e = win[(r + 1) % 5][c] + win[r % 5][c];
+                        const uint32_t o = win[(r + 2) % 5][c] + win[(r + 4) % 5][c];
+                        v[c] = e + 4u * o + 6u * win[(r + 3) % 5][c];
+                    }
+                    xlo[(r & 1) * 64] = make_uint2(v[0], v[1]);
+                    xhi[(r & 1) * 64] = make_uint2(v[2], v[3]);
+                    __syncwarp();
+                    const uint2 L = xL[(r & 1) * 64];
+                    const uint2 R = xR[(r & 1) * 64];
+                    // BORDER_REFLECT_101 in x: col -2 -> 2, -1 -> 1 ; cols -> cols-2, cols+1 -> cols-3
+                    const uint32_t e0 = left_edge ? v[2] : L.x, e1 = left_edge ? v[1] : L.y;
+                    const uint32_t e6 = right_edge ? v[2] : R.x, e7 = right_edge ? v[1] : R.y;
+                    uint32_t h[4];
+                    h[0] = (e0 + v[2]) + 4u * (e1 + v[1]) + 6u * v[0] + RND2;
+                    h[1] = (e1 + v[3]) + 4u * (v[0] + v[2]) + 6u * v[1] + RND2;
+                    h[2] = (v[0] + e6) + 4u * (v[1] + v[3]) + 6u * v[2] + RND2;
+                    h[3] = (v[1] + e7) + 4u * (v[2] + e6) + 6u * v[3] + RND2;
+                    const uint32_t z = (h[0] | h[1] | h[2] | h[3]) & 0xFF00FF00u;
+                    uint32_t packed = 0;
+                    if (z != 0 && out_lane) {
+#pragma unroll
+                        for (int c = 0; c < 4; c++) {
+                            const uint32_t P = (h[c] >> 8) & 0xFFu, N = h[c] >> 24;
+                            uint32_t o = __usad(P, N, 0u);
+                            if (MODE == 1 && (int)o <= tozero) o = 0;
+                            if (o != 0) {
+                                atomicAdd(&sh_hist[o], 1u);
+                                packed |= o << (8 * c);
+                            }
+                        }
+                    }
+                    if (MODE == 1) {
+                        if (out_lane) *reinterpret_cast<uint32_t*>(po) = packed;
+                        po += pitch;
+                    }
+                }
+            }
+        }
+    }
+}
+
+// strip dispatcher: fast path when the pitch allows aligned word access
+template <int MODE>
+__device__ __forceinline__ void k1_strip_any(const uint8_t* A, const uint8_t* B, const uint32_t* K, int rows, int cols,
+                                             int y0, int th, int x0, uint32_t* sh_hist, uint32_t* xch, uint8_t* out,
+                                             int tozero) {
+    if ((cols & 3) == 0 && cols >= 8) {
+        const bool edge_y = (y0 < 2) || (y0 + th + 2 > rows);
+        if (edge_y) k1_strip_fast<MODE, true>(A, B, K, rows, cols, y0, th, x0, sh_hist, xch, out, tozero);
+        else        k1_strip_fast<MODE, false>(A, B, K, rows, cols, y0, th, x0, sh_hist, xch, out, tozero);
+    } else {
+        k1_strip<MODE>(A, B, K, rows, cols, y0, th, x0, sh_hist, xch, out, tozero);
+    }
+}
+
+constexpr int K1_TH_TARGET = 105;   // output rows per strip (1050 = 10 x 105): 4 halo rows per 105
 
 // grid: x = strip, y = j-1, z = (slot-slot_first)*ncams + cam ; block = 32 * ceil(cols/120)
 __global__ void k1_trigger_kernel(uint8_t* const* __restrict__ slot_ptrs, const int* __restrict__ nframes,
                                   const int* __restrict__ tss, uint32_t* const* __restrict__ k32_ptrs,
                                   uint32_t* __restrict__ hist, int slot_first, int rows, int cols,
-                                  int ncams, int max_frames) {
+                                  int ncams, int max_frames, int th) {
     extern __shared__ uint32_t smem[];
     uint32_t* sh_hist = smem;                       // 256
     const int warp = threadIdx.x >> 5;
@@ -180,10 +299,10 @@ __global__ void k1_trigger_kernel(uint8_t* const* __restrict__ slot_ptrs, const 
     const uint8_t* base = slot_ptrs[slot] + (size_t)cam * max_frames * npix;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
     __syncthreads();
-    const int y0 = blockIdx.x * K1_TH;
+    const int y0 = blockIdx.x * th;
     if (y0 < rows)
-        k1_strip<0>(base + (size_t)j * npix, base + (size_t)jp * npix, k32_ptrs[cam], rows, cols, y0, K1_TH,
-                    warp * ABUB_K1_TILE_W, sh_hist, xch, nullptr, -1);
+        k1_strip_any<0>(base + (size_t)j * npix, base + (size_t)jp * npix, k32_ptrs[cam], rows, cols, y0, th,
+                        warp * ABUB_K1_TILE_W, sh_hist, xch, nullptr, -1);
     __syncthreads();
     uint32_t* H = hist + (((size_t)slot * ncams + cam) * max_frames + j) * 256;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -213,16 +332,16 @@ __global__ void k1_fill_bin0_kernel(uint32_t* __restrict__ hist, const int* __re
 // single frame pair (parity tap + localizer genesis frame)
 __global__ void k1_single_kernel(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B,
                                  const uint32_t* __restrict__ K, uint8_t* __restrict__ out,
-                                 uint32_t* __restrict__ hist, int rows, int cols, int tozero) {
+                                 uint32_t* __restrict__ hist, int rows, int cols, int tozero, int th) {
     extern __shared__ uint32_t smem[];
     uint32_t* sh_hist = smem;
     const int warp = threadIdx.x >> 5;
     uint32_t* xch = smem + 256 + warp * 256;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
     __syncthreads();
-    const int y0 = blockIdx.x * K1_TH;
+    const int y0 = blockIdx.x * th;
     if (y0 < rows)
-        k1_strip<1>(A, B, K, rows, cols, y0, K1_TH, warp * ABUB_K1_TILE_W, sh_hist, xch, out, tozero);
+        k1_strip_any<1>(A, B, K, rows, cols, y0, th, warp * ABUB_K1_TILE_W, sh_hist, xch, out, tozero);
     __syncthreads();
     if (hist)
         for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -233,7 +352,7 @@ __global__ void k1_single_kernel(const uint8_t* __restrict__ A, const uint8_t* _
 
 // localizer genesis jobs (CalculateInitialBubbleParams, L3Localizer.cpp:232,252): ProcessFrame,
 // THRESH_TOZERO at loc_thres, histogram of the result; grid.y = job (non-genesis jobs return)
-__global__ void k1_genesis_jobs_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols) {
+__global__ void k1_genesis_jobs_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols, int th) {
     extern __shared__ uint32_t smem[];
     const abub_loc_job job = jobs[blockIdx.y];
     if (!job.genesis) return;
@@ -242,10 +361,10 @@ __global__ void k1_genesis_jobs_kernel(const abub_loc_job* __restrict__ jobs, in
     uint32_t* xch = smem + 256 + warp * 256;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
     __syncthreads();
-    const int y0 = blockIdx.x * K1_TH;
+    const int y0 = blockIdx.x * th;
     if (y0 < rows)
-        k1_strip<1>(job.a, job.b, job.k32, rows, cols, y0, K1_TH, warp * ABUB_K1_TILE_W, sh_hist, xch, job.tz,
-                    job.tozero);
+        k1_strip_any<1>(job.a, job.b, job.k32, rows, cols, y0, th, warp * ABUB_K1_TILE_W, sh_hist, xch, job.tz,
+                        job.tozero);
     __syncthreads();
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         const uint32_t c = sh_hist[i];
@@ -273,6 +392,10 @@ __global__ void k1_build_k32_kernel(const uint8_t* __restrict__ sigma, uint32_t*
 
 }  // namespace
 
+static inline void k1_strips(int rows, int* nstrips, int* th) {
+    *nstrips = (rows + K1_TH_TARGET - 1) / K1_TH_TARGET;
+    *th = (rows + *nstrips - 1) / *nstrips;
+}
 static inline int k1_block_threads(int cols) { return 32 * ((cols + ABUB_K1_TILE_W - 1) / ABUB_K1_TILE_W); }
 static inline size_t k1_smem_bytes(int threads) { return (256 + (threads / 32) * 256) * sizeof(uint32_t); }
 
@@ -290,7 +413,8 @@ int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots) {
     const size_t hist_off = (size_t)slot_first * ctx->ncams * ctx->max_frames * 256;
     const size_t hist_n = (size_t)nslots * ctx->ncams * ctx->max_frames * 256;
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(ctx->d_hist + hist_off, 0, hist_n * sizeof(uint32_t), ctx->stream));
-    const int nstrips = (ctx->rows + K1_TH - 1) / K1_TH;
+    int nstrips, th;
+    k1_strips(ctx->rows, &nstrips, &th);
     // z is limited to 65535: chunk the (slot,cam) range
     const int per = 65535 / ctx->ncams;
     for (int s0 = 0; s0 < nslots; s0 += per) {
@@ -298,7 +422,7 @@ int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots) {
         dim3 grid(nstrips, ctx->max_frames - 1, ns * ctx->ncams);
         k1_trigger_kernel<<<grid, threads, k1_smem_bytes(threads), ctx->stream>>>(
             ctx->d_slot_ptrs, ctx->d_nframes, ctx->d_tss, ctx->d_k32_ptrs, ctx->d_hist, slot_first + s0,
-            ctx->rows, ctx->cols, ctx->ncams, ctx->max_frames);
+            ctx->rows, ctx->cols, ctx->ncams, ctx->max_frames, th);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     const int total_w = nslots * ctx->ncams * ctx->max_frames;
@@ -313,9 +437,10 @@ int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b,
     const int threads = k1_block_threads(ctx->cols);
     ABUB_REQUIRE(ctx, threads <= 1024, "cols too large for K1 (max 3840)");
     if (d_hist) ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_hist, 0, 256 * sizeof(uint32_t), ctx->stream));
-    const int nstrips = (ctx->rows + K1_TH - 1) / K1_TH;
+    int nstrips, th;
+    k1_strips(ctx->rows, &nstrips, &th);
     k1_single_kernel<<<nstrips, threads, k1_smem_bytes(threads), ctx->stream>>>(d_a, d_b, d_k32, d_out, d_hist,
-                                                                                 ctx->rows, ctx->cols, tozero_thres);
+                                                                                 ctx->rows, ctx->cols, tozero_thres, th);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     if (d_hist) {
         k1_fill_bin0_single<<<1, 32, 0, ctx->stream>>>(d_hist, (uint32_t)ctx->npix);
@@ -327,11 +452,12 @@ int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b,
 int abub_k1_launch_genesis_jobs(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs) {
     const int threads = k1_block_threads(ctx->cols);
     ABUB_REQUIRE(ctx, threads <= 1024, "cols too large for K1 (max 3840)");
-    const int nstrips = (ctx->rows + K1_TH - 1) / K1_TH;
+    int nstrips, th;
+    k1_strips(ctx->rows, &nstrips, &th);
     for (int j0 = 0; j0 < njobs; j0 += 65535) {
         const int nj = (njobs - j0 < 65535) ? njobs - j0 : 65535;
         k1_genesis_jobs_kernel<<<dim3(nstrips, nj), threads, k1_smem_bytes(threads), ctx->stream>>>(d_jobs + j0, ctx->rows,
-                                                                                                   ctx->cols);
+                                                                                                   ctx->cols, th);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     return ABUB_OK;
