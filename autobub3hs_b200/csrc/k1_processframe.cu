@@ -159,16 +159,37 @@ __device__ __forceinline__ void k1_strip(const uint8_t* __restrict__ A, const ui
 
 
 // ---- fast strip (cols % 4 == 0) -------------------------------------------------------
-// Same arithmetic as k1_strip, restructured for instruction count: word loads only (lanes
-// outside the image load a clamped address and are ignored), column reflection done by
-// register selects on the lanes that touch the image border, row pointers advanced by the
-// pitch (reflection only when EDGE_Y), 10-row unroll so that the 5-row window, the 2-deep
-// load prefetch and the exchange double buffer all have static register names.
+// Same arithmetic as k1_strip, restructured for instruction count:
+//  * word loads only (lanes outside the image load a clamped address and are ignored); column
+//    reflection is a register select on the two lanes that touch the image border;
+//  * row pointers step by +-pitch (the sign flips inside the reflected rows when EDGE_Y);
+//  * stage A keeps the +510 lane bias (word' = max.u16x2(y,510)); the vertical pass removes
+//    16*510 from both lanes with one constant folded into an IADD3 -- plain 32-bit adds are
+//    exact mod 2^32, so transient lane borrows cancel as long as the final lanes are in range;
+//  * 10-row unroll: the 5-row window, the 2-deep load prefetch and the exchange double buffer
+//    all get static register names;
+//  * histogram updates are red.shared on a precomputed shared-window address.
+__device__ __forceinline__ uint32_t stageA1_biased(int s255, uint32_t k) {
+    return __vmaxu2((uint32_t)s255 * 0xFFFF0001u + k, BIAS2);
+}
+__device__ __forceinline__ void stageA_biased(uint32_t a4, uint32_t b4, const uint4 k, uint32_t w[4]) {
+    const uint32_t p01 = __byte_perm(a4, b4, 0x5140);
+    const uint32_t p23 = __byte_perm(a4, b4, 0x7362);
+    w[0] = stageA1_biased(dp4a_us(p01, 0x0000FF01, 255), k.x);
+    w[1] = stageA1_biased(dp4a_us(p01, (int)0xFF010000, 255), k.y);
+    w[2] = stageA1_biased(dp4a_us(p23, 0x0000FF01, 255), k.z);
+    w[3] = stageA1_biased(dp4a_us(p23, (int)0xFF010000, 255), k.w);
+}
+__device__ __forceinline__ void red_shared_inc(uint32_t saddr) {
+    asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(saddr) : "memory");
+}
+
 template <int MODE, bool EDGE_Y>
 __device__ __forceinline__ void k1_strip_fast(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B,
                                               const uint32_t* __restrict__ K, int rows, int cols, int y0, int th,
                                               int x0, uint32_t* sh_hist, uint32_t* xch, uint8_t* __restrict__ out,
                                               int tozero) {
+    constexpr uint32_t FIX = RND2 - 256u * 510u * 0x00010001u;          // mod 2^32
     const int lane = threadIdx.x & 31;
     const int gx = x0 - 4 + lane * 4;
     const int gxl = min(max(gx, 0), cols - 4);                 // clamped load column
@@ -176,15 +197,13 @@ __device__ __forceinline__ void k1_strip_fast(const uint8_t* __restrict__ A, con
     const bool left_edge = (gx == 0), right_edge = (gx + 4 == cols);
     const int nout = min(th, rows - y0);
     const int nloc = nout + 4;
-    const size_t pitch = (size_t)cols;
-    const uint8_t* pa = A + gxl;
-    const uint8_t* pb = B + gxl;
-    const uint32_t* pk = K + gxl;
-    if (!EDGE_Y) {
-        const size_t o = (size_t)(y0 - 2) * pitch;
-        pa += o; pb += o; pk += o;
-    }
-    uint8_t* po = (MODE == 1) ? out + (size_t)y0 * pitch + gxl : nullptr;
+    const long long pitch = cols;
+    const int yfirst = EDGE_Y ? reflect101(y0 - 2, rows) : y0 - 2;
+    const uint8_t* pa = A + (size_t)yfirst * cols + gxl;
+    const uint8_t* pb = B + (size_t)yfirst * cols + gxl;
+    const uint32_t* pk = K + (size_t)yfirst * cols + gxl;
+    uint8_t* po = (MODE == 1) ? out + (size_t)y0 * cols + gxl : nullptr;
+    const uint32_t hist_s = (uint32_t)__cvta_generic_to_shared(sh_hist);
     uint2* const xlo = reinterpret_cast<uint2*>(xch) + lane;        // (v0,v1) of this lane, buffer 0
     uint2* const xhi = xlo + 32;                                    // (v2,v3)
     const uint2* const xL = reinterpret_cast<const uint2*>(xch) + 32 + ((lane + 31) & 31);
@@ -192,12 +211,9 @@ __device__ __forceinline__ void k1_strip_fast(const uint8_t* __restrict__ A, con
     uint32_t win[5][4];
     uint32_t ra[2], rb[2];
     uint4 rk[2];
-    {
-        const size_t o = EDGE_Y ? (size_t)reflect101(y0 - 2, rows) * pitch : 0;
-        ra[0] = __ldg(reinterpret_cast<const uint32_t*>(pa + o));
-        rb[0] = __ldg(reinterpret_cast<const uint32_t*>(pb + o));
-        rk[0] = __ldg(reinterpret_cast<const uint4*>(pk + o));
-    }
+    ra[0] = __ldg(reinterpret_cast<const uint32_t*>(pa));
+    rb[0] = __ldg(reinterpret_cast<const uint32_t*>(pb));
+    rk[0] = __ldg(reinterpret_cast<const uint4*>(pk));
 #pragma unroll 1
     for (int rb0 = 0; rb0 < nloc; rb0 += 10) {
 #pragma unroll
@@ -205,19 +221,19 @@ __device__ __forceinline__ void k1_strip_fast(const uint8_t* __restrict__ A, con
             const int rl = rb0 + r;
             if (rl < nloc) {
                 if (rl + 1 < nloc) {
-                    size_t o;
+                    long long step = pitch;
                     if (EDGE_Y) {
-                        o = (size_t)reflect101(y0 - 2 + rl + 1, rows) * pitch;
-                    } else {
-                        pa += pitch; pb += pitch; pk += pitch;
-                        o = 0;
+                        const int yn = y0 - 2 + rl + 1;             // unreflected row being fetched
+                        if (yn <= 0 || yn >= rows) step = -pitch;   // BORDER_REFLECT_101 walks backwards there
                     }
-                    ra[(r + 1) & 1] = __ldg(reinterpret_cast<const uint32_t*>(pa + o));
-                    rb[(r + 1) & 1] = __ldg(reinterpret_cast<const uint32_t*>(pb + o));
-                    rk[(r + 1) & 1] = __ldg(reinterpret_cast<const uint4*>(pk + o));
+                    pa += step; pb += step; pk += step;
+                    ra[(r + 1) & 1] = __ldg(reinterpret_cast<const uint32_t*>(pa));
+                    rb[(r + 1) & 1] = __ldg(reinterpret_cast<const uint32_t*>(pb));
+                    rk[(r + 1) & 1] = __ldg(reinterpret_cast<const uint4*>(pk));
                 }
-                stageA(ra[r & 1], rb[r & 1], rk[r & 1], win[r % 5]);
+                stageA_biased(ra[r & 1], rb[r & 1], rk[r & 1], win[r % 5]);
                 if (rl >= 4) {
+                    // vertical pass on biased words (each lane carries +16*510 afterwards)
                     uint32_t v[4];
 #pragma unroll
                     for (int c = 0; c < 4; c++) {
@@ -233,23 +249,30 @@ __device__ __forceinline__ void k1_strip_fast(const uint8_t* __restrict__ A, con
                     // BORDER_REFLECT_101 in x: col -2 -> 2, -1 -> 1 ; cols -> cols-2, cols+1 -> cols-3
                     const uint32_t e0 = left_edge ? v[2] : L.x, e1 = left_edge ? v[1] : L.y;
                     const uint32_t e6 = right_edge ? v[2] : R.x, e7 = right_edge ? v[1] : R.y;
+                    // horizontal pass; FIX = +128 rounding - 256*510 bias in both lanes (mod 2^32: the
+                    // transient lane overflow of the biased sums cancels exactly)
                     uint32_t h[4];
-                    h[0] = (e0 + v[2]) + 4u * (e1 + v[1]) + 6u * v[0] + RND2;
-                    h[1] = (e1 + v[3]) + 4u * (v[0] + v[2]) + 6u * v[1] + RND2;
-                    h[2] = (v[0] + e6) + 4u * (v[1] + v[3]) + 6u * v[2] + RND2;
-                    h[3] = (v[1] + e7) + 4u * (v[2] + e6) + 6u * v[3] + RND2;
+                    h[0] = (e0 + v[2]) + 4u * (e1 + v[1]) + 6u * v[0] + FIX;
+                    h[1] = (e1 + v[3]) + 4u * (v[0] + v[2]) + 6u * v[1] + FIX;
+                    h[2] = (v[0] + e6) + 4u * (v[1] + v[3]) + 6u * v[2] + FIX;
+                    h[3] = (v[1] + e7) + 4u * (v[2] + e6) + 6u * v[3] + FIX;
                     const uint32_t z = (h[0] | h[1] | h[2] | h[3]) & 0xFF00FF00u;
                     uint32_t packed = 0;
                     if (z != 0 && out_lane) {
+                        // P = byte 1, N = byte 3 of each h: gather the four P's and N's, one VABSDIFF4
+                        const uint32_t p4 = __byte_perm(__byte_perm(h[0], h[1], 0x0051), __byte_perm(h[2], h[3], 0x0051), 0x5410);
+                        const uint32_t n4 = __byte_perm(__byte_perm(h[0], h[1], 0x0073), __byte_perm(h[2], h[3], 0x0073), 0x5410);
+                        uint32_t o4 = __vabsdiffu4(p4, n4);
+                        if (MODE == 1) {
+#pragma unroll
+                            for (int c = 0; c < 4; c++)
+                                if ((int)((o4 >> (8 * c)) & 0xFFu) <= tozero) o4 &= ~(0xFFu << (8 * c));
+                        }
+                        packed = o4;
 #pragma unroll
                         for (int c = 0; c < 4; c++) {
-                            const uint32_t P = (h[c] >> 8) & 0xFFu, N = h[c] >> 24;
-                            uint32_t o = __usad(P, N, 0u);
-                            if (MODE == 1 && (int)o <= tozero) o = 0;
-                            if (o != 0) {
-                                atomicAdd(&sh_hist[o], 1u);
-                                packed |= o << (8 * c);
-                            }
+                            const uint32_t o = (o4 >> (8 * c)) & 0xFFu;
+                            if (o != 0) red_shared_inc(hist_s + o * 4u);
                         }
                     }
                     if (MODE == 1) {
