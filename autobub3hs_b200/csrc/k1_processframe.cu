@@ -180,6 +180,14 @@ __device__ __forceinline__ void stageA_biased(uint32_t a4, uint32_t b4, const ui
     w[2] = stageA1_biased(dp4a_us(p23, 0x0000FF01, 255), k.z);
     w[3] = stageA1_biased(dp4a_us(p23, (int)0xFF010000, 255), k.w);
 }
+__device__ __forceinline__ void cp_async4(uint32_t saddr, const void* g) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(saddr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void* g) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait4() { asm volatile("cp.async.wait_group 4;" ::: "memory"); }
 __device__ __forceinline__ void red_shared_inc(uint32_t saddr) {
     asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(saddr) : "memory");
 }
@@ -209,29 +217,49 @@ __device__ __forceinline__ void k1_strip_fast(const uint8_t* __restrict__ A, con
     const uint2* const xL = reinterpret_cast<const uint2*>(xch) + 32 + ((lane + 31) & 31);
     const uint2* const xR = reinterpret_cast<const uint2*>(xch) + ((lane + 1) & 31);
     uint32_t win[5][4];
-    uint32_t ra[2], rb[2];
-    uint4 rk[2];
-    ra[0] = __ldg(reinterpret_cast<const uint32_t*>(pa));
-    rb[0] = __ldg(reinterpret_cast<const uint32_t*>(pb));
-    rk[0] = __ldg(reinterpret_cast<const uint4*>(pk));
+    // 5-stage cp.async ring per warp (after the 256 exchange words): stage s holds one row of this
+    // warp: a[32] | b[32] | k32[128] words.  Every lane copies and later reads only its own words,
+    // so cp.async.wait_group is the only synchronisation the ring needs.
+    const uint32_t* const stg = xch + 256;
+    const uint32_t stg_a = (uint32_t)__cvta_generic_to_shared(stg) + lane * 4u;
+    const uint32_t stg_k = (uint32_t)__cvta_generic_to_shared(stg) + 256u + lane * 16u;
+#pragma unroll
+    for (int s0 = 0; s0 < 4; s0++) {
+        if (s0 < nloc) {
+            if (s0 > 0) {
+                long long step = pitch;
+                if (EDGE_Y) { const int yn = y0 - 2 + s0; if (yn <= 0 || yn >= rows) step = -pitch; }
+                pa += step; pb += step; pk += step;
+            }
+            cp_async4(stg_a + s0 * 768u, pa);
+            cp_async4(stg_a + s0 * 768u + 128u, pb);
+            cp_async16(stg_k + s0 * 768u, pk);
+        }
+        cp_async_commit();
+    }
 #pragma unroll 1
     for (int rb0 = 0; rb0 < nloc; rb0 += 10) {
 #pragma unroll
         for (int r = 0; r < 10; r++) {
             const int rl = rb0 + r;
             if (rl < nloc) {
-                if (rl + 1 < nloc) {
+                if (rl + 4 < nloc) {
                     long long step = pitch;
                     if (EDGE_Y) {
-                        const int yn = y0 - 2 + rl + 1;             // unreflected row being fetched
+                        const int yn = y0 - 2 + rl + 4;             // unreflected row being fetched
                         if (yn <= 0 || yn >= rows) step = -pitch;   // BORDER_REFLECT_101 walks backwards there
                     }
                     pa += step; pb += step; pk += step;
-                    ra[(r + 1) & 1] = __ldg(reinterpret_cast<const uint32_t*>(pa));
-                    rb[(r + 1) & 1] = __ldg(reinterpret_cast<const uint32_t*>(pb));
-                    rk[(r + 1) & 1] = __ldg(reinterpret_cast<const uint4*>(pk));
+                    cp_async4(stg_a + ((r + 4) % 5) * 768u, pa);
+                    cp_async4(stg_a + ((r + 4) % 5) * 768u + 128u, pb);
+                    cp_async16(stg_k + ((r + 4) % 5) * 768u, pk);
                 }
-                stageA_biased(ra[r & 1], rb[r & 1], rk[r & 1], win[r % 5]);
+                cp_async_commit();
+                cp_async_wait4();
+                const uint32_t ra_ = stg[(r % 5) * 192 + lane];
+                const uint32_t rb_ = stg[(r % 5) * 192 + 32 + lane];
+                const uint4 rk_ = *reinterpret_cast<const uint4*>(stg + (r % 5) * 192 + 64 + lane * 4);
+                stageA_biased(ra_, rb_, rk_, win[r % 5]);
                 if (rl >= 4) {
                     // vertical pass on biased words (each lane carries +16*510 afterwards)
                     uint32_t v[4];
@@ -299,17 +327,19 @@ __device__ __forceinline__ void k1_strip_any(const uint8_t* A, const uint8_t* B,
     }
 }
 
+constexpr int K1_MAX_THREADS = 512;             // 16 warps = 1920 columns per CTA; wider images add CTAs in x
+constexpr int K1_WARP_WORDS = 256 + 5 * 192;   // exchange double buffer + 5-stage cp.async ring
 constexpr int K1_TH_TARGET = 105;   // output rows per strip (1050 = 10 x 105): 4 halo rows per 105
 
 // grid: x = strip, y = j-1, z = (slot-slot_first)*ncams + cam ; block = 32 * ceil(cols/120)
-__global__ void k1_trigger_kernel(uint8_t* const* __restrict__ slot_ptrs, const int* __restrict__ nframes,
+__global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_trigger_kernel(uint8_t* const* __restrict__ slot_ptrs, const int* __restrict__ nframes,
                                   const int* __restrict__ tss, uint32_t* const* __restrict__ k32_ptrs,
                                   uint32_t* __restrict__ hist, int slot_first, int rows, int cols,
-                                  int ncams, int max_frames, int th) {
-    extern __shared__ uint32_t smem[];
+                                  int ncams, int max_frames, int th, int nxg) {
+    extern __shared__ __align__(16) uint32_t smem[];
     uint32_t* sh_hist = smem;                       // 256
     const int warp = threadIdx.x >> 5;
-    uint32_t* xch = smem + 256 + warp * 256;        // 2 x 128 words per warp
+    uint32_t* xch = smem + 256 + warp * K1_WARP_WORDS;        // 2 x 128 words per warp
     const int rel = blockIdx.z;
     const int slot = slot_first + rel / ncams;
     const int cam = rel % ncams;
@@ -322,10 +352,11 @@ __global__ void k1_trigger_kernel(uint8_t* const* __restrict__ slot_ptrs, const 
     const uint8_t* base = slot_ptrs[slot] + (size_t)cam * max_frames * npix;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
     __syncthreads();
-    const int y0 = blockIdx.x * th;
-    if (y0 < rows)
+    const int y0 = (blockIdx.x / nxg) * th;
+    const int x0 = ((blockIdx.x % nxg) * (blockDim.x >> 5) + warp) * ABUB_K1_TILE_W;
+    if (y0 < rows && x0 < cols)
         k1_strip_any<0>(base + (size_t)j * npix, base + (size_t)jp * npix, k32_ptrs[cam], rows, cols, y0, th,
-                        warp * ABUB_K1_TILE_W, sh_hist, xch, nullptr, -1);
+                        x0, sh_hist, xch, nullptr, -1);
     __syncthreads();
     uint32_t* H = hist + (((size_t)slot * ncams + cam) * max_frames + j) * 256;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -353,18 +384,19 @@ __global__ void k1_fill_bin0_kernel(uint32_t* __restrict__ hist, const int* __re
 }
 
 // single frame pair (parity tap + localizer genesis frame)
-__global__ void k1_single_kernel(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B,
+__global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_single_kernel(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B,
                                  const uint32_t* __restrict__ K, uint8_t* __restrict__ out,
-                                 uint32_t* __restrict__ hist, int rows, int cols, int tozero, int th) {
-    extern __shared__ uint32_t smem[];
+                                 uint32_t* __restrict__ hist, int rows, int cols, int tozero, int th, int nxg) {
+    extern __shared__ __align__(16) uint32_t smem[];
     uint32_t* sh_hist = smem;
     const int warp = threadIdx.x >> 5;
-    uint32_t* xch = smem + 256 + warp * 256;
+    uint32_t* xch = smem + 256 + warp * K1_WARP_WORDS;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
     __syncthreads();
-    const int y0 = blockIdx.x * th;
-    if (y0 < rows)
-        k1_strip_any<1>(A, B, K, rows, cols, y0, th, warp * ABUB_K1_TILE_W, sh_hist, xch, out, tozero);
+    const int y0 = (blockIdx.x / nxg) * th;
+    const int x0 = ((blockIdx.x % nxg) * (blockDim.x >> 5) + warp) * ABUB_K1_TILE_W;
+    if (y0 < rows && x0 < cols)
+        k1_strip_any<1>(A, B, K, rows, cols, y0, th, x0, sh_hist, xch, out, tozero);
     __syncthreads();
     if (hist)
         for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -375,19 +407,19 @@ __global__ void k1_single_kernel(const uint8_t* __restrict__ A, const uint8_t* _
 
 // localizer genesis jobs (CalculateInitialBubbleParams, L3Localizer.cpp:232,252): ProcessFrame,
 // THRESH_TOZERO at loc_thres, histogram of the result; grid.y = job (non-genesis jobs return)
-__global__ void k1_genesis_jobs_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols, int th) {
-    extern __shared__ uint32_t smem[];
+__global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_genesis_jobs_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols, int th, int nxg) {
+    extern __shared__ __align__(16) uint32_t smem[];
     const abub_loc_job job = jobs[blockIdx.y];
     if (!job.genesis) return;
     uint32_t* sh_hist = smem;
     const int warp = threadIdx.x >> 5;
-    uint32_t* xch = smem + 256 + warp * 256;
+    uint32_t* xch = smem + 256 + warp * K1_WARP_WORDS;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
     __syncthreads();
-    const int y0 = blockIdx.x * th;
-    if (y0 < rows)
-        k1_strip_any<1>(job.a, job.b, job.k32, rows, cols, y0, th, warp * ABUB_K1_TILE_W, sh_hist, xch, job.tz,
-                        job.tozero);
+    const int y0 = (blockIdx.x / nxg) * th;
+    const int x0 = ((blockIdx.x % nxg) * (blockDim.x >> 5) + warp) * ABUB_K1_TILE_W;
+    if (y0 < rows && x0 < cols)
+        k1_strip_any<1>(job.a, job.b, job.k32, rows, cols, y0, th, x0, sh_hist, xch, job.tz, job.tozero);
     __syncthreads();
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         const uint32_t c = sh_hist[i];
@@ -419,8 +451,21 @@ static inline void k1_strips(int rows, int* nstrips, int* th) {
     *nstrips = (rows + K1_TH_TARGET - 1) / K1_TH_TARGET;
     *th = (rows + *nstrips - 1) / *nstrips;
 }
-static inline int k1_block_threads(int cols) { return 32 * ((cols + ABUB_K1_TILE_W - 1) / ABUB_K1_TILE_W); }
-static inline size_t k1_smem_bytes(int threads) { return (256 + (threads / 32) * 256) * sizeof(uint32_t); }
+template <typename KernelT>
+static int k1_allow_smem(abub_ctx* ctx, KernelT kernel, size_t bytes) {
+    if (bytes > 48 * 1024)
+        ABUB_CHECK_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return ABUB_OK;
+}
+static inline int k1_block_threads(int cols) {
+    const int ntx = (cols + ABUB_K1_TILE_W - 1) / ABUB_K1_TILE_W;
+    return 32 * (ntx < K1_MAX_THREADS / 32 ? ntx : K1_MAX_THREADS / 32);
+}
+static inline int k1_xgroups(int cols) {
+    const int ntx = (cols + ABUB_K1_TILE_W - 1) / ABUB_K1_TILE_W, wpc = k1_block_threads(cols) / 32;
+    return (ntx + wpc - 1) / wpc;
+}
+static inline size_t k1_smem_bytes(int threads) { return (256 + (threads / 32) * K1_WARP_WORDS) * sizeof(uint32_t); }
 
 int abub_k1_build_k32(abub_ctx* ctx, int cam) {
     abub_cam_state& c = ctx->cam[cam];
@@ -432,20 +477,20 @@ int abub_k1_build_k32(abub_ctx* ctx, int cam) {
 
 int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots) {
     const int threads = k1_block_threads(ctx->cols);
-    ABUB_REQUIRE(ctx, threads <= 1024, "cols too large for K1 (max 3840)");
     const size_t hist_off = (size_t)slot_first * ctx->ncams * ctx->max_frames * 256;
     const size_t hist_n = (size_t)nslots * ctx->ncams * ctx->max_frames * 256;
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(ctx->d_hist + hist_off, 0, hist_n * sizeof(uint32_t), ctx->stream));
     int nstrips, th;
     k1_strips(ctx->rows, &nstrips, &th);
+    if (int rc = k1_allow_smem(ctx, k1_trigger_kernel, k1_smem_bytes(threads))) return rc;
     // z is limited to 65535: chunk the (slot,cam) range
     const int per = 65535 / ctx->ncams;
     for (int s0 = 0; s0 < nslots; s0 += per) {
         const int ns = (nslots - s0 < per) ? nslots - s0 : per;
-        dim3 grid(nstrips, ctx->max_frames - 1, ns * ctx->ncams);
+        dim3 grid(nstrips * k1_xgroups(ctx->cols), ctx->max_frames - 1, ns * ctx->ncams);
         k1_trigger_kernel<<<grid, threads, k1_smem_bytes(threads), ctx->stream>>>(
             ctx->d_slot_ptrs, ctx->d_nframes, ctx->d_tss, ctx->d_k32_ptrs, ctx->d_hist, slot_first + s0,
-            ctx->rows, ctx->cols, ctx->ncams, ctx->max_frames, th);
+            ctx->rows, ctx->cols, ctx->ncams, ctx->max_frames, th, k1_xgroups(ctx->cols));
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     const int total_w = nslots * ctx->ncams * ctx->max_frames;
@@ -458,12 +503,13 @@ int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots) {
 int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b, const uint32_t* d_k32,
                           uint8_t* d_out, uint32_t* d_hist, int tozero_thres) {
     const int threads = k1_block_threads(ctx->cols);
-    ABUB_REQUIRE(ctx, threads <= 1024, "cols too large for K1 (max 3840)");
     if (d_hist) ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_hist, 0, 256 * sizeof(uint32_t), ctx->stream));
     int nstrips, th;
     k1_strips(ctx->rows, &nstrips, &th);
-    k1_single_kernel<<<nstrips, threads, k1_smem_bytes(threads), ctx->stream>>>(d_a, d_b, d_k32, d_out, d_hist,
-                                                                                 ctx->rows, ctx->cols, tozero_thres, th);
+    if (int rc = k1_allow_smem(ctx, k1_single_kernel, k1_smem_bytes(threads))) return rc;
+    const int nxg = k1_xgroups(ctx->cols);
+    k1_single_kernel<<<nstrips * nxg, threads, k1_smem_bytes(threads), ctx->stream>>>(d_a, d_b, d_k32, d_out, d_hist, ctx->rows,
+                                                                                       ctx->cols, tozero_thres, th, nxg);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     if (d_hist) {
         k1_fill_bin0_single<<<1, 32, 0, ctx->stream>>>(d_hist, (uint32_t)ctx->npix);
@@ -474,13 +520,14 @@ int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b,
 
 int abub_k1_launch_genesis_jobs(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs) {
     const int threads = k1_block_threads(ctx->cols);
-    ABUB_REQUIRE(ctx, threads <= 1024, "cols too large for K1 (max 3840)");
     int nstrips, th;
     k1_strips(ctx->rows, &nstrips, &th);
+    if (int rc = k1_allow_smem(ctx, k1_genesis_jobs_kernel, k1_smem_bytes(threads))) return rc;
     for (int j0 = 0; j0 < njobs; j0 += 65535) {
         const int nj = (njobs - j0 < 65535) ? njobs - j0 : 65535;
-        k1_genesis_jobs_kernel<<<dim3(nstrips, nj), threads, k1_smem_bytes(threads), ctx->stream>>>(d_jobs + j0, ctx->rows,
-                                                                                                   ctx->cols, th);
+        const int nxg = k1_xgroups(ctx->cols);
+        k1_genesis_jobs_kernel<<<dim3(nstrips * nxg, nj), threads, k1_smem_bytes(threads), ctx->stream>>>(
+            d_jobs + j0, ctx->rows, ctx->cols, th, nxg);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     return ABUB_OK;
