@@ -18,6 +18,7 @@ struct abub_cam_state {
     uint8_t*  d_sigma = nullptr;    // TrainedSigmaImage
     uint32_t* d_k32 = nullptr;      // per pixel (255-t)|(765-t)<<16, t=min(6*sigma,255)  (K1 stage A)
     uint8_t*  d_t8 = nullptr;       // t = min(6*sigma,255)
+    int16_t*  d_k16 = nullptr;      // per pixel -(255+t) as s16 (TMA trigger kernel stage A)
     int training_set_size = 0;
     bool has_background = false;
     // training: kept frames live in device chunks until abub_train_finish
@@ -62,6 +63,7 @@ struct abub_ctx {
     uint8_t*  d_tmp8[4] = {nullptr, nullptr, nullptr, nullptr};
     uint32_t* d_hist_tmp = nullptr; // 16 x 256
     void*     loc = nullptr;        // localizer arena (k5_localize.cu)
+    void*     d_tmaps = nullptr;    // CUtensorMap[2*max_slots + 2*ncams] (k1_trigger_tma.cu); null = TMA path off
 };
 
 #define ABUB_CHECK_CUDA(ctx, call)                                                        \
@@ -87,6 +89,11 @@ int abub_k1_build_k32(abub_ctx* ctx, int cam);
 int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots);
 int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b, const uint32_t* d_k32,
                           uint8_t* d_out, uint32_t* d_hist, int tozero_thres);
+// K1 TMA trigger path (k1_trigger_tma.cu)
+bool abub_k1_tma_supported(const abub_ctx* ctx);
+int abub_k1_tma_init(abub_ctx* ctx);
+int abub_k1_build_k16(abub_ctx* ctx, int cam);
+int abub_k1_launch_trigger_tma(abub_ctx* ctx, int slot_first, int nslots);
 // K2 (k2_trigger_scan.cu)
 int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots);
 // K3/K4 (k34_trainer.cu)

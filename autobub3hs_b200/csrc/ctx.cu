@@ -31,6 +31,7 @@ extern "C" int abub_ctx_create(int device, int rows, int cols, int ncams, int ma
         ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_sigma, n));
         ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_t8, n));
         ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_k32, n * sizeof(uint32_t)));
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_k16, n * sizeof(int16_t)));
     }
     const size_t frames_per_slot = (size_t)ncams * max_frames;
     std::vector<uint8_t*> sp(max_slots);
@@ -58,7 +59,7 @@ extern "C" int abub_ctx_create(int device, int rows, int cols, int ncams, int ma
     ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_hist_tmp, 16 * 256 * sizeof(uint32_t)));
     int rc = abub_loc_init(ctx);
     if (rc != ABUB_OK) return rc;
-    return ABUB_OK;
+    return abub_k1_tma_init(ctx);
 }
 
 static void train_release(abub_cam_state& cs) {
@@ -75,7 +76,7 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     abub_loc_free(ctx);
     for (int c = 0; c < ABUB_MAX_CAMS; c++) {
         abub_cam_state& cs = ctx->cam[c];
-        cudaFree(cs.d_mean); cudaFree(cs.d_sigma); cudaFree(cs.d_t8); cudaFree(cs.d_k32);
+        cudaFree(cs.d_mean); cudaFree(cs.d_sigma); cudaFree(cs.d_t8); cudaFree(cs.d_k32); cudaFree(cs.d_k16);
         cudaFree(cs.d_sum); cudaFree(cs.d_sumsq); cudaFree(cs.d_count); cudaFree(cs.d_flag);
         cudaFree((void*)cs.d_table);
         train_release(cs);
@@ -88,6 +89,7 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     cudaFree(ctx->d_sig); cudaFree(ctx->d_tss); cudaFree(ctx->d_k32_ptrs); cudaFree(ctx->d_slot_ptrs);
     for (int i = 0; i < 4; i++) cudaFree(ctx->d_tmp8[i]);
     cudaFree(ctx->d_hist_tmp);
+    cudaFree(ctx->d_tmaps);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -109,6 +111,7 @@ static int install_background(abub_ctx* ctx, int cam, int tss) {
                                          ctx->stream));
     int rc = abub_k1_build_k32(ctx, cam);
     if (rc) return rc;
+    if ((rc = abub_k1_build_k16(ctx, cam))) return rc;
     for (auto& s : ctx->slots) s.hist_valid = false;
     ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // &training_set_size must outlive the copy
     return ABUB_OK;

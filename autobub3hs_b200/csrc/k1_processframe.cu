@@ -20,6 +20,8 @@
 //     conflict-free 8-byte neighbour exchange through shared memory (one __syncwarp);
 //   * only non-zero outputs touch the shared-memory histogram; bin 0 is recovered as
 //     rows*cols - sum(other bins) by a finalize kernel.
+#include <stdlib.h>
+
 #include "abub_internal.cuh"
 
 namespace {
@@ -335,7 +337,7 @@ constexpr int K1_TH_TARGET = 105;   // output rows per strip (1050 = 10 x 105): 
 __global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_trigger_kernel(uint8_t* const* __restrict__ slot_ptrs, const int* __restrict__ nframes,
                                   const int* __restrict__ tss, uint32_t* const* __restrict__ k32_ptrs,
                                   uint32_t* __restrict__ hist, int slot_first, int rows, int cols,
-                                  int ncams, int max_frames, int th, int nxg) {
+                                  int ncams, int max_frames, int th, int nxg, int border_only) {
     extern __shared__ __align__(16) uint32_t smem[];
     uint32_t* sh_hist = smem;                       // 256
     const int warp = threadIdx.x >> 5;
@@ -352,7 +354,9 @@ __global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_trigger_kernel(uint8_t* 
     const uint8_t* base = slot_ptrs[slot] + (size_t)cam * max_frames * npix;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
     __syncthreads();
-    const int y0 = (blockIdx.x / nxg) * th;
+    // border_only: two strips of `th` (= 2) rows at the top and bottom of the frame -- the rows that need
+    // BORDER_REFLECT_101 in y; the TMA kernel (k1_trigger_tma.cu) covers [2, rows-2)
+    const int y0 = border_only ? ((blockIdx.x / nxg) == 0 ? 0 : rows - th) : (blockIdx.x / nxg) * th;
     const int x0 = ((blockIdx.x % nxg) * (blockDim.x >> 5) + warp) * ABUB_K1_TILE_W;
     if (y0 < rows && x0 < cols)
         k1_strip_any<0>(base + (size_t)j * npix, base + (size_t)jp * npix, k32_ptrs[cam], rows, cols, y0, th,
@@ -485,12 +489,17 @@ int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots) {
     if (int rc = k1_allow_smem(ctx, k1_trigger_kernel, k1_smem_bytes(threads))) return rc;
     // z is limited to 65535: chunk the (slot,cam) range
     const int per = 65535 / ctx->ncams;
+    static const bool legacy = getenv("ABUB_K1_LEGACY") != nullptr;     // A/B switch for profiling
+    const bool tma = ctx->d_tmaps && !legacy;
+    if (tma)
+        if (int rc = abub_k1_launch_trigger_tma(ctx, slot_first, nslots)) return rc;
     for (int s0 = 0; s0 < nslots; s0 += per) {
         const int ns = (nslots - s0 < per) ? nslots - s0 : per;
-        dim3 grid(nstrips * k1_xgroups(ctx->cols), ctx->max_frames - 1, ns * ctx->ncams);
+        // with the TMA kernel on rows [2, rows-2) this kernel only does the 2+2 border rows
+        dim3 grid((tma ? 2 : nstrips) * k1_xgroups(ctx->cols), ctx->max_frames - 1, ns * ctx->ncams);
         k1_trigger_kernel<<<grid, threads, k1_smem_bytes(threads), ctx->stream>>>(
             ctx->d_slot_ptrs, ctx->d_nframes, ctx->d_tss, ctx->d_k32_ptrs, ctx->d_hist, slot_first + s0,
-            ctx->rows, ctx->cols, ctx->ncams, ctx->max_frames, th, k1_xgroups(ctx->cols));
+            ctx->rows, ctx->cols, ctx->ncams, ctx->max_frames, tma ? 2 : th, k1_xgroups(ctx->cols), tma ? 1 : 0);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     const int total_w = nslots * ctx->ncams * ctx->max_frames;

@@ -1,0 +1,360 @@
+// K1 (trigger form, TMA-fed) -- AnalyzerUnit::ProcessFrame fused with the 256-bin calcHist
+// (reference: AnalyzerUnit.cpp:346-377 and :441-456), batched over every (slot, camera, j).
+//
+// Same arithmetic as k1_processframe.cu (which stays as the generic-pitch / store-mode path);
+// this file is the hot trigger path for pitches that TMA can address (cols % 16 == 0):
+//
+//   * one warp owns a strip of 240 output columns x TH rows; lane l holds 8 adjacent pixels
+//     (lanes 0 and 31 are the halo, so 256 columns are loaded per row);
+//   * rows arrive through a per-warp ring of TMA boxes (cp.async.bulk.tensor, 256 columns x
+//     T_R rows of frame j, frame j-d and the per-pixel constant plane) completed on
+//     per-warp mbarriers: no per-lane global addressing at all.  Lane 0 re-arms a stage as
+//     soon as the warp has consumed it.  BORDER_REFLECT_101 rows are fetched as single-row
+//     boxes at the reflected row index; TMA zero-fills columns outside the image and the two
+//     lanes on the image border reflect in registers;
+//   * pixels are packed two per 32-bit word, one word per plane:  pos01 = p0 | p1<<16,
+//     neg01 = n0 | n1<<16.  Stage A is
+//         x = (a0 | a1<<16) + ((255-b0) | (255-b1)<<16)        lanes a-b+255  (no borrows)
+//         pos = VIADDMNMX.S16x2.RELU(x, K16, 0)                 K16 = -(255+t) per lane
+//         neg = VIADDMNMX.S16x2.RELU(0x01FE01FE - x, K16, 0)
+//     with t = min(6 sigma, 255) (2 bytes per pixel of L2-resident constants);
+//   * the vertical [1 4 6 4 1] is a cascade of four [1 1] adds on carried state
+//     (lanes <= 4080), the horizontal pass takes the two halo words from the neighbour lanes
+//     with SHFL and builds the odd taps with one PRMT per word;
+//   * (sum + 128) >> 8 per lane, |P - N|; only non-zero outputs touch the shared histogram;
+//     bin 0 is recovered as rows*cols - sum(other bins) by k1_fill_bin0_kernel.
+#include <cuda.h>
+
+#include "abub_internal.cuh"
+
+namespace {
+
+#ifndef ABUB_K1T_R
+#define ABUB_K1T_R 4
+#endif
+#ifndef ABUB_K1T_S
+#define ABUB_K1T_S 2
+#endif
+#ifndef ABUB_K1T_MINCTA
+#define ABUB_K1T_MINCTA 20
+#endif
+constexpr int T_R = ABUB_K1T_R;           // rows per TMA box
+constexpr int T_S = ABUB_K1T_S;           // ring stages per warp
+constexpr int T_OW = 240;                 // output columns per warp (lanes 1..30 x 8 px)
+constexpr int T_BW = 272;                 // box width in pixels: [x0-16, x0+256) -- TMA needs a 16-byte aligned start
+constexpr int T_A_OFF = 0;                                        // frame j rows      (T_R x 272 B)
+constexpr int T_B_OFF = ((T_R * T_BW + 127) / 128) * 128;         // frame j-d rows
+constexpr int T_K_OFF = 2 * T_B_OFF;                              // K16 rows          (T_R x 544 B)
+constexpr int T_TX_BYTES = T_R * T_BW * 4;                        // bytes one stage receives
+constexpr int T_STAGE_BYTES = ((T_K_OFF + T_R * T_BW * 2 + 127) / 128) * 128;
+constexpr int T_MAX_WARPS = 1;            // one warp per CTA: nothing to wait for at the end of a strip, and every
+                                          // TMA operand (ring, barrier, coordinates) lives in uniform registers
+constexpr int T_TH_TARGET = 150;          // output rows per strip
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int x, int y, int z, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(z), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar) : "memory");
+}
+// relu(x + k) per s16 lane.  k < 0 in both lanes, so max(x + k, k) clamps nothing that the relu would
+// not: passing k as the max operand saves materialising a zero register.
+__device__ __forceinline__ uint32_t relu_add_s16x2(uint32_t x, uint32_t k) {
+    return __viaddmax_s16x2_relu(x, k, k);
+}
+
+// Issue the TMA loads of ring stage `s`: image rows y0 - 2 + s*T_R .. +T_R-1 (always >= 0; rows past the
+// image bottom are zero-filled and never consumed).  Called by lane 0 only.  xe = (x0-16)/2: the maps
+// address the planes as 2-byte (frames) / 4-byte (K16) elements so that one box spans 272 pixels.
+__device__ __forceinline__ void k1t_issue(const CUtensorMap* smap, const CUtensorMap* kmap, uint32_t stage_base,
+                                          uint32_t bar, int s, int y0, int xe, int za, int zb) {
+    const int ys = y0 - 2 + s * T_R;
+    mbar_expect_tx(bar, T_TX_BYTES);
+    tma_load_3d(stage_base + T_A_OFF, smap, xe, ys, za, bar);
+    tma_load_3d(stage_base + T_B_OFF, smap, xe, ys, zb, bar);
+    tma_load_2d(stage_base + T_K_OFF, kmap, xe, ys, bar);
+}
+
+// horizontal [1 4 6 4 1] of one plane: W[0..5] = words -1..4 (two pixels each), out H[0..3] incl. +128
+__device__ __forceinline__ void k1t_hpass(const uint32_t W[6], uint32_t H[4]) {
+    uint32_t S[5];
+#pragma unroll
+    for (int k = 0; k < 5; k++) S[k] = __byte_perm(W[k], W[k + 1], 0x5432);    // (hi of W[k], lo of W[k+1])
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t e = W[k] + W[k + 2] + 0x00800080u;
+        const uint32_t t = S[k] + S[k + 1];
+        H[k] = e + 6u * W[k + 1] + 4u * t;
+    }
+}
+
+// grid: x = strip * nxg + xg, y = j-1, z = (slot-slot_first)*ncams + cam ; block = 32 * warps_per_cta
+__global__ void __launch_bounds__(32 * T_MAX_WARPS, ABUB_K1T_MINCTA)
+k1_trigger_tma_kernel(const CUtensorMap* __restrict__ slot_maps, const CUtensorMap* __restrict__ k16_maps,
+                      const int* __restrict__ nframes, const int* __restrict__ tss, uint32_t* __restrict__ hist,
+                      int slot_first, int rows, int cols, int ncams, int max_frames, int th, int nxg) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int warp = (T_MAX_WARPS == 1) ? 0 : (int)(threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int wpc = (T_MAX_WARPS == 1) ? 1 : (int)(blockDim.x >> 5);
+    // layout: [ring stages, 1024-aligned][hist 256 u32][mbarriers]
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t ring = (raw + 127u) & ~127u;
+    uint8_t* const ring_p = smem_raw + (ring - raw);
+    uint32_t* const sh_hist = reinterpret_cast<uint32_t*>(ring_p + (size_t)wpc * T_S * T_STAGE_BYTES);
+    const uint32_t bars = ring + (uint32_t)wpc * T_S * T_STAGE_BYTES + 1024u + (uint32_t)warp * T_S * 8u;
+    const uint32_t my_ring = ring + (uint32_t)warp * T_S * T_STAGE_BYTES;
+    const uint8_t* const my_ring_p = ring_p + (size_t)warp * T_S * T_STAGE_BYTES;
+
+    const int rel = blockIdx.z;
+    const int slot = slot_first + rel / ncams;
+    const int cam = rel % ncams;
+    const int j = blockIdx.y + 1;
+    const int nf = nframes[slot * ncams + cam];
+    if (j >= nf) return;
+    const int d = (tss[cam] < 6) ? 1 : 2;           // twoFrameOffset, AnalyzerUnit.cpp:182-188
+    const int jp = (j - d < 0) ? 0 : j - d;         // j==1 uses frame 0 (:176)
+
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < T_S; s++) mbar_init(bars + s * 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    // strips tile the output rows [2, rows-2): no strip ever needs a reflected row (the two border
+    // rows at the top and bottom go through the generic kernel, see abub_k1_launch_trigger)
+    const int strip = blockIdx.x / nxg, xg = blockIdx.x % nxg;
+    const int y0 = 2 + strip * th;
+    const int x0 = (xg * wpc + warp) * T_OW;
+    if (y0 < rows - 2 && x0 < cols) {
+        const int nout = min(th, rows - 2 - y0);
+        const int nloc = nout + 4;
+        const int nst = (nloc + T_R - 1) / T_R;
+        const int xe = (x0 - 16) / 2;
+        const int gx = x0 - 8 + lane * 8;
+        const bool out_lane = lane >= 1 && lane <= 30 && gx < cols;
+        const bool left_edge = (gx == 0), right_edge = (gx + 8 == cols);
+        const bool edge_warp = (x0 == 0) || (x0 + T_OW >= cols);
+        const CUtensorMap* smap = slot_maps + slot;
+        const CUtensorMap* kmap = k16_maps + cam;
+        const int za = cam * max_frames + j, zb = cam * max_frames + jp;
+
+        if (lane == 0) {
+#pragma unroll
+            for (int s = 0; s < T_S; s++)
+                if (s < nst) k1t_issue(smap, kmap, my_ring + s * T_STAGE_BYTES, bars + s * 8, s, y0, xe, za, zb);
+        }
+        // carried state of the vertical cascade: X = previous row, P,Q,Rr = partial binomials
+        uint32_t X[8], P[8], Q[8], Rr[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) X[i] = P[i] = Q[i] = Rr[i] = 0;
+
+        int stage = 0;
+        uint32_t parity = 0;
+#pragma unroll 1
+        for (int s = 0; s < nst; s++) {
+            mbar_wait(bars + stage * 8, parity);
+            const uint8_t* st = my_ring_p + stage * T_STAGE_BYTES;
+#pragma unroll
+            for (int r = 0; r < T_R; r++) {
+                const int rl = s * T_R + r;
+                {
+                    const uint2 a = *reinterpret_cast<const uint2*>(st + T_A_OFF + r * T_BW + 8 + lane * 8);
+                    const uint2 b = *reinterpret_cast<const uint2*>(st + T_B_OFF + r * T_BW + 8 + lane * 8);
+                    const uint4 k = *reinterpret_cast<const uint4*>(st + T_K_OFF + r * 2 * T_BW + 16 + lane * 16);
+                    const uint32_t nbx = ~b.x, nby = ~b.y;
+                    uint32_t w[8];
+                    {
+                        const uint32_t x0_ = __byte_perm(a.x, 0, 0x4140) + __byte_perm(nbx, 0, 0x4140);
+                        const uint32_t x1_ = __byte_perm(a.x, 0, 0x4342) + __byte_perm(nbx, 0, 0x4342);
+                        const uint32_t x2_ = __byte_perm(a.y, 0, 0x4140) + __byte_perm(nby, 0, 0x4140);
+                        const uint32_t x3_ = __byte_perm(a.y, 0, 0x4342) + __byte_perm(nby, 0, 0x4342);
+                        w[0] = relu_add_s16x2(x0_, k.x); w[4] = relu_add_s16x2(0x01FE01FEu - x0_, k.x);
+                        w[1] = relu_add_s16x2(x1_, k.y); w[5] = relu_add_s16x2(0x01FE01FEu - x1_, k.y);
+                        w[2] = relu_add_s16x2(x2_, k.z); w[6] = relu_add_s16x2(0x01FE01FEu - x2_, k.z);
+                        w[3] = relu_add_s16x2(x3_, k.w); w[7] = relu_add_s16x2(0x01FE01FEu - x3_, k.w);
+                    }
+                    uint32_t v[8];
+#pragma unroll
+                    for (int i = 0; i < 8; i++) {
+                        const uint32_t p = w[i] + X[i];
+                        const uint32_t q = p + P[i];
+                        const uint32_t rr = q + Q[i];
+                        v[i] = rr + Rr[i];
+                        X[i] = w[i]; P[i] = p; Q[i] = q; Rr[i] = rr;
+                    }
+                    // rows past nloc (tail of the last box) are computed and dropped: keeping the
+                    // state update unconditional lets the cascade registers rotate without moves
+                    if (rl >= 4 && rl < nloc) {
+                        uint32_t Wp[6], Wn[6];
+                        Wp[0] = __shfl_up_sync(0xffffffffu, v[3], 1);
+                        Wn[0] = __shfl_up_sync(0xffffffffu, v[7], 1);
+                        Wp[5] = __shfl_down_sync(0xffffffffu, v[0], 1);
+                        Wn[5] = __shfl_down_sync(0xffffffffu, v[4], 1);
+#pragma unroll
+                        for (int i = 0; i < 4; i++) { Wp[1 + i] = v[i]; Wn[1 + i] = v[4 + i]; }
+                        if (edge_warp) {
+                            // BORDER_REFLECT_101 in x: cols -2,-1 -> 2,1 ; cols, cols+1 -> cols-2, cols-3
+                            if (left_edge)  { Wp[0] = __byte_perm(v[0], v[1], 0x3254); Wn[0] = __byte_perm(v[4], v[5], 0x3254); }
+                            if (right_edge) { Wp[5] = __byte_perm(v[2], v[3], 0x3254); Wn[5] = __byte_perm(v[6], v[7], 0x3254); }
+                        }
+                        uint32_t Hp[4], Hn[4];
+                        k1t_hpass(Wp, Hp);
+                        k1t_hpass(Wn, Hn);
+                        const uint32_t z = ((Hp[0] | Hp[1] | Hp[2]) | (Hp[3] | Hn[0] | Hn[1]) | (Hn[2] | Hn[3])) & 0xFF00FF00u;
+                        if (z != 0 && out_lane) {
+                            // P = byte 1 / byte 3 of each word
+                            const uint32_t p03 = __byte_perm(Hp[0], Hp[1], 0x7531), n03 = __byte_perm(Hn[0], Hn[1], 0x7531);
+                            const uint32_t p47 = __byte_perm(Hp[2], Hp[3], 0x7531), n47 = __byte_perm(Hn[2], Hn[3], 0x7531);
+                            const uint32_t o03 = __vabsdiffu4(p03, n03), o47 = __vabsdiffu4(p47, n47);
+                            // all eight bytes go to the histogram, zeros included: bin 0 of the shared table is
+                            // scratch (the real bin 0 is rows*cols - sum of the others), which keeps this block
+                            // free of branches and predicates
+#pragma unroll
+                            for (int c = 0; c < 4; c++) {
+                                atomicAdd(&sh_hist[__byte_perm(o03, 0, 0x4440 + c)], 1u);
+                                atomicAdd(&sh_hist[__byte_perm(o47, 0, 0x4440 + c)], 1u);
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0 && s + T_S < nst)
+                k1t_issue(smap, kmap, my_ring + stage * T_STAGE_BYTES, bars + stage * 8, s + T_S, y0, xe, za, zb);
+            if (++stage == T_S) { stage = 0; parity ^= 1u; }
+        }
+    }
+    __syncthreads();
+    uint32_t* H = hist + (((size_t)slot * ncams + cam) * max_frames + j) * 256;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        const uint32_t c = sh_hist[i];
+        if (c && i) atomicAdd(&H[i], c);       // bin 0 of the shared table is scratch
+    }
+}
+
+// K16 = -(255 + t) as s16, t = min(6*sigma, 255)
+__global__ void k1_build_k16_kernel(const uint8_t* __restrict__ sigma, int16_t* __restrict__ k16, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int t = min(6 * (int)sigma[i], 255);
+    k16[i] = (int16_t)(-(255 + t));
+}
+
+}  // namespace
+
+// ---- host side: tensor maps -----------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+    static PFN_encodeTiled fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_encodeTiled>(p);
+    }
+    return fn;
+}
+
+bool abub_k1_tma_supported(const abub_ctx* ctx) { return (ctx->cols % 16) == 0 && ctx->cols >= 16 && ctx->rows >= 5; }
+
+// Builds the device array of tensor maps: [slot] then [cam].  Called once from abub_ctx_create.
+// The u8 frames are described as 2-byte elements and the s16 constant plane as 4-byte elements: a box
+// is limited to 256 elements per dimension and one box must span 272 pixels.
+int abub_k1_tma_init(abub_ctx* ctx) {
+    ctx->d_tmaps = nullptr;
+    if (!abub_k1_tma_supported(ctx)) return ABUB_OK;
+    PFN_encodeTiled enc = get_encode();
+    if (!enc) { ctx->err = "cuTensorMapEncodeTiled not available from the driver"; return ABUB_E_CUDA; }
+    const int nmaps = ctx->max_slots + ctx->ncams;
+    std::vector<CUtensorMap> maps(nmaps);
+    const cuuint32_t ones[3] = {1, 1, 1};
+    for (int s = 0; s < ctx->max_slots; s++) {
+        const cuuint64_t dims[3] = {(cuuint64_t)ctx->cols / 2, (cuuint64_t)ctx->rows, (cuuint64_t)ctx->ncams * ctx->max_frames};
+        const cuuint64_t strides[2] = {(cuuint64_t)ctx->cols, (cuuint64_t)ctx->npix};
+        const cuuint32_t box[3] = {(cuuint32_t)T_BW / 2, (cuuint32_t)T_R, 1};
+        CUresult r = enc(&maps[s], CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, ctx->slots[s].d_frames, dims, strides, box, ones,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { ctx->err = "cuTensorMapEncodeTiled(slot) failed: " + std::to_string((int)r); return ABUB_E_CUDA; }
+    }
+    for (int c = 0; c < ctx->ncams; c++) {
+        const cuuint64_t dims[2] = {(cuuint64_t)ctx->cols / 2, (cuuint64_t)ctx->rows};
+        const cuuint64_t strides[1] = {(cuuint64_t)ctx->cols * 2};
+        const cuuint32_t box[2] = {(cuuint32_t)T_BW / 2, (cuuint32_t)T_R};
+        CUresult r = enc(&maps[ctx->max_slots + c], CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, ctx->cam[c].d_k16, dims, strides, box,
+                         ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { ctx->err = "cuTensorMapEncodeTiled(k16) failed: " + std::to_string((int)r); return ABUB_E_CUDA; }
+    }
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_tmaps, (size_t)nmaps * sizeof(CUtensorMap)));
+    ABUB_CHECK_CUDA(ctx, cudaMemcpy(ctx->d_tmaps, maps.data(), (size_t)nmaps * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+    return ABUB_OK;
+}
+
+int abub_k1_build_k16(abub_ctx* ctx, int cam) {
+    abub_cam_state& c = ctx->cam[cam];
+    const size_t n = ctx->npix;
+    k1_build_k16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(c.d_sigma, c.d_k16, n);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    return ABUB_OK;
+}
+
+static inline int k1t_wpc(int cols) {
+    const int nw = (cols + T_OW - 1) / T_OW;
+    return nw < T_MAX_WARPS ? nw : T_MAX_WARPS;
+}
+
+// launches the TMA trigger kernel over [slot_first, slot_first+nslots); the caller zeroes the
+// histogram table before and runs k1_fill_bin0_kernel after.
+int abub_k1_launch_trigger_tma(abub_ctx* ctx, int slot_first, int nslots) {
+    const int wpc = k1t_wpc(ctx->cols);
+    const int nw = (ctx->cols + T_OW - 1) / T_OW;
+    const int nxg = (nw + wpc - 1) / wpc;
+    const int nmain = ctx->rows - 4;              // output rows [2, rows-2)
+    const int nstrips = (nmain + T_TH_TARGET - 1) / T_TH_TARGET;
+    const int th = (nmain + nstrips - 1) / nstrips;
+    const size_t smem = 128 + (size_t)wpc * T_S * T_STAGE_BYTES + 1024 + (size_t)wpc * T_S * 8;
+    ABUB_CHECK_CUDA(ctx, cudaFuncSetAttribute(k1_trigger_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const CUtensorMap* maps = reinterpret_cast<const CUtensorMap*>(ctx->d_tmaps);
+    const int per = 65535 / ctx->ncams;
+    for (int s0 = 0; s0 < nslots; s0 += per) {
+        const int ns = (nslots - s0 < per) ? nslots - s0 : per;
+        dim3 grid(nstrips * nxg, ctx->max_frames - 1, ns * ctx->ncams);
+        k1_trigger_tma_kernel<<<grid, 32 * wpc, smem, ctx->stream>>>(
+            maps, maps + ctx->max_slots, ctx->d_nframes, ctx->d_tss, ctx->d_hist, slot_first + s0, ctx->rows,
+            ctx->cols, ctx->ncams, ctx->max_frames, th, nxg);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
+    return ABUB_OK;
+}

@@ -157,3 +157,36 @@ def test_significance_corner_cases(capi):
                 assert t == r.trig and l == r.loc_thres
             for (i, sv) in r.sig:
                 assert sig[i] == sv or (np.isnan(sv) and np.isnan(sig[i])), (tss, i, sv, sig[i])
+
+
+@pytest.mark.parametrize("shape", [(64, 16), (37, 256), (151, 240), (300, 496), (163, 1696), (9, 32)])
+def test_trigger_hist_tma_path(capi, shape):
+    """cols % 16 == 0 takes the TMA-fed trigger kernel (k1_trigger_tma.cu): strips that start
+    and end inside the reflected border rows, partially filled last warp, image-edge lanes,
+    ragged frame counts, saturated sigma, both frame offsets."""
+    import oracle.cv2_oracle as o
+    rows, cols = shape
+    rng = np.random.default_rng(rows * 7 + cols)
+    ncams, nfr = 2, 7
+    with capi.Context(rows, cols, ncams=ncams, max_frames=nfr, max_slots=2) as ctx:
+        for tss in (12, 3):
+            sig = []
+            for c in range(ncams):
+                s = rng.integers(0, 3 + 45 * c, (rows, cols)).astype(np.uint8)
+                sig.append(s)
+                ctx.set_background(c, np.zeros_like(s), s, tss)
+            stacks = {}
+            for slot in range(2):
+                for c in range(ncams):
+                    n = nfr - (slot + c) % 3
+                    base = rng.integers(0, 256, (rows, cols)).astype(np.float32)
+                    fr = np.clip(base[None] + rng.normal(0, 3 + 25 * slot, (n, rows, cols)), 0, 255).astype(np.uint8)
+                    fr[n // 2:, rows // 3: rows // 3 + 6, : min(cols, 9)] = 255      # blob on the left border
+                    fr[n // 2:, -3:, -5:] = 0                                          # and in the bottom-right corner
+                    stacks[(slot, c)] = fr
+                    ctx.event_upload(slot, c, fr)
+            ctx.trigger_hist(0, 2)
+            for (slot, c), fr in stacks.items():
+                H = ctx.trigger_hist_read(slot, c)
+                Href = _oracle_hists(o, fr, sig[c], tss)
+                assert np.array_equal(H[:len(fr)], Href), (shape, tss, slot, c)
