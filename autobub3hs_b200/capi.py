@@ -13,7 +13,7 @@ from typing import List, Optional, Sequence, Tuple
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libabub_cuda.so")
+LIB_PATH = os.environ.get("ABUB_LIB") or os.path.join(_HERE, "libabub_cuda.so")   # ABUB_LIB: kernel-variant sweeps (tools/k1_sweep.sh)
 
 ABUB_MAX_TRACK = 10
 

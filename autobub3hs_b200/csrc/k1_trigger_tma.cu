@@ -49,7 +49,7 @@ constexpr int T_TX_BYTES = T_R * T_BW * 4;                        // bytes one s
 constexpr int T_STAGE_BYTES = ((T_K_OFF + T_R * T_BW * 2 + 127) / 128) * 128;
 constexpr int T_MAX_WARPS = 1;            // one warp per CTA: nothing to wait for at the end of a strip, and every
                                           // TMA operand (ring, barrier, coordinates) lives in uniform registers
-constexpr int T_TH_TARGET = 150;          // output rows per strip
+constexpr int T_TH_TARGET = 350;          // output rows per strip (4 halo rows per strip)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
