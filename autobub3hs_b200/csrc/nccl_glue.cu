@@ -1,0 +1,195 @@
+// NCCL side of the path: the one collective is the all-reduce of the Trainer's exact
+// integer partials; this file adds what a process-per-GPU host needs around it -- communicator set-up
+// through an id file, a barrier, and the exact boundary fix-up (all-gather of the flagged pixels'
+// samples, then the reference's sequential float32 recurrence in global push order).
+// libnccl is resolved with dlopen/dlsym: libabub_cuda.so has no link-time NCCL dependency.
+#include <dlfcn.h>
+#include <unistd.h>
+
+#include <cub/cub.cuh>
+
+#include "abub_internal.cuh"
+
+namespace {
+
+struct NcclId { char internal[128]; };      // ncclUniqueId
+typedef int (*fn_get_id)(NcclId*);
+typedef int (*fn_init_rank)(void**, int, NcclId, int);
+typedef int (*fn_destroy)(void*);
+typedef int (*fn_count)(void*, int*);
+typedef int (*fn_allreduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*fn_allgather)(const void*, void*, size_t, int, void*, cudaStream_t);
+
+void* nccl_sym(const char* name) {
+    static void* handle = nullptr;
+    void* s = dlsym(RTLD_DEFAULT, name);      // already loaded by the host process (e.g. torch)
+    if (s) return s;
+    if (!handle) handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!handle) handle = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    return handle ? dlsym(handle, name) : nullptr;
+}
+
+enum { NCCL_U8 = 1, NCCL_I32 = 2, NCCL_SUM = 0 };
+
+__device__ __forceinline__ void wf_step(float x, float cnt, float& mean, float& m2) {   // Trainer.cpp:185-187
+    const float delta = __fsub_rn(x, mean);
+    mean = __fadd_rn(mean, __fdiv_rn(delta, cnt));
+    m2 = __fadd_rn(m2, __fmul_rn(delta, __fsub_rn(x, mean)));
+}
+
+// samples of the flagged pixels from this rank's kept frames: out[i*stride + f]
+__global__ void gather_flagged_kernel(const uint8_t* const* __restrict__ frames, int n_local, const int* __restrict__ idx,
+                                      int n_flagged, int stride, uint8_t* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_flagged) return;
+    const int p = idx[i];
+    for (int f = 0; f < n_local; f++) out[(size_t)i * stride + f] = frames[f][p];
+}
+
+// sequential float32 recurrence over the ranks' samples in rank order (= global push order)
+__global__ void fixup_gathered_kernel(const uint8_t* __restrict__ all, const int* __restrict__ counts, int world,
+                                      const int* __restrict__ idx, int n_flagged, int stride, int n_total,
+                                      uint8_t* __restrict__ mean_out, uint8_t* __restrict__ sigma_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_flagged) return;
+    float mean = 0.f, m2 = 0.f;
+    int k = 0;
+    for (int r = 0; r < world; r++) {
+        const uint8_t* src = all + ((size_t)r * n_flagged + i) * stride;
+        for (int f = 0; f < counts[r]; f++) wf_step((float)src[f], (float)(++k), mean, m2);
+    }
+    const float var = __fdiv_rn(m2, (float)(n_total - 1));                 // Trainer.cpp:191 (0/0 -> NaN when N == 1)
+    const float sg = __fsqrt_rn(var);
+    const int p = idx[i];
+    sigma_out[p] = (sg == sg) ? (uint8_t)(int)sg : (uint8_t)0;             // (int)NaN is INT_MIN on x86 -> u8 0
+    mean_out[p] = (uint8_t)mean;
+}
+
+}  // namespace
+
+extern "C" int abub_nccl_comm_create(abub_ctx* ctx, const char* id_file, int rank, int world, void** comm) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, id_file && comm && world >= 1 && rank >= 0 && rank < world, "abub_nccl_comm_create");
+    fn_get_id get_id = (fn_get_id)nccl_sym("ncclGetUniqueId");
+    fn_init_rank init_rank = (fn_init_rank)nccl_sym("ncclCommInitRank");
+    if (!get_id || !init_rank) { ctx->err = "libnccl not found"; return ABUB_E_NCCL; }
+    cudaSetDevice(ctx->device);
+    NcclId id;
+    const std::string tmp = std::string(id_file) + ".tmp";
+    if (rank == 0) {
+        if (get_id(&id)) { ctx->err = "ncclGetUniqueId failed"; return ABUB_E_NCCL; }
+        FILE* f = fopen(tmp.c_str(), "wb");
+        if (!f || fwrite(&id, 1, sizeof(id), f) != sizeof(id)) { if (f) fclose(f); ctx->err = "cannot write the NCCL id file"; return ABUB_E_NCCL; }
+        fclose(f);
+        rename(tmp.c_str(), id_file);        // atomic publish
+    } else {
+        bool got = false;
+        for (int t = 0; t < 6000 && !got; t++) {           // up to 10 minutes
+            FILE* f = fopen(id_file, "rb");
+            if (f) { got = fread(&id, 1, sizeof(id), f) == sizeof(id); fclose(f); }
+            if (!got) usleep(100000);
+        }
+        if (!got) { ctx->err = "timed out waiting for the NCCL id file"; return ABUB_E_NCCL; }
+    }
+    void* c = nullptr;
+    const int r = init_rank(&c, world, id, rank);
+    if (r) { ctx->err = "ncclCommInitRank failed with code " + std::to_string(r); return ABUB_E_NCCL; }
+    *comm = c;
+    if (rank == 0) {
+        // every rank has read the id once the communicator exists
+        unlink(id_file);
+    }
+    return ABUB_OK;
+}
+
+extern "C" int abub_nccl_comm_destroy(void* comm) {
+    fn_destroy d = (fn_destroy)nccl_sym("ncclCommDestroy");
+    if (!d || !comm) return ABUB_E_NCCL;
+    return d(comm) ? ABUB_E_NCCL : ABUB_OK;
+}
+
+extern "C" int abub_nccl_barrier(abub_ctx* ctx, void* comm) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, comm != nullptr, "abub_nccl_barrier");
+    fn_allreduce ar = (fn_allreduce)nccl_sym("ncclAllReduce");
+    if (!ar) { ctx->err = "libnccl not found"; return ABUB_E_NCCL; }
+    cudaSetDevice(ctx->device);
+    int* d = reinterpret_cast<int*>(ctx->d_hist_tmp);
+    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d, 0, sizeof(int), ctx->stream));
+    if (ar(d, d, 1, NCCL_I32, NCCL_SUM, comm, ctx->stream)) { ctx->err = "ncclAllReduce (barrier) failed"; return ABUB_E_NCCL; }
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ABUB_OK;
+}
+
+// After abub_train_partials + abub_train_allreduce: planes from the reduced partials, then the flagged
+// pixels are recomputed exactly from every rank's samples.  Result replicated on all ranks.
+extern "C" int abub_train_finish_allreduced(abub_ctx* ctx, int cam, void* comm, uint8_t* mean, uint8_t* sigma,
+                                            int* set_size, int* status, int* n_flagged) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, cam >= 0 && cam < ctx->ncams && comm, "abub_train_finish_allreduced");
+    abub_cam_state& cs = ctx->cam[cam];
+    ABUB_REQUIRE(ctx, cs.d_sum != nullptr, "abub_train_partials not called");
+    fn_count cnt_fn = (fn_count)nccl_sym("ncclCommCount");
+    fn_allgather ag = (fn_allgather)nccl_sym("ncclAllGather");
+    if (!cnt_fn || !ag) { ctx->err = "libnccl not found"; return ABUB_E_NCCL; }
+    cudaSetDevice(ctx->device);
+    int world = 1;
+    if (cnt_fn(comm, &world)) { ctx->err = "ncclCommCount failed"; return ABUB_E_NCCL; }
+    int cnt[4];
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(cnt, cs.d_count, sizeof(cnt), cudaMemcpyDeviceToHost, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int n = cnt[0];
+    if (set_size) *set_size = n;
+    if (n_flagged) *n_flagged = 0;
+    cs.training = false;
+    if (n == 0) { if (status) *status = -7; return ABUB_OK; }
+    int rc = abub_k4_finish_from_partials(ctx, cs.d_sum, cs.d_sumsq, n, cs.d_mean, cs.d_sigma, cs.d_count + 1, cs.d_flag);
+    if (rc) return rc;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(cnt, cs.d_count, sizeof(cnt), cudaMemcpyDeviceToHost, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int F = cnt[1];                      // identical on every rank: flags derive from the reduced partials
+    if (n_flagged) *n_flagged = F;
+    // kept-frame counts of every rank
+    const int n_local = (int)cs.kept.size();
+    int* d_counts = nullptr;
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_counts, (size_t)(world + 1) * sizeof(int)));
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(d_counts + world, &n_local, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    int nr = ag(d_counts + world, d_counts, 1, NCCL_I32, comm, ctx->stream);
+    std::vector<int> counts(world);
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(counts.data(), d_counts, world * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (nr) { cudaFree(d_counts); ctx->err = "ncclAllGather(counts) failed"; return ABUB_E_NCCL; }
+    if (F > 0) {
+        int stride = 1;
+        for (int c : counts) stride = c > stride ? c : stride;
+        stride = (stride + 15) & ~15;
+        int* d_idx = nullptr; int* d_nsel = nullptr; void* d_tmp = nullptr; uint8_t* d_loc = nullptr; uint8_t* d_all = nullptr;
+        size_t tmp_bytes = 0;
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_idx, (size_t)F * sizeof(int)));
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_nsel, sizeof(int)));
+        cub::CountingInputIterator<int> it(0);
+        cub::DeviceSelect::Flagged(nullptr, tmp_bytes, it, cs.d_flag, d_idx, d_nsel, (int)ctx->npix, ctx->stream);
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_tmp, tmp_bytes));
+        cub::DeviceSelect::Flagged(d_tmp, tmp_bytes, it, cs.d_flag, d_idx, d_nsel, (int)ctx->npix, ctx->stream);
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_loc, (size_t)F * stride));
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_all, (size_t)world * F * stride));
+        ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_loc, 0, (size_t)F * stride, ctx->stream));
+        gather_flagged_kernel<<<(F + 127) / 128, 128, 0, ctx->stream>>>(cs.d_table, n_local, d_idx, F, stride, d_loc);
+        nr = ag(d_loc, d_all, (size_t)F * stride, NCCL_U8, comm, ctx->stream);
+        if (!nr)
+            fixup_gathered_kernel<<<(F + 127) / 128, 128, 0, ctx->stream>>>(d_all, d_counts, world, d_idx, F, stride, n,
+                                                                             cs.d_mean, cs.d_sigma);
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        cudaFree(d_idx); cudaFree(d_nsel); cudaFree(d_tmp); cudaFree(d_loc); cudaFree(d_all);
+        if (nr) { cudaFree(d_counts); ctx->err = "ncclAllGather(samples) failed"; return ABUB_E_NCCL; }
+        ABUB_CHECK_CUDA(ctx, e);
+    }
+    cudaFree(d_counts);
+    cs.training_set_size = n;
+    cs.has_background = true;
+    if (status) *status = 0;
+    if (mean) ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(mean, cs.d_mean, ctx->npix, cudaMemcpyDeviceToHost, ctx->stream));
+    if (sigma) ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(sigma, cs.d_sigma, ctx->npix, cudaMemcpyDeviceToHost, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ABUB_OK;
+}

@@ -1,0 +1,82 @@
+// AbubDevice -- the one piece of the host side that has no counterpart in the reference: it owns
+// the abub_ctx (libabub_cuda.so, include/abub_cuda.h) that Trainer / AnalyzerUnit / L3Localizer
+// call instead of OpenCV, and the event slots in HBM.
+//
+//   * Configure() is called once by main (or a test) with the device ordinal and capacities; the
+//     context itself is created when the first frame tells the image size.
+//   * An event occupies one slot ([cam][frame][rows*cols] in HBM).  Analyzers of the same event share
+//     the slot (AcquireSlot is reference counted by event key); each camera's frames are decoded
+//     straight into the slot's pinned staging buffer and sent with cudaMemcpyAsync.
+//   * PrefetchEvents() lets the driver loop stage a whole batch of events (decode on every host core,
+//     one K1 launch for the batch) before the per-camera objects are built; analyzers then find their
+//     frames and histograms resident.
+//   * The ctx is not internally locked (one CUDA stream): every C-ABI call goes through lock().
+#ifndef ABUB_DEVICE_HPP
+#define ABUB_DEVICE_HPP
+
+#include <map>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/abub_cuda.h"
+#include "Parser.hpp"
+
+struct AbubError : public std::runtime_error {
+    explicit AbubError(const std::string& what) : std::runtime_error(what) {}
+};
+
+struct AbubSlot {
+    std::string key;                 // "<run folder>|<event id>"
+    int refs = 0;
+    bool loaded[8] = {false};        // frames of this camera are in HBM
+    int nframes[8] = {0};
+    std::vector<int> bad[8];         // frame indices that failed to load/decode
+};
+
+class AbubDevice {
+public:
+    static AbubDevice& Get();
+
+    void Configure(int device, int ncams, int max_frames, int max_slots);
+    bool configured() const { return ncams_ > 0; }
+    int ncams() const { return ncams_; }
+    int max_frames() const { return max_frames_; }
+    int max_slots() const { return max_slots_; }
+    int rows() const { return rows_; }
+    int cols() const { return cols_; }
+
+    // Creates the context on first use (rows x cols from the first decoded frame); throws AbubError
+    // if a later frame has another size or the device cannot be opened.
+    abub_ctx* Context(int rows, int cols);
+    abub_ctx* ctx() const { return ctx_; }
+    std::recursive_mutex& lock() { return mu_; }
+    void Check(int rc, const char* what);       // throws AbubError(abub_last_error) when rc != 0
+
+    // Slot of an event (allocated on first request, freed when the last holder releases it).
+    int AcquireSlot(const std::string& key);
+    void ReleaseSlot(const std::string& key);
+    AbubSlot& slot(int s) { return slots_[s]; }
+
+    // Decodes (in parallel over frames) and uploads the frames of one camera of an event into its slot;
+    // no-op when already resident.  Frame names as listed by Parser::ParseAndSortFramesInFolder.
+    void LoadCamera(int slot, int cam, Parser* parser, const std::string& event_id,
+                    const std::vector<std::string>& frames);
+    // Stages a batch: for every event all cameras are loaded, then one K1 launch covers the batch.
+    // keys[i] is the slot key of events[i] (the one its analyzers use).  Returns the slots; every key holds one
+    // reference that the caller releases with ReleaseSlot when the event is done.
+    std::vector<int> PrefetchEvents(Parser* parser, const std::vector<std::string>& keys, const std::vector<std::string>& events);
+
+    void Shutdown();
+
+private:
+    AbubDevice() {}
+    int device_ = 0, ncams_ = 0, max_frames_ = 0, max_slots_ = 0, rows_ = 0, cols_ = 0;
+    abub_ctx* ctx_ = nullptr;
+    std::recursive_mutex mu_;
+    std::vector<AbubSlot> slots_;
+    std::map<std::string, int> by_key_;
+};
+
+#endif

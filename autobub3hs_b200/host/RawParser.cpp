@@ -1,0 +1,83 @@
+// RawParser (reference: ParseFolder/RawParser.cpp:28-157) on std::filesystem / std::regex instead of Boost.
+#include "RawParser.hpp"
+
+#include <algorithm>
+#include <filesystem>
+#include <regex>
+
+#include "ImageCodec.hpp"
+
+namespace fs = std::filesystem;
+
+RawParser::RawParser(std::string RunFolder, std::string ImageFolder, std::string ImageFormat)
+    : Parser(RunFolder, ImageFolder, ImageFormat) {}
+RawParser::~RawParser() {}
+
+RawParser* RawParser::clone() { return new RawParser(RunFolder, ImageFolder, ImageFormat); }
+
+std::string RawParser::FramePath(const std::string& EventID, const std::string& FrameName) const {
+    // boost::filesystem operator/ : an absolute right-hand side ("/Images/") replaces the path in newer
+    // Boost but appends in the Boost the reference was written against; the run layout needs "append".
+    std::string p = RunFolder;
+    auto join = [&p](const std::string& part) {
+        size_t a = 0;
+        while (a < part.size() && part[a] == '/') a++;
+        if (!p.empty() && p.back() != '/') p += '/';
+        p += part.substr(a);
+    };
+    join(EventID);
+    join(ImageFolder);
+    join(FrameName);
+    return p;
+}
+
+int RawParser::GetImageBytes(std::string EventID, std::string FrameName, std::vector<uint8_t>& Bytes) {
+    return abubcodec::read_file(FramePath(EventID, FrameName), Bytes) ? 1 : 0;
+}
+
+// RawParser.cpp:34-47: cv::imread(path, 0); returns !Image.empty()
+int RawParser::GetImage(std::string EventID, std::string FrameName, Image8& Image) {
+    std::vector<uint8_t> bytes;
+    Image.release();
+    if (!abubcodec::read_file(FramePath(EventID, FrameName), bytes)) return 0;
+    abubcodec::decode(bytes.data(), bytes.size(), Image);
+    return !Image.empty();
+}
+
+// RawParser.cpp:52-86: names in EventFolder containing camera_out_name, hidden files skipped
+void RawParser::GetFileLists(const char* EventFolder, std::vector<std::string>& FileList, const char* camera_out_name) {
+    std::error_code ec;
+    fs::directory_iterator it(EventFolder, ec);
+    if (ec) { StatusCode = 1; return; }
+    for (const auto& e : it) {
+        const std::string name = e.path().filename().string();
+        if (name.empty() || name[0] == '.') continue;
+        if (name.find(camera_out_name) != std::string::npos) FileList.push_back(name);
+    }
+}
+
+// RawParser.cpp:89-137: every sub-directory of the run folder is an event
+void RawParser::GetEventDirLists(std::vector<std::string>& EventList) {
+    std::error_code ec;
+    fs::directory_iterator it(RunFolder, ec);
+    if (ec) { StatusCode = 1; return; }
+    for (const auto& e : it) {
+        const std::string name = e.path().filename().string();
+        if (name.empty() || name[0] == '.') continue;
+        std::error_code ec2;
+        if (fs::is_directory(e.path(), ec2)) EventList.push_back(name);
+    }
+}
+
+// RawParser.cpp:139-157: full-path regex "^.*cam<N>.*(png|bmp)", lexicographic sort of the file names
+void RawParser::ParseAndSortFramesInFolder(std::string EventID, int Camera, std::vector<std::string>& Contents) {
+    std::string dir = FramePath(EventID, "");
+    const std::regex re("^.*cam" + std::to_string(Camera) + ".*(png|bmp)");
+    std::error_code ec;
+    if (fs::exists(dir, ec) && fs::is_directory(dir, ec)) {
+        for (const auto& x : fs::directory_iterator(dir, ec)) {
+            if (std::regex_match(x.path().string(), re)) Contents.push_back(x.path().filename().string());
+        }
+        std::sort(Contents.begin(), Contents.end());
+    }
+}

@@ -135,6 +135,22 @@ int abub_train_allreduce(abub_ctx* ctx, int cam, void* nccl_comm);
 int abub_train_finish_partials(abub_ctx* ctx, int cam, uint8_t* mean, uint8_t* sigma,
                                int* set_size, int* status, int* n_flagged);
 
+/* Exact multi-rank finish (after abub_train_partials + abub_train_allreduce on every rank): planes from the
+ * reduced partials, then the flagged pixels are recomputed with the reference's sequential float32
+ * recurrence from an ncclAllGather of their samples, ranks in order (= push order when ranks own
+ * contiguous event ranges).  The result is bit-identical to abub_train_finish on one GPU and is
+ * replicated on every rank. */
+int abub_train_finish_allreduced(abub_ctx* ctx, int cam, void* nccl_comm, uint8_t* mean, uint8_t* sigma,
+                                 int* set_size, int* status, int* n_flagged);
+
+/* ---- NCCL plumbing for a process-per-GPU host (nothing in the reference: it is one OpenMP process) ----- */
+/* ncclCommInitRank with the unique id published by rank 0 through `id_file` (written atomically, removed by
+ * rank 0 once the communicator exists).  *comm receives the ncclComm_t. */
+int abub_nccl_comm_create(abub_ctx* ctx, const char* id_file, int rank, int world, void** comm);
+int abub_nccl_comm_destroy(void* comm);
+/* all ranks wait for each other (one-int all-reduce on the ctx stream + stream synchronise) */
+int abub_nccl_barrier(abub_ctx* ctx, void* comm);
+
 /* ---- localizer: L3Localizer::LocalizeOMatic (L3Localizer.cpp:881-968) ----------- */
 /* For the trigger frame (k=0: CalculateInitialBubbleParams :215-290, frames `trig` and
  * `pre_trig`, TOZERO at loc_thres, Otsu, external contours) and the post-trigger

@@ -1,0 +1,112 @@
+"""The drop-in binary: abub3hs (host C++ class surface over libabub_cuda.so) on synthetic runs written
+to disk, its abub3hs_<run>.txt compared byte for byte with the oracle's text."""
+import json
+import os
+import subprocess
+import zipfile
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+HOST = os.path.join(ROOT, "autobub3hs_b200", "host")
+GOLD = os.path.join(HERE, "golden")
+
+
+@pytest.fixture(scope="module")
+def abub3hs():
+    from autobub3hs_b200 import build
+    build.build()
+    subprocess.check_call(["make", "-s", "-C", HOST])
+    return os.path.join(HOST, "abub3hs")
+
+
+def _run(abub3hs, data_dir, out_dir, mask_dir, extra=()):
+    os.makedirs(out_dir, exist_ok=True)
+    cmd = [abub3hs, "-D", "40l-19", "-d", data_dir, "-r", "20210101_0", "-o", out_dir, "-c", mask_dir, *extra]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    return open(os.path.join(out_dir, "abub3hs_20210101_0.txt")).read()
+
+
+def test_golden_run_raw(abub3hs, tmp_path):
+    """The committed golden run (all event classes, 132x212: generic-pitch kernels) from BMP files."""
+    from autobub3hs_b200 import synth
+    meta = json.load(open(os.path.join(GOLD, "e2e_small_run.json")))
+    run = synth.make_run(8, meta["classes"], rows=meta["rows"], cols=meta["cols"], seed=meta["seed"])
+    synth.write_run(run, str(tmp_path / "data"), str(tmp_path / "masks"))
+    gold = open(os.path.join(GOLD, "e2e_small_run.txt")).read()
+    for batch in ("1", "3", "8"):
+        text = _run(abub3hs, str(tmp_path / "data"), str(tmp_path / ("out" + batch)), str(tmp_path / "masks"), ["--batch", batch])
+        assert text == gold, "batch " + batch
+    # -e: a single event index (AutoBubStart3.cpp:350)
+    text = _run(abub3hs, str(tmp_path / "data"), str(tmp_path / "out_e"), str(tmp_path / "masks"), ["-e", "1"])
+    import oracle.cv2_oracle as o
+    hdr = o.write_header()
+    rows = [l for l in gold[len(hdr):].splitlines(True) if l.split("  ")[1] == "1"]
+    assert text == hdr + "".join(rows)
+
+
+@pytest.fixture(scope="module")
+def tma_run():
+    """208 columns (multiple of 16): the TMA-fed trigger kernel is on the path."""
+    from autobub3hs_b200 import synth
+    import oracle.cv2_oracle as o
+    run = synth.make_run(6, ["normal", "multi", "notrigger", "flicker", "short5", "highnoise"], rows=136, cols=208, seed=21)
+    trained = o.train_all(run.events, 4)
+    text, _ = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks)
+    return run, o.write_header() + text
+
+
+def test_tma_pitch_raw_png_and_zip(abub3hs, tma_run, tmp_path):
+    import cv2
+    from autobub3hs_b200 import synth
+    run, gold = tma_run
+    synth.write_run(run, str(tmp_path / "data"), str(tmp_path / "masks"))
+    assert _run(abub3hs, str(tmp_path / "data"), str(tmp_path / "out_bmp"), str(tmp_path / "masks")) == gold
+    # the same run as PNG files inside a zip archive (-z)
+    zdir = tmp_path / "zdata"
+    zdir.mkdir()
+    with zipfile.ZipFile(str(zdir / "20210101_0.zip"), "w", zipfile.ZIP_STORED) as z:
+        z.writestr("20210101_0/", "")
+        for evn, ev in zip(run.event_numbers, run.events):
+            z.writestr(f"20210101_0/{evn}/", "")
+            z.writestr(f"20210101_0/{evn}/Images/", "")
+            for c, stack in enumerate(ev):
+                for f in range(len(stack)):
+                    ok, buf = cv2.imencode(".png", stack[f])
+                    z.writestr(f"20210101_0/{evn}/Images/cam{c}_image{run.frame_offset + f}.png", buf.tobytes())
+    assert _run(abub3hs, str(zdir), str(tmp_path / "out_zip"), str(tmp_path / "masks"), ["-z", "--batch", "4"]) == gold
+
+
+def test_unreadable_run_is_minus5_and_bad_training_is_minus7(abub3hs, tmp_path):
+    from autobub3hs_b200 import synth
+    import oracle.cv2_oracle as o
+    out = tmp_path / "out"
+    out.mkdir()
+    r = subprocess.run([abub3hs, "-D", "40l-19", "-z", "-d", str(tmp_path / "nowhere"), "-r", "20210101_0", "-o", str(out)],
+                       capture_output=True, text=True)
+    assert r.returncode == (-5) % 256
+    text = open(out / "abub3hs_20210101_0.txt").read()
+    exp = o.write_header() + o.write_camera_output("20210101_0", [o.CameraOutput(-5, 0, -1) for _ in range(4)], 30)
+    assert text == exp
+    # every event fails the Trainer gate (frame 1 differs wildly from frame 0) -> -7 rows for all events
+    rng = np.random.default_rng(0)
+    data = tmp_path / "data"
+    for ev in range(2):
+        d = data / "20210101_0" / str(ev) / "Images"
+        d.mkdir(parents=True)
+        for c in range(4):
+            for f in range(6):
+                synth.write_bmp8(str(d / f"cam{c}_image{30 + f}.bmp"), rng.integers(0, 256, (48, 64)).astype(np.uint8))
+    out7 = tmp_path / "out7"
+    out7.mkdir()
+    r = subprocess.run([abub3hs, "-D", "40l-19", "-d", str(data), "-r", "20210101_0", "-o", str(out7)], capture_output=True, text=True)
+    assert r.returncode == (-7) % 256, r.stdout[-1500:]
+    exp = o.write_header()
+    for ev in range(2):
+        exp += o.write_camera_output("20210101_0", [o.CameraOutput(-7, 0, ev) for _ in range(4)], 30)
+    assert open(out7 / "abub3hs_20210101_0.txt").read() == exp
