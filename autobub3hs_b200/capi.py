@@ -24,7 +24,8 @@ EXPORTS = [
     "abub_event_set_nframes",
     "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_hist_write", "abub_trigger_scan", "abub_trigger_results", "abub_trigger",
     "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_finish",
-    "abub_train_partials", "abub_train_allreduce", "abub_train_finish_partials",
+    "abub_train_partials", "abub_train_allreduce", "abub_train_finish_partials", "abub_train_finish_allreduced",
+    "abub_nccl_comm_create", "abub_nccl_comm_destroy", "abub_nccl_barrier",
     "abub_localize", "abub_localize_batch", "abub_localize_binary", "abub_process_frame",
 ]
 
@@ -87,6 +88,10 @@ def load() -> C.CDLL:
     lib.abub_train_partials.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     lib.abub_train_allreduce.argtypes = [vp, C.c_int, vp]
     lib.abub_train_finish_partials.argtypes = [vp, C.c_int, u8p, u8p, ip, ip, ip]
+    lib.abub_train_finish_allreduced.argtypes = [vp, C.c_int, vp, u8p, u8p, ip, ip, ip]
+    lib.abub_nccl_comm_create.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.POINTER(vp)]
+    lib.abub_nccl_comm_destroy.argtypes = [vp]
+    lib.abub_nccl_barrier.argtypes = [vp, vp]
     lib.abub_localize.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(Blob), C.c_int, ip]
     lib.abub_localize_batch.argtypes = [vp, C.POINTER(LocItem), C.c_int, C.POINTER(Blob), C.c_int, ip, ip]
     lib.abub_localize_binary.argtypes = [vp, C.c_int, u8p]
@@ -256,6 +261,29 @@ class Context:
         n, st, nf = C.c_int(), C.c_int(), C.c_int()
         self._ck(self.lib.abub_train_finish_partials(self.h, cam, _p(mean), _p(sigma), C.byref(n), C.byref(st),
                                                      C.byref(nf)), "abub_train_finish_partials")
+        return mean, sigma, n.value, st.value, nf.value
+
+    # ---- multi-GPU (one process per GPU) ----
+    def nccl_comm_create(self, id_file: str, rank: int, world: int) -> int:
+        c = C.c_void_p()
+        self._ck(self.lib.abub_nccl_comm_create(self.h, id_file.encode(), rank, world, C.byref(c)), "abub_nccl_comm_create")
+        return int(c.value)
+
+    def nccl_comm_destroy(self, comm: int) -> None:
+        self.lib.abub_nccl_comm_destroy(C.c_void_p(comm))
+
+    def nccl_barrier(self, comm: int) -> None:
+        self._ck(self.lib.abub_nccl_barrier(self.h, C.c_void_p(comm)), "abub_nccl_barrier")
+
+    def train_allreduce(self, cam: int, comm: int) -> None:
+        self._ck(self.lib.abub_train_allreduce(self.h, cam, C.c_void_p(comm)), "abub_train_allreduce")
+
+    def train_finish_allreduced(self, cam: int, comm: int):
+        mean = np.zeros((self.rows, self.cols), np.uint8)
+        sigma = np.zeros((self.rows, self.cols), np.uint8)
+        n, st, nf = C.c_int(), C.c_int(), C.c_int()
+        self._ck(self.lib.abub_train_finish_allreduced(self.h, cam, C.c_void_p(comm), _p(mean), _p(sigma), C.byref(n),
+                                                       C.byref(st), C.byref(nf)), "abub_train_finish_allreduced")
         return mean, sigma, n.value, st.value, nf.value
 
     # ---- localizer ----

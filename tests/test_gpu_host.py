@@ -110,3 +110,31 @@ def test_unreadable_run_is_minus5_and_bad_training_is_minus7(abub3hs, tmp_path):
     for ev in range(2):
         exp += o.write_camera_output("20210101_0", [o.CameraOutput(-7, 0, ev) for _ in range(4)], 30)
     assert open(out7 / "abub3hs_20210101_0.txt").read() == exp
+
+
+def _ngpus():
+    try:
+        out = subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True).stdout
+        return sum(1 for l in out.splitlines() if l.startswith("GPU "))
+    except Exception:
+        return 0
+
+
+@pytest.mark.skipif(_ngpus() < 2, reason="needs 2 GPUs")
+def test_two_ranks_same_text(abub3hs, tma_run, tmp_path):
+    """One process per GPU (--rank/--world): contiguous event ranges, Trainer partials all-reduced over
+    NCCL with the exact fix-up, rank-ordered concatenation of the rows == the single-process file."""
+    from autobub3hs_b200 import synth
+    run, gold = tma_run
+    synth.write_run(run, str(tmp_path / "data"), str(tmp_path / "masks"))
+    out = tmp_path / "out2"
+    out.mkdir()
+    procs = []
+    for r in range(2):
+        cmd = [abub3hs, "-D", "40l-19", "-d", str(tmp_path / "data"), "-r", "20210101_0", "-o", str(out), "-c",
+               str(tmp_path / "masks"), "--rank", str(r), "--world", "2", "--batch", "2"]
+        procs.append(subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    logs = [p.communicate(timeout=600)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), "\n".join(l[-1500:] for l in logs)
+    assert open(out / "abub3hs_20210101_0.txt").read() == gold
+    assert not [f for f in os.listdir(out) if "rank" in f or "ncclid" in f]
