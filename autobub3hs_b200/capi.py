@@ -22,7 +22,7 @@ EXPORTS = [
     "abub_set_background", "abub_set_background_from_training",
     "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_device_ptr",
     "abub_event_set_nframes",
-    "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_hist_write", "abub_trigger_scan", "abub_trigger_results", "abub_trigger",
+    "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_hist_write", "abub_trigger_scan", "abub_trigger_results", "abub_trigger", "abub_trigger_stream",
     "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_finish",
     "abub_train_partials", "abub_train_allreduce", "abub_train_finish_partials", "abub_train_finish_allreduced",
     "abub_nccl_comm_create", "abub_nccl_comm_destroy", "abub_nccl_barrier",
@@ -81,6 +81,7 @@ def load() -> C.CDLL:
     lib.abub_trigger_scan.argtypes = [vp, C.c_int, C.c_int, vp]
     lib.abub_trigger_results.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp]
     lib.abub_trigger.argtypes = [vp, C.c_int, C.c_int, C.c_int, ip, ip, ip, vp]
+    lib.abub_trigger_stream.argtypes = [vp, C.c_int, C.c_int, ip, C.c_int, vp, vp, vp, vp]
     lib.abub_train_begin.argtypes = [vp, C.c_int]
     lib.abub_train_add_event.argtypes = [vp, C.c_int, u8p, C.POINTER(C.c_float), ip]
     lib.abub_train_add_slot.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float), ip]
@@ -262,6 +263,16 @@ class Context:
         self._ck(self.lib.abub_train_finish_partials(self.h, cam, _p(mean), _p(sigma), C.byref(n), C.byref(st),
                                                      C.byref(nf)), "abub_train_finish_partials")
         return mean, sigma, n.value, st.value, nf.value
+
+    def trigger_stream(self, slot_first: int, nslots: int, nframes, chunk_frames: int = 4):
+        """Streamed FindTriggerFrame from the pinned staging buffers; returns trig, status, loc_thres, frames_sent
+        as [nslots, ncams] arrays."""
+        n = nslots * self.ncams
+        nf = (C.c_int * n)(*[int(v) for v in np.asarray(nframes).ravel()])
+        out = [np.zeros((nslots, self.ncams), np.int32) for _ in range(4)]
+        self._ck(self.lib.abub_trigger_stream(self.h, slot_first, nslots, nf, chunk_frames, *[_p(o) for o in out]),
+                 "abub_trigger_stream")
+        return tuple(out)
 
     # ---- multi-GPU (one process per GPU) ----
     def nccl_comm_create(self, id_file: str, rank: int, world: int) -> int:

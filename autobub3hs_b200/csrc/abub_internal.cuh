@@ -54,6 +54,7 @@ struct abub_ctx {
     uint32_t* d_hist = nullptr;     // [slot][cam][frame][256]
     int*      d_nframes = nullptr;  // [slot][cam]
     int*      d_start = nullptr;    // [slot][cam]
+    int*      d_avail = nullptr;    // [slot][cam] frames resident so far (abub_trigger_stream)
     int*      d_trig = nullptr;     // [slot][cam] x {trig,status,loc_thres,scanned}
     double*   d_sig = nullptr;      // [slot][cam][frame]
     int*      d_tss = nullptr;      // [cam] TrainingSetSize
@@ -87,15 +88,21 @@ struct abub_ctx {
 // K1 (k1_processframe.cu)
 int abub_k1_build_k32(abub_ctx* ctx, int cam);
 int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots);
+int abub_k1_launch_trigger_range(abub_ctx* ctx, int slot_first, int nslots, int j_first, int j_last, const int* d_limit,
+                                 bool zero_hist);
 int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b, const uint32_t* d_k32,
                           uint8_t* d_out, uint32_t* d_hist, int tozero_thres);
 // K1 TMA trigger path (k1_trigger_tma.cu)
 bool abub_k1_tma_supported(const abub_ctx* ctx);
 int abub_k1_tma_init(abub_ctx* ctx);
 int abub_k1_build_k16(abub_ctx* ctx, int cam);
-int abub_k1_launch_trigger_tma(abub_ctx* ctx, int slot_first, int nslots);
+int abub_k1_launch_trigger_tma(abub_ctx* ctx, int slot_first, int nslots, int j_first, int j_last, const int* d_limit);
 // K2 (k2_trigger_scan.cu)
 int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots);
+// streamed form: d_avail[slot*ncams+cam] frames are resident; a search that needs a frame beyond them reports
+// ABUB_STATUS_PENDING
+int abub_k2_launch_avail(abub_ctx* ctx, int slot_first, int nslots, const int* d_avail);
+#define ABUB_STATUS_PENDING (-100)
 // K3/K4 (k34_trainer.cu)
 int abub_k3_gate_hist16(abub_ctx* ctx, const uint8_t* d_f0, const uint8_t* d_f1, uint32_t* d_hist16);
 int abub_k4_welford(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint8_t* d_mean, uint8_t* d_sigma);

@@ -43,6 +43,7 @@ extern "C" int abub_ctx_create(int device, int rows, int cols, int ncams, int ma
     ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_hist, sc * max_frames * 256 * sizeof(uint32_t)));
     ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_nframes, sc * sizeof(int)));
     ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_start, sc * sizeof(int)));
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_avail, sc * sizeof(int)));
     ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_trig, sc * 4 * sizeof(int)));
     ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_sig, sc * max_frames * sizeof(double)));
     ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_tss, ABUB_MAX_CAMS * sizeof(int)));
@@ -85,7 +86,7 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
         cudaFree(s.d_frames);
         if (s.h_pinned) cudaFreeHost(s.h_pinned);
     }
-    cudaFree(ctx->d_hist); cudaFree(ctx->d_nframes); cudaFree(ctx->d_start); cudaFree(ctx->d_trig);
+    cudaFree(ctx->d_hist); cudaFree(ctx->d_nframes); cudaFree(ctx->d_start); cudaFree(ctx->d_avail); cudaFree(ctx->d_trig);
     cudaFree(ctx->d_sig); cudaFree(ctx->d_tss); cudaFree(ctx->d_k32_ptrs); cudaFree(ctx->d_slot_ptrs);
     for (int i = 0; i < 4; i++) cudaFree(ctx->d_tmp8[i]);
     cudaFree(ctx->d_hist_tmp);
@@ -311,6 +312,93 @@ extern "C" int abub_trigger(abub_ctx* ctx, int slot, int cam, int start_frame, i
     if (status) *status = s[cam];
     if (loc_thres) *loc_thres = l[cam];
     if (sig) memcpy(sig, sg.data() + (size_t)cam * ctx->max_frames, ctx->max_frames * sizeof(double));
+    return ABUB_OK;
+}
+
+// Streamed FindTriggerFrame: the frames wait in the slots' pinned staging buffers and are sent `chunk_frames` at a
+// time; after every chunk K1 runs on the new frame pairs and K2 on what is resident, and a camera whose search is
+// decided receives no further frames -- the device-side form of the reference reading frames one by one and
+// stopping at the trigger (AnalyzerUnit.cpp:191-213: GetImage inside the loop, early exit at :297-300).
+extern "C" int abub_trigger_stream(abub_ctx* ctx, int slot_first, int nslots, const int* nframes, int chunk_frames,
+                                   int* trig, int* status, int* loc_thres, int* frames_sent) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot_first >= 0 && nslots >= 1 && slot_first + nslots <= ctx->max_slots && nframes, "slot range");
+    ABUB_REQUIRE(ctx, chunk_frames >= 1, "chunk_frames");
+    int rc = require_backgrounds(ctx);
+    if (rc) return rc;
+    cudaSetDevice(ctx->device);
+    const int nc = ctx->ncams;
+    const size_t n = (size_t)nslots * nc;
+    std::vector<int> nf(n), sent(n, 0), avail(n, 0), res_t(n, 0), res_s(n, -3), res_l(n, -1), start(n, 1);
+    std::vector<char> done(n, 0);
+    int nf_max = 0;
+    for (int s = 0; s < nslots; s++) {
+        abub_slot_state& st = ctx->slots[slot_first + s];
+        ABUB_REQUIRE(ctx, st.h_pinned != nullptr, "slot has no pinned buffer (call abub_pinned_acquire)");
+        for (int c = 0; c < nc; c++) {
+            const int v = nframes[s * nc + c];
+            ABUB_REQUIRE(ctx, v >= 0 && v <= ctx->max_frames, "nframes out of range");
+            nf[s * nc + c] = st.nframes[c] = v;
+            if (v < 5) { done[s * nc + c] = 1; res_s[s * nc + c] = -9; }          // AnalyzerUnit.cpp:122-126
+            else if (v > nf_max) nf_max = v;
+        }
+        st.hist_valid = false;
+    }
+    int* d_nf = ctx->d_nframes + (size_t)slot_first * nc;
+    int* d_av = ctx->d_avail + (size_t)slot_first * nc;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(d_nf, nf.data(), n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_start + (size_t)slot_first * nc, start.data(), n * sizeof(int),
+                                         cudaMemcpyHostToDevice, ctx->stream));
+    const size_t hist_n = n * ctx->max_frames * 256;
+    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(ctx->d_hist + (size_t)slot_first * nc * ctx->max_frames * 256, 0,
+                                         hist_n * sizeof(uint32_t), ctx->stream));
+    std::vector<int> raw(n * 4);
+    for (int lo = 0; lo < nf_max; lo += chunk_frames) {
+        const int hi = lo + chunk_frames < nf_max ? lo + chunk_frames : nf_max;
+        bool any = false;
+        for (int s = 0; s < nslots; s++) {
+            abub_slot_state& st = ctx->slots[slot_first + s];
+            for (int c = 0; c < nc; c++) {
+                const size_t i = (size_t)s * nc + c;
+                avail[i] = 0;
+                if (done[i]) continue;
+                any = true;
+                const int upto = hi < nf[i] ? hi : nf[i];
+                if (upto > sent[i]) {
+                    const size_t off = ((size_t)c * ctx->max_frames + sent[i]) * ctx->npix;
+                    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(st.d_frames + off, st.h_pinned + off, (size_t)(upto - sent[i]) * ctx->npix,
+                                                         cudaMemcpyHostToDevice, ctx->stream));
+                    sent[i] = upto;
+                }
+                avail[i] = sent[i];
+            }
+        }
+        if (!any) break;
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(d_av, avail.data(), n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        rc = abub_k1_launch_trigger_range(ctx, slot_first, nslots, lo, hi, ctx->d_avail, false);
+        if (rc) return rc;
+        rc = abub_k2_launch_avail(ctx, slot_first, nslots, ctx->d_avail);
+        if (rc) return rc;
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(raw.data(), ctx->d_trig + (size_t)slot_first * nc * 4, n * 4 * sizeof(int),
+                                             cudaMemcpyDeviceToHost, ctx->stream));
+        ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        for (size_t i = 0; i < n; i++) {
+            if (done[i] || raw[i * 4 + 1] == ABUB_STATUS_PENDING) continue;
+            done[i] = 1;
+            res_t[i] = raw[i * 4 + 0]; res_s[i] = raw[i * 4 + 1]; res_l[i] = raw[i * 4 + 2];
+        }
+    }
+    // leave the result table as abub_trigger_results expects it
+    for (size_t i = 0; i < n; i++) { raw[i * 4] = res_t[i]; raw[i * 4 + 1] = res_s[i]; raw[i * 4 + 2] = res_l[i]; raw[i * 4 + 3] = sent[i]; }
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_trig + (size_t)slot_first * nc * 4, raw.data(), n * 4 * sizeof(int),
+                                         cudaMemcpyHostToDevice, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (size_t i = 0; i < n; i++) {
+        if (trig) trig[i] = res_t[i];
+        if (status) status[i] = res_s[i];
+        if (loc_thres) loc_thres[i] = res_l[i];
+        if (frames_sent) frames_sent[i] = sent[i];
+    }
     return ABUB_OK;
 }
 

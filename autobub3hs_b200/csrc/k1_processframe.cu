@@ -337,7 +337,7 @@ constexpr int K1_TH_TARGET = 105;   // output rows per strip (1050 = 10 x 105): 
 __global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_trigger_kernel(uint8_t* const* __restrict__ slot_ptrs, const int* __restrict__ nframes,
                                   const int* __restrict__ tss, uint32_t* const* __restrict__ k32_ptrs,
                                   uint32_t* __restrict__ hist, int slot_first, int rows, int cols,
-                                  int ncams, int max_frames, int th, int nxg, int border_only) {
+                                  int ncams, int max_frames, int th, int nxg, int border_only, int j_first) {
     extern __shared__ __align__(16) uint32_t smem[];
     uint32_t* sh_hist = smem;                       // 256
     const int warp = threadIdx.x >> 5;
@@ -345,7 +345,7 @@ __global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_trigger_kernel(uint8_t* 
     const int rel = blockIdx.z;
     const int slot = slot_first + rel / ncams;
     const int cam = rel % ncams;
-    const int j = blockIdx.y + 1;
+    const int j = blockIdx.y + j_first;
     const int nf = nframes[slot * ncams + cam];
     if (j >= nf) return;
     const int d = (tss[cam] < 6) ? 1 : 2;           // twoFrameOffset, AnalyzerUnit.cpp:182-188
@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_trigger_kernel(uint8_t* 
 
 // bin 0 = rows*cols - sum(bins 1..255); one warp per (slot,cam,j)
 __global__ void k1_fill_bin0_kernel(uint32_t* __restrict__ hist, const int* __restrict__ nframes, int slot_first,
-                                    int nslots, int ncams, int max_frames, uint32_t npix) {
+                                    int nslots, int ncams, int max_frames, uint32_t npix, int j_first, int j_last) {
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     const int total = nslots * ncams * max_frames;
@@ -379,7 +379,7 @@ __global__ void k1_fill_bin0_kernel(uint32_t* __restrict__ hist, const int* __re
     const int j = w % max_frames;
     const int sc = w / max_frames;
     const int slot = slot_first + sc / ncams, cam = sc % ncams;
-    if (j < 1 || j >= nframes[slot * ncams + cam]) return;
+    if (j < j_first || j >= j_last || j >= nframes[slot * ncams + cam]) return;
     uint32_t* H = hist + (((size_t)slot * ncams + cam) * max_frames + j) * 256;
     uint32_t s = 0;
     for (int i = lane; i < 256; i += 32) s += (i == 0) ? 0u : H[i];
@@ -479,11 +479,20 @@ int abub_k1_build_k32(abub_ctx* ctx, int cam) {
     return ABUB_OK;
 }
 
-int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots) {
+// Histograms of the frame pairs j in [j_first, j_last) of every (slot, camera) of the range; a pair is skipped
+// when j >= d_limit[slot*ncams+cam] (d_limit = the frame counts, or the number of frames resident so far in the
+// streamed form, 0 = this camera is finished).  zero_hist clears the whole table of the range first.
+int abub_k1_launch_trigger_range(abub_ctx* ctx, int slot_first, int nslots, int j_first, int j_last, const int* d_limit,
+                                 bool zero_hist) {
     const int threads = k1_block_threads(ctx->cols);
-    const size_t hist_off = (size_t)slot_first * ctx->ncams * ctx->max_frames * 256;
-    const size_t hist_n = (size_t)nslots * ctx->ncams * ctx->max_frames * 256;
-    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(ctx->d_hist + hist_off, 0, hist_n * sizeof(uint32_t), ctx->stream));
+    if (zero_hist) {
+        const size_t hist_off = (size_t)slot_first * ctx->ncams * ctx->max_frames * 256;
+        const size_t hist_n = (size_t)nslots * ctx->ncams * ctx->max_frames * 256;
+        ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(ctx->d_hist + hist_off, 0, hist_n * sizeof(uint32_t), ctx->stream));
+    }
+    if (j_first < 1) j_first = 1;
+    if (j_last > ctx->max_frames) j_last = ctx->max_frames;
+    if (j_last <= j_first) return ABUB_OK;
     int nstrips, th;
     k1_strips(ctx->rows, &nstrips, &th);
     if (int rc = k1_allow_smem(ctx, k1_trigger_kernel, k1_smem_bytes(threads))) return rc;
@@ -492,21 +501,25 @@ int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots) {
     static const bool legacy = getenv("ABUB_K1_LEGACY") != nullptr;     // A/B switch for profiling
     const bool tma = ctx->d_tmaps && !legacy;
     if (tma)
-        if (int rc = abub_k1_launch_trigger_tma(ctx, slot_first, nslots)) return rc;
+        if (int rc = abub_k1_launch_trigger_tma(ctx, slot_first, nslots, j_first, j_last, d_limit)) return rc;
     for (int s0 = 0; s0 < nslots; s0 += per) {
         const int ns = (nslots - s0 < per) ? nslots - s0 : per;
         // with the TMA kernel on rows [2, rows-2) this kernel only does the 2+2 border rows
-        dim3 grid((tma ? 2 : nstrips) * k1_xgroups(ctx->cols), ctx->max_frames - 1, ns * ctx->ncams);
+        dim3 grid((tma ? 2 : nstrips) * k1_xgroups(ctx->cols), j_last - j_first, ns * ctx->ncams);
         k1_trigger_kernel<<<grid, threads, k1_smem_bytes(threads), ctx->stream>>>(
-            ctx->d_slot_ptrs, ctx->d_nframes, ctx->d_tss, ctx->d_k32_ptrs, ctx->d_hist, slot_first + s0,
-            ctx->rows, ctx->cols, ctx->ncams, ctx->max_frames, tma ? 2 : th, k1_xgroups(ctx->cols), tma ? 1 : 0);
+            ctx->d_slot_ptrs, d_limit, ctx->d_tss, ctx->d_k32_ptrs, ctx->d_hist, slot_first + s0,
+            ctx->rows, ctx->cols, ctx->ncams, ctx->max_frames, tma ? 2 : th, k1_xgroups(ctx->cols), tma ? 1 : 0, j_first);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     const int total_w = nslots * ctx->ncams * ctx->max_frames;
     k1_fill_bin0_kernel<<<(total_w * 32 + 255) / 256, 256, 0, ctx->stream>>>(
-        ctx->d_hist, ctx->d_nframes, slot_first, nslots, ctx->ncams, ctx->max_frames, (uint32_t)ctx->npix);
+        ctx->d_hist, d_limit, slot_first, nslots, ctx->ncams, ctx->max_frames, (uint32_t)ctx->npix, j_first, j_last);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
+}
+
+int abub_k1_launch_trigger(abub_ctx* ctx, int slot_first, int nslots) {
+    return abub_k1_launch_trigger_range(ctx, slot_first, nslots, 1, ctx->max_frames, ctx->d_nframes, true);
 }
 
 int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b, const uint32_t* d_k32,

@@ -114,7 +114,7 @@ __device__ __forceinline__ void k1t_hpass(const uint32_t W[6], uint32_t H[4]) {
 __global__ void __launch_bounds__(32 * T_MAX_WARPS, ABUB_K1T_MINCTA)
 k1_trigger_tma_kernel(const CUtensorMap* __restrict__ slot_maps, const CUtensorMap* __restrict__ k16_maps,
                       const int* __restrict__ nframes, const int* __restrict__ tss, uint32_t* __restrict__ hist,
-                      int slot_first, int rows, int cols, int ncams, int max_frames, int th, int nxg) {
+                      int slot_first, int rows, int cols, int ncams, int max_frames, int th, int nxg, int j_first) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int warp = (T_MAX_WARPS == 1) ? 0 : (int)(threadIdx.x >> 5), lane = threadIdx.x & 31;
     const int wpc = (T_MAX_WARPS == 1) ? 1 : (int)(blockDim.x >> 5);
@@ -130,7 +130,7 @@ k1_trigger_tma_kernel(const CUtensorMap* __restrict__ slot_maps, const CUtensorM
     const int rel = blockIdx.z;
     const int slot = slot_first + rel / ncams;
     const int cam = rel % ncams;
-    const int j = blockIdx.y + 1;
+    const int j = blockIdx.y + j_first;
     const int nf = nframes[slot * ncams + cam];
     if (j >= nf) return;
     const int d = (tss[cam] < 6) ? 1 : 2;           // twoFrameOffset, AnalyzerUnit.cpp:182-188
@@ -337,7 +337,7 @@ static inline int k1t_wpc(int cols) {
 
 // launches the TMA trigger kernel over [slot_first, slot_first+nslots); the caller zeroes the
 // histogram table before and runs k1_fill_bin0_kernel after.
-int abub_k1_launch_trigger_tma(abub_ctx* ctx, int slot_first, int nslots) {
+int abub_k1_launch_trigger_tma(abub_ctx* ctx, int slot_first, int nslots, int j_first, int j_last, const int* d_limit) {
     const int wpc = k1t_wpc(ctx->cols);
     const int nw = (ctx->cols + T_OW - 1) / T_OW;
     const int nxg = (nw + wpc - 1) / wpc;
@@ -350,10 +350,10 @@ int abub_k1_launch_trigger_tma(abub_ctx* ctx, int slot_first, int nslots) {
     const int per = 65535 / ctx->ncams;
     for (int s0 = 0; s0 < nslots; s0 += per) {
         const int ns = (nslots - s0 < per) ? nslots - s0 : per;
-        dim3 grid(nstrips * nxg, ctx->max_frames - 1, ns * ctx->ncams);
+        dim3 grid(nstrips * nxg, j_last - j_first, ns * ctx->ncams);
         k1_trigger_tma_kernel<<<grid, 32 * wpc, smem, ctx->stream>>>(
-            maps, maps + ctx->max_slots, ctx->d_nframes, ctx->d_tss, ctx->d_hist, slot_first + s0, ctx->rows,
-            ctx->cols, ctx->ncams, ctx->max_frames, th, nxg);
+            maps, maps + ctx->max_slots, d_limit, ctx->d_tss, ctx->d_hist, slot_first + s0, ctx->rows,
+            ctx->cols, ctx->ncams, ctx->max_frames, th, nxg, j_first);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     return ABUB_OK;

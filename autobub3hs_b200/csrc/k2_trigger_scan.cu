@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(32 * K2_WARPS)
 k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict__ nframes,
                        const int* __restrict__ start, const int* __restrict__ tss_cam,
                        int* __restrict__ result, double* __restrict__ sig_out, int slot_first, int nslots,
-                       int ncams, int max_frames) {
+                       int ncams, int max_frames, const int* __restrict__ avail) {
     __shared__ WarpScratch scratch[K2_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int item = blockIdx.x * K2_WARPS + warp;
@@ -79,6 +79,10 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
     double* so = sig_out + (size_t)sc * max_frames;
     int* res = result + sc * 4;
     const int nf = nframes[sc];
+    // streamed form (abub_trigger_stream): only the first `av` frames are resident; a decision that needs a
+    // later frame is reported as ABUB_STATUS_PENDING and the search is repeated when more frames have arrived
+    const int av = avail ? min(avail[sc], nf) : nf;
+    if (avail && avail[sc] <= 0) return;                          // finished earlier (or nothing resident): leave its results
     const int tss = tss_cam[cam];
     for (int f = lane; f < max_frames; f += 32) so[f] = 0.0;
 
@@ -107,6 +111,7 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
 
     int status = -3, trig = 0, loc_thres = -1, scanned = 0;      // :180
     for (int i = s; i < nf; i++) {                                // :191
+        if (i >= av) { status = ABUB_STATUS_PENDING; break; }
         const uint32_t* Hi = H + (size_t)i * 256;
 #pragma unroll
         for (int q = 0; q < 8; q++) {                             // store = true (:461)
@@ -129,6 +134,7 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
             if (i != nf - 1) {                                    // :261
                 double max_so_far = (double)single;              // :280
                 for (int ii = 1; ii <= 2 && ii + i < nf; ii++) {  // :282
+                    if (i + ii >= av) { status = ABUB_STATUS_PENDING; break; }
                     int fo2, madc2;
                     const double s2v = significance(H + (size_t)(i + ii) * 256, ws, i, lane, &fo2, &madc2);
                     single = (float)s2v;                          // :292  (store = false)
@@ -138,7 +144,7 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
                     else if (ii == 2) { status = 0; trig = i; }   // :297-300
                     if ((double)single > max_so_far) max_so_far = (double)single;   // :302
                 }
-                if (status == 0) break;
+                if (status == 0 || status == ABUB_STATUS_PENDING) break;
             }
         }
     }
@@ -147,11 +153,13 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
 
 }  // namespace
 
-int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots) {
+int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots) { return abub_k2_launch_avail(ctx, slot_first, nslots, nullptr); }
+
+int abub_k2_launch_avail(abub_ctx* ctx, int slot_first, int nslots, const int* d_avail) {
     const int items = nslots * ctx->ncams;
     k2_trigger_scan_kernel<<<(items + K2_WARPS - 1) / K2_WARPS, 32 * K2_WARPS, 0, ctx->stream>>>(
         ctx->d_hist, ctx->d_nframes, ctx->d_start, ctx->d_tss, ctx->d_trig, ctx->d_sig, slot_first, nslots,
-        ctx->ncams, ctx->max_frames);
+        ctx->ncams, ctx->max_frames, d_avail);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
 }

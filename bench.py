@@ -35,6 +35,7 @@ sys.path.insert(0, ROOT)
 ROWS, COLS, NCAMS, NFRAMES = 1050, 1680, 4, 40
 NPIX = ROWS * COLS
 K1_BYTES_PER_EVENT_CAM = (NFRAMES + 1) * NPIX          # every frame once + the sigma plane once
+K1_DRAM_TRAFFIC_125 = 39.413751e9 + 11.749e6            # bytes per 125-event launch, measured (profiles/)
 WORKLOAD = "trigger-only: 1000 events x 4 cams x 40 frames, 1050x1680 u8 (BASELINE.json configs[1])"
 
 
@@ -291,16 +292,27 @@ def run_ours(args, rank, world, local_rank):
         pin_t.copy_(slot_tensor(torch, ctx, s).cpu())
     torch.cuda.synchronize()
 
+    nf_arr = np.full((Be, NCAMS), NFRAMES, np.int32)
+    sent_total = [0]
+
     def e2e_step():
+        if args.e2e_mode == "stream":
+            # frames leave the pinned buffers chunk by chunk; a camera whose trigger search is decided gets no
+            # more of them (the reference reads frame by frame and returns at the trigger, AnalyzerUnit.cpp:191-300)
+            t_, s_, l_, sent = ctx.trigger_stream(0, Be, nf_arr, args.e2e_chunk)
+            sent_total[0] += int(sent.sum())
+            return t_, s_, l_, None
         for s in range(Be):
-            ctx.event_submit(s, nf)                 # cudaMemcpyAsync H2D from pinned staging
+            ctx.event_submit(s, nf)                 # cudaMemcpyAsync H2D of every frame from pinned staging
         ctx.trigger_hist(0, Be)
         ctx.trigger_scan(0, Be)
+        sent_total[0] += Be * NCAMS * NFRAMES
         return ctx.trigger_results(0, Be, want_sig=False)   # D2H of the step's result
 
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
     for _ in range(1):
         e2e_step()
+    sent_total[0] = 0
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -359,11 +371,19 @@ def run_ours(args, rank, world, local_rank):
         "config": {"workload": WORKLOAD, "events_per_step": B, "l2": "inputs (35 GB/step at 125 events) exceed L2; no flush",
                    "event_mix": "90% normal (1-3 bubbles), 5% multi (>=20), 5% no-trigger; noise sigma 2.0",
                    "train_events": n_train, "generated_on": "device (torch RNG), seconds=%.1f" % t_gen},
-        "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": Be * NCAMS * NFRAMES * NPIX,
-                "d2h_bytes_per_step": Be * NCAMS * 16, "events_per_step": Be, "steps": e2e_steps},
-        "gpu_launches": args.steps * 3,
+        "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": sent_total[0] * NPIX // e2e_steps,
+                "d2h_bytes_per_step": Be * NCAMS * 16 * (1 if args.e2e_mode == "full" else (NFRAMES + args.e2e_chunk - 1) // args.e2e_chunk),
+                "events_per_step": Be, "steps": e2e_steps, "mode": args.e2e_mode,
+                "note": ("abub_trigger_stream: host frames in pinned memory, sent %d frames at a time, a camera stops "
+                         "receiving frames once its trigger search is decided (the reference's early exit); "
+                         "frames_sent/frames_total = %.3f" % (args.e2e_chunk, sent_total[0] / max(1, e2e_steps * Be * NCAMS * NFRAMES)))
+                        if args.e2e_mode == "stream" else "every frame of every event copied H2D, then K1+K2"},
+        "gpu_launches": args.steps * 4,      # k1_trigger_tma + k1_trigger (border rows) + k1_fill_bin0 + k2_trigger_scan
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "k1_trigger_kernel", "ms_per_launch": k1_ms,
+                     "traffic": K1_DRAM_TRAFFIC_125 if B == 125 else None,
+                     "traffic_source": "profiles/r1_k1_v5_125ev_full.txt (ncu --set full, dram read+write of one 125-event launch)",
+                     "kernel": "k1_trigger_tma_kernel (+ k1_trigger_kernel on the 4 border rows, k1_fill_bin0_kernel)",
+                     "ms_per_launch": k1_ms,
                      "algorithmic_bytes_per_launch": k1_bytes,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
         "cpu_baseline": cpu,
@@ -378,13 +398,15 @@ def run_ours(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--events-per-step", type=int, default=125)
     ap.add_argument("--train-events", type=int, default=25)
     ap.add_argument("--e2e-events", type=int, default=8)
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-mode", default="stream", choices=["stream", "full"])
+    ap.add_argument("--e2e-chunk", type=int, default=4)
     ap.add_argument("--cpu-events", type=int, default=8)
     ap.add_argument("--ref-events", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -111,6 +111,15 @@ int abub_trigger_results(abub_ctx* ctx, int slot_first, int nslots, int* trig, i
 int abub_trigger(abub_ctx* ctx, int slot, int cam, int start_frame, int* trig, int* status,
                  int* loc_thres, double* sig);
 
+/* Streamed form of FindTriggerFrame (start frame 1) for every (slot,cam) of the range.  The frames wait in the
+ * slots' pinned staging buffers (abub_pinned_acquire); nframes[(slot-slot_first)*ncams+cam] of them exist.  They are
+ * sent chunk_frames at a time and a camera whose search is decided receives no further frames: the device-side
+ * form of the reference reading frames one by one and returning at the trigger (AnalyzerUnit.cpp:191-213,
+ * :297-300).  Results as abub_trigger_results; frames_sent (may be NULL) = frames transferred per (slot,cam).
+ * The frames that were not sent are not resident: upload the slot before calling abub_localize on it. */
+int abub_trigger_stream(abub_ctx* ctx, int slot_first, int nslots, const int* nframes, int chunk_frames,
+                        int* trig, int* status, int* loc_thres, int* frames_sent);
+
 /* ---- training: Trainer::MakeAvgSigmaImage (Trainer.cpp:221-331) ----------------- */
 int abub_train_begin(abub_ctx* ctx, int cam);
 /* Gate (Trainer.cpp:279-287): 16-bin histogram of frame1-frame0 on the device, entropy

@@ -190,3 +190,39 @@ def test_trigger_hist_tma_path(capi, shape):
                 H = ctx.trigger_hist_read(slot, c)
                 Href = _oracle_hists(o, fr, sig[c], tss)
                 assert np.array_equal(H[:len(fr)], Href), (shape, tss, slot, c)
+
+
+@pytest.mark.parametrize("chunk", [1, 4, 7, 40])
+def test_trigger_stream_equals_batch(capi, small_run, small_trained, chunk):
+    """abub_trigger_stream (frames sent chunk by chunk from pinned memory, nothing sent to a camera after its
+    search is decided) returns exactly what the resident batch path returns."""
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    nev = len(run.events)
+    with capi.Context(rows, cols, ncams=4, max_frames=40, max_slots=nev) as ctx:
+        for c in range(4):
+            ctx.set_background(c, trained[c].avg, trained[c].sigma, trained[c].training_set_size)
+        nf = np.zeros((nev, 4), np.int32)
+        for ev in range(nev):
+            pin = ctx.pinned(ev)
+            for c in range(4):
+                fr = run.events[ev][c]
+                nf[ev, c] = len(fr)
+                pin[c, :len(fr)] = fr
+                ctx.event_upload(ev, c, fr)
+        ctx.trigger_hist(0, nev)
+        ctx.trigger_scan(0, nev)
+        trig, status, lt, _ = ctx.trigger_results(0, nev)
+        t2, s2, l2, sent = ctx.trigger_stream(0, nev, nf, chunk)
+        assert np.array_equal(s2, status)
+        ok = status == 0
+        assert np.array_equal(t2[ok], trig[ok])
+        live = status != -9
+        assert np.array_equal(l2[live], lt[live])
+        assert np.all(sent <= nf) and np.all(sent[status == -9] == 0) and np.all(sent[status == -3] == nf[status == -3])
+        # a triggered camera needs frames up to trig+2 and gets at most one chunk beyond that
+        need = np.minimum(trig + 3, nf)
+        assert np.all(sent[ok] >= need[ok]) and np.all(sent[ok] < need[ok] + chunk)
+        # the result table is left as abub_trigger_results expects it
+        t3, s3, l3, _ = ctx.trigger_results(0, nev, want_sig=False)
+        assert np.array_equal(s3, status) and np.array_equal(t3[ok], trig[ok])
