@@ -106,6 +106,94 @@ k5_post_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols) {
     if (c && threadIdx.x) atomicAdd(&job.hist[threadIdx.x], c);
 }
 
+// Streaming form of K5b for pitches that allow 8-byte loads (cols % 8 == 0): one warp owns a strip of 240 output
+// columns (lane l holds the 8 pixels x0-8+8l.., lanes 0/31 are the halo) and walks down PS_TH rows.
+//   d   = sat_u8(|a - avg| - t8)                  VABSDIFF4 + byte-wise saturating subtract, 4 px per word
+//   3x3 = vertical sum of three rows in 16-bit lanes (two pixels per word), horizontal sum after taking the halo
+//         words from the neighbour lanes (SHFL) and one PRMT per word for the odd alignment
+//   v   = (sum + 4) / 9  (cv::blur rounding), THRESH_TOZERO -- only evaluated when some sum in the lane can exceed
+//         the threshold, which is rare: frames are almost empty after the 6-sigma cut
+// 3 bytes read + 1 byte written per pixel, no shared-memory tile.
+constexpr int PS_TH = 64;
+constexpr int PS_WARPS = 4;
+
+__device__ __forceinline__ uint2 ps_ld8(const uint8_t* p) { return __ldg(reinterpret_cast<const uint2*>(p)); }
+
+__global__ void __launch_bounds__(32 * PS_WARPS)
+k5_post_stream_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols, int nxw, int nstrips) {
+    __shared__ uint32_t sh_hist[256];
+    const abub_loc_job job = jobs[blockIdx.z];
+    if (job.genesis) return;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
+    __syncthreads();
+    const int unit = blockIdx.x * PS_WARPS + warp;
+    if (unit < nxw * nstrips) {
+        const int x0 = (unit % nxw) * 240, y0 = (unit / nxw) * PS_TH;
+        const int gx = x0 - 8 + lane * 8;
+        const int gxl = min(max(gx, 0), cols - 8);
+        const bool out_lane = lane >= 1 && lane <= 30 && gx < cols;
+        const bool left_edge = (gx == 0), right_edge = (gx + 8 == cols);
+        const int nout = min(PS_TH, rows - y0);
+        const uint32_t lim = 9u * (uint32_t)job.tozero + 5u;            // (sum+4)/9 <= tozero  <=>  sum < lim
+        uint32_t r1[4] = {0, 0, 0, 0}, r2[4] = {0, 0, 0, 0};           // rows y-1 and y-2, widened (2 px per word)
+        for (int rl = 0; rl < nout + 2; rl++) {
+            int y = y0 - 1 + rl;                                        // BORDER_REFLECT_101
+            if (y < 0) y = -y;
+            if (y >= rows) y = 2 * (rows - 1) - y;
+            y = min(max(y, 0), rows - 1);
+            const size_t off = (size_t)y * cols + gxl;
+            const uint2 a = ps_ld8(job.a + off), m = ps_ld8(job.b + off), t = ps_ld8(job.t8 + off);
+            const uint32_t d0 = __vsubus4(__vabsdiffu4(a.x, m.x), t.x);     // L3Localizer.cpp:779-782
+            const uint32_t d1 = __vsubus4(__vabsdiffu4(a.y, m.y), t.y);
+            uint32_t w[4];
+            w[0] = __byte_perm(d0, 0, 0x4140); w[1] = __byte_perm(d0, 0, 0x4342);
+            w[2] = __byte_perm(d1, 0, 0x4140); w[3] = __byte_perm(d1, 0, 0x4342);
+            if (rl >= 2) {
+                uint32_t W[6];
+#pragma unroll
+                for (int k = 0; k < 4; k++) W[k + 1] = w[k] + r1[k] + r2[k];
+                W[0] = __shfl_up_sync(0xffffffffu, W[4], 1);
+                W[5] = __shfl_down_sync(0xffffffffu, W[1], 1);
+                if (left_edge) W[0] = __byte_perm(W[1], 0, 0x3232);     // column -1 -> column 1 (hi lane is what is read)
+                if (right_edge) W[5] = __byte_perm(W[4], 0, 0x1010);    // column cols -> column cols-2 (lo lane is read)
+                uint32_t H[4], mx = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t sl = __byte_perm(W[k], W[k + 1], 0x5432);      // (x-1, x) pairs
+                    const uint32_t sr = __byte_perm(W[k + 1], W[k + 2], 0x5432);  // (x+1, x+2) pairs
+                    H[k] = sl + W[k + 1] + sr;
+                    mx = __vmaxu2(mx, H[k]);
+                }
+                uint2 o = make_uint2(0u, 0u);
+                if (out_lane && ((mx & 0xFFFFu) >= lim || (mx >> 16) >= lim)) {
+                    uint32_t ob[8];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        ob[2 * k] = (((H[k] & 0xFFFFu) + 4u) * 7282u) >> 16;       // (sum+4)/9, exact for sum <= 2295
+                        ob[2 * k + 1] = (((H[k] >> 16) + 4u) * 7282u) >> 16;
+                    }
+#pragma unroll
+                    for (int c = 0; c < 8; c++) {
+                        if ((int)ob[c] <= job.tozero) ob[c] = 0;                   // THRESH_TOZERO (:786)
+                        if (ob[c]) atomicAdd(&sh_hist[ob[c]], 1u);
+                    }
+                    o.x = ob[0] | (ob[1] << 8) | (ob[2] << 16) | (ob[3] << 24);
+                    o.y = ob[4] | (ob[5] << 8) | (ob[6] << 16) | (ob[7] << 24);
+                }
+                if (out_lane) *reinterpret_cast<uint2*>(job.tz + (size_t)(y0 + rl - 2) * cols + gx) = o;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; k++) { r2[k] = r1[k]; r1[k] = w[k]; }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        const uint32_t c = sh_hist[i];
+        if (c && i) atomicAdd(&job.hist[i], c);
+    }
+}
+
 // ------------------------------------------------------------------------------------
 // K5c: Otsu (OpenCV getThreshVal_Otsu_8u), one thread per job; also fills bin 0
 // ------------------------------------------------------------------------------------
@@ -147,6 +235,36 @@ k6_candidates_kernel(const abub_loc_job* __restrict__ jobs, const int* __restric
     const uint8_t* tz = jobs[jl].tz;
     const int t = thr[jl];
     const size_t npix = (size_t)rows * cols;
+    if ((cols & 15) == 0) {
+        // 16 pixels per load; the TOZERO'd frames are almost empty, so nearly every group is rejected by one OR
+        const size_t ngroups = npix / 16;
+        for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += (size_t)gridDim.x * blockDim.x) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(tz) + g);
+            if ((v.x | v.y | v.z | v.w) == 0u) continue;
+            const uint32_t wds[4] = {v.x, v.y, v.z, v.w};
+            for (int c = 0; c < 16; c++) {
+                if ((int)((wds[c >> 2] >> (8 * (c & 3))) & 0xFFu) <= t) continue;
+                const size_t p = g * 16 + c;
+                const int y = (int)(p / cols), x = (int)(p % cols);
+                bool earlier = false;
+                if (x > 0 && tz[p - 1] > t) earlier = true;
+                if (y > 0) {
+                    const uint8_t* up = tz + p - cols;
+                    if (up[0] > t) earlier = true;
+                    if (x > 0 && up[-1] > t) earlier = true;
+                    if (x + 1 < cols && up[1] > t) earlier = true;
+                }
+                if (!earlier) {
+                    const int slot = atomicAdd(&counters[0], 1);
+                    if (slot < cand_cap)
+                        keys[slot] = ((unsigned long long)(unsigned)(job0 + jl) << 32) | (unsigned)(0xFFFFFFFFu - (unsigned)p);
+                    else
+                        counters[3] = 1;
+                }
+            }
+        }
+        return;
+    }
     for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += (size_t)gridDim.x * blockDim.x) {
         if (tz[p] <= t) continue;
         const int y = (int)(p / cols), x = (int)(p % cols);
@@ -348,7 +466,12 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_hist, 0, (size_t)njobs * 256 * sizeof(uint32_t), st));
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_npf, 0, (size_t)njobs * sizeof(int), st));
     if ((rc = abub_k1_launch_genesis_jobs(ctx, a->d_jobs, njobs))) return rc;
-    {
+    if ((ctx->cols % 8) == 0 && ctx->cols >= 16) {
+        const int nxw = (ctx->cols + 239) / 240, nstrips = (ctx->rows + PS_TH - 1) / PS_TH;
+        dim3 grid((nxw * nstrips + PS_WARPS - 1) / PS_WARPS, 1, njobs);
+        k5_post_stream_kernel<<<grid, 32 * PS_WARPS, 0, st>>>(a->d_jobs, ctx->rows, ctx->cols, nxw, nstrips);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    } else {
         dim3 grid((ctx->cols + PT_W - 1) / PT_W, (ctx->rows + PT_H - 1) / PT_H, njobs);
         k5_post_kernel<<<grid, 256, 0, st>>>(a->d_jobs, ctx->rows, ctx->cols);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());

@@ -189,3 +189,28 @@ def test_end_to_end_text_matches_oracle(capi, small_run, small_trained):
                     for c in range(4)]
             text.append(o.write_camera_output(run.run_id, cams, run.frame_offset))
     assert "".join(text) == ref_text
+
+
+@pytest.mark.parametrize("shape", [(40, 16), (67, 248), (130, 496), (33, 1696)])
+def test_post_trigger_binary_stream_kernel(capi, shape):
+    """cols % 8 == 0 takes the streaming K5b kernel (and cols % 16 == 0 the vectorised candidate scan):
+    binarised post-trigger frames and blob records against cv2, dense and sparse content, image borders."""
+    import oracle.cv2_oracle as o
+    rows, cols = shape
+    rng = np.random.default_rng(rows + cols)
+    with capi.Context(rows, cols, 1, 12, max_slots=1) as ctx:
+        for trial in range(3):
+            avg = rng.integers(0, 256, (rows, cols)).astype(np.uint8)
+            sigma = rng.integers(0, 2 + 20 * trial, (rows, cols)).astype(np.uint8)
+            ctx.set_background(0, avg, sigma, 12)
+            noise = rng.normal(0, 3 + 25 * trial, (12, rows, cols))
+            frames = np.clip(avg[None].astype(np.float64) + noise, 0, 255).astype(np.uint8)
+            frames[3:, : min(rows, 9), :7] = 255 - avg[: min(rows, 9), :7]          # blobs touching the corners
+            frames[5:, -6:, -9:] = 255 - avg[-6:, -9:]
+            ctx.event_upload(0, 0, frames)
+            res = ctx.localize_batch([(0, 0, 1, 0, 3, 10)], cap=1 << 17)[0]
+            for k in range(1, 11):
+                ref = o.post_trigger_binary(frames[1 + k], avg, sigma)
+                _check_blobs(o, res[k], ref)
+            for k in (1, 4, 10):
+                assert np.array_equal(ctx.localize_binary(k), o.post_trigger_binary(frames[1 + k], avg, sigma)), (shape, trial, k)

@@ -1,0 +1,105 @@
+#!/usr/bin/env python
+"""Per-stage timings of the path on one B200 (not the headline bench: bench.py is):
+  trainer    K3 gate + K4 Welford over `--train-events` events (BASELINE.json configs[2] shape on 1 GPU)
+  localizer  K5-K7 over every triggered (event, camera) of a resident batch
+  recon      K1+K2 followed by the localizer = the device part of a full recon (configs[3])
+Each line carries the algorithmic bytes of SURVEY.md 8(d) and the GB/s they imply.  Wall-clock
+around synchronising C-ABI calls (the localizer has host round trips inside, they are part of it)."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench as B  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--events", type=int, default=32)
+    ap.add_argument("--train-events", type=int, default=200)
+    ap.add_argument("--reps", type=int, default=3)
+    args = ap.parse_args()
+    import torch
+    from autobub3hs_b200 import capi, synth
+    from tests import glue
+
+    E = args.events
+    ctx = capi.Context(B.ROWS, B.COLS, B.NCAMS, B.NFRAMES, max_slots=E)
+    cam_masks, bellows = synth.make_masks(B.ROWS, B.COLS, B.NCAMS)
+    bgs = [torch.from_numpy(synth.make_background(c, B.ROWS, B.COLS).astype(np.float32)).cuda() for c in range(B.NCAMS)]
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(7919)
+    classes = B.event_classes(E, 0)
+    for s in range(E):
+        es = synth.make_event_spec(s, classes[s], cam_masks, bellows, seed=11)
+        B.fill_slot(torch, B.slot_tensor(torch, ctx, s), bgs, es.bubbles, gen)
+        ctx.event_set_nframes(s, [B.NFRAMES] * B.NCAMS)
+    torch.cuda.synchronize()
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0) if os.path.exists(
+        os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+
+    # ---- trainer: the ring of E resident events is reused until --train-events have been added ----
+    best = None
+    for _ in range(args.reps):
+        t0 = time.perf_counter()
+        for c in range(B.NCAMS):
+            ctx.train_begin(c)
+            for i in range(args.train_events):
+                ctx.train_add_slot(c, i % E)
+            _, _, n, st = ctx.train_finish(c)
+            assert st == 0
+            ctx.set_background_from_training(c)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    byt = B.NCAMS * (args.train_events * 2 * B.NPIX + n * B.NPIX + 2 * B.NPIX)      # gate reads + Welford reads + planes
+    print(json.dumps({"stage": "trainer", "train_events": args.train_events, "kept_frames_per_cam": n, "seconds": best,
+                      "algorithmic_GB": byt / 1e9, "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak,
+                      "note": "includes one device-to-device copy per kept frame (parking) and one sync per event"}))
+
+    # ---- trigger + localizer ----
+    ctx.trigger_hist(0, E)
+    ctx.trigger_scan(0, E)
+    trig, status, lt, _ = ctx.trigger_results(0, E, want_sig=False)
+    items = []
+    for s in range(E):
+        for c in range(B.NCAMS):
+            if status[s, c] == 0:
+                t = int(trig[s, c])
+                items.append((s, c, t, max(0, t - 2), int(lt[s, c]), glue.n_post_frames(t, B.NFRAMES)))
+    nplanes = sum(3 + it[5] + 2 for it in items)
+    best = None
+    for _ in range(args.reps):
+        t0 = time.perf_counter()
+        res = ctx.localize_batch(items, cap=1 << 18)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    nblobs = sum(len(f) for r in res for f in r)
+    byt = nplanes * B.NPIX
+    print(json.dumps({"stage": "localizer", "items": len(items), "frames": sum(it[5] + 1 for it in items), "blobs": nblobs,
+                      "seconds": best, "items_per_s": len(items) / best, "algorithmic_GB": byt / 1e9,
+                      "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak}))
+
+    best = None
+    for _ in range(args.reps):
+        t0 = time.perf_counter()
+        ctx.trigger_hist(0, E)
+        ctx.trigger_scan(0, E)
+        ctx.trigger_results(0, E, want_sig=False)
+        ctx.localize_batch(items, cap=1 << 18)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    byt = E * B.NCAMS * B.K1_BYTES_PER_EVENT_CAM + nplanes * B.NPIX
+    print(json.dumps({"stage": "recon (K1+K2+K5-K7, resident)", "events": E, "seconds": best, "events_per_s": E / best,
+                      "algorithmic_GB": byt / 1e9, "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak}))
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()
