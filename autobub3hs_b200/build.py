@@ -40,7 +40,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(out)
         if p.returncode:
             raise RuntimeError(f"nvcc failed on {s}")
-    cmd = [nvcc, "-shared", "-o", LIB, *objs, "-lcudart", "-ldl"]
+    cmd = [nvcc, *NVCC_FLAGS[:2], "-shared", "-o", LIB, *objs, "-lcudart", "-ldl"]
     subprocess.check_call(cmd)
     return LIB
 

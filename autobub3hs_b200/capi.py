@@ -23,7 +23,8 @@ EXPORTS = [
     "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_device_ptr",
     "abub_event_set_nframes",
     "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_hist_write", "abub_trigger_scan", "abub_trigger_results", "abub_trigger", "abub_trigger_stream",
-    "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_finish",
+    "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_add_slots",
+    "abub_train_add_events", "abub_train_finish", "abub_selftest_fdiv", "abub_k4_fdiv1_max",
     "abub_train_partials", "abub_train_allreduce", "abub_train_finish_partials", "abub_train_finish_allreduced",
     "abub_nccl_comm_create", "abub_nccl_comm_destroy", "abub_nccl_barrier",
     "abub_localize", "abub_localize_batch", "abub_localize_binary", "abub_process_frame",
@@ -85,6 +86,10 @@ def load() -> C.CDLL:
     lib.abub_train_begin.argtypes = [vp, C.c_int]
     lib.abub_train_add_event.argtypes = [vp, C.c_int, u8p, C.POINTER(C.c_float), ip]
     lib.abub_train_add_slot.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float), ip]
+    lib.abub_train_add_slots.argtypes = [vp, C.c_int, ip, C.c_int, C.POINTER(C.c_float), ip]
+    lib.abub_train_add_events.argtypes = [vp, C.c_int, u8p, C.c_int, C.POINTER(C.c_float), ip]
+    lib.abub_selftest_fdiv.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
+    lib.abub_k4_fdiv1_max.argtypes = []
     lib.abub_train_finish.argtypes = [vp, C.c_int, u8p, u8p, ip, ip]
     lib.abub_train_partials.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     lib.abub_train_allreduce.argtypes = [vp, C.c_int, vp]
@@ -242,6 +247,32 @@ class Context:
         e, k = C.c_float(), C.c_int()
         self._ck(self.lib.abub_train_add_slot(self.h, cam, slot, C.byref(e), C.byref(k)), "abub_train_add_slot")
         return e.value, bool(k.value)
+
+    def train_add_slots(self, cam: int, slots) -> Tuple[np.ndarray, np.ndarray]:
+        sl = np.ascontiguousarray(slots, dtype=np.int32)
+        e = np.zeros(len(sl), np.float32)
+        k = np.zeros(len(sl), np.int32)
+        self._ck(self.lib.abub_train_add_slots(self.h, cam, sl.ctypes.data_as(C.POINTER(C.c_int)), len(sl),
+                                               e.ctypes.data_as(C.POINTER(C.c_float)), k.ctypes.data_as(C.POINTER(C.c_int))),
+                 "abub_train_add_slots")
+        return e, k.astype(bool)
+
+    def train_add_events(self, cam: int, frames01: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+        """frames01: uint8 [n, 2, rows, cols]."""
+        f = np.ascontiguousarray(frames01, dtype=np.uint8)
+        assert f.ndim == 4 and f.shape[1:] == (2, self.rows, self.cols)
+        n = f.shape[0]
+        e = np.zeros(n, np.float32)
+        k = np.zeros(n, np.int32)
+        self._ck(self.lib.abub_train_add_events(self.h, cam, _p(f), n, e.ctypes.data_as(C.POINTER(C.c_float)),
+                                                k.ctypes.data_as(C.POINTER(C.c_int))), "abub_train_add_events")
+        return e, k.astype(bool)
+
+    def selftest_fdiv(self, steps: int, k_first: int, k_last: int) -> Tuple[int, Tuple[int, int]]:
+        n = C.c_ulonglong()
+        ex = (C.c_ulonglong * 2)()
+        self._ck(self.lib.abub_selftest_fdiv(self.h, steps, k_first, k_last, C.byref(n), ex), "abub_selftest_fdiv")
+        return n.value, (ex[0], ex[1])
 
     def train_finish(self, cam: int):
         mean = np.zeros((self.rows, self.cols), np.uint8)

@@ -63,6 +63,9 @@ struct abub_ctx {
     // scratch for single-frame ops / training
     uint8_t*  d_tmp8[4] = {nullptr, nullptr, nullptr, nullptr};
     uint32_t* d_hist_tmp = nullptr; // 16 x 256
+    const uint8_t** d_gate_tab = nullptr;   // batched entropy gate: [n][2] frame pointers ...
+    uint32_t* d_gate_hist = nullptr;        // ... and [n][16] histograms
+    int gate_cap = 0;
     void*     loc = nullptr;        // localizer arena (k5_localize.cu)
     void*     d_tmaps = nullptr;    // CUtensorMap[2*max_slots + 2*ncams] (k1_trigger_tma.cu); null = TMA path off
 };
@@ -105,6 +108,7 @@ int abub_k2_launch_avail(abub_ctx* ctx, int slot_first, int nslots, const int* d
 #define ABUB_STATUS_PENDING (-100)
 // K3/K4 (k34_trainer.cu)
 int abub_k3_gate_hist16(abub_ctx* ctx, const uint8_t* d_f0, const uint8_t* d_f1, uint32_t* d_hist16);
+int abub_k3_gate_batch(abub_ctx* ctx, const uint8_t* const* d_pairs, int n, uint32_t* d_hist16);
 int abub_k4_welford(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint8_t* d_mean, uint8_t* d_sigma);
 int abub_k4_partials(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint32_t* d_sum, uint64_t* d_sumsq);
 int abub_k4_finish_from_partials(abub_ctx* ctx, const uint32_t* d_sum, const uint64_t* d_sumsq, int n, uint8_t* d_mean,

@@ -90,6 +90,7 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     cudaFree(ctx->d_sig); cudaFree(ctx->d_tss); cudaFree(ctx->d_k32_ptrs); cudaFree(ctx->d_slot_ptrs);
     for (int i = 0; i < 4; i++) cudaFree(ctx->d_tmp8[i]);
     cudaFree(ctx->d_hist_tmp);
+    cudaFree((void*)ctx->d_gate_tab); cudaFree(ctx->d_gate_hist);
     cudaFree(ctx->d_tmaps);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;

@@ -12,6 +12,8 @@
 //     contraction (the reference is compiled at -O0).
 // K4p: exact integer partials (u32 sum x, u64 sum x^2) for the multi-GPU all-reduce, and
 //     the fp64 finish from reduced partials with boundary flagging.
+#include <stdlib.h>
+
 #include "abub_internal.cuh"
 
 namespace {
@@ -52,6 +54,50 @@ __global__ void k3_fill_bin0(uint32_t* hist16, uint32_t npix) {
     uint32_t s = 0;
     for (int i = 1; i < 16; i++) s += hist16[i];
     hist16[0] = npix - s;
+}
+
+// Batched gate: blockIdx.y = event, pairs[2e] = frame 0, pairs[2e+1] = frame 1, hist16 + 16e its histogram.
+__global__ void k3_gate_batch_kernel(const uint8_t* const* __restrict__ pairs, uint32_t* __restrict__ hist16, size_t npix) {
+    __shared__ uint32_t sh[16];
+    const uint8_t* __restrict__ f0 = pairs[2 * blockIdx.y];
+    const uint8_t* __restrict__ f1 = pairs[2 * blockIdx.y + 1];
+    if (threadIdx.x < 16) sh[threadIdx.x] = 0;
+    __syncthreads();
+    const bool aligned = (((uintptr_t)f0 | (uintptr_t)f1) & 15) == 0;
+    const size_t nvec = aligned ? npix / 16 : 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(f1) + i);
+        const uint4 b = __ldg(reinterpret_cast<const uint4*>(f0) + i);
+        // bin = sat(f1-f0) >> 4 is non-zero iff f1 >= f0 + 16: absdiff keeps that visible in the high nibbles
+        // whenever it can be true, so the (5-instruction) saturating subtract runs only on words that need it
+        const uint32_t q[4] = {__vabsdiffu4(a.x, b.x), __vabsdiffu4(a.y, b.y), __vabsdiffu4(a.z, b.z), __vabsdiffu4(a.w, b.w)};
+        if (((q[0] | q[1] | q[2] | q[3]) & 0xF0F0F0F0u) != 0) {
+            const uint32_t d[4] = {__vsubus4(a.x, b.x), __vsubus4(a.y, b.y), __vsubus4(a.z, b.z), __vsubus4(a.w, b.w)};
+#pragma unroll
+            for (int w = 0; w < 4; w++)
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const uint32_t bin = (d[w] >> (8 * c + 4)) & 0xFu;
+                    if (bin) atomicAdd(&sh[bin], 1u);
+                }
+        }
+    }
+    for (size_t p = nvec * 16 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += stride) {
+        const int v = (int)f1[p] - (int)f0[p];
+        const uint32_t bin = (uint32_t)(v > 0 ? v : 0) >> 4;
+        if (bin) atomicAdd(&sh[bin], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x > 0 && threadIdx.x < 16 && sh[threadIdx.x]) atomicAdd(&hist16[16 * blockIdx.y + threadIdx.x], sh[threadIdx.x]);
+}
+
+__global__ void k3_fill_bin0_batch(uint32_t* hist16, int n, uint32_t npix) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    uint32_t s = 0;
+    for (int i = 1; i < 16; i++) s += hist16[16 * e + i];
+    hist16[16 * e] = npix - s;
 }
 
 __device__ __forceinline__ void welford_step(float x, float fdiv, float& mean, float& m2) {
@@ -150,6 +196,147 @@ __global__ void k4_fixup_kernel(const uint8_t* const* __restrict__ frames, int n
     welford_finish(mean, m2, (float)(size_t)(n - 1), mean_out[p], sigma_out[p]);
 }
 
+// ---- K4 fast path ---------------------------------------------------------------------------------
+// The generic kernel above spends ~28 instructions per sample: __fdiv_rn expands to MUFU.RCP + FCHK + a
+// refinement chain + a slow-path call per sample, and the u8 -> f32 conversions are quarter-rate I2F.  Both
+// are avoided here without changing one bit of the result:
+//   * the divisor (frame index + 1) is the same for every pixel, so its correctly rounded reciprocal
+//     r = RN(1/k) is formed once per frame per thread and the quotient is
+//         q0 = RN(a*r);  e = RN(a - q0*k) (one FMA, exact);  q = RN(q0 + e*r)
+//     -- Markstein's correction step.  One step returns RN(a/k) whenever q0 is within one ulp of a/k; that it
+//     does so for every value a Welford delta can take (+0 and 2^-50 <= |a| <= 256, see k4_fdiv_check_kernel)
+//     and every k <= ABUB_FDIV1_MAX is checked exhaustively against __fdiv_rn on the device by abub_selftest_fdiv
+//     (tests/test_gpu_train_localize.py).
+//     Above that bound a second step is applied (q0 is then faithful, for which the step is proven exact).
+//   * byte c of a word becomes a float by PRMT into the mantissa of 2^23 and one exact FADD of -2^23.
+// Each thread owns 16 pixels (one 16-byte load per frame, 16 independent recurrences), 4 frames in flight.
+#define ABUB_FDIV1_MAX 4096
+
+template <int STEPS>
+__device__ __forceinline__ float div_by_count(float a, float k, float r) {
+    float q = __fmul_rn(a, r);
+    float e = __fmaf_rn(-q, k, a);
+    q = __fmaf_rn(e, r, q);
+    if (STEPS == 2) {
+        e = __fmaf_rn(-q, k, a);
+        q = __fmaf_rn(e, r, q);
+    }
+    return q;
+}
+
+__device__ __forceinline__ float byte_to_float(uint32_t w, int c) {
+    return __fadd_rn(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7540 + c)), -8388608.0f);
+}
+
+template <int STEPS>
+__device__ __forceinline__ void welford_word(uint32_t w, float k, float r, float* mean, float* m2) {
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const float x = byte_to_float(w, c);
+        const float delta = __fsub_rn(x, mean[c]);                                   // Trainer.cpp:185
+        mean[c] = __fadd_rn(mean[c], div_by_count<STEPS>(delta, k, r));              // :186
+        m2[c] = __fadd_rn(m2[c], __fmul_rn(delta, __fsub_rn(x, mean[c])));           // :187
+    }
+}
+
+template <int STEPS>
+__global__ void __launch_bounds__(64) k4_welford16_kernel(const uint8_t* const* __restrict__ frames, int n,
+                                                          uint8_t* __restrict__ mean_out, uint8_t* __restrict__ sigma_out,
+                                                          size_t nvec) {
+    const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= nvec) return;
+    float mean[16], m2[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) mean[i] = m2[i] = 0.f;
+    int f = 0;
+    // groups of 4 frames, the next group's loads issued before the current group's arithmetic
+    uint4 w[4], nx[4];
+    if (n >= 4) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) w[u] = __ldg(reinterpret_cast<const uint4*>(frames[u]) + g);
+    }
+#pragma unroll 1
+    for (; f + 4 <= n; f += 4) {
+        if (f + 8 <= n) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) nx[u] = __ldg(reinterpret_cast<const uint4*>(frames[f + 4 + u]) + g);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const float k = (float)(f + u + 1);
+            const float r = __frcp_rn(k);
+            welford_word<STEPS>(w[u].x, k, r, mean + 0, m2 + 0);
+            welford_word<STEPS>(w[u].y, k, r, mean + 4, m2 + 4);
+            welford_word<STEPS>(w[u].z, k, r, mean + 8, m2 + 8);
+            welford_word<STEPS>(w[u].w, k, r, mean + 12, m2 + 12);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) w[u] = nx[u];
+    }
+    for (; f < n; f++) {
+        const uint4 w = __ldg(reinterpret_cast<const uint4*>(frames[f]) + g);
+        const float k = (float)(f + 1);
+        const float r = __frcp_rn(k);
+        welford_word<STEPS>(w.x, k, r, mean + 0, m2 + 0);
+        welford_word<STEPS>(w.y, k, r, mean + 4, m2 + 4);
+        welford_word<STEPS>(w.z, k, r, mean + 8, m2 + 8);
+        welford_word<STEPS>(w.w, k, r, mean + 12, m2 + 12);
+    }
+    const float nm1 = (float)(size_t)(n - 1);                                       // :191
+    uint32_t mo[4], so[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        mo[q] = so[q] = 0;
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            uint8_t mu, su;
+            welford_finish(mean[4 * q + c], m2[4 * q + c], nm1, mu, su);
+            mo[q] |= (uint32_t)mu << (8 * c);
+            so[q] |= (uint32_t)su << (8 * c);
+        }
+    }
+    reinterpret_cast<uint4*>(mean_out)[g] = make_uint4(mo[0], mo[1], mo[2], mo[3]);
+    reinterpret_cast<uint4*>(sigma_out)[g] = make_uint4(so[0], so[1], so[2], so[3]);
+}
+
+// Exhaustive check of div_by_count<STEPS> against __fdiv_rn over the whole set a Welford delta can come from:
+// a = +0 and every float with 2^-50 <= |a| <= 256, both signs (blockIdx.y picks the divisor).
+// Why nothing smaller can occur (x = sample, an integer 0..255; m = running mean >= 0; delta = RN(x - m)):
+//   * m becomes non-zero only from m < 1/2 with x >= 1, where delta >= 1/2 and the new m >= (1/2k)(1 - 2^-23);
+//     afterwards a step shrinks it by at most (1 - 1/k)(1 - 2^-23) (x = 0), so after K <= 2^24 frames a non-zero m
+//     is still above 2^-25 e^-2 > 2^-28 -- except k = 1 with x = 0, which gives m = 0 exactly;
+//   * hence for x = 0, |delta| = m is 0 or > 2^-28; for x >= 1, |delta| >= 1/2 when m < 1/2, and otherwise x - m is a
+//     multiple of ulp(1/2)/2 = 2^-25: 0 or >= 2^-25.  RN(x - x) is +0, never -0.
+// 2^-50 leaves 22 binades of margin; quotients and residuals of this set stay far from the subnormal range, which
+// is where the shortcut (like any multiply-by-reciprocal scheme) would stop being exact.
+// mismatches[0] counts, mismatches[1..2] keep one failing (a bits, k).
+template <int STEPS>
+__global__ void k4_fdiv_check_kernel(int k_first, unsigned long long* __restrict__ mismatches) {
+    const float k = (float)(k_first + (int)blockIdx.y);
+    const float r = __frcp_rn(k);
+    const uint32_t lo = 0x26800000u, hi = 0x43800000u;                              // bits of 2^-50 and of 256
+    unsigned bad = 0;
+    uint32_t bad_bits = 0;
+    for (uint64_t i = (uint64_t)lo + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= hi; i += (uint64_t)gridDim.x * blockDim.x) {
+        const float a = __uint_as_float((uint32_t)i);
+        const float want = __fdiv_rn(a, k), got = div_by_count<STEPS>(a, k, r);
+        const float wantn = __fdiv_rn(-a, k), gotn = div_by_count<STEPS>(-a, k, r);
+        if (__float_as_uint(want) != __float_as_uint(got) || __float_as_uint(wantn) != __float_as_uint(gotn)) {
+            bad++;
+            bad_bits = (uint32_t)i;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && __float_as_uint(div_by_count<STEPS>(0.0f, k, r)) != 0u) {
+        bad++;
+        bad_bits = 0;
+    }
+    if (bad) {
+        atomicAdd(&mismatches[0], (unsigned long long)bad);
+        mismatches[1] = bad_bits;
+        mismatches[2] = (unsigned long long)(k_first + (int)blockIdx.y);
+    }
+}
+
 }  // namespace
 
 int abub_k3_gate_hist16(abub_ctx* ctx, const uint8_t* d_f0, const uint8_t* d_f1, uint32_t* d_hist16) {
@@ -161,7 +348,34 @@ int abub_k3_gate_hist16(abub_ctx* ctx, const uint8_t* d_f0, const uint8_t* d_f1,
     return ABUB_OK;
 }
 
+int abub_k3_gate_batch(abub_ctx* ctx, const uint8_t* const* d_pairs, int n, uint32_t* d_hist16) {
+    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_hist16, 0, (size_t)n * 16 * sizeof(uint32_t), ctx->stream));
+    // 32 CTAs x 256 threads x 16 B per sweep of one pair; the event index rides on grid.y
+    for (int e0 = 0; e0 < n; e0 += 65535) {
+        const int ne = n - e0 < 65535 ? n - e0 : 65535;
+        k3_gate_batch_kernel<<<dim3(32, ne), 256, 0, ctx->stream>>>(d_pairs + 2 * (size_t)e0, d_hist16 + 16 * (size_t)e0, ctx->npix);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
+    k3_fill_bin0_batch<<<(n + 127) / 128, 128, 0, ctx->stream>>>(d_hist16, n, (uint32_t)ctx->npix);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    return ABUB_OK;
+}
+
+// d_frame_table holds frames parked by train.cu (cudaMalloc'd chunks, frame stride npix): 16-byte aligned whenever
+// npix is a multiple of 16
 int abub_k4_welford(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint8_t* d_mean, uint8_t* d_sigma) {
+    const bool fast = n <= (1 << 24) && ctx->npix % 16 == 0 && (((uintptr_t)d_mean | (uintptr_t)d_sigma) & 15) == 0 &&
+                      !getenv("ABUB_K4_GENERIC");
+    if (fast) {
+        const size_t nvec = ctx->npix / 16;
+        const unsigned nb = (unsigned)((nvec + 63) / 64);
+        if (n <= ABUB_FDIV1_MAX)
+            k4_welford16_kernel<1><<<nb, 64, 0, ctx->stream>>>(d_frame_table, n, d_mean, d_sigma, nvec);
+        else
+            k4_welford16_kernel<2><<<nb, 64, 0, ctx->stream>>>(d_frame_table, n, d_mean, d_sigma, nvec);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+        return ABUB_OK;
+    }
     const size_t nthreads = (ctx->npix + 3) / 4;
     k4_welford_kernel<<<(unsigned)((nthreads + 127) / 128), 128, 0, ctx->stream>>>(d_frame_table, n, d_mean, d_sigma,
                                                                                   ctx->npix);
@@ -193,3 +407,30 @@ int abub_k4_fixup(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, con
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
 }
+
+// Self-test of the K4 division shortcut: compares div_by_count<steps> with __fdiv_rn for a = +0 and every float a,
+// 2^-50 <= |a| <= 256, and every divisor in [k_first, k_last].  n_mismatch = 0 is the pass condition.
+extern "C" int abub_selftest_fdiv(abub_ctx* ctx, int steps, int k_first, int k_last, unsigned long long* n_mismatch,
+                                  unsigned long long* example) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, (steps == 1 || steps == 2) && k_first >= 1 && k_last >= k_first && k_last - k_first < 65535 && n_mismatch,
+                 "abub_selftest_fdiv");
+    cudaSetDevice(ctx->device);
+    unsigned long long* d = nullptr;
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&d, 3 * sizeof(unsigned long long)));
+    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d, 0, 3 * sizeof(unsigned long long), ctx->stream));
+    const dim3 grid(148 * 2, (unsigned)(k_last - k_first + 1));
+    if (steps == 1) k4_fdiv_check_kernel<1><<<grid, 256, 0, ctx->stream>>>(k_first, d);
+    else k4_fdiv_check_kernel<2><<<grid, 256, 0, ctx->stream>>>(k_first, d);
+    unsigned long long h[3] = {0, 0, 0};
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h, d, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    ABUB_CHECK_CUDA(ctx, e);
+    *n_mismatch = h[0];
+    if (example) { example[0] = h[1]; example[1] = h[2]; }
+    return ABUB_OK;
+}
+
+int abub_k4_fdiv1_max(void) { return ABUB_FDIV1_MAX; }

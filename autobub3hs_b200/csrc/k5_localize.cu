@@ -22,6 +22,7 @@
 //        component's outer border (= in one of its holes), decided by crack parity on the
 //        stored chain
 //   compaction in order -> abub_blob records
+#include <cstdlib>
 #include <cub/cub.cuh>
 
 #include "abub_internal.cuh"
@@ -552,8 +553,11 @@ extern "C" int abub_localize_batch(abub_ctx* ctx, const abub_loc_item* items, in
         ABUB_REQUIRE(ctx, it.trig >= 0 && it.trig < nf && it.pre_trig >= 0 && it.pre_trig < nf, "trig/pre_trig out of range");
         ABUB_REQUIRE(ctx, it.n_post >= 0 && it.n_post <= ABUB_MAX_TRACK && it.trig + it.n_post < nf, "n_post out of range");
     }
-    // chunk so that the TOZERO'd scratch stays around 1 GB
-    size_t max_jobs = ((size_t)1 << 30) / npix;
+    // chunk so that the TOZERO'd scratch stays around 4 GB (ABUB_LOC_SCRATCH_MB overrides): every chunk costs
+    // three stream synchronisations, and 180 GB of HBM leaves room for a whole batch's frames
+    size_t scratch = (size_t)4 << 30;
+    if (const char* e = getenv("ABUB_LOC_SCRATCH_MB")) { const long mb = atol(e); if (mb > 0) scratch = (size_t)mb << 20; }
+    size_t max_jobs = scratch / npix;
     if (max_jobs < ABUB_MAX_TRACK + 1) max_jobs = ABUB_MAX_TRACK + 1;
     std::vector<abub_blob> blobs;
     std::vector<int> npf;

@@ -96,6 +96,125 @@ extern "C" int abub_train_add_slot(abub_ctx* ctx, int cam, int slot, float* entr
     return gate_and_keep(ctx, cam, entropy, kept);
 }
 
+
+// ---- batched forms: one K3 launch and one device->host read for n events --------------------------
+static int ensure_gate(abub_ctx* ctx, int n) {
+    if (n <= ctx->gate_cap) return ABUB_OK;
+    cudaFree((void*)ctx->d_gate_tab);
+    cudaFree(ctx->d_gate_hist);
+    ctx->d_gate_tab = nullptr;
+    ctx->d_gate_hist = nullptr;
+    ctx->gate_cap = 0;
+    const int cap = n + n / 2 + 64;
+    ABUB_CHECK_CUDA(ctx, cudaMalloc((void**)&ctx->d_gate_tab, (size_t)cap * 2 * sizeof(uint8_t*)));
+    ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_gate_hist, (size_t)cap * 16 * sizeof(uint32_t)));
+    ctx->gate_cap = cap;
+    return ABUB_OK;
+}
+
+// gate of n pairs given by host table `pairs` (device pointers); fills e[] and keep[]
+static int gate_batch(abub_ctx* ctx, const std::vector<const uint8_t*>& pairs, int n, std::vector<float>& e,
+                      std::vector<char>& keep) {
+    int rc = ensure_gate(ctx, n);
+    if (rc) return rc;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync((void*)ctx->d_gate_tab, pairs.data(), (size_t)n * 2 * sizeof(uint8_t*),
+                                         cudaMemcpyHostToDevice, ctx->stream));
+    if ((rc = abub_k3_gate_batch(ctx, ctx->d_gate_tab, n, ctx->d_gate_hist))) return rc;
+    std::vector<uint32_t> h((size_t)n * 16);
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(h.data(), ctx->d_gate_hist, h.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                         ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    e.resize(n);
+    keep.resize(n);
+    for (int i = 0; i < n; i++) {
+        e[i] = entropy16(&h[(size_t)i * 16], ctx->npix);
+        keep[i] = e[i] <= 0.0005;                                   // Trainer.cpp:287
+    }
+    return ABUB_OK;
+}
+
+extern "C" int abub_train_add_slots(abub_ctx* ctx, int cam, const int* slots, int n, float* entropy, int* kept) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, cam >= 0 && cam < ctx->ncams && slots && n >= 0, "abub_train_add_slots");
+    ABUB_REQUIRE(ctx, ctx->cam[cam].training, "abub_train_begin not called");
+    if (n == 0) return ABUB_OK;
+    cudaSetDevice(ctx->device);
+    abub_cam_state& cs = ctx->cam[cam];
+    std::vector<const uint8_t*> pairs((size_t)n * 2);
+    for (int i = 0; i < n; i++) {
+        ABUB_REQUIRE(ctx, slots[i] >= 0 && slots[i] < ctx->max_slots, "slot");
+        ABUB_REQUIRE(ctx, ctx->slots[slots[i]].nframes[cam] >= 2, "slot has fewer than 2 frames for this camera");
+        const uint8_t* src = ctx->slots[slots[i]].d_frames + (size_t)cam * ctx->max_frames * ctx->npix;
+        pairs[2 * i] = src;
+        pairs[2 * i + 1] = src + ctx->npix;
+    }
+    std::vector<float> e;
+    std::vector<char> keep;
+    int rc = gate_batch(ctx, pairs, n, e, keep);
+    if (rc) return rc;
+    // park the kept pairs (frames 0 and 1 are adjacent in the slot: one copy per event), in event order
+    for (int i = 0; i < n; i++) {
+        if (entropy) entropy[i] = e[i];
+        if (kept) kept[i] = keep[i];
+        if (!keep[i]) continue;
+        if ((rc = ensure_room(ctx, cs, 2))) return rc;
+        uint8_t* f0 = store_ptr(ctx, cs, cs.n_stored);
+        uint8_t* f1 = store_ptr(ctx, cs, cs.n_stored + 1);
+        if (f1 == f0 + ctx->npix) {
+            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(f0, pairs[2 * i], 2 * ctx->npix, cudaMemcpyDeviceToDevice, ctx->stream));
+        } else {
+            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(f0, pairs[2 * i], ctx->npix, cudaMemcpyDeviceToDevice, ctx->stream));
+            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(f1, pairs[2 * i + 1], ctx->npix, cudaMemcpyDeviceToDevice, ctx->stream));
+        }
+        cs.kept.push_back(f0);
+        cs.kept.push_back(f1);
+        cs.n_stored += 2;
+    }
+    // the slots may be overwritten as soon as this returns
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ABUB_OK;
+}
+
+extern "C" int abub_train_add_events(abub_ctx* ctx, int cam, const uint8_t* frames01, int n, float* entropy, int* kept) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, cam >= 0 && cam < ctx->ncams && frames01 && n >= 0, "abub_train_add_events");
+    ABUB_REQUIRE(ctx, ctx->cam[cam].training, "abub_train_begin not called");
+    if (n == 0) return ABUB_OK;
+    cudaSetDevice(ctx->device);
+    abub_cam_state& cs = ctx->cam[cam];
+    int rc = ensure_room(ctx, cs, 2 * n);
+    if (rc) return rc;
+    // every pair is uploaded to the next free positions; a rejected pair's position is simply not listed in
+    // the frame table (ABUB_TRAIN_CHUNK is even, so a pair never straddles two chunks)
+    std::vector<const uint8_t*> pairs((size_t)n * 2);
+    for (int i = 0; i < n; i++) {
+        uint8_t* f0 = store_ptr(ctx, cs, cs.n_stored + 2 * i);
+        pairs[2 * i] = f0;
+        pairs[2 * i + 1] = f0 + ctx->npix;
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(f0, frames01 + (size_t)i * 2 * ctx->npix, 2 * ctx->npix, cudaMemcpyHostToDevice,
+                                             ctx->stream));
+    }
+    std::vector<float> e;
+    std::vector<char> keep;
+    if ((rc = gate_batch(ctx, pairs, n, e, keep))) return rc;
+    // compact: a kept pair moves down over the holes left by rejected ones (device copy, rarely needed)
+    int w = cs.n_stored;
+    for (int i = 0; i < n; i++) {
+        if (entropy) entropy[i] = e[i];
+        if (kept) kept[i] = keep[i];
+        if (!keep[i]) continue;
+        uint8_t* dst = store_ptr(ctx, cs, w);
+        if (dst != pairs[2 * i])
+            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(dst, pairs[2 * i], 2 * ctx->npix, cudaMemcpyDeviceToDevice, ctx->stream));
+        cs.kept.push_back(dst);
+        cs.kept.push_back(dst + ctx->npix);
+        w += 2;
+    }
+    cs.n_stored = w;
+    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ABUB_OK;
+}
+
 static int upload_table(abub_ctx* ctx, abub_cam_state& cs) {
     const int n = (int)cs.kept.size();
     if (n > cs.table_cap) {

@@ -105,14 +105,20 @@ void Trainer::MakeAvgSigmaImage(bool PerformLBPOnImages) {
         }
         std::lock_guard<std::recursive_mutex> g(dev.lock());
         if (!began) { dev.Check(abub_train_begin(dev.ctx(), camera), "abub_train_begin"); began = true; }
-        for (int e = 0; e < nev; e++) {
-            if (!good[e]) continue;
-            float entropy = 0.f;
-            int kept = 0;
-            dev.Check(abub_train_add_event(dev.ctx(), camera, px.data() + 2 * (size_t)e * npix, &entropy, &kept),
-                      "abub_train_add_event");
-            GateEntropies.push_back(entropy);
-            if (kept) kept_frames += 2;
+        // runs of readable events are contiguous in px: one gate launch and one read-back per run
+        std::vector<float> entropy(nev);
+        std::vector<int> kept(nev);
+        for (int e = 0; e < nev;) {
+            if (!good[e]) { e++; continue; }
+            int e1 = e;
+            while (e1 < nev && good[e1]) e1++;
+            dev.Check(abub_train_add_events(dev.ctx(), camera, px.data() + 2 * (size_t)e * npix, e1 - e, entropy.data() + e,
+                                            kept.data() + e), "abub_train_add_events");
+            for (int i = e; i < e1; i++) {
+                GateEntropies.push_back(entropy[i]);
+                if (kept[i]) kept_frames += 2;
+            }
+            e = e1;
         }
     }
 

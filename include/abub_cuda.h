@@ -128,10 +128,24 @@ int abub_train_begin(abub_ctx* ctx, int cam);
 int abub_train_add_event(abub_ctx* ctx, int cam, const uint8_t* frames01, float* entropy, int* kept);
 /* Same with the two frames taken from a resident slot (frames 0 and 1 of `cam`). */
 int abub_train_add_slot(abub_ctx* ctx, int cam, int slot, float* entropy, int* kept);
+/* Batched forms of the two calls above, for the event loop of Trainer.cpp:262-296 run over many events at
+ * once: n events in the loop's order, one gate launch and one device->host read for all of them;
+ * entropy[n] / kept[n] out (either may be NULL).  abub_train_add_events takes n consecutive
+ * frame pairs (n * 2*rows*cols host bytes, pinned memory makes the upload asynchronous). */
+int abub_train_add_slots(abub_ctx* ctx, int cam, const int* slots, int n, float* entropy, int* kept);
+int abub_train_add_events(abub_ctx* ctx, int cam, const uint8_t* frames01, int n, float* entropy, int* kept);
 /* CalculateMeanSigmaImageVector (Trainer.cpp:144-216): exact sequential float32
  * Welford in push order.  mean/sigma host out (may be NULL), *set_size =
  * TrainingSetSize, *status = 0 or -7 (nothing kept, Trainer.cpp:308-313). */
 int abub_train_finish(abub_ctx* ctx, int cam, uint8_t* mean, uint8_t* sigma, int* set_size, int* status);
+/* Device self-test of the division shortcut inside the Welford kernel (Trainer.cpp:186 divides by the frame count):
+ * the `steps`-step reciprocal-and-correct quotient is compared with the IEEE quotient for a = +0 and every float a,
+ * 2^-50 <= |a| <= 256 (all that a difference sample - mean can be),
+ * and every divisor k_first..k_last; *n_mismatch must come back 0.  example[2] (may be NULL) = {bits of a, k} of
+ * one mismatch.  abub_k4_fdiv1_max() = the largest frame count for which the kernel uses steps = 1. */
+int abub_selftest_fdiv(abub_ctx* ctx, int steps, int k_first, int k_last, unsigned long long* n_mismatch,
+                       unsigned long long* example);
+int abub_k4_fdiv1_max(void);
 /* Multi-GPU: exact integer partial sums (u32 sum x, u64 sum x^2, kept-frame count) of
  * the frames this rank added; device buffers of rows*cols elements owned by the ctx,
  * exposed so that the host can all-reduce them (NCCL sum) in place. */

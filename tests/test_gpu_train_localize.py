@@ -214,3 +214,111 @@ def test_post_trigger_binary_stream_kernel(capi, shape):
                 _check_blobs(o, res[k], ref)
             for k in (1, 4, 10):
                 assert np.array_equal(ctx.localize_binary(k), o.post_trigger_binary(frames[1 + k], avg, sigma)), (shape, trial, k)
+
+
+# ---- K4 fast path (16 px per thread, reciprocal-and-correct division) and batched K3 gate ----------------
+def test_fdiv_shortcut_is_ieee_division_exhaustively(capi):
+    """+0 and every float a with 2^-50 <= |a| <= 256 (the values sample - mean can take) against every frame count the
+    one-step kernel may see; the two-step form (larger counts) on three windows of divisors up to 2^24."""
+    fmax = capi.load().abub_k4_fdiv1_max()
+    with capi.Context(32, 32, 1, 4, max_slots=1) as ctx:
+        for k0 in range(1, fmax + 1, 512):
+            bad, ex = ctx.selftest_fdiv(1, k0, min(k0 + 511, fmax))
+            assert bad == 0, f"one-step quotient differs from IEEE division, e.g. a bits {ex[0]:#x} / {ex[1]}"
+        for k0 in (fmax + 1, 1_000_000, (1 << 24) - 64):
+            bad, ex = ctx.selftest_fdiv(2, k0, k0 + 63)
+            assert bad == 0, f"two-step quotient differs from IEEE division, e.g. a bits {ex[0]:#x} / {ex[1]}"
+
+
+@pytest.mark.parametrize("shape,n", [((48, 64), 2), ((48, 64), 6), ((48, 64), 36), ((64, 80), 300), ((50, 68), 36)])
+def test_welford_fast_path_vs_oracle(capi, shape, n):
+    """Noisy frames (every sample differs) over enough frames to exercise many divisors; (50,68) is the generic kernel."""
+    import oracle.cv2_oracle as o
+    rows, cols = shape
+    rng = np.random.default_rng(1000 + n)
+    base = rng.integers(0, 256, (rows, cols))
+    frames = np.clip(base[None] + rng.normal(0, 9, (n, rows, cols)).round(), 0, 255).astype(np.uint8)
+    pairs = np.stack([frames[0::2], frames[0::2]], axis=1)            # identical pairs pass the gate
+    kept = [f for p in pairs for f in p]
+    with capi.Context(rows, cols, 1, 4, max_slots=1) as ctx:
+        ctx.train_begin(0)
+        e, k = ctx.train_add_events(0, pairs)
+        assert k.all() and np.abs(e).max() <= 1e-6
+        mean, sigma, cnt, st = ctx.train_finish(0)
+    m_ref, s_ref = o.welford_mean_sigma(kept)
+    assert st == 0 and cnt == len(kept)
+    assert np.array_equal(mean, m_ref) and np.array_equal(sigma, s_ref)
+
+
+def test_welford_fast_equals_generic_kernel(capi, monkeypatch):
+    """Same frames through k4_welford16_kernel and the __fdiv_rn kernel (ABUB_K4_GENERIC): identical planes."""
+    rows, cols, n = 96, 128, 500
+    rng = np.random.default_rng(77)
+    frames = rng.integers(0, 256, (n // 2, 1, rows, cols), dtype=np.uint8)
+    pairs = np.concatenate([frames, frames], axis=1)
+    out = []
+    for generic in (False, True):
+        if generic:
+            monkeypatch.setenv("ABUB_K4_GENERIC", "1")
+        else:
+            monkeypatch.delenv("ABUB_K4_GENERIC", raising=False)
+        with capi.Context(rows, cols, 1, 4, max_slots=1) as ctx:
+            ctx.train_begin(0)
+            ctx.train_add_events(0, pairs)
+            out.append(ctx.train_finish(0))
+    assert out[0][2] == out[1][2] == n
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+
+
+def test_train_batched_gate_equals_single_calls(capi, small_run, small_trained):
+    """abub_train_add_events / abub_train_add_slots vs one abub_train_add_event per event and vs the oracle."""
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    nev = len(run.events)
+    with capi.Context(rows, cols, 4, 40, max_slots=nev) as ctx:
+        for s in range(nev):
+            for c in range(4):
+                ctx.event_upload(s, c, np.stack(run.events[s][c]))
+        for c in range(4):
+            ctx.train_begin(c)
+            single = [ctx.train_add_event(c, run.events[ev][c][0], run.events[ev][c][1]) for ev in range(nev)]
+            ref = ctx.train_finish(c)
+            ctx.train_begin(c)
+            pairs = np.stack([np.stack(run.events[ev][c][:2]) for ev in range(nev)])
+            e1, k1 = ctx.train_add_events(c, pairs)
+            got1 = ctx.train_finish(c)
+            ctx.train_begin(c)
+            # two batches, to cross a batch boundary
+            e2a, k2a = ctx.train_add_slots(c, list(range(0, nev // 2)))
+            e2b, k2b = ctx.train_add_slots(c, list(range(nev // 2, nev)))
+            got2 = ctx.train_finish(c)
+            e2, k2 = np.concatenate([e2a, e2b]), np.concatenate([k2a, k2b])
+            for ev in range(nev):
+                assert single[ev][0] == e1[ev] == e2[ev]
+                assert single[ev][1] == bool(k1[ev]) == bool(k2[ev]) == (ev in trained[c].kept_events)
+            for got in (got1, got2):
+                assert got[2:] == ref[2:] == (trained[c].training_set_size, trained[c].status)
+                assert np.array_equal(got[0], trained[c].avg) and np.array_equal(got[1], trained[c].sigma)
+
+
+def test_train_add_events_with_rejected_pairs(capi):
+    """Rejected pairs in the middle of a batch leave no trace in the statistics (compaction of the parked frames)."""
+    import oracle.cv2_oracle as o
+    rows, cols = 48, 64
+    rng = np.random.default_rng(5)
+    quiet = [np.clip(120 + rng.normal(0, 2, (rows, cols)).round(), 0, 255).astype(np.uint8) for _ in range(5)]
+    loud = rng.integers(0, 256, (rows, cols), dtype=np.uint8)
+    dark = rng.integers(0, 30, (rows, cols), dtype=np.uint8)
+    pairs = np.stack([np.stack([quiet[0], quiet[0]]), np.stack([dark, loud]), np.stack([quiet[1], quiet[1]]),
+                      np.stack([dark, loud]), np.stack([dark, loud]), np.stack([quiet[2], quiet[2]])])
+    with capi.Context(rows, cols, 1, 4, max_slots=1) as ctx:
+        ctx.train_begin(0)
+        e, k = ctx.train_add_events(0, pairs)
+        assert k.tolist() == [True, False, True, False, False, True]
+        e2, k2 = ctx.train_add_events(0, pairs[1:3])
+        assert k2.tolist() == [False, True]
+        mean, sigma, cnt, st = ctx.train_finish(0)
+    kept = [quiet[0]] * 2 + [quiet[1]] * 2 + [quiet[2]] * 2 + [quiet[1]] * 2
+    m_ref, s_ref = o.welford_mean_sigma(kept)
+    assert (cnt, st) == (8, 0)
+    assert np.array_equal(mean, m_ref) and np.array_equal(sigma, s_ref)
