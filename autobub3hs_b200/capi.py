@@ -27,6 +27,7 @@ EXPORTS = [
     "abub_train_add_events", "abub_train_finish", "abub_selftest_fdiv", "abub_k4_fdiv1_max",
     "abub_train_partials", "abub_train_allreduce", "abub_train_finish_partials", "abub_train_finish_allreduced",
     "abub_nccl_comm_create", "abub_nccl_comm_destroy", "abub_nccl_barrier",
+    "abub_set_bellows_template", "abub_bellows_track", "abub_bellows_map", "abub_localize_bellows",
     "abub_localize", "abub_localize_batch", "abub_localize_binary", "abub_process_frame",
 ]
 
@@ -101,6 +102,12 @@ def load() -> C.CDLL:
     lib.abub_localize.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(Blob), C.c_int, ip]
     lib.abub_localize_batch.argtypes = [vp, C.POINTER(LocItem), C.c_int, C.POINTER(Blob), C.c_int, ip, ip]
     lib.abub_localize_binary.argtypes = [vp, C.c_int, u8p]
+    fp = C.POINTER(C.c_float)
+    lib.abub_set_bellows_template.argtypes = [vp, C.c_int, u8p, C.c_int, C.c_int]
+    lib.abub_bellows_track.argtypes = [vp, C.c_int, C.c_int, C.c_int, fp, fp, ip]
+    lib.abub_bellows_map.argtypes = [vp, fp, C.c_int, ip, ip]
+    lib.abub_localize_bellows.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, fp, fp, C.POINTER(Blob), C.c_int,
+                                          ip, ip, ip]
     lib.abub_process_frame.argtypes = [vp, C.c_int, u8p, u8p, u8p, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
@@ -355,6 +362,39 @@ class Context:
             out.append(frames)
         assert off == tot.value
         return out
+
+    # ---- bellows veto ----
+    def set_bellows_template(self, cam: int, templ: Optional[np.ndarray]) -> None:
+        if templ is None:
+            self._ck(self.lib.abub_set_bellows_template(self.h, cam, None, 0, 0), "abub_set_bellows_template")
+            return
+        t = _u8(templ)
+        self._ck(self.lib.abub_set_bellows_template(self.h, cam, _p(t), t.shape[0], t.shape[1]), "abub_set_bellows_template")
+
+    def bellows_track(self, slot: int, cam: int, frame: int):
+        """-> (x, y) np.float32, (peak_x, peak_y)"""
+        x, y = C.c_float(), C.c_float()
+        pk = (C.c_int * 2)()
+        self._ck(self.lib.abub_bellows_track(self.h, slot, cam, frame, C.byref(x), C.byref(y), pk), "abub_bellows_track")
+        return (np.float32(x.value), np.float32(y.value)), (pk[0], pk[1])
+
+    def bellows_map(self) -> np.ndarray:
+        r, c = C.c_int(), C.c_int()
+        self._ck(self.lib.abub_bellows_map(self.h, None, 0, C.byref(r), C.byref(c)), "abub_bellows_map")
+        out = np.zeros((r.value, c.value), np.float32)
+        self._ck(self.lib.abub_bellows_map(self.h, out.ctypes.data_as(C.POINTER(C.c_float)), out.size, None, None), "abub_bellows_map")
+        return out
+
+    def localize_bellows(self, slot: int, cam: int, trig: int, pre_trig: int, loc_thres: int, pos_trig, pos_pre, cap: int = 65536):
+        """-> (blobs, status, roi)"""
+        pt = (C.c_float * 2)(float(pos_trig[0]), float(pos_trig[1]))
+        pp = (C.c_float * 2)(float(pos_pre[0]), float(pos_pre[1]))
+        out = (Blob * cap)()
+        n, st = C.c_int(), C.c_int()
+        roi = (C.c_int * 4)()
+        self._ck(self.lib.abub_localize_bellows(self.h, slot, cam, trig, pre_trig, loc_thres, pt, pp, out, cap, C.byref(n),
+                                                C.byref(st), roi), "abub_localize_bellows")
+        return [out[i] for i in range(n.value)], st.value, tuple(roi)
 
     def localize_binary(self, k: int) -> np.ndarray:
         out = np.zeros((self.rows, self.cols), np.uint8)

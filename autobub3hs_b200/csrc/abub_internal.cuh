@@ -32,6 +32,10 @@ struct abub_cam_state {
     int*      d_count = nullptr;    // [0]=kept frames (this rank, then reduced), [1]=flag count
     uint8_t*  d_flag = nullptr;
     bool training = false;
+    // bellows veto (k8_bellows.cu): cam<c>_bellows_template.png, rows padded to a 16-byte pitch
+    uint8_t* d_templ = nullptr;
+    int templ_rows = 0, templ_cols = 0, templ_pitch = 0;
+    double templ_sum2 = 0;
 };
 
 #define ABUB_TRAIN_CHUNK 32
@@ -67,6 +71,7 @@ struct abub_ctx {
     uint32_t* d_gate_hist = nullptr;        // ... and [n][16] histograms
     int gate_cap = 0;
     void*     loc = nullptr;        // localizer arena (k5_localize.cu)
+    void*     bel = nullptr;        // bellows-veto arena (k8_bellows.cu)
     void*     d_tmaps = nullptr;    // CUtensorMap[2*max_slots + 2*ncams] (k1_trigger_tma.cu); null = TMA path off
 };
 
@@ -132,3 +137,6 @@ int abub_k1_launch_genesis_jobs(abub_ctx* ctx, const abub_loc_job* d_jobs, int n
 // K5-K7 (k5_localize.cu)
 int abub_loc_init(abub_ctx* ctx);
 void abub_loc_free(abub_ctx* ctx);
+int abub_loc_run_prepared(abub_ctx* ctx, const uint8_t* d_over, int tozero, abub_blob* out, int cap, int* n_out);
+// K8 (k8_bellows.cu)
+void abub_bel_free(abub_ctx* ctx);

@@ -75,11 +75,13 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     abub_loc_free(ctx);
+    abub_bel_free(ctx);
     for (int c = 0; c < ABUB_MAX_CAMS; c++) {
         abub_cam_state& cs = ctx->cam[c];
         cudaFree(cs.d_mean); cudaFree(cs.d_sigma); cudaFree(cs.d_t8); cudaFree(cs.d_k32); cudaFree(cs.d_k16);
         cudaFree(cs.d_sum); cudaFree(cs.d_sumsq); cudaFree(cs.d_count); cudaFree(cs.d_flag);
         cudaFree((void*)cs.d_table);
+        cudaFree(cs.d_templ);
         train_release(cs);
     }
     for (auto& s : ctx->slots) {

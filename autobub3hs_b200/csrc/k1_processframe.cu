@@ -414,7 +414,7 @@ __global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_single_kernel(const uint
 __global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_genesis_jobs_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols, int th, int nxg) {
     extern __shared__ __align__(16) uint32_t smem[];
     const abub_loc_job job = jobs[blockIdx.y];
-    if (!job.genesis) return;
+    if (job.genesis != 1) return;
     uint32_t* sh_hist = smem;
     const int warp = threadIdx.x >> 5;
     uint32_t* xch = smem + 256 + warp * K1_WARP_WORDS;

@@ -198,6 +198,25 @@ k5_post_stream_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols,
 // ------------------------------------------------------------------------------------
 // K5c: Otsu (OpenCV getThreshVal_Otsu_8u), one thread per job; also fills bin 0
 // ------------------------------------------------------------------------------------
+// Prepared jobs (genesis == 2; the bellows veto, k8_bellows.cu): `a` already holds overTheSigma; THRESH_TOZERO at
+// job.tozero (L3Localizer.cpp:365) + histogram of the non-zero bytes.  grid.y = job, other jobs return.
+__global__ void __launch_bounds__(256) k5_prepared_kernel(const abub_loc_job* __restrict__ jobs, size_t npix) {
+    const abub_loc_job job = jobs[blockIdx.y];
+    if (job.genesis != 2) return;
+    __shared__ uint32_t sh[256];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    const int t = job.tozero;
+    for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += (size_t)gridDim.x * blockDim.x) {
+        const uint8_t v = job.a[p];
+        const uint8_t o = v > t ? v : 0;
+        job.tz[p] = o;
+        if (o) atomicAdd(&sh[o], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x > 0 && sh[threadIdx.x]) atomicAdd(&job.hist[threadIdx.x], sh[threadIdx.x]);
+}
+
 __global__ void k5_otsu_kernel(const abub_loc_job* __restrict__ jobs, int* __restrict__ thr, int njobs, uint32_t npix) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= njobs) return;
@@ -459,7 +478,8 @@ static int ensure_cands(abub_ctx* ctx, LocArena* a, int n) {
 }
 
 // one chunk of jobs already described in a->h_jobs[0..njobs)
-static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blob>& blobs_out, std::vector<int>& npf_out) {
+static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blob>& blobs_out, std::vector<int>& npf_out,
+                     bool has_prepared = false) {
     cudaStream_t st = ctx->stream;
     const size_t npix = ctx->npix;
     int rc;
@@ -475,6 +495,10 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     } else {
         dim3 grid((ctx->cols + PT_W - 1) / PT_W, (ctx->rows + PT_H - 1) / PT_H, njobs);
         k5_post_kernel<<<grid, 256, 0, st>>>(a->d_jobs, ctx->rows, ctx->cols);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
+    if (has_prepared) {
+        k5_prepared_kernel<<<dim3(148 * 2, njobs), 256, 0, st>>>(a->d_jobs, npix);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     k5_otsu_kernel<<<(njobs + 63) / 64, 64, 0, st>>>(a->d_jobs, a->d_thr, njobs, (uint32_t)npix);
@@ -609,6 +633,38 @@ extern "C" int abub_localize_batch(abub_ctx* ctx, const abub_loc_item* items, in
     if (n_total) *n_total = written;
     if (written > cap) {
         ctx->err = "abub_localize_batch: output capacity too small (" + std::to_string(written) + " blobs)";
+        return ABUB_E_CAPACITY;
+    }
+    return ABUB_OK;
+}
+
+// One prepared frame (d_over = overTheSigma already on the device): TOZERO at `tozero`, Otsu, every external contour.
+// Used by the bellows veto (k8_bellows.cu); blobs come back with k = 0 in findContours order.
+int abub_loc_run_prepared(abub_ctx* ctx, const uint8_t* d_over, int tozero, abub_blob* out, int cap, int* n_out) {
+    LocArena* a = arena_of(ctx);
+    int rc;
+    if ((rc = ensure_jobs(ctx, a, 1))) return rc;
+    abub_loc_job& jb = a->h_jobs[0];
+    memset(&jb, 0, sizeof(jb));
+    jb.a = d_over;
+    jb.tz = a->d_tz;
+    jb.hist = a->d_hist;
+    jb.tozero = tozero;
+    jb.genesis = 2;
+    std::vector<abub_blob> blobs;
+    std::vector<int> npf;
+    if ((rc = run_chunk(ctx, a, 1, blobs, npf, true))) return rc;
+    int written = 0;
+    for (const abub_blob& b : blobs) {
+        if (written < cap) {
+            out[written] = b;
+            out[written].reserved = 0;
+        }
+        written++;
+    }
+    if (n_out) *n_out = written;
+    if (written > cap) {
+        ctx->err = "bellows veto: output capacity too small (" + std::to_string(written) + " blobs)";
         return ABUB_E_CAPACITY;
     }
     return ABUB_OK;

@@ -26,6 +26,8 @@ FRAME_OFFSET = 30
 RUN_ID = "20210101_0"
 
 EVENT_CLASSES = ("normal", "multi", "notrigger", "late", "short4", "short5", "flicker", "highnoise")
+# classes that need a run made with bellows_object=True (cameras 1 and 3 show a moving bellows, L3Localizer.cpp:292-390)
+BELLOWS_CLASSES = ("bellows", "bellows_bubble")
 
 
 @dataclass
@@ -46,6 +48,7 @@ class EventSpec:
     noise_sigma: float = 2.0
     bubbles: Dict[int, List[BubbleSpec]] = field(default_factory=dict)   # per camera
     flicker_frame: int = -1
+    bellows_move: Dict[int, Tuple[int, int, int]] = field(default_factory=dict)   # per camera (f_move, dx, dy) per step
 
 
 def _rng(*key: int) -> np.random.Generator:
@@ -89,6 +92,26 @@ def make_background(cam: int, rows: int = ROWS, cols: int = COLS) -> np.ndarray:
     return np.clip(np.rint(base), 0, 255).astype(np.uint8)
 
 
+def make_bellows_object(cam: int, rows: int = ROWS, cols: int = COLS):
+    """(pattern u8 [th, tw], (x, y) rest position) of the bellows seen by an odd camera, None for the others.
+    Sizes follow the reference templates (cam1 557x178, cam3 509x152 at 1050x1680); horizontal ridges + fixed texture."""
+    if cam % 2 == 0:
+        return None
+    th = int(rows * (0.53 if cam == 1 else 0.485))
+    tw = int(cols * (0.106 if cam == 1 else 0.0905))
+    rng = _rng(777, cam)
+    yy, xx = np.mgrid[0:th, 0:tw].astype(np.float32)
+    period = max(6.0, rows / 40.0)
+    pat = 62.0 + 50.0 * np.sin(2 * np.pi * yy / period + 0.8 * np.sin(xx / tw * 3.0)) + 5.0 * rng.standard_normal((th, tw))
+    pat *= (0.75 + 0.25 * np.cos((xx / tw - 0.5) * 2.2))
+    pat = np.clip(np.rint(pat), 4, 123).astype(np.uint8)
+    sx0, sx1 = int(cols * 0.80), cols - 1
+    sy0, sy1 = int(rows * 0.11), int(rows * 0.87)
+    x = sx0 + (sx1 - sx0 - tw) // 2
+    y = sy0 + (sy1 - sy0 - th) // 2
+    return pat, (x, y)
+
+
 def _pick_centres(rng, n, cam_mask, bellows_mask, margin=40):
     rows, cols = cam_mask.shape
     ok = (cam_mask > 0) & (bellows_mask == 0)
@@ -122,6 +145,20 @@ def make_event_spec(event: int, klass: str, cam_masks, bellows_masks, seed: int 
         es.nframes = 5
     if klass == "flicker":
         es.flicker_frame = int(rng.integers(lo, hi))
+    if klass in BELLOWS_CLASSES:
+        f_move = int(rng.integers(lo, hi))
+        for c in range(ncams):
+            if c % 2 == 1:
+                es.bellows_move[c] = (f_move, int(rng.integers(0, 2)), int(rng.integers(1, 3)))
+                if klass == "bellows_bubble":
+                    # a bubble beside the bellows, inside both the camera mask and the bellows mask
+                    ok = (cam_masks[c] > 0) & (bellows_masks[c] > 0)
+                    obj = make_bellows_object(c, rows, cols)
+                    ok[:, obj[1][0] - 6:] = False
+                    ys, xs = np.nonzero(ok)
+                    if len(xs):
+                        i = int(rng.integers(0, len(xs)))
+                        es.bubbles[c] = [BubbleSpec(float(xs[i]), float(ys[i]), 2.0, 1.0, 120, f_move)]
     nb = {"normal": (1, 4), "multi": (20, 27), "highnoise": (1, 4), "late": (1, 3)}.get(klass)
     if nb is not None:
         f_trig = 0 if klass == "late" else int(rng.integers(lo, hi))
@@ -137,14 +174,24 @@ def make_event_spec(event: int, klass: str, cam_masks, bellows_masks, seed: int 
     return es
 
 
-def render_camera(es: EventSpec, cam: int, background: np.ndarray, seed: int = 0) -> np.ndarray:
-    """[nframes, rows, cols] u8 stack of one camera of one event."""
+def render_camera(es: EventSpec, cam: int, background: np.ndarray, seed: int = 0, bellows_object=None) -> np.ndarray:
+    """[nframes, rows, cols] u8 stack of one camera of one event.  `bellows_object` = make_bellows_object(cam, ...):
+    pasted (opaque) at its rest position, displaced by up to 3 steps from the event's f_move on."""
     rows, cols = background.shape
     rng = _rng(101, seed, es.event, cam)
     out = np.empty((es.nframes, rows, cols), np.uint8)
     bg = background.astype(np.float32)
     for f in range(es.nframes):
-        img = bg + rng.standard_normal((rows, cols), dtype=np.float32) * np.float32(es.noise_sigma)
+        scene = bg
+        if bellows_object is not None:
+            pat, (bx, by) = bellows_object
+            mv = es.bellows_move.get(cam)
+            if mv is not None and f >= mv[0]:
+                k = min(f - mv[0] + 1, 3)
+                bx, by = bx + k * mv[1], by + k * mv[2]
+            scene = bg.copy()
+            scene[by:by + pat.shape[0], bx:bx + pat.shape[1]] = pat
+        img = scene + rng.standard_normal((rows, cols), dtype=np.float32) * np.float32(es.noise_sigma)
         if f == es.flicker_frame:
             img += 8.0
         for b in es.bubbles.get(cam, ()):
@@ -170,20 +217,25 @@ class SyntheticRun:
     bellows_masks: List[np.ndarray]
     backgrounds: List[np.ndarray]
     frame_offset: int = FRAME_OFFSET
+    bellows_templates: Optional[List[Optional[np.ndarray]]] = None   # cam<c>_bellows_template.png (bellows_object runs)
 
 
 def make_run(n_events: int, classes: Optional[Sequence[str]] = None, rows: int = ROWS, cols: int = COLS,
-             ncams: int = NCAMS, nframes: int = NFRAMES, seed: int = 0, run_id: str = RUN_ID) -> SyntheticRun:
-    """`classes[i]` = class of event i (cycled); default all "normal"."""
+             ncams: int = NCAMS, nframes: int = NFRAMES, seed: int = 0, run_id: str = RUN_ID,
+             bellows_object: bool = False) -> SyntheticRun:
+    """`classes[i]` = class of event i (cycled); default all "normal".  bellows_object=True puts the bellows of
+    make_bellows_object into every frame of cameras 1 and 3 and provides their templates (BELLOWS_CLASSES move it)."""
     cam_masks, bellows = make_masks(rows, cols, ncams)
     bgs = [make_background(c, rows, cols) for c in range(ncams)]
+    objs = [make_bellows_object(c, rows, cols) if bellows_object else None for c in range(ncams)]
     classes = list(classes) if classes else ["normal"]
     specs, events = [], []
     for ev in range(n_events):
         es = make_event_spec(ev, classes[ev % len(classes)], cam_masks, bellows, seed, nframes)
         specs.append(es)
-        events.append([render_camera(es, c, bgs[c], seed) for c in range(ncams)])
-    return SyntheticRun(run_id, list(range(n_events)), specs, events, cam_masks, bellows, bgs)
+        events.append([render_camera(es, c, bgs[c], seed, objs[c]) for c in range(ncams)])
+    templates = [None if o is None else o[0] for o in objs] if bellows_object else None
+    return SyntheticRun(run_id, list(range(n_events)), specs, events, cam_masks, bellows, bgs, FRAME_OFFSET, templates)
 
 
 # ---------------------------------------------------------------------------------------
@@ -203,6 +255,20 @@ def write_bmp8(path: str, img: np.ndarray) -> None:
         f.write(hdr + dib + pal + body.tobytes())
 
 
+def write_png8(path: str, img: np.ndarray) -> None:
+    """8-bit greyscale PNG (filter 0 on every row) -- for cam<c>_bellows_template.png (L3Localizer.cpp:294)."""
+    import zlib
+    rows, cols = img.shape
+
+    def chunk(tag: bytes, data: bytes) -> bytes:
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    raw = b"".join(b"\x00" + np.ascontiguousarray(img[r]).tobytes() for r in range(rows))
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", cols, rows, 8, 0, 0, 0, 0))
+                + chunk(b"IDAT", zlib.compress(raw, 6)) + chunk(b"IEND", b""))
+
+
 def write_run(run: SyntheticRun, data_dir: str, mask_dir: Optional[str] = None) -> str:
     """Writes ``<data_dir>/<run>/<ev>/Images/cam{c}_image{30+f}.bmp`` (+ masks) and returns the run dir."""
     rdir = os.path.join(data_dir, run.run_id)
@@ -217,4 +283,6 @@ def write_run(run: SyntheticRun, data_dir: str, mask_dir: Optional[str] = None) 
         for c in range(len(run.cam_masks)):
             write_bmp8(os.path.join(mask_dir, f"cam{c}_mask.bmp"), run.cam_masks[c])
             write_bmp8(os.path.join(mask_dir, f"cam{c}_bellows_mask.bmp"), run.bellows_masks[c])
+            if run.bellows_templates is not None and run.bellows_templates[c] is not None:
+                write_png8(os.path.join(mask_dir, f"cam{c}_bellows_template.png"), run.bellows_templates[c])
     return rdir

@@ -166,6 +166,29 @@ int abub_train_finish_partials(abub_ctx* ctx, int cam, uint8_t* mean, uint8_t* s
 int abub_train_finish_allreduced(abub_ctx* ctx, int cam, void* nccl_comm, uint8_t* mean, uint8_t* sigma,
                                  int* set_size, int* status, int* n_flagged);
 
+/* ---- bellows veto: L3Localizer.cpp:292-390 (taken when every genesis contour lies in the bellows mask) ---- */
+/* The camera's cam<c>_bellows_template.png as rows*cols grey bytes (L3Localizer.cpp:294-295); NULL clears it
+ * ("template not loadable", :297-301). */
+int abub_set_bellows_template(abub_ctx* ctx, int cam, const uint8_t* templ, int trows, int tcols);
+/* L3Localizer::TrackAFeature (L3Localizer.cpp:473-543) on frame `frame` of (slot, cam): matchTemplate(CCORR_NORMED)
+ * over the whole frame, min-max normalisation, first maximum, 3x3 value-weighted centroid in float.
+ * x, y = BestMatchLoc; peak_xy[2] (may be NULL) = the integer maximum.  The numerators are exact integers here,
+ * OpenCV's come from a float32 DFT: the map agrees to ~1e-6 and the position to ~1e-3 px.
+ * ABUB_E_INVALID when the maximum lies on the edge of the map (the reference reads out of bounds there). */
+int abub_bellows_track(abub_ctx* ctx, int slot, int cam, int frame, float* x, float* y, int* peak_xy);
+/* The CCORR_NORMED map of the last abub_bellows_track ((rows-th+1) x (cols-tw+1) floats, before normalisation);
+ * out may be NULL to query the size. */
+int abub_bellows_map(abub_ctx* ctx, float* out, int cap, int* map_rows, int* map_cols);
+/* Block :303-390 given the two TrackAFeature results (pos_trig / pos_pre = {x, y} as returned, before the
+ * one-pixel nudge of :316-323): the template is pasted at both positions, ProcessFrame on their overlap ROI
+ * (GetDiffROI, :462-470) gives the bellows-motion model, which is subtracted from overTheSigma of (trig, pre_trig);
+ * then TOZERO(loc_thres), Otsu and findContours as before.  out / *n_out = every external contour (k = 0), in
+ * findContours order, with no bellows-mask filtering (:374-389).  *status = 0, or -6 where the reference throws
+ * (a Rect outside the frame or an empty ROI).  roi_out[4] (may be NULL) = the ROI {x, y, w, h}. */
+int abub_localize_bellows(abub_ctx* ctx, int slot, int cam, int trig, int pre_trig, int loc_thres,
+                          const float* pos_trig, const float* pos_pre, abub_blob* out, int cap, int* n_out,
+                          int* status, int* roi_out);
+
 /* ---- NCCL plumbing for a process-per-GPU host (nothing in the reference: it is one OpenMP process) ----- */
 /* ncclCommInitRank with the unique id published by rank 0 through `id_file` (written atomically, removed by
  * rank 0 once the communicator exists).  *comm receives the ncclComm_t. */

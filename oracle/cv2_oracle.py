@@ -41,6 +41,24 @@ def process_frame(work: np.ndarray, prev: np.ndarray, sigma: np.ndarray,
     return cv2.absdiff(pos, neg)                             # :370
 
 
+def process_frame_roi(work: np.ndarray, prev: np.ndarray, sigma: np.ndarray, roi, blur_diam: int = 5) -> np.ndarray:
+    """AnalyzerUnit.cpp:346-377 with a ROI (x, y, w, h): the MatExpr results are fresh ROI-sized matrices, so the
+    blur reflects at the ROI's own edges; outside the ROI the result is zero (:349, :370).  A ROI that leaves the
+    frame makes cv::Mat::operator() throw (caught in AnyCamAnalysis -> -6)."""
+    x, y, w, h = roi
+    rows, cols = work.shape
+    if not (0 <= x and 0 <= w and x + w <= cols and 0 <= y and 0 <= h and y + h <= rows):
+        raise ValueError("ROI outside the frame (cv::Mat::operator() assertion)")
+    if w == 0 or h == 0:
+        raise ValueError("empty ROI (cv::GaussianBlur asserts on an empty matrix)")
+    out = np.zeros_like(work)                                # :349
+    cw = np.ascontiguousarray(work[y:y + h, x:x + w])
+    cp = np.ascontiguousarray(prev[y:y + h, x:x + w])
+    cs = np.ascontiguousarray(sigma[y:y + h, x:x + w])
+    out[y:y + h, x:x + w] = process_frame(cw, cp, cs, blur_diam)
+    return out
+
+
 # ----------------------------------------------------------------------------
 # a2  calcHist, 256 bins, no mask  (AnalyzerUnit.cpp:441-456)
 # ----------------------------------------------------------------------------
@@ -436,20 +454,117 @@ def _measure(c: np.ndarray, genesis: bool) -> BubbleImageFrame:
 # a8  L3Localizer::CalculateInitialBubbleParams  (L3Localizer.cpp:215-460)
 # ----------------------------------------------------------------------------
 class BellowsBranchTaken(Exception):
-    """Raised when every genesis contour lies in the bellows mask (a14, deferred)."""
+    """Kept for callers that want to know: never raised since the bellows veto (a14) is restated below."""
 
 
-def genesis_binary(trig_frame, pre_frame, sigma, loc_thres) -> np.ndarray:
-    over = process_frame(trig_frame, pre_frame, sigma, 5)                        # :232
-    _, thr = cv2.threshold(over, loc_thres, 255, cv2.THRESH_TOZERO)              # :252
-    _, thr = cv2.threshold(thr, 0, 255, cv2.THRESH_BINARY | cv2.THRESH_OTSU)     # :254
+def genesis_over_the_sigma(trig_frame, pre_frame, sigma) -> np.ndarray:
+    return process_frame(trig_frame, pre_frame, sigma, 5)                        # :232
+
+
+def binarise_over_the_sigma(over, loc_thres) -> np.ndarray:
+    _, thr = cv2.threshold(over, loc_thres, 255, cv2.THRESH_TOZERO)              # :252 / :365
+    _, thr = cv2.threshold(thr, 0, 255, cv2.THRESH_BINARY | cv2.THRESH_OTSU)     # :254 / :367
     return thr
 
 
+def genesis_binary(trig_frame, pre_frame, sigma, loc_thres) -> np.ndarray:
+    return binarise_over_the_sigma(genesis_over_the_sigma(trig_frame, pre_frame, sigma), loc_thres)
+
+
+# ---- a14  bellows veto: TrackAFeature / GetDiffROI / block :292-390 -------------------------------------
+def ccorr_normed_map(frame: np.ndarray, templ: np.ndarray) -> np.ndarray:
+    """cv::matchTemplate(CV_TM_CCORR_NORMED) (L3Localizer.cpp:500), float32 [rows-th+1, cols-tw+1]."""
+    return cv2.matchTemplate(frame, templ, cv2.TM_CCORR_NORMED)
+
+
+def subpixel_from_map(result: np.ndarray):
+    """L3Localizer.cpp:501-540 on a correlation map: min-max normalisation to [0,1] (:501), first maximum in raster
+    order (:507), 3x3 value-weighted centroid accumulated in float (:522-533).  Returns (x, y) as np.float32 and the
+    integer peak.  The reference reads the 3x3 neighbourhood without a bounds check; a peak on the map's edge is
+    undefined behaviour there and an IndexError here."""
+    res = cv2.normalize(result, None, 0, 1, cv2.NORM_MINMAX, -1)
+    _, _, _, max_loc = cv2.minMaxLoc(res)
+    mx, my = int(max_loc[0]), int(max_loc[1])
+    if not (1 <= mx < res.shape[1] - 1 and 1 <= my < res.shape[0] - 1):
+        raise IndexError("correlation peak on the edge of the map")
+    sx = F32(0.0)
+    sy = F32(0.0)
+    total = F32(0.0)
+    for i in (-1, 0, 1):                                   # :522 i = x offset (outer), j = y offset (inner)
+        for j in (-1, 0, 1):
+            v = F32(res[my + j, mx + i])
+            sx = F32(sx + F32(F32(mx + i) * v))            # Point2f * float, then +=
+            sy = F32(sy + F32(F32(my + j) * v))
+            total = F32(total + v)
+    with np.errstate(all="ignore"):
+        inv = F32(F64(1.0) / F64(total))                   # :531  double division stored to float
+    x = F32(F32(sx * inv) + F32(0))                        # :532, :538 (+ TemplateSearchZone.x = 0)
+    y = F32(F32(sy * inv) + F32(0))
+    return x, y, (mx, my)
+
+
+def track_a_feature(frame: np.ndarray, templ: np.ndarray):
+    """L3Localizer::TrackAFeature (L3Localizer.cpp:473-543): (x, y) float32 of the best template match."""
+    x, y, _ = subpixel_from_map(ccorr_normed_map(frame, templ))
+    return x, y
+
+
+def nudge_apart(pos_trig, pos_pre):
+    """:316-323  the two x positions are pushed one pixel apart (float ++ / --)."""
+    tx, ty = pos_trig
+    px, py = pos_pre
+    if tx >= px:
+        tx = F32(tx + F32(1))
+        px = F32(px - F32(1))
+    else:
+        tx = F32(tx - F32(1))
+        px = F32(px + F32(1))
+    return (tx, ty), (px, py)
+
+
+def get_diff_roi(p1, p2, templ_shape):
+    """L3Localizer::GetDiffROI (:462-470): float arithmetic, truncated into ints."""
+    th, tw = templ_shape
+    start_x = int(max(F32(p1[0]), F32(p2[0])))
+    start_y = int(max(F32(p1[1]), F32(p2[1])))
+    delta_x = int(F32(F32(min(F32(p1[0]), F32(p2[0])) + F32(tw)) - F32(start_x)))
+    delta_y = int(F32(F32(min(F32(p1[1]), F32(p2[1])) + F32(th)) - F32(start_y)))
+    return start_x, start_y, delta_x, delta_y
+
+
+def _paste(shape, templ, pos):
+    """:347-349  Mat::zeros + TemplateImage.copyTo(frame(Rect(x, y, tw, th))) with Rect built from floats (truncation)."""
+    rows, cols = shape
+    th, tw = templ.shape
+    x, y = int(pos[0]), int(pos[1])
+    if not (0 <= x and x + tw <= cols and 0 <= y and y + th <= rows):
+        raise ValueError("template pasted outside the frame (cv::Mat::operator() assertion)")
+    out = np.zeros(shape, np.uint8)
+    out[y:y + th, x:x + tw] = templ
+    return out
+
+
+def bellows_veto(over, trig_frame, pre_frame, sigma, templ, positions=None):
+    """Block :303-364: returns overTheSigma with the bellows-motion model subtracted, and the positions used.
+    `positions` = ((tx,ty),(px,py)) float32 from TrackAFeature; computed with cv2 when None."""
+    if positions is None:
+        positions = (track_a_feature(trig_frame, templ), track_a_feature(pre_frame, templ))   # :313-314
+    pos_trig, pos_pre = nudge_apart(*positions)
+    trig_copy = _paste(trig_frame.shape, templ, pos_trig)                        # :347
+    pre_copy = _paste(pre_frame.shape, templ, pos_pre)                           # :349
+    roi = get_diff_roi(pos_trig, pos_pre, templ.shape)                           # :355
+    diff = process_frame_roi(trig_copy, pre_copy, sigma, roi, 5)                 # :356
+    return cv2.subtract(over, diff), (pos_trig, pos_pre, roi)                    # :363 saturating -=
+
+
 def calculate_initial_bubble_params(trig_frame, pre_frame, sigma, loc_thres,
-                                    cam_mask, bellows_mask, mask_dir_set=True):
-    """Returns (list of genesis BubbleImageFrame that become bubbles, all measured blobs)."""
-    thr = genesis_binary(trig_frame, pre_frame, sigma, loc_thres)
+                                    cam_mask, bellows_mask, mask_dir_set=True, bellows_template=None,
+                                    info: Optional[dict] = None):
+    """Returns the list of genesis BubbleImageFrame that become bubbles.  `bellows_template`: the camera's
+    cam<c>_bellows_template.png (None = not loadable, :297-301).  `info` (optional dict) receives what the bellows
+    branch did."""
+    over = genesis_over_the_sigma(trig_frame, pre_frame, sigma)
+    thr = binarise_over_the_sigma(over, loc_thres)
     contours = find_external_contours(thr)                                       # :264
     rects = []
     kept = []
@@ -463,8 +578,20 @@ def calculate_initial_bubble_params(trig_frame, pre_frame, sigma, loc_thres,
                 largest = r[2] * r[3]
             kept.append(c)
             rects.append(r)
-    if all_in_bellows:
-        raise BellowsBranchTaken()
+    if info is not None:
+        info["bellows_branch"] = bool(all_in_bellows)
+    if all_in_bellows:                                                           # :292-390
+        if bellows_template is not None:
+            over, used = bellows_veto(over, trig_frame, pre_frame, sigma, bellows_template)
+            thr = binarise_over_the_sigma(over, loc_thres)                       # :365-367
+            if info is not None:
+                info["bellows_positions"] = used
+        kept = find_external_contours(thr)                                       # :374 (all of them, no bellows filter)
+        rects = [cv2.boundingRect(c) for c in kept]
+        largest = 0
+        for r in rects:                                                          # :383-389
+            if largest < r[2] * r[3]:
+                largest = r[2] * r[3]
     out = []
     for c, r in zip(kept, rects):                                                # :392-444
         box_area = r[2] * r[3]
@@ -518,7 +645,8 @@ def track_candidates(bubbles: List[Bubble], cands: List[BubbleImageFrame]) -> No
 # a11  L3Localizer::LocalizeOMatic  (L3Localizer.cpp:881-968)
 # ----------------------------------------------------------------------------
 def localize_o_matic(src: FrameSource, trained: TrainedData, trig: int, loc_thres: int,
-                     cam_mask, bellows_mask, bubbles: List[Bubble], mask_dir_set=True) -> bool:
+                     cam_mask, bellows_mask, bubbles: List[Bubble], mask_dir_set=True, bellows_template=None,
+                     info: Optional[dict] = None) -> bool:
     """Appends to `bubbles` (AnalyzerUnit::BubbleList).  Returns okToProceed."""
     n = len(src)
     if n <= 5:                                                                   # :889
@@ -526,7 +654,7 @@ def localize_o_matic(src: FrameSource, trained: TrainedData, trig: int, loc_thre
     prev_offset = 1 if trained.training_set_size < 6 else 2                      # :919-926
     pre = max(0, trig - prev_offset)                                             # :932-933
     for g in calculate_initial_bubble_params(src.frames[trig], src.frames[pre], trained.sigma,
-                                             loc_thres, cam_mask, bellows_mask, mask_dir_set):
+                                             loc_thres, cam_mask, bellows_mask, mask_dir_set, bellows_template, info):
         bubbles.append(Bubble(g))
     kmax = NUM_FRAMES_BUBBLE_TRACK if trig < 29 else 39 - trig                   # :944-954
     for k in range(1, kmax + 1):
@@ -630,10 +758,11 @@ def write_camera_output(run: str, cams: List[CameraOutput], frame_offset: int) -
 class CamAnalysis:
     out: CameraOutput
     triggers: List[TriggerResult] = field(default_factory=list)
+    bellows: List[dict] = field(default_factory=list)        # one per LocalizeOMatic call: what the a14 branch did
 
 
 def any_cam_analysis(src: FrameSource, trained: TrainedData, cam_mask, bellows_mask,
-                     event_number: int, mask_dir_set: bool = True) -> CamAnalysis:
+                     event_number: int, mask_dir_set: bool = True, bellows_template=None) -> CamAnalysis:
     st = SignificanceState()
     hp = HistProvider(src, trained.sigma)
     bubbles: List[Bubble] = []
@@ -648,8 +777,10 @@ def any_cam_analysis(src: FrameSource, trained: TrainedData, cam_mask, bellows_m
             mat_trig = tr.trig
             ok = ok and tr.ok
             if ok:
+                info: dict = {}
                 ok = localize_o_matic(src, trained, mat_trig, tr.loc_thres, cam_mask,
-                                      bellows_mask, bubbles, mask_dir_set)  # :94
+                                      bellows_mask, bubbles, mask_dir_set, bellows_template, info)  # :94
+                res.bellows.append(info)
                 if ok:
                     res.out = stage_camera_output(bubbles, mat_trig, event_number)  # :97
                 else:
@@ -660,8 +791,6 @@ def any_cam_analysis(src: FrameSource, trained: TrainedData, cam_mask, bellows_m
                 break
             if len(bubbles) != 0:                                                     # :110
                 break
-    except BellowsBranchTaken:
-        raise
     except Exception:                                                                 # :114-118
         res.out = CameraOutput(-6, 0, event_number)
     return res
@@ -680,7 +809,7 @@ def train_all(run_events: Sequence[Sequence[Optional[np.ndarray]]], ncams: int) 
 
 
 def run_detect(run: str, event_numbers: Sequence[int], run_events, trained: List[TrainedData],
-               cam_masks, bellows_masks, frame_offset: int = 30) -> Tuple[str, list]:
+               cam_masks, bellows_masks, frame_offset: int = 30, bellows_templates=None) -> Tuple[str, list]:
     """Detect loop of main (AutoBubStart3.cpp:342-388): returns the text appended after
     the header and the per-(event,cam) analysis records."""
     text = []
@@ -691,7 +820,8 @@ def run_detect(run: str, event_numbers: Sequence[int], run_events, trained: List
         rr = []
         for cam in range(ncams):
             a = any_cam_analysis(FrameSource(ev[cam]), trained[cam], cam_masks[cam],
-                                 bellows_masks[cam], evn)
+                                 bellows_masks[cam], evn, True,
+                                 None if bellows_templates is None else bellows_templates[cam])
             cams.append(a.out)
             rr.append(a)
         text.append(write_camera_output(run, cams, frame_offset))

@@ -31,8 +31,10 @@ def n_post_frames(trig: int, nframes: int) -> int:
     return n
 
 
-def genesis_from_blobs(blobs, cam_mask, bellows_mask):
-    """CalculateInitialBubbleParams bookkeeping (L3Localizer.cpp:273-290, 392-444)."""
+def genesis_from_blobs(blobs, cam_mask, bellows_mask, bellows_veto=None):
+    """CalculateInitialBubbleParams bookkeeping (L3Localizer.cpp:273-290, 392-444).  `bellows_veto` is called when
+    every contour lies in the bellows mask (:292-390) and returns the blobs of the re-binarised frame, or None when
+    the camera has no template (the reference then re-reads the contours it already had, :374)."""
     kept, largest = [], 0
     all_in_bellows = len(blobs) > 0
     for b in blobs:
@@ -41,7 +43,11 @@ def genesis_from_blobs(blobs, cam_mask, bellows_mask):
             largest = max(largest, b.w * b.h)
             kept.append(b)
     if all_in_bellows:
-        raise o.BellowsBranchTaken()
+        again = bellows_veto() if bellows_veto is not None else None
+        kept = list(blobs) if again is None else list(again)
+        largest = 0
+        for b in kept:                                               # :383-389
+            largest = max(largest, b.w * b.h)
     out = []
     for b in kept:
         if b.w * b.h > 10 or b.w * b.h >= largest:
@@ -61,27 +67,52 @@ def post_from_blobs(blobs, cam_mask):
     return out
 
 
-def gpu_any_cam_analysis(ctx, slot, cam, nframes, tss, cam_mask, bellows_mask, event_number):
-    """AnyCamAnalysis (AutoBubStart3.cpp:67-125) with trigger + localizer on the device."""
+class _Minus6(Exception):
+    """Where the reference throws inside AnyCamAnalysis (caught at AutoBubStart3.cpp:114 -> -6)."""
+
+
+def gpu_any_cam_analysis(ctx, slot, cam, nframes, tss, cam_mask, bellows_mask, event_number, has_template=False,
+                         log=None):
+    """AnyCamAnalysis (AutoBubStart3.cpp:67-125) with trigger + localizer on the device.  has_template: the context
+    holds this camera's bellows template (abub_set_bellows_template).  log (list) receives the bellows positions."""
     bubbles, mat_trig, loc_thres = [], 0, 3
     out = o.CameraOutput()
-    while True:
-        t, status, lt, _ = ctx.trigger(slot, cam, mat_trig + 1)
-        if status == 0:
-            mat_trig = t
-        if lt >= 0:
-            loc_thres = lt
-        if status != 0:
-            return o.CameraOutput(status, 0, event_number)
-        if nframes <= 5:
-            return o.CameraOutput(-8, 0, event_number)
-        pre = max(0, mat_trig - (1 if tss < 6 else 2))
-        npost = n_post_frames(mat_trig, nframes)
-        frames = ctx.localize_batch([(slot, cam, mat_trig, pre, loc_thres, npost)])[0]
-        for g in genesis_from_blobs(frames[0], cam_mask, bellows_mask):
-            bubbles.append(o.Bubble(g))
-        for k in range(1, npost + 1):
-            o.track_candidates(bubbles, post_from_blobs(frames[k], cam_mask))
-        out = o.stage_camera_output(bubbles, mat_trig, event_number)
-        if bubbles:
-            return out
+    try:
+        while True:
+            t, status, lt, _ = ctx.trigger(slot, cam, mat_trig + 1)
+            if status == 0:
+                mat_trig = t
+            if lt >= 0:
+                loc_thres = lt
+            if status != 0:
+                return o.CameraOutput(status, 0, event_number)
+            if nframes <= 5:
+                return o.CameraOutput(-8, 0, event_number)
+            pre = max(0, mat_trig - (1 if tss < 6 else 2))
+            npost = n_post_frames(mat_trig, nframes)
+            frames = ctx.localize_batch([(slot, cam, mat_trig, pre, loc_thres, npost)])[0]
+
+            def veto():
+                if not has_template:
+                    return None
+                try:
+                    pt, _ = ctx.bellows_track(slot, cam, mat_trig)           # :313
+                    pp, _ = ctx.bellows_track(slot, cam, pre)                # :314
+                except RuntimeError as e:
+                    raise _Minus6(str(e))
+                blobs, st, roi = ctx.localize_bellows(slot, cam, mat_trig, pre, loc_thres, pt, pp)
+                if log is not None:
+                    log.append((pt, pp, roi, st))
+                if st != 0:
+                    raise _Minus6("Rect outside the frame")
+                return blobs
+
+            for g in genesis_from_blobs(frames[0], cam_mask, bellows_mask, veto):
+                bubbles.append(o.Bubble(g))
+            for k in range(1, npost + 1):
+                o.track_candidates(bubbles, post_from_blobs(frames[k], cam_mask))
+            out = o.stage_camera_output(bubbles, mat_trig, event_number)
+            if bubbles:
+                return out
+    except _Minus6:
+        return o.CameraOutput(-6, 0, event_number)
