@@ -45,8 +45,26 @@ abub_ctx* AbubDevice::Context(int rows, int cols) {
     return ctx_;
 }
 
+bool AbubDevice::EnsureBellowsTemplate(int cam, const std::string& mask_dir) {
+    std::lock_guard<std::recursive_mutex> g(mu_);
+    const std::string key = mask_dir + "|" + std::to_string(cam);
+    auto it = templates_.find(key);
+    if (it != templates_.end()) return it->second;
+    bool ok = false;
+    std::vector<uint8_t> bytes;
+    Image8 t;
+    if (ctx_ && abubcodec::read_file(mask_dir + "/cam" + std::to_string(cam) + "_bellows_template.png", bytes) &&
+        abubcodec::decode(bytes.data(), bytes.size(), t) && !t.empty()) {
+        Check(abub_set_bellows_template(ctx_, cam, t.ptr(), t.rows, t.cols), "abub_set_bellows_template");
+        ok = true;
+    }
+    templates_[key] = ok;
+    return ok;
+}
+
 void AbubDevice::Shutdown() {
     std::lock_guard<std::recursive_mutex> g(mu_);
+    templates_.clear();
     if (ctx_) abub_ctx_destroy(ctx_);
     ctx_ = nullptr; rows_ = cols_ = 0;
     by_key_.clear();

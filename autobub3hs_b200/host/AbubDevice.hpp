@@ -68,6 +68,10 @@ public:
     // reference that the caller releases with ReleaseSlot when the event is done.
     std::vector<int> PrefetchEvents(Parser* parser, const std::vector<std::string>& keys, const std::vector<std::string>& events);
 
+    // cam<c>_bellows_template.png of `mask_dir` (L3Localizer.cpp:294-295), decoded and handed to the device on first
+    // use; false when the file cannot be read or decoded ("template not loadable", :297-301).
+    bool EnsureBellowsTemplate(int cam, const std::string& mask_dir);
+
     void Shutdown();
 
 private:
@@ -77,6 +81,7 @@ private:
     std::recursive_mutex mu_;
     std::vector<AbubSlot> slots_;
     std::map<std::string, int> by_key_;
+    std::map<std::string, bool> templates_;     // "<mask dir>|<cam>" -> loadable
 };
 
 #endif

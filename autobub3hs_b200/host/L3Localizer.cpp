@@ -83,9 +83,21 @@ void L3Localizer::GenesisFromBlobs(const abub_blob* blobs, int n) {
             kept.push_back(&blobs[i]);
         }
     }
-    if (all_in_bellows)
-        /* template-match veto of bellows motion (L3Localizer.cpp:292-390): SURVEY.md 8(f)-1, not built yet */
-        throw AbubError("every genesis contour lies in the bellows mask: the bellows veto branch is not implemented");
+    std::vector<abub_blob> again;
+    if (all_in_bellows) {
+        /* :292-390  subtract the bellows movement and see if contours remain.  The contours are found anew (:374) and
+         * this time none is dropped for lying in the bellows mask; `largest` runs over all of them (:383-389).  Without
+         * a loadable template the binary image is unchanged, i.e. the contours are the ones already found. */
+        kept.clear();
+        if (BellowsVeto(again)) {
+            for (const abub_blob& b : again) kept.push_back(&b);
+        } else {
+            for (int i = 0; i < n; i++) kept.push_back(&blobs[i]);
+        }
+        largest = 0;
+        for (const abub_blob* b : kept)
+            if (largest < b->w * b->h) largest = b->w * b->h;
+    }
     for (const abub_blob* b : kept) {                                      // :392-444
         const int BoxArea = b->w * b->h;
         if (BoxArea > 10 || BoxArea >= largest) {
@@ -94,6 +106,35 @@ void L3Localizer::GenesisFromBlobs(const abub_blob* blobs, int n) {
             BubbleList.push_back(new bubble(f));
         }
     }
+}
+
+bool L3Localizer::BellowsVeto(std::vector<abub_blob>& again) {
+    AbubDevice& dev = AbubDevice::Get();
+    std::lock_guard<std::recursive_mutex> g(dev.lock());
+    if (!dev.EnsureBellowsTemplate(CameraNumber, MaskDir)) {               // :297-301
+        std::cout << "Template image not loadable for event " << EventID << " camera " << CameraNumber
+                  << "; cannot veto bellows movement triggers" << std::endl;
+        std::cout << "Template path: " << MaskDir + "/cam" + std::to_string(CameraNumber) + "_bellows_template.png" << std::endl;
+        return false;
+    }
+    float pos_trig[2], pos_pre[2];
+    /* TrackAFeature on the trigger and the pre-trigger frame (:313-314); a peak on the edge of the correlation map is
+     * an out-of-bounds read in the reference -- here it ends the camera like any other exception (-6) */
+    dev.Check(abub_bellows_track(dev.ctx(), Slot, CameraNumber, MatTrigFrame, &pos_trig[0], &pos_trig[1], nullptr), "abub_bellows_track");
+    dev.Check(abub_bellows_track(dev.ctx(), Slot, CameraNumber, preTrigNumber, &pos_pre[0], &pos_pre[1], nullptr), "abub_bellows_track");
+    again.resize(1024);
+    int n = 0, status = 0;
+    for (;;) {
+        const int rc = abub_localize_bellows(dev.ctx(), Slot, CameraNumber, MatTrigFrame, preTrigNumber, loc_thres, pos_trig, pos_pre,
+                                             again.data(), (int)again.size(), &n, &status, nullptr);
+        if (rc == ABUB_E_CAPACITY && again.size() < (1u << 22)) { again.resize(again.size() * 4); continue; }
+        dev.Check(rc, "abub_localize_bellows");
+        break;
+    }
+    if (status != 0)   /* cv::Mat::operator()(Rect) / GaussianBlur throw in the reference (:347-356) */
+        throw AbubError("bellows template pasted outside the frame in event " + EventID + " camera " + std::to_string(CameraNumber));
+    again.resize(n);
+    return true;
 }
 
 void L3Localizer::TrackFromBlobs(const abub_blob* blobs, int n) {
@@ -131,6 +172,7 @@ void L3Localizer::LocalizeOMatic(std::string) {
     }
     int preTrigNum = MatTrigFrame - prev_offset;
     if (preTrigNum < 0) preTrigNum = 0;
+    preTrigNumber = preTrigNum;
     /* :944-954 */
     const int kmax = MatTrigFrame < 29 ? NumFramesBubbleTrack : 39 - MatTrigFrame;
     int n_post = 0;

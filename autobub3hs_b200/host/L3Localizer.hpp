@@ -16,7 +16,9 @@ private:
     bool cam_mask_tried = false, bellows_mask_tried = false;
 
     static BubbleImageFrame FrameFromBlob(const abub_blob& b, bool genesis);
+    int preTrigNumber = 0;                                           // frame used as preTrigFrame (:932-934)
     void GenesisFromBlobs(const abub_blob* blobs, int n);            // CalculateInitialBubbleParams bookkeeping
+    bool BellowsVeto(std::vector<abub_blob>& again);                 // block :292-372; false = template not loadable
     void TrackFromBlobs(const abub_blob* blobs, int n);              // CalculatePostTriggerFrameParams bookkeeping
 
 public:

@@ -77,7 +77,33 @@ def hist_tables(seed, n):
     return tabs, total
 
 
+BELLOWS_CLASSES = ["normal", "bellows", "bellows_bubble", "notrigger", "bellows", "normal"]
+
+
+def bellows_golden():
+    """6. a run whose cameras 1 and 3 show a moving bellows (a14, L3Localizer.cpp:292-390): text, and for every time
+    the veto branch was taken the two TrackAFeature positions after the nudge (float32, hex) and the ROI."""
+    run = synth.make_run(6, BELLOWS_CLASSES, rows=264, cols=420, seed=5, bellows_object=True)
+    trained = o.train_all(run.events, 4)
+    text, recs = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks, 30,
+                              run.bellows_templates)
+    open(os.path.join(OUT, "bellows_run.txt"), "w").write(o.write_header() + text)
+    branch = []
+    for ev, rr in enumerate(recs):
+        for cam, a in enumerate(rr):
+            for info in a.bellows:
+                if info.get("bellows_branch"):
+                    pt, pp, roi = info["bellows_positions"]
+                    branch.append({"event": ev, "cam": cam, "pos_trig": [float(v).hex() for v in pt],
+                                   "pos_pre": [float(v).hex() for v in pp], "roi": [int(v) for v in roi]})
+    json.dump({"rows": 264, "cols": 420, "seed": 5, "classes": BELLOWS_CLASSES, "branch": branch},
+              open(os.path.join(OUT, "bellows_run.json"), "w"))
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "--only-bellows":
+        bellows_golden()
+        return
     # 1. ProcessFrame + histogram
     pf = {}
     for i, (a, b, s) in enumerate(frame_pairs(101, 8, 61, 133)):
@@ -159,6 +185,7 @@ def main():
     json.dump({"rows": 132, "cols": 212, "seed": 9, "classes": list(synth.EVENT_CLASSES), "triggers": trig,
                "training": [[t.status, t.training_set_size, t.kept_events] for t in trained]},
               open(os.path.join(OUT, "e2e_small_run.json"), "w"))
+    bellows_golden()
     print("golden vectors written to", OUT)
 
 

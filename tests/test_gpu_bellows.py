@@ -172,6 +172,9 @@ def test_bellows_run_text_matches_oracle(capi, bellows_run, bellows_trained):
             text.append(o.write_camera_output(run.run_id, cams, 30))
     assert len(log) == taken
     assert "".join(text) == want
+    import os
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "bellows_run.txt")
+    assert o.write_header() + "".join(text) == open(gold).read()              # the committed vector of the same run
 
 
 def test_branch_without_template_keeps_all_contours(capi, bellows_run, bellows_trained):
@@ -191,3 +194,30 @@ def test_branch_without_template_keeps_all_contours(capi, bellows_run, bellows_t
         got = glue.gpu_any_cam_analysis(ctx, 0, cam, len(run.events[ev][cam]), trained[cam].training_set_size, run.cam_masks[cam],
                                         run.bellows_masks[cam], ev, False)
     assert o.write_camera_output(run.run_id, [got], 30) == o.write_camera_output(run.run_id, [a.out], 30)
+
+
+def test_track_full_size_frame(capi):
+    """BASELINE.json frame size (1050x1680) with a template of the reference's size (557x178, cam1_bellows_template.png)."""
+    import oracle.cv2_oracle as o
+    from autobub3hs_b200 import synth
+    rows, cols = synth.ROWS, synth.COLS
+    pat, (bx, by) = synth.make_bellows_object(1, rows, cols)
+    assert pat.shape == (556, 178) or pat.shape[1] == 178
+    rng = np.random.default_rng(3)
+    bg = synth.make_background(1, rows, cols).astype(np.float32)
+    frames = []
+    for dx, dy in ((0, 0), (1, 3)):
+        scene = bg.copy()
+        scene[by + dy:by + dy + pat.shape[0], bx + dx:bx + dx + pat.shape[1]] = pat
+        frames.append(np.clip(np.rint(scene + 2.0 * rng.standard_normal((rows, cols), dtype=np.float32)), 0, 255).astype(np.uint8))
+    with capi.Context(rows, cols, 1, 4, max_slots=1) as ctx:
+        ctx.set_bellows_template(0, pat)
+        ctx.event_upload(0, 0, np.stack(frames))
+        for f, (dx, dy) in enumerate(((0, 0), (1, 3))):
+            (x, y), peak = ctx.bellows_track(0, 0, f)
+            got = ctx.bellows_map()
+            want = o.ccorr_normed_map(frames[f], pat)
+            assert np.abs(got - want).max() <= MAP_TOL
+            ox, oy, opeak = o.subpixel_from_map(want)
+            assert peak == opeak == (bx + dx, by + dy)
+            assert abs(float(x) - float(ox)) <= POS_TOL and abs(float(y) - float(oy)) <= POS_TOL

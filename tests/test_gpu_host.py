@@ -138,3 +138,23 @@ def test_two_ranks_same_text(abub3hs, tma_run, tmp_path):
     assert all(p.returncode == 0 for p in procs), "\n".join(l[-1500:] for l in logs)
     assert open(out / "abub3hs_20210101_0.txt").read() == gold
     assert not [f for f in os.listdir(out) if "rank" in f or "ncclid" in f]
+
+
+def test_bellows_run_with_and_without_template(abub3hs, tmp_path):
+    """Cameras 1 and 3 show a moving bellows: every genesis contour lies in the bellows mask and the veto branch
+    (L3Localizer.cpp:292-390) runs -- with the template PNG in the mask directory, and with it missing."""
+    from autobub3hs_b200 import synth
+    import oracle.cv2_oracle as o
+    run = synth.make_run(6, ["normal", "bellows", "bellows_bubble", "notrigger", "bellows", "normal"], rows=264, cols=420, seed=5,
+                         bellows_object=True)
+    trained = o.train_all(run.events, 4)
+    synth.write_run(run, str(tmp_path / "data"), str(tmp_path / "masks"))
+    want, recs = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks, 30,
+                              run.bellows_templates)
+    assert sum(1 for rr in recs for a in rr for i in a.bellows if i.get("bellows_branch")) >= 6
+    assert _run(abub3hs, str(tmp_path / "data"), str(tmp_path / "out"), str(tmp_path / "masks"), ["--batch", "3"]) == o.write_header() + want
+    for c in (1, 3):
+        os.remove(str(tmp_path / "masks" / f"cam{c}_bellows_template.png"))
+    want2, _ = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks, 30, None)
+    assert want2 != want
+    assert _run(abub3hs, str(tmp_path / "data"), str(tmp_path / "out2"), str(tmp_path / "masks")) == o.write_header() + want2

@@ -208,3 +208,46 @@ def test_writer_formats():
     err, _ = o.form_each_bubble_output("r", 1, o.CameraOutput(-3, 0, 9), 1, 0, 30)
     assert err.startswith("r  9  0  0  1  -3  0.00  0.00  0  0  0.00  0.00  0  0")
     assert err.count("0.00") == 2 + 2 + 50
+
+
+def test_bellows_golden_run():
+    """a14: the oracle's bellows veto (cv2.matchTemplate positions, ROI, final text) against the committed vectors."""
+    from autobub3hs_b200 import synth
+    meta = json.load(open(os.path.join(GOLD, "bellows_run.json")))
+    run = synth.make_run(6, meta["classes"], rows=meta["rows"], cols=meta["cols"], seed=meta["seed"], bellows_object=True)
+    trained = o.train_all(run.events, 4)
+    text, recs = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks, 30,
+                              run.bellows_templates)
+    assert o.write_header() + text == open(os.path.join(GOLD, "bellows_run.txt")).read()
+    got = []
+    for ev, rr in enumerate(recs):
+        for cam, a in enumerate(rr):
+            for info in a.bellows:
+                if info.get("bellows_branch"):
+                    pt, pp, roi = info["bellows_positions"]
+                    got.append((ev, cam, [float(v).hex() for v in pt], [float(v).hex() for v in pp], [int(v) for v in roi]))
+    want = [(b["event"], b["cam"], b["pos_trig"], b["pos_pre"], b["roi"]) for b in meta["branch"]]
+    assert got == want and len(got) >= 6
+    assert {b["cam"] for b in meta["branch"]} == {1, 3}
+
+
+def test_bellows_helpers():
+    """GetDiffROI / nudge arithmetic (L3Localizer.cpp:316-323, :462-470) and the ROI ProcessFrame."""
+    F = np.float32
+    (t, p) = o.nudge_apart((F(10.25), F(7.5)), (F(10.25), F(9.0)))
+    assert t == (F(11.25), F(7.5)) and p == (F(9.25), F(9.0))                     # >= : trig moves right
+    (t, p) = o.nudge_apart((F(3.0), F(1.0)), (F(4.5), F(1.0)))
+    assert t == (F(2.0), F(1.0)) and p == (F(5.5), F(1.0))
+    assert o.get_diff_roi((F(11.25), F(7.5)), (F(9.25), F(9.0)), (30, 20)) == (11, 9, 18, 28)
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 256, (40, 50), dtype=np.uint8)
+    b = rng.integers(0, 256, (40, 50), dtype=np.uint8)
+    s = rng.integers(0, 4, (40, 50), dtype=np.uint8)
+    roi = (7, 5, 20, 11)
+    d = o.process_frame_roi(a, b, s, roi)
+    assert np.array_equal(d[5:16, 7:27], o.process_frame(a[5:16, 7:27].copy(), b[5:16, 7:27].copy(), s[5:16, 7:27].copy()))
+    d[5:16, 7:27] = 0
+    assert not d.any()
+    for bad in ((45, 5, 20, 11), (-1, 0, 5, 5), (0, 0, 0, 5)):
+        with pytest.raises(ValueError):
+            o.process_frame_roi(a, b, s, bad)

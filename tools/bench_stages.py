@@ -109,6 +109,20 @@ def main():
     byt = E * B.NCAMS * B.K1_BYTES_PER_EVENT_CAM + nplanes * B.NPIX
     print(json.dumps({"stage": "recon (K1+K2+K5-K7, resident)", "events": E, "seconds": best, "events_per_s": E / best,
                       "algorithmic_GB": byt / 1e9, "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak}))
+    # ---- bellows veto: TrackAFeature at full size (a14; rare branch, timed for completeness) ----
+    pat, _ = synth.make_bellows_object(1, B.ROWS, B.COLS)
+    ctx.set_bellows_template(1, pat)
+    ctx.bellows_track(0, 1, 0)
+    best = None
+    for _ in range(args.reps):
+        t0 = time.perf_counter()
+        ctx.bellows_track(0, 1, 0)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    macs = (B.ROWS - pat.shape[0] + 1) * (B.COLS - pat.shape[1] + 1) * pat.shape[0] * pat.shape[1]
+    print(json.dumps({"stage": "bellows TrackAFeature (K8, one frame)", "template": list(pat.shape), "seconds": best,
+                      "u8_MACs": macs, "TMAC_per_s": macs / best / 1e12,
+                      "note": "exact integer CCORR_NORMED numerators with dp4a; includes window sums, min/max/argmax and the read-back"}))
     ctx.close()
 
 
