@@ -344,6 +344,17 @@ class Context:
         counts = [npf[k] for k in range(n_post + 1)]
         return [blobs[i] for i in range(sum(counts))], counts
 
+    def localize_batch_raw(self, items: Sequence[Tuple[int, int, int, int, int, int]], cap: int = 65536, buffers=None):
+        """The bare C call (no per-blob Python objects): returns (blobs ctypes array, npf ctypes array, total, buffers);
+        pass `buffers` back in to reuse the allocations."""
+        n = len(items)
+        if buffers is None or buffers[3] != n or buffers[4] != cap:
+            buffers = ((LocItem * n)(*[LocItem(*it) for it in items]), (Blob * cap)(), (C.c_int * (n * (ABUB_MAX_TRACK + 1)))(), n, cap)
+        arr, blobs, npf = buffers[0], buffers[1], buffers[2]
+        tot = C.c_int()
+        self._ck(self.lib.abub_localize_batch(self.h, arr, n, blobs, cap, npf, C.byref(tot)), "abub_localize_batch")
+        return blobs, npf, tot.value, buffers
+
     def localize_batch(self, items: Sequence[Tuple[int, int, int, int, int, int]], cap: int = 65536):
         """items: (slot, cam, trig, pre_trig, loc_thres, n_post).  Returns per item a list (k=0..n_post) of blob lists."""
         n = len(items)

@@ -4,25 +4,29 @@
 // Same arithmetic as k1_processframe.cu (which stays as the generic-pitch / store-mode path);
 // this file is the hot trigger path for pitches that TMA can address (cols % 16 == 0):
 //
-//   * one warp owns a strip of 240 output columns x TH rows; lane l holds 8 adjacent pixels
-//     (lanes 0 and 31 are the halo, so 256 columns are loaded per row);
-//   * rows arrive through a per-warp ring of TMA boxes (cp.async.bulk.tensor, 256 columns x
-//     T_R rows of frame j, frame j-d and the per-pixel constant plane) completed on
-//     per-warp mbarriers: no per-lane global addressing at all.  Lane 0 re-arms a stage as
-//     soon as the warp has consumed it.  BORDER_REFLECT_101 rows are fetched as single-row
-//     boxes at the reflected row index; TMA zero-fills columns outside the image and the two
-//     lanes on the image border reflect in registers;
-//   * pixels are packed two per 32-bit word, one word per plane:  pos01 = p0 | p1<<16,
-//     neg01 = n0 | n1<<16.  Stage A is
-//         x = (a0 | a1<<16) + ((255-b0) | (255-b1)<<16)        lanes a-b+255  (no borrows)
-//         pos = VIADDMNMX.S16x2.RELU(x, K16, 0)                 K16 = -(255+t) per lane
-//         neg = VIADDMNMX.S16x2.RELU(0x01FE01FE - x, K16, 0)
+//   * one warp (= one CTA) owns a strip of 240 output columns x ~350 rows of one frame pair; lane l holds 8 adjacent
+//     pixels x0-8+8l .. x0-1+8l (lanes 0 and 31 are the +-2-column halo; the neighbouring strip recomputes them);
+//   * rows arrive through a two-stage ring of TMA boxes (cp.async.bulk.tensor) completed on mbarriers: frame j,
+//     frame j-d (u8 frames described as a 3-D UINT16 tensor {cols/2, rows, cam*frame}) and the per-pixel constant
+//     plane K16 (s16, described as a 2-D UINT32 tensor), each box 272 pixels x T_R rows starting at x0-16.  The
+//     box limit of 256 counts ELEMENTS, hence the wider element types; the x origin must be 16-byte aligned (an
+//     unaligned origin is an illegal instruction, tools/tma_probe.cu), hence the 16-pixel left margin.  No
+//     per-lane global addressing at all; lane 0 re-arms a stage as soon as the warp has consumed it.  TMA
+//     zero-fills coordinates outside the image; the two lanes on the image's left/right border reflect in
+//     registers (BORDER_REFLECT_101);
+//   * strips tile output rows [2, rows-2): the four border rows, whose vertical reflection a streaming strip
+//     cannot express, are computed by k1_trigger_kernel (k1_processframe.cu) in border_only mode;
+//   * pixels are packed two per 32-bit word, one word per plane.  Stage A:
+//         x   = prmt(a) + prmt(~b)                               s16x2 lanes a-b-1+256k (two PRMTs per operand)
+//         pos = __viaddmax_s16x2_relu(x, K16, K16)               one VIADDMNMX.S16x2.RELU, K16 = -(255+t) per lane
+//         neg = __viaddmax_s16x2_relu(0x01FE01FE - x, K16, K16)
 //     with t = min(6 sigma, 255) (2 bytes per pixel of L2-resident constants);
-//   * the vertical [1 4 6 4 1] is a cascade of four [1 1] adds on carried state
-//     (lanes <= 4080), the horizontal pass takes the two halo words from the neighbour lanes
-//     with SHFL and builds the odd taps with one PRMT per word;
-//   * (sum + 128) >> 8 per lane, |P - N|; only non-zero outputs touch the shared histogram;
-//     bin 0 is recovered as rows*cols - sum(other bins) by k1_fill_bin0_kernel.
+//   * the vertical [1 4 6 4 1] is a cascade of four [1 1] adds on carried state, updated unconditionally (rows beyond
+//     the strip are computed and dropped, which keeps the loop branch-free); the horizontal pass takes the two halo
+//     words from the neighbour lanes with SHFL and builds the odd-aligned pairs with PRMT 0x5432;
+//   * (sum + 128) >> 8 per lane, packed to bytes, |P - N| with VABSDIFF4.U8.  A warp-wide vote skips the histogram
+//     for all-zero rows; otherwise all 8 bytes of every lane are added to the shared histogram without branching
+//     (bin 0 is a scratch bin) and the true bin 0 is recovered as rows*cols - sum(other bins) by k1_fill_bin0_kernel.
 #include <cuda.h>
 
 #include "abub_internal.cuh"
