@@ -192,6 +192,24 @@ extern "C" int abub_event_upload(abub_ctx* ctx, int slot, int cam, const uint8_t
     return push_nframes(ctx, slot);
 }
 
+// frames of one camera already decoded into the slot's pinned staging buffer: asynchronous H2D on the ctx stream
+extern "C" int abub_event_submit_cam(abub_ctx* ctx, int slot, int cam, int nframes) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && cam >= 0 && cam < ctx->ncams, "slot/cam");
+    ABUB_REQUIRE(ctx, nframes >= 0 && nframes <= ctx->max_frames, "nframes");
+    cudaSetDevice(ctx->device);
+    abub_slot_state& s = ctx->slots[slot];
+    ABUB_REQUIRE(ctx, s.h_pinned != nullptr, "slot has no pinned buffer (call abub_pinned_acquire)");
+    s.nframes[cam] = nframes;
+    s.hist_valid = false;
+    if (nframes > 0) {
+        const size_t off = (size_t)cam * ctx->max_frames * ctx->npix;
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(s.d_frames + off, s.h_pinned + off, (size_t)nframes * ctx->npix, cudaMemcpyHostToDevice,
+                                             ctx->stream));
+    }
+    return push_nframes(ctx, slot);
+}
+
 extern "C" int abub_event_device_ptr(abub_ctx* ctx, int slot, uint8_t** dev_ptr) {
     if (!ctx) return ABUB_E_INVALID;
     ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && dev_ptr, "abub_event_device_ptr");

@@ -3,6 +3,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 
 #include "ImageCodec.hpp"
 
@@ -62,9 +63,24 @@ bool AbubDevice::EnsureBellowsTemplate(int cam, const std::string& mask_dir) {
     return ok;
 }
 
+const Image8* AbubDevice::Mask(int cam, bool bellows, const std::string& mask_dir) {
+    std::lock_guard<std::recursive_mutex> g(mu_);
+    const std::string key = mask_dir + "|" + std::to_string(cam) + (bellows ? "|b" : "|m");
+    auto it = masks_.find(key);
+    if (it == masks_.end()) {
+        Image8 m;
+        std::vector<uint8_t> bytes;
+        if (abubcodec::read_file(mask_dir + "/cam" + std::to_string(cam) + (bellows ? "_bellows" : "") + "_mask.bmp", bytes))
+            abubcodec::decode(bytes.data(), bytes.size(), m);
+        it = masks_.emplace(key, std::move(m)).first;
+    }
+    return it->second.empty() ? nullptr : &it->second;
+}
+
 void AbubDevice::Shutdown() {
     std::lock_guard<std::recursive_mutex> g(mu_);
     templates_.clear();
+    masks_.clear();
     if (ctx_) abub_ctx_destroy(ctx_);
     ctx_ = nullptr; rows_ = cols_ = 0;
     by_key_.clear();
@@ -104,14 +120,17 @@ void AbubDevice::LoadCamera(int slot, int cam, Parser* parser, const std::string
     const int n = (int)frames.size();
     if (n > max_frames_) throw AbubError("event " + event_id + " has " + std::to_string(n) + " frames for camera " +
                                          std::to_string(cam) + " (capacity " + std::to_string(max_frames_) + ")");
-    // the encoded bytes are read serially (a parser owns one file handle), decoded on every core
-    std::vector<std::vector<uint8_t>> enc(n);
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
     std::vector<char> ok(n, 0);
-    for (int i = 0; i < n; i++) ok[i] = parser->GetImageBytes(event_id, frames[i], enc[i]) != parser->FailureCode() && !enc[i].empty();
     if (!ctx_) {
+        // size the context from the first frame whose header can be read
+        std::vector<uint8_t> enc;
         for (int i = 0; i < n && !ctx_; i++) {
             int r, c;
-            if (ok[i] && abubcodec::peek_size(enc[i].data(), enc[i].size(), &r, &c)) Context(r, c);
+            if (parser->GetImageBytes(event_id, frames[i], enc) != parser->FailureCode() && !enc.empty() &&
+                abubcodec::peek_size(enc.data(), enc.size(), &r, &c))
+                Context(r, c);
         }
         if (!ctx_) throw AbubError("no decodable frame to size the device context from (event " + event_id + ")");
     }
@@ -119,20 +138,30 @@ void AbubDevice::LoadCamera(int slot, int cam, Parser* parser, const std::string
     Check(abub_pinned_acquire(ctx_, slot, &pinned), "abub_pinned_acquire");
     const size_t npix = (size_t)rows_ * cols_;
     uint8_t* base = pinned + (size_t)cam * max_frames_ * npix;
+    const double t1 = now();
+    // every core reads and decodes its own frames straight into the pinned staging buffer (RawParser: one file per
+    // frame; ZipParser: positional reads on the shared descriptor)
 #pragma omp parallel for schedule(dynamic, 1)
     for (int i = 0; i < n; i++) {
-        if (ok[i]) ok[i] = abubcodec::decode_into(enc[i].data(), enc[i].size(), base + (size_t)i * npix, rows_, cols_);
-        if (!ok[i]) memset(base + (size_t)i * npix, 0, npix);
+        std::vector<uint8_t> enc;
+        bool good = parser->GetImageBytes(event_id, frames[i], enc) != parser->FailureCode() && !enc.empty();
+        if (good) good = abubcodec::decode_into(enc.data(), enc.size(), base + (size_t)i * npix, rows_, cols_);
+        if (!good) memset(base + (size_t)i * npix, 0, npix);
+        ok[i] = good;
     }
     st.bad[cam].clear();
     for (int i = 0; i < n; i++)
         if (!ok[i]) st.bad[cam].push_back(i);
-    Check(abub_event_upload(ctx_, slot, cam, base, n), "abub_event_upload");
+    const double t2 = now();
+    Check(abub_event_submit_cam(ctx_, slot, cam, n), "abub_event_submit_cam");     // asynchronous: the next camera decodes meanwhile
+    const double t3 = now();
+    t_read += t1 - t0; t_decode += t2 - t1; t_upload += t3 - t2;      // t_read = context sizing + pinned allocation
     st.nframes[cam] = n;
     st.loaded[cam] = true;
 }
 
-std::vector<int> AbubDevice::PrefetchEvents(Parser* parser, const std::vector<std::string>& keys, const std::vector<std::string>& events) {
+std::vector<int> AbubDevice::PrefetchEvents(Parser* parser, const std::vector<std::string>& keys, const std::vector<std::string>& events,
+                                            const int* training_set_sizes) {
     std::lock_guard<std::recursive_mutex> g(mu_);
     std::vector<int> out;
     for (size_t e = 0; e < events.size(); e++) {
@@ -153,11 +182,88 @@ std::vector<int> AbubDevice::PrefetchEvents(Parser* parser, const std::vector<st
     std::vector<int> sorted(out);
     std::sort(sorted.begin(), sorted.end());
     size_t i = 0;
+    const auto h0 = std::chrono::steady_clock::now();
     while (ctx_ && i < sorted.size()) {
         size_t j = i + 1;
         while (j < sorted.size() && sorted[j] == sorted[j - 1] + 1) j++;
         Check(abub_trigger_hist(ctx_, sorted[i], (int)(j - i)), "abub_trigger_hist");
         i = j;
     }
+    if (ctx_) abub_sync(ctx_);
+    const auto h1 = std::chrono::steady_clock::now();
+    t_hist += std::chrono::duration<double>(h1 - h0).count();
+    if (!ctx_) return out;
+
+    // FindTriggerFrame(startframe = 1) of every (event, camera) of the batch: one K2 launch per slot range
+    i = 0;
+    while (i < sorted.size()) {
+        size_t j = i + 1;
+        while (j < sorted.size() && sorted[j] == sorted[j - 1] + 1) j++;
+        const int first = sorted[i], ns = (int)(j - i);
+        std::vector<int> tr(ns * ncams_), stt(ns * ncams_), lt(ns * ncams_);
+        std::vector<double> sg((size_t)ns * ncams_ * max_frames_);
+        Check(abub_trigger_scan(ctx_, first, ns, nullptr), "abub_trigger_scan");
+        Check(abub_trigger_results(ctx_, first, ns, tr.data(), stt.data(), lt.data(), sg.data()), "abub_trigger_results");
+        for (int s = 0; s < ns; s++)
+            for (int c = 0; c < ncams_; c++) {
+                AbubSlot& st = slots_[first + s];
+                if (!st.loaded[c] || st.nframes[c] < 5) continue;
+                const int k = s * ncams_ + c;
+                st.trig[c] = tr[k]; st.trig_status[c] = stt[k]; st.trig_loc_thres[c] = lt[k];
+                st.sig[c].assign(sg.begin() + (size_t)k * max_frames_, sg.begin() + (size_t)(k + 1) * max_frames_);
+                st.trig_valid[c] = true;
+            }
+        i = j;
+    }
+    const auto h2 = std::chrono::steady_clock::now();
+    t_scan += std::chrono::duration<double>(h2 - h1).count();
+    if (!training_set_sizes) return out;
+
+    // LocalizeOMatic of every triggered (event, camera): one abub_localize_batch
+    std::vector<abub_loc_item> items;
+    std::vector<std::pair<int, int>> who;
+    for (int s : out)
+        for (int c = 0; c < ncams_; c++) {
+            AbubSlot& st = slots_[s];
+            if (!st.trig_valid[c] || st.trig_status[c] != 0 || st.nframes[c] <= 5 || !st.bad[c].empty()) continue;
+            const int trig = st.trig[c], N = st.nframes[c];
+            int pre = trig - (training_set_sizes[c] < 6 ? 1 : 2);                    // L3Localizer.cpp:919-934
+            if (pre < 0) pre = 0;
+            const int kmax = trig < 29 ? ABUB_MAX_TRACK : 39 - trig;                 // :944-954
+            int n_post = 0;
+            for (int k = 1; k <= kmax; k++) {
+                if (trig + k >= N) break;
+                n_post++;
+            }
+            items.push_back(abub_loc_item{s, c, trig, pre, st.trig_loc_thres[c], n_post});
+            who.push_back({s, c});
+        }
+    if (!items.empty()) {
+        std::vector<abub_blob> blobs((size_t)1 << 16);
+        std::vector<int> npf(items.size() * (ABUB_MAX_TRACK + 1));
+        int total = 0;
+        for (;;) {
+            const int rc = abub_localize_batch(ctx_, items.data(), (int)items.size(), blobs.data(), (int)blobs.size(), npf.data(), &total);
+            if (rc == ABUB_E_CAPACITY && blobs.size() < ((size_t)1 << 26)) { blobs.resize((size_t)total + 1024); continue; }
+            Check(rc, "abub_localize_batch");
+            break;
+        }
+        size_t off = 0;
+        for (size_t it = 0; it < items.size(); it++) {
+            AbubSlot& st = slots_[who[it].first];
+            const int c = who[it].second;
+            size_t cnt = 0;
+            for (int k = 0; k <= ABUB_MAX_TRACK; k++) {
+                st.loc_npf[c][k] = npf[it * (ABUB_MAX_TRACK + 1) + k];
+                cnt += (size_t)st.loc_npf[c][k];
+            }
+            st.loc_blobs[c].assign(blobs.begin() + off, blobs.begin() + off + cnt);
+            off += cnt;
+            st.loc_trig[c] = items[it].trig; st.loc_pre[c] = items[it].pre_trig; st.loc_thres[c] = items[it].loc_thres;
+            st.loc_npost[c] = items[it].n_post;
+            st.loc_valid[c] = true;
+        }
+    }
+    t_loc += std::chrono::duration<double>(std::chrono::steady_clock::now() - h2).count();
     return out;
 }

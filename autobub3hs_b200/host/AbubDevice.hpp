@@ -33,6 +33,15 @@ struct AbubSlot {
     bool loaded[8] = {false};        // frames of this camera are in HBM
     int nframes[8] = {0};
     std::vector<int> bad[8];         // frame indices that failed to load/decode
+    // results computed for the whole batch by PrefetchEvents (one K2 launch, one localizer call); an analyzer that asks
+    // for exactly this work takes it from here instead of launching its own
+    bool trig_valid[8] = {false};
+    int trig[8] = {0}, trig_status[8] = {0}, trig_loc_thres[8] = {0};
+    std::vector<double> sig[8];      // stored significance per frame
+    bool loc_valid[8] = {false};
+    int loc_trig[8] = {0}, loc_pre[8] = {0}, loc_thres[8] = {0}, loc_npost[8] = {0};
+    int loc_npf[8][ABUB_MAX_TRACK + 1] = {{0}};
+    std::vector<abub_blob> loc_blobs[8];
 };
 
 class AbubDevice {
@@ -66,13 +75,22 @@ public:
     // Stages a batch: for every event all cameras are loaded, then one K1 launch covers the batch.
     // keys[i] is the slot key of events[i] (the one its analyzers use).  Returns the slots; every key holds one
     // reference that the caller releases with ReleaseSlot when the event is done.
-    std::vector<int> PrefetchEvents(Parser* parser, const std::vector<std::string>& keys, const std::vector<std::string>& events);
+    // training_set_sizes ([ncams], may be NULL): with it the trigger scan and the localizer also run for the whole
+    // batch (the pre-trigger frame offset depends on TrainingSetSize, L3Localizer.cpp:919-934).
+    std::vector<int> PrefetchEvents(Parser* parser, const std::vector<std::string>& keys, const std::vector<std::string>& events,
+                                    const int* training_set_sizes = nullptr);
 
     // cam<c>_bellows_template.png of `mask_dir` (L3Localizer.cpp:294-295), decoded and handed to the device on first
     // use; false when the file cannot be read or decoded ("template not loadable", :297-301).
     bool EnsureBellowsTemplate(int cam, const std::string& mask_dir);
+    // cam<c>_mask.bmp / cam<c>_bellows_mask.bmp of `mask_dir`, read once per run (the reference re-reads the file in
+    // every isInMask call, L3Localizer.cpp:983-984); nullptr when unreadable.
+    const Image8* Mask(int cam, bool bellows, const std::string& mask_dir);
 
     void Shutdown();
+
+    // wall-clock seconds spent in the ingest stages (printed by abub3hs when ABUB_TIMING is set)
+    double t_read = 0, t_decode = 0, t_upload = 0, t_hist = 0, t_scan = 0, t_loc = 0;
 
 private:
     AbubDevice() {}
@@ -82,6 +100,7 @@ private:
     std::vector<AbubSlot> slots_;
     std::map<std::string, int> by_key_;
     std::map<std::string, bool> templates_;     // "<mask dir>|<cam>" -> loadable
+    std::map<std::string, Image8> masks_;       // "<mask dir>|<cam>|<bellows>" -> image (empty = unreadable)
 };
 
 #endif

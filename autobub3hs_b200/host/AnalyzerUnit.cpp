@@ -57,7 +57,13 @@ void AnalyzerUnit::FindTriggerFrame(bool nonStopMode, int startframe) {
     std::vector<double> sig(dev.max_frames(), 0.0);
     {
         std::lock_guard<std::recursive_mutex> g(dev.lock());
-        dev.Check(abub_trigger(dev.ctx(), Slot, CameraNumber, startframe, &trig, &status, &lt, sig.data()), "abub_trigger");
+        AbubSlot& st = dev.slot(Slot);
+        if (startframe == 1 && st.trig_valid[CameraNumber]) {      // scanned with the rest of the batch (PrefetchEvents)
+            trig = st.trig[CameraNumber]; status = st.trig_status[CameraNumber]; lt = st.trig_loc_thres[CameraNumber];
+            sig = st.sig[CameraNumber];
+        } else {
+            dev.Check(abub_trigger(dev.ctx(), Slot, CameraNumber, startframe, &trig, &status, &lt, sig.data()), "abub_trigger");
+        }
     }
     /* frames the reference would have read: startframe-2 .. trig+2 on a trigger, everything otherwise.  An
      * unreadable frame among them stops the search: -9 through the zip reader (AnalyzerUnit.cpp:207-213);

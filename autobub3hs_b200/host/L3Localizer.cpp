@@ -27,22 +27,13 @@ bool L3Localizer::isInMask(RectI* r, bool bellows) {
     const int xpix = (int)(r->x + r->width / 2.);
     const int ypix = r->y + r->height / 2;
     if (MaskDir == "") return !bellows;                                   // silently skip the mask check
-    Image8& mask = bellows ? bellows_mask : cam_mask;
-    bool& tried = bellows ? bellows_mask_tried : cam_mask_tried;
-    if (mask.empty() && !tried) {
-        // the reference re-reads the file on every call while it is unreadable; one attempt is equivalent
-        tried = true;
-        std::string path = MaskDir + "/cam" + std::to_string(CameraNumber);
-        if (bellows) path += "_bellows";
-        path += "_mask.bmp";
-        std::vector<uint8_t> bytes;
-        if (abubcodec::read_file(path, bytes)) abubcodec::decode(bytes.data(), bytes.size(), mask);
-    }
-    if (mask.empty()) {
+    const Image8* mp = AbubDevice::Get().Mask(CameraNumber, bellows, MaskDir);
+    if (!mp) {
         std::cout << "Mask image not loadable for event " << EventID << " camera " << CameraNumber
                   << "; skipping mask check" << std::endl;
         return !bellows;
     }
+    const Image8& mask = *mp;
     if (ypix < 0 || ypix >= mask.rows || xpix < 0 || xpix >= mask.cols) return false;   // cv::Mat::at would read out of bounds
     if ((int)mask.at(ypix, xpix) > 0) return true;
     if (!nonStopMode && !bellows)
@@ -191,12 +182,20 @@ void L3Localizer::LocalizeOMatic(std::string) {
     int npf[ABUB_MAX_TRACK + 1] = {0};
     {
         std::lock_guard<std::recursive_mutex> g(dev.lock());
-        for (;;) {
-            const int rc = abub_localize(dev.ctx(), Slot, CameraNumber, MatTrigFrame, preTrigNum, loc_thres, n_post,
-                                         blobs.data(), (int)blobs.size(), npf);
-            if (rc == ABUB_E_CAPACITY && blobs.size() < (1u << 22)) { blobs.resize(blobs.size() * 4); continue; }
-            dev.Check(rc, "abub_localize");
-            break;
+        AbubSlot& st = dev.slot(Slot);
+        const int c = CameraNumber;
+        if (st.loc_valid[c] && st.loc_trig[c] == MatTrigFrame && st.loc_pre[c] == preTrigNum && st.loc_thres[c] == loc_thres &&
+            st.loc_npost[c] == n_post) {                                    // localized with the rest of the batch
+            blobs = st.loc_blobs[c];
+            for (int k = 0; k <= ABUB_MAX_TRACK; k++) npf[k] = st.loc_npf[c][k];
+        } else {
+            for (;;) {
+                const int rc = abub_localize(dev.ctx(), Slot, CameraNumber, MatTrigFrame, preTrigNum, loc_thres, n_post,
+                                             blobs.data(), (int)blobs.size(), npf);
+                if (rc == ABUB_E_CAPACITY && blobs.size() < (1u << 22)) { blobs.resize(blobs.size() * 4); continue; }
+                dev.Check(rc, "abub_localize");
+                break;
+            }
         }
     }
     const abub_blob* p = blobs.data();

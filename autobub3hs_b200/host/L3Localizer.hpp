@@ -12,8 +12,6 @@
 class L3Localizer : public AnalyzerUnit {
 private:
     bool nonStopMode;
-    Image8 cam_mask, bellows_mask;
-    bool cam_mask_tried = false, bellows_mask_tried = false;
 
     static BubbleImageFrame FrameFromBlob(const abub_blob& b, bool genesis);
     int preTrigNumber = 0;                                           // frame used as preTrigFrame (:932-934)

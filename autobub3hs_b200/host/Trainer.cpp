@@ -67,22 +67,28 @@ void Trainer::MakeAvgSigmaImage(bool PerformLBPOnImages) {
         const int nev = c1 - c0;
         std::vector<std::vector<uint8_t>> enc(2 * (size_t)nev);
         std::vector<char> good(nev, 0);
+        std::vector<std::string> names(2 * (size_t)nev);
         for (int e = 0; e < nev; e++) {
             CameraFrames.clear();
             FileParser->ParseAndSortFramesInFolder(EventList[c0 + e], camera, CameraFrames);
             if (CameraFrames.size() >= 2) {                       // Trainer.cpp:254: frames {0,1} of the event
                 good[e] = 1;
-                for (int k = 0; k < 2; k++) {
-                    const int err = FileParser->GetImageBytes(EventList[c0 + e], CameraFrames[TrainingSequence[k]], enc[2 * e + k]);
-                    if (err == failure || enc[2 * e + k].empty()) {
-                        std::cout << "Skipping corrupted image for training.\n";
-                        good[e] = 0;
-                    }
-                }
+                for (int k = 0; k < 2; k++) names[2 * e + k] = CameraFrames[TrainingSequence[k]];
             } else {
                 std::cout << "Event " << EventList[c0 + e] << " is nonexistant on the disk. Skipping training on this event\n";
             }
             CameraFrames.clear();
+        }
+        // the two files of every event are read on all cores (positional reads in the zip case)
+#pragma omp parallel for schedule(dynamic, 1)
+        for (int i = 0; i < 2 * nev; i++) {
+            const int e = i / 2;
+            if (names[i].empty()) continue;
+            const int err = FileParser->GetImageBytes(EventList[c0 + e], names[i], enc[i]);
+            if (err == failure || enc[i].empty()) {
+#pragma omp critical
+                { std::cout << "Skipping corrupted image for training.\n"; good[e] = 0; }
+            }
         }
         // size the context from the first readable frame
         if (!dev.ctx()) {

@@ -1,6 +1,8 @@
 // ZipParser (reference: ParseFolder/ZipParser.cpp:38-327).
 #include "ZipParser.hpp"
 
+#include <unistd.h>
+
 #include <string.h>
 #include <zlib.h>
 
@@ -15,9 +17,16 @@ inline uint16_t r16(const uint8_t* p) { return (uint16_t)(p[0] | (p[1] << 8)); }
 inline uint32_t r32(const uint8_t* p) { return p[0] | (p[1] << 8) | (p[2] << 16) | ((uint32_t)p[3] << 24); }
 inline uint64_t r64(const uint8_t* p) { return (uint64_t)r32(p) | ((uint64_t)r32(p + 4) << 32); }
 
+// positional read on the descriptor: no shared file position, so entries can be read from several threads at once
 bool read_at(FILE* f, uint64_t off, void* dst, size_t n) {
-    if (fseeko(f, (off_t)off, SEEK_SET) != 0) return false;
-    return fread(dst, 1, n, f) == n;
+    const int fd = fileno(f);
+    uint8_t* p = static_cast<uint8_t*>(dst);
+    while (n) {
+        const ssize_t got = pread(fd, p, n, (off_t)off);
+        if (got <= 0) return false;
+        p += got; off += (uint64_t)got; n -= (size_t)got;
+    }
+    return true;
 }
 }  // namespace
 

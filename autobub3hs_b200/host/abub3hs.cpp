@@ -22,6 +22,8 @@
 #include "L3Localizer.hpp"
 #include "PICOFormatWriterV4.hpp"
 #include "RawParser.hpp"
+#include <chrono>
+
 #include "Trainer.hpp"
 #include "ZipParser.hpp"
 
@@ -218,6 +220,9 @@ int main(int argc, char** argv) {
     const int ev_lo = (int)((long long)nEvents * opt.rank / opt.world), ev_hi = (int)((long long)nEvents * (opt.rank + 1) / opt.world);
 
     printf("**Starting training. AutoBub is in learn mode**\n");
+    auto wall = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double T_train0 = wall();
+    double T_stage = 0, T_analyze = 0, T_write = 0;
     std::vector<Trainer*> Trainers;
     for (int icam = 0; icam < numCams; icam++)
         Trainers.push_back(new Trainer(icam, EventList, eventDir, imageFormat, imageFolder, FileParser->clone(), debug_mode / 100));
@@ -261,6 +266,7 @@ int main(int argc, char** argv) {
     }
     printf("***Training complete. AutoBub is now in detect mode***\n");
     delete PICO60Output;
+    const double T_train1 = wall();
 
     /* Detect mode: batches of events staged on the device, rows appended in event order */
     const std::string part_name = out_dir + "abub3hs_" + run_number + ".txt" + (opt.world > 1 ? ".rank" + std::to_string(opt.rank) : "");
@@ -274,13 +280,17 @@ int main(int argc, char** argv) {
         /* stage the batch under the keys the analyzers will ask for (AnalyzerUnit: ImageDir|EventID) */
         std::vector<std::string> keys;
         for (const std::string& ev : chunk) keys.push_back(eventDir + ev + "/Images/" + "|" + ev);
+        const double ts0 = wall();
         try {
             Parser* stage_parser = FileParser->clone();
-            AbubDevice::Get().PrefetchEvents(stage_parser, keys, chunk);
+            std::vector<int> tss;
+            for (int icam = 0; icam < numCams; icam++) tss.push_back(Trainers[icam]->TrainingSetSize);
+            AbubDevice::Get().PrefetchEvents(stage_parser, keys, chunk, tss.data());
             delete stage_parser;
         } catch (std::exception& e) {
             std::cout << e.what() << std::endl;       /* the analyzers will meet the same problem and report -6 */
         }
+        T_stage += wall() - ts0;
         for (size_t ci = 0; ci < chunk.size(); ci++) {
             const std::string& ev = chunk[ci];
             OutputWriter* EventOutput = new OutputWriter(out_dir, run_number, frameOffset, numCams);
@@ -289,12 +299,15 @@ int main(int argc, char** argv) {
             printf("\rProcessing event: %s / %d  ... ", ev.c_str(), nEvents - 1);
             advance_cursor();
             std::vector<AnalyzerUnit*> Analyzers;
+            const double ta0 = wall();
             for (int icam = 0; icam < numCams; icam++) {
                 Parser* tp = FileParser->clone();
                 Analyzers.push_back(new L3Localizer(ev, imageDir, icam, debug_mode / 100 ? false : true, &Trainers[icam], mask_dir, tp));
                 AnyCamAnalysis(ev, imageDir, icam, debug_mode % 10 ? false : true, &Trainers[icam], &EventOutput, out_dir,
                                actualEventNumber, &Analyzers[icam]);
             }
+            const double ta1 = wall();
+            T_analyze += ta1 - ta0;
             /* write and commit after each event, so in the event of a crash it is not lost (:379-383) */
             const std::string rows = EventOutput->formatCameraOutput();
             std::ofstream f(part_name, std::fstream::out | std::fstream::app);
@@ -303,9 +316,15 @@ int main(int argc, char** argv) {
             delete EventOutput;
             for (int icam = 0; icam < numCams; icam++) delete Analyzers[icam];
             AbubDevice::Get().ReleaseSlot(keys[ci]);
+            T_write += wall() - ta1;
         }
     }
     printf("run complete.\n");
+    if (getenv("ABUB_TIMING")) {
+        AbubDevice& d = AbubDevice::Get();
+        fprintf(stderr, "ABUB_TIMING train %.3f s | detect: stage %.3f s (setup %.3f read+decode %.3f upload %.3f K1 %.3f K2 %.3f localizer %.3f) analyze %.3f s write %.3f s\n",
+                T_train1 - T_train0, T_stage, d.t_read, d.t_decode, d.t_upload, d.t_hist, d.t_scan, d.t_loc, T_analyze, T_write);
+    }
 
     if (opt.world > 1) {
         /* every rank has flushed its part; rank 0 concatenates in rank order = event order (omp ordered, :380) */

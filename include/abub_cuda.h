@@ -79,6 +79,10 @@ int abub_pinned_acquire(abub_ctx* ctx, int slot, uint8_t** host_ptr);
 int abub_event_submit(abub_ctx* ctx, int slot, const int* nframes);
 /* Copy one camera's frames from arbitrary host memory (pageable ok) into a slot. */
 int abub_event_upload(abub_ctx* ctx, int slot, int cam, const uint8_t* frames, int nframes);
+/* One camera of a slot whose frames were decoded straight into the pinned staging buffer (abub_pinned_acquire):
+ * asynchronous H2D of its first `nframes` frames on the ctx stream.  The staging region must stay untouched until the
+ * next synchronising call (abub_sync, abub_trigger_results, ...). */
+int abub_event_submit_cam(abub_ctx* ctx, int slot, int cam, int nframes);
 /* Device address of the slot's [cam][frame][rows*cols] stack (for producers that
  * already live on the device) and the matching frame counts. */
 int abub_event_device_ptr(abub_ctx* ctx, int slot, uint8_t** dev_ptr);
