@@ -127,6 +127,8 @@ struct abub_loc_job {
     const uint32_t* k32;     // genesis: K32 plane of the camera
     const uint8_t* t8;       // post: min(6 sigma, 255)
     uint8_t* tz;             // out: TOZERO'd image (rows*cols)
+    uint8_t* segflags;       // [rows][ceil(cols/240)] per 240-px row segment of tz: bit0 = holds a non-zero pixel now,
+                             // bit1 = memory not known to be all zero (k5_localize.cu, sparse TOZERO frames)
     uint32_t* hist;          // out: 256-bin histogram of tz
     int tozero;              // loc_thres (genesis) or 3 (post)
     int genesis;

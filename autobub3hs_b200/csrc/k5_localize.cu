@@ -44,6 +44,7 @@ struct LocArena {
     // job-level
     abub_loc_job* d_jobs = nullptr;  abub_loc_job* h_jobs = nullptr;  int jobs_cap = 0;
     uint8_t* d_tz = nullptr;         size_t tz_cap = 0;       // jobs_cap * npix
+    uint8_t* d_segflags = nullptr;                              // jobs_cap * rows * nxw (see abub_loc_job::segflags)
     uint32_t* d_hist = nullptr;                                 // jobs_cap * 256
     int* d_thr = nullptr;                                       // jobs_cap
     // candidates
@@ -138,13 +139,27 @@ k5_post_stream_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols,
         const int nout = min(PS_TH, rows - y0);
         const uint32_t lim = 9u * (uint32_t)job.tozero + 5u;            // (sum+4)/9 <= tozero  <=>  sum < lim
         uint32_t r1[4] = {0, 0, 0, 0}, r2[4] = {0, 0, 0, 0};           // rows y-1 and y-2, widened (2 px per word)
-        for (int rl = 0; rl < nout + 2; rl++) {
+        // loads run two rows ahead of the arithmetic (the loop is otherwise bound by load latency)
+        struct RowIn { uint2 a, m, t; uint8_t prev; };
+        auto fetch = [&](int rl) {
             int y = y0 - 1 + rl;                                        // BORDER_REFLECT_101
             if (y < 0) y = -y;
             if (y >= rows) y = 2 * (rows - 1) - y;
             y = min(max(y, 0), rows - 1);
             const size_t off = (size_t)y * cols + gxl;
-            const uint2 a = ps_ld8(job.a + off), m = ps_ld8(job.b + off), t = ps_ld8(job.t8 + off);
+            RowIn r;
+            r.a = ps_ld8(job.a + off); r.m = ps_ld8(job.b + off); r.t = ps_ld8(job.t8 + off);
+            r.prev = job.segflags[(size_t)min(max(y0 + rl - 2, 0), rows - 1) * nxw + (unit % nxw)];   // same byte for every lane
+            return r;
+        };
+        RowIn q0 = fetch(0), q1 = fetch(1);
+        for (int rl = 0; rl < nout + 2; rl++) {
+            const RowIn cur = q0;
+            q0 = q1;
+            if (rl + 2 < nout + 2) q1 = fetch(rl + 2);
+            const uint2 a = cur.a, m = cur.m, t = cur.t;
+            uint8_t* const flagp = job.segflags + (size_t)min(max(y0 + rl - 2, 0), rows - 1) * nxw + (unit % nxw);
+            const uint8_t prev = cur.prev;
             const uint32_t d0 = __vsubus4(__vabsdiffu4(a.x, m.x), t.x);     // L3Localizer.cpp:779-782
             const uint32_t d1 = __vsubus4(__vabsdiffu4(a.y, m.y), t.y);
             uint32_t w[4];
@@ -182,7 +197,11 @@ k5_post_stream_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols,
                     o.x = ob[0] | (ob[1] << 8) | (ob[2] << 16) | (ob[3] << 24);
                     o.y = ob[4] | (ob[5] << 8) | (ob[6] << 16) | (ob[7] << 24);
                 }
-                if (out_lane) *reinterpret_cast<uint2*>(job.tz + (size_t)(y0 + rl - 2) * cols + gx) = o;
+                // the segment is stored when it holds something, or when what the memory holds is not known to be zero
+                const bool nz = __any_sync(0xffffffffu, (o.x | o.y) != 0u);
+                if (out_lane && (nz || (prev & 2))) *reinterpret_cast<uint2*>(job.tz + (size_t)(y0 + rl - 2) * cols + gx) = o;
+                const uint8_t nf = nz ? 3 : 0;
+                if (lane == 0 && nf != prev) *flagp = nf;
             }
 #pragma unroll
             for (int k = 0; k < 4; k++) { r2[k] = r1[k]; r1[k] = w[k]; }
@@ -302,6 +321,55 @@ k6_candidates_kernel(const abub_loc_job* __restrict__ jobs, const int* __restric
                 keys[slot] = ((unsigned long long)(unsigned)(job0 + jl) << 32) | (unsigned)(0xFFFFFFFFu - (unsigned)p);
             else
                 counters[3] = 1;
+        }
+    }
+}
+
+// Jobs whose frame was written in full (genesis K1 store mode, prepared jobs, the tiled K5b fallback): every
+// segment may hold anything.
+__global__ void k5_flag_fill_kernel(const abub_loc_job* __restrict__ jobs, size_t nseg, int all_jobs) {
+    const abub_loc_job job = jobs[blockIdx.y];
+    if (!all_jobs && job.genesis == 0) return;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nseg; i += (size_t)gridDim.x * blockDim.x) job.segflags[i] = 3;
+}
+
+// K6 over the segment flags (cols % 16 == 0): one thread per 240-px row segment; only flagged segments are read.
+__global__ void __launch_bounds__(256)
+k6_candidates_seg_kernel(const abub_loc_job* __restrict__ jobs, const int* __restrict__ thr, int rows, int cols, int nxw,
+                         unsigned long long* __restrict__ keys, int* __restrict__ counters, int cand_cap, int job0) {
+    const int jl = blockIdx.y;
+    const abub_loc_job job = jobs[jl];
+    const uint8_t* tz = job.tz;
+    const int t = thr[jl];
+    const int nseg = rows * nxw;
+    for (int sgi = blockIdx.x * blockDim.x + threadIdx.x; sgi < nseg; sgi += gridDim.x * blockDim.x) {
+        if (!(job.segflags[sgi] & 1)) continue;
+        const int y = sgi / nxw, xs = (sgi - y * nxw) * 240, xe = min(xs + 240, cols);
+        for (int xg = xs; xg < xe; xg += 16) {
+            const size_t pg = (size_t)y * cols + xg;
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(tz + pg));
+            if ((v.x | v.y | v.z | v.w) == 0u) continue;
+            const uint32_t wds[4] = {v.x, v.y, v.z, v.w};
+            for (int c = 0; c < 16; c++) {
+                if ((int)((wds[c >> 2] >> (8 * (c & 3))) & 0xFFu) <= t) continue;
+                const size_t p = pg + c;
+                const int x = xg + c;
+                bool earlier = false;
+                if (x > 0 && tz[p - 1] > t) earlier = true;
+                if (y > 0) {
+                    const uint8_t* up = tz + p - cols;
+                    if (up[0] > t) earlier = true;
+                    if (x > 0 && up[-1] > t) earlier = true;
+                    if (x + 1 < cols && up[1] > t) earlier = true;
+                }
+                if (!earlier) {
+                    const int slot = atomicAdd(&counters[0], 1);
+                    if (slot < cand_cap)
+                        keys[slot] = ((unsigned long long)(unsigned)(job0 + jl) << 32) | (unsigned)(0xFFFFFFFFu - (unsigned)p);
+                    else
+                        counters[3] = 1;
+                }
+            }
         }
     }
 }
@@ -430,7 +498,7 @@ int abub_loc_init(abub_ctx* ctx) {
 void abub_loc_free(abub_ctx* ctx) {
     LocArena* a = arena_of(ctx);
     if (!a) return;
-    cudaFree(a->d_jobs); cudaFree(a->d_tz); cudaFree(a->d_hist); cudaFree(a->d_thr);
+    cudaFree(a->d_jobs); cudaFree(a->d_tz); cudaFree(a->d_segflags); cudaFree(a->d_hist); cudaFree(a->d_thr);
     cudaFree(a->d_keys); cudaFree(a->d_keys_alt); cudaFree(a->d_cand); cudaFree(a->d_counters);
     cudaFree(a->d_scan); cudaFree(a->d_iscan); cudaFree(a->d_cub_tmp); cudaFree(a->d_chain);
     cudaFree(a->d_blobs); cudaFree(a->d_npf);
@@ -444,6 +512,12 @@ static int ensure_jobs(abub_ctx* ctx, LocArena* a, int njobs) {
     int rc;
     if ((rc = grow(ctx, &a->d_jobs, (size_t)njobs))) return rc;
     if ((rc = grow(ctx, &a->d_tz, (size_t)njobs * ctx->npix))) return rc;
+    const size_t nseg = (size_t)ctx->rows * ((ctx->cols + 239) / 240);
+    if ((rc = grow(ctx, &a->d_segflags, (size_t)njobs * nseg))) return rc;
+    // sparse TOZERO frames: a row segment is written only when it holds a non-zero pixel or may still hold one from an
+    // earlier call, so the scratch starts out all zero with every flag clear
+    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_tz, 0, (size_t)njobs * ctx->npix, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_segflags, 0, (size_t)njobs * nseg, ctx->stream));
     if ((rc = grow(ctx, &a->d_hist, (size_t)njobs * 256))) return rc;
     if ((rc = grow(ctx, &a->d_thr, (size_t)njobs))) return rc;
     if ((rc = grow(ctx, &a->d_npf, (size_t)njobs))) return rc;
@@ -501,6 +575,10 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
         k5_prepared_kernel<<<dim3(148 * 2, njobs), 256, 0, st>>>(a->d_jobs, npix);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
+    const int nxw_f = (ctx->cols + 239) / 240;
+    const bool stream_k5b = (ctx->cols % 8) == 0 && ctx->cols >= 16;
+    k5_flag_fill_kernel<<<dim3(4, njobs), 256, 0, st>>>(a->d_jobs, (size_t)ctx->rows * nxw_f, stream_k5b ? 0 : 1);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     k5_otsu_kernel<<<(njobs + 63) / 64, 64, 0, st>>>(a->d_jobs, a->d_thr, njobs, (uint32_t)npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     a->last_njobs = njobs;
@@ -509,9 +587,15 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     if (a->cand_cap == 0 && (rc = ensure_cands(ctx, a, 1 << 16))) return rc;
     for (;;) {
         ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_counters, 0, 8 * sizeof(int), st));
-        const int gx = (int)((npix + 256 * 16 - 1) / (256 * 16));
-        k6_candidates_kernel<<<dim3(gx, njobs), 256, 0, st>>>(a->d_jobs, a->d_thr, ctx->rows, ctx->cols, a->d_keys,
-                                                             a->d_counters, a->cand_cap, 0);
+        if ((ctx->cols & 15) == 0 && !getenv("ABUB_K6_DENSE")) {
+            const int nseg = ctx->rows * nxw_f;
+            k6_candidates_seg_kernel<<<dim3((nseg + 255) / 256, njobs), 256, 0, st>>>(a->d_jobs, a->d_thr, ctx->rows, ctx->cols, nxw_f,
+                                                                                     a->d_keys, a->d_counters, a->cand_cap, 0);
+        } else {
+            const int gx = (int)((npix + 256 * 16 - 1) / (256 * 16));
+            k6_candidates_kernel<<<dim3(gx, njobs), 256, 0, st>>>(a->d_jobs, a->d_thr, ctx->rows, ctx->cols, a->d_keys,
+                                                                 a->d_counters, a->cand_cap, 0);
+        }
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
         ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(counters, a->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
         ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(st));
@@ -603,6 +687,7 @@ extern "C" int abub_localize_batch(abub_ctx* ctx, const abub_loc_item* items, in
                 jb.k32 = cs.d_k32;
                 jb.t8 = cs.d_t8;
                 jb.tz = a->d_tz + (size_t)j * npix;
+                jb.segflags = a->d_segflags + (size_t)j * ctx->rows * ((ctx->cols + 239) / 240);
                 jb.hist = a->d_hist + (size_t)j * 256;
                 if (k == 0) {
                     jb.a = base + (size_t)it.trig * npix;        // L3Localizer.cpp:929
@@ -648,6 +733,7 @@ int abub_loc_run_prepared(abub_ctx* ctx, const uint8_t* d_over, int tozero, abub
     memset(&jb, 0, sizeof(jb));
     jb.a = d_over;
     jb.tz = a->d_tz;
+    jb.segflags = a->d_segflags;
     jb.hist = a->d_hist;
     jb.tozero = tozero;
     jb.genesis = 2;
