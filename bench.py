@@ -201,6 +201,32 @@ def run_reference(args, rank, world):
 # --------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------
+def bind_to_gpu_numa_node(local_rank):
+    """Pins this process to the CPUs of the NUMA node its GPU hangs off, so that the pinned staging buffers of the
+    end-to-end leg are allocated (first touch) in memory local to that GPU's PCIe root.  Best effort: returns the
+    node number or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(local_rank)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dev = "/sys/bus/pci/devices/" + bus.lower()[-12:]
+        node = int(open(dev + "/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -209,6 +235,7 @@ def run_ours(args, rank, world, local_rank):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    numa_node = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     B = args.events_per_step
@@ -373,7 +400,7 @@ def run_ours(args, rank, world, local_rank):
                    "train_events": n_train, "generated_on": "device (torch RNG), seconds=%.1f" % t_gen},
         "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": sent_total[0] * NPIX // e2e_steps,
                 "d2h_bytes_per_step": Be * NCAMS * 16 * (1 if args.e2e_mode == "full" else (NFRAMES + args.e2e_chunk - 1) // args.e2e_chunk),
-                "events_per_step": Be, "steps": e2e_steps, "mode": args.e2e_mode,
+                "events_per_step": Be, "steps": e2e_steps, "mode": args.e2e_mode, "rank0_numa_node": numa_node,
                 "note": ("abub_trigger_stream: host frames in pinned memory, sent %d frames at a time, a camera stops "
                          "receiving frames once its trigger search is decided (the reference's early exit); "
                          "frames_sent/frames_total = %.3f" % (args.e2e_chunk, sent_total[0] / max(1, e2e_steps * Be * NCAMS * NFRAMES)))
