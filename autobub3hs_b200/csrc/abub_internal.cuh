@@ -51,6 +51,10 @@ struct abub_ctx {
     int device = 0, rows = 0, cols = 0, ncams = 0, max_frames = 0, max_slots = 0;
     size_t npix = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;     // second stream of abub_trigger_stream (copy/compute overlap between slot groups)
+    cudaEvent_t ev_stream = nullptr;
+    int* h_raw = nullptr;               // pinned result table of abub_trigger_stream
+    size_t h_raw_cap = 0;
     std::string err;
     abub_cam_state cam[ABUB_MAX_CAMS];
     std::vector<abub_slot_state> slots;

@@ -94,6 +94,9 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     cudaFree(ctx->d_hist_tmp);
     cudaFree((void*)ctx->d_gate_tab); cudaFree(ctx->d_gate_hist);
     cudaFree(ctx->d_tmaps);
+    if (ctx->h_raw) cudaFreeHost(ctx->h_raw);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
+    if (ctx->ev_stream) cudaEventDestroy(ctx->ev_stream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -373,45 +376,86 @@ extern "C" int abub_trigger_stream(abub_ctx* ctx, int slot_first, int nslots, co
     const size_t hist_n = n * ctx->max_frames * 256;
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(ctx->d_hist + (size_t)slot_first * nc * ctx->max_frames * 256, 0,
                                          hist_n * sizeof(uint32_t), ctx->stream));
-    std::vector<int> raw(n * 4);
-    for (int lo = 0; lo < nf_max; lo += chunk_frames) {
-        const int hi = lo + chunk_frames < nf_max ? lo + chunk_frames : nf_max;
-        bool any = false;
-        for (int s = 0; s < nslots; s++) {
-            abub_slot_state& st = ctx->slots[slot_first + s];
-            for (int c = 0; c < nc; c++) {
-                const size_t i = (size_t)s * nc + c;
-                avail[i] = 0;
-                if (done[i]) continue;
-                any = true;
-                const int upto = hi < nf[i] ? hi : nf[i];
-                if (upto > sent[i]) {
-                    const size_t off = ((size_t)c * ctx->max_frames + sent[i]) * ctx->npix;
-                    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(st.d_frames + off, st.h_pinned + off, (size_t)(upto - sent[i]) * ctx->npix,
-                                                         cudaMemcpyHostToDevice, ctx->stream));
-                    sent[i] = upto;
-                }
-                avail[i] = sent[i];
-            }
-        }
-        if (!any) break;
-        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(d_av, avail.data(), n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-        rc = abub_k1_launch_trigger_range(ctx, slot_first, nslots, lo, hi, ctx->d_avail, false);
-        if (rc) return rc;
-        rc = abub_k2_launch_avail(ctx, slot_first, nslots, ctx->d_avail);
-        if (rc) return rc;
-        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(raw.data(), ctx->d_trig + (size_t)slot_first * nc * 4, n * 4 * sizeof(int),
-                                             cudaMemcpyDeviceToHost, ctx->stream));
-        ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        for (size_t i = 0; i < n; i++) {
+    // Two groups of slots take turns on two streams: while one group's K1/K2/read-back runs, the other group's
+    // frames are crossing PCIe, so the copy engine never waits for a decision.
+    const int ngroups = nslots >= 2 ? 2 : 1;
+    if (ngroups == 2 && !ctx->stream2) ABUB_CHECK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+    if (!ctx->ev_stream) ABUB_CHECK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_stream, cudaEventDisableTiming));
+    cudaStream_t gstream[2] = {ctx->stream, ngroups == 2 ? ctx->stream2 : ctx->stream};
+    const int gfirst[2] = {0, nslots / 2}, gcount[2] = {ngroups == 2 ? nslots / 2 : nslots, nslots - nslots / 2};
+    if (ngroups == 2) {                                           // the tables above must be in place before group 1 starts
+        ABUB_CHECK_CUDA(ctx, cudaEventRecord(ctx->ev_stream, ctx->stream));
+        ABUB_CHECK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->ev_stream, 0));
+    }
+    // read-backs must be asynchronous for the two groups to overlap: pinned result table
+    if (ctx->h_raw_cap < n * 4) {
+        if (ctx->h_raw) cudaFreeHost(ctx->h_raw);
+        ctx->h_raw = nullptr;
+        ctx->h_raw_cap = 0;
+        ABUB_CHECK_CUDA(ctx, cudaHostAlloc((void**)&ctx->h_raw, n * 4 * sizeof(int), cudaHostAllocDefault));
+        ctx->h_raw_cap = n * 4;
+    }
+    int* const raw = ctx->h_raw;
+    bool pending[2] = {false, false};                             // results of the group's last chunk not read yet
+    bool active[2] = {true, ngroups == 2};
+    cudaStream_t const main_stream = ctx->stream;
+    auto harvest = [&](int g) -> int {
+        if (!pending[g]) return ABUB_OK;
+        ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(gstream[g]));
+        pending[g] = false;
+        for (size_t i = (size_t)gfirst[g] * nc; i < (size_t)(gfirst[g] + gcount[g]) * nc; i++) {
             if (done[i] || raw[i * 4 + 1] == ABUB_STATUS_PENDING) continue;
             done[i] = 1;
             res_t[i] = raw[i * 4 + 0]; res_s[i] = raw[i * 4 + 1]; res_l[i] = raw[i * 4 + 2];
         }
+        return ABUB_OK;
+    };
+    for (int lo = 0; lo < nf_max && (active[0] || active[1]); lo += chunk_frames) {
+        const int hi = lo + chunk_frames < nf_max ? lo + chunk_frames : nf_max;
+        for (int g = 0; g < ngroups; g++) {
+            if (!active[g]) continue;
+            if ((rc = harvest(g))) { ctx->stream = main_stream; return rc; }
+            cudaStream_t st_g = gstream[g];
+            bool any = false;
+            for (int s = gfirst[g]; s < gfirst[g] + gcount[g]; s++) {
+                abub_slot_state& st = ctx->slots[slot_first + s];
+                for (int c = 0; c < nc; c++) {
+                    const size_t i = (size_t)s * nc + c;
+                    avail[i] = 0;
+                    if (done[i]) continue;
+                    any = true;
+                    const int upto = hi < nf[i] ? hi : nf[i];
+                    if (upto > sent[i]) {
+                        const size_t off = ((size_t)c * ctx->max_frames + sent[i]) * ctx->npix;
+                        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(st.d_frames + off, st.h_pinned + off, (size_t)(upto - sent[i]) * ctx->npix,
+                                                             cudaMemcpyHostToDevice, st_g));
+                        sent[i] = upto;
+                    }
+                    avail[i] = sent[i];
+                }
+            }
+            if (!any) { active[g] = false; continue; }
+            const size_t o = (size_t)gfirst[g] * nc, cnt = (size_t)gcount[g] * nc;
+            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(d_av + o, avail.data() + o, cnt * sizeof(int), cudaMemcpyHostToDevice, st_g));
+            ctx->stream = st_g;                                   // the launchers enqueue on ctx->stream
+            rc = abub_k1_launch_trigger_range(ctx, slot_first + gfirst[g], gcount[g], lo, hi, ctx->d_avail, false);
+            if (!rc) rc = abub_k2_launch_avail(ctx, slot_first + gfirst[g], gcount[g], ctx->d_avail);
+            ctx->stream = main_stream;
+            if (rc) return rc;
+            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(raw + o * 4, ctx->d_trig + ((size_t)slot_first * nc + o) * 4, cnt * 4 * sizeof(int),
+                                                 cudaMemcpyDeviceToHost, st_g));
+            pending[g] = true;
+        }
+    }
+    for (int g = 0; g < ngroups; g++)
+        if ((rc = harvest(g))) return rc;
+    if (ngroups == 2) {                                           // later work on the main stream follows both groups
+        ABUB_CHECK_CUDA(ctx, cudaEventRecord(ctx->ev_stream, ctx->stream2));
+        ABUB_CHECK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_stream, 0));
     }
     // leave the result table as abub_trigger_results expects it
     for (size_t i = 0; i < n; i++) { raw[i * 4] = res_t[i]; raw[i * 4 + 1] = res_s[i]; raw[i * 4 + 2] = res_l[i]; raw[i * 4 + 3] = sent[i]; }
-    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_trig + (size_t)slot_first * nc * 4, raw.data(), n * 4 * sizeof(int),
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_trig + (size_t)slot_first * nc * 4, raw, n * 4 * sizeof(int),
                                          cudaMemcpyHostToDevice, ctx->stream));
     ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     for (size_t i = 0; i < n; i++) {
