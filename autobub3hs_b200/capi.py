@@ -20,7 +20,7 @@ ABUB_MAX_TRACK = 10
 EXPORTS = [
     "abub_ctx_create", "abub_ctx_destroy", "abub_last_error", "abub_sync", "abub_stream",
     "abub_set_background", "abub_set_background_from_training",
-    "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_submit_cam", "abub_event_device_ptr",
+    "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_submit_cam", "abub_event_decode_png", "abub_event_device_ptr",
     "abub_event_set_nframes",
     "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_hist_write", "abub_trigger_scan", "abub_trigger_results", "abub_trigger", "abub_trigger_stream",
     "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_add_slots",
@@ -38,6 +38,14 @@ class Blob(C.Structure):
                 ("npts", C.c_int32), ("first_px", C.c_int32), ("reserved", C.c_int32),
                 ("sum_x", C.c_int64), ("sum_y", C.c_int64),
                 ("area", C.c_double), ("m00", C.c_double), ("m10", C.c_double), ("m01", C.c_double)]
+
+
+_cudart = None
+
+
+class PngJob(C.Structure):
+    """struct abub_png_job."""
+    _fields_ = [("slot", C.c_int32), ("cam", C.c_int32), ("frame", C.c_int32), ("zlen", C.c_uint32)]
 
 
 class LocItem(C.Structure):
@@ -88,6 +96,7 @@ def load() -> C.CDLL:
     lib.abub_train_add_event.argtypes = [vp, C.c_int, u8p, C.POINTER(C.c_float), ip]
     lib.abub_train_add_slot.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float), ip]
     lib.abub_event_submit_cam.argtypes = [vp, C.c_int, C.c_int, C.c_int]
+    lib.abub_event_decode_png.argtypes = [vp, C.POINTER(PngJob), C.c_int, ip]
     lib.abub_train_add_slots.argtypes = [vp, C.c_int, ip, C.c_int, C.POINTER(C.c_float), ip]
     lib.abub_train_add_events.argtypes = [vp, C.c_int, u8p, C.c_int, C.POINTER(C.c_float), ip]
     lib.abub_selftest_fdiv.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
@@ -202,6 +211,26 @@ class Context:
         p = C.c_void_p()
         self._ck(self.lib.abub_event_device_ptr(self.h, slot, C.byref(p)), "abub_event_device_ptr")
         return int(p.value)
+
+    def download_frames(self, slot: int) -> np.ndarray:
+        """[ncams, max_frames, rows, cols] copy of the slot's device memory (test helper; cudaMemcpy through libcudart)."""
+        global _cudart
+        if _cudart is None:
+            for name in ("libcudart.so.12", "libcudart.so"):
+                try:
+                    _cudart = C.CDLL(name)
+                    break
+                except OSError:
+                    continue
+            if _cudart is None:
+                raise AbubError("libcudart not found")
+            _cudart.cudaMemcpy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
+        self.sync()
+        out = np.empty((self.ncams, self.max_frames, self.rows, self.cols), np.uint8)
+        rc = _cudart.cudaMemcpy(out.ctypes.data, self.event_device_ptr(slot), out.size, 2)
+        if rc != 0:
+            raise AbubError(f"cudaMemcpy D2H failed ({rc})")
+        return out
 
     def event_set_nframes(self, slot: int, nframes: Sequence[int]) -> None:
         nf = (C.c_int * self.ncams)(*nframes)
@@ -374,6 +403,22 @@ class Context:
             out.append(frames)
         assert off == tot.value
         return out
+
+    def decode_png(self, jobs) -> np.ndarray:
+        """jobs: (slot, cam, frame, zlib_bytes).  The streams are copied into the slots' pinned staging regions and
+        decoded on the device; returns ok[n] (bool)."""
+        n = len(jobs)
+        arr = (PngJob * n)()
+        pins = {}
+        for i, (slot, cam, frame, z) in enumerate(jobs):
+            if slot not in pins:
+                pins[slot] = self.pinned(slot)
+            zb = np.frombuffer(z, dtype=np.uint8)
+            pins[slot][cam, frame].reshape(-1)[:len(zb)] = zb
+            arr[i] = PngJob(slot, cam, frame, len(zb))
+        ok = (C.c_int * n)()
+        self._ck(self.lib.abub_event_decode_png(self.h, arr, n, ok), "abub_event_decode_png")
+        return np.array([ok[i] for i in range(n)], dtype=bool)
 
     # ---- bellows veto ----
     def set_bellows_template(self, cam: int, templ: Optional[np.ndarray]) -> None:

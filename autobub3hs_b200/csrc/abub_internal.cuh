@@ -76,6 +76,7 @@ struct abub_ctx {
     int gate_cap = 0;
     void*     loc = nullptr;        // localizer arena (k5_localize.cu)
     void*     bel = nullptr;        // bellows-veto arena (k8_bellows.cu)
+    void*     png = nullptr;        // on-device PNG decode arena (k9_png.cu)
     void*     d_tmaps = nullptr;    // CUtensorMap[2*max_slots + 2*ncams] (k1_trigger_tma.cu); null = TMA path off
 };
 
@@ -146,3 +147,5 @@ void abub_loc_free(abub_ctx* ctx);
 int abub_loc_run_prepared(abub_ctx* ctx, const uint8_t* d_over, int tozero, abub_blob* out, int cap, int* n_out);
 // K8 (k8_bellows.cu)
 void abub_bel_free(abub_ctx* ctx);
+// K9 (k9_png.cu)
+void abub_png_free(abub_ctx* ctx);

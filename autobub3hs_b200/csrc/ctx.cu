@@ -76,6 +76,7 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     abub_loc_free(ctx);
     abub_bel_free(ctx);
+    abub_png_free(ctx);
     for (int c = 0; c < ABUB_MAX_CAMS; c++) {
         abub_cam_state& cs = ctx->cam[c];
         cudaFree(cs.d_mean); cudaFree(cs.d_sigma); cudaFree(cs.d_t8); cudaFree(cs.d_k32); cudaFree(cs.d_k16);

@@ -170,6 +170,21 @@ int abub_train_finish_partials(abub_ctx* ctx, int cam, uint8_t* mean, uint8_t* s
 int abub_train_finish_allreduced(abub_ctx* ctx, int cam, void* nccl_comm, uint8_t* mean, uint8_t* sigma,
                                  int* set_size, int* status, int* n_flagged);
 
+/* ---- on-device PNG decode (replaces cv::imread / cv::imdecode of RawParser.cpp:39, ZipParser.cpp:222
+ * for the DAQ's 8-bit greyscale, non-interlaced PNG frames) ----
+ * The caller parses the PNG container (signature, IHDR, IDAT chunks) and places the zlib stream -- the concatenated
+ * IDAT payloads -- at the START of the frame's own region of the slot's pinned staging buffer (abub_pinned_acquire:
+ * region of frame f of camera c begins at ((c * max_frames + f) * rows * cols)).  The library sends the zlen
+ * compressed bytes to the device, inflates them (RFC 1951, one warp per frame), undoes the PNG row filters and
+ * leaves the pixels in the frame.  ok[i] = 1 when job i decoded to exactly rows*(cols+1) filtered bytes with valid
+ * filter types; otherwise the frame is zero-filled and ok[i] = 0 (decode it on the host instead).
+ * Frame counts are set separately (abub_event_set_nframes).  Synchronises the stream. */
+typedef struct abub_png_job {
+    int32_t slot, cam, frame;
+    uint32_t zlen;
+} abub_png_job;
+int abub_event_decode_png(abub_ctx* ctx, const abub_png_job* jobs, int n, int* ok);
+
 /* ---- bellows veto: L3Localizer.cpp:292-390 (taken when every genesis contour lies in the bellows mask) ---- */
 /* The camera's cam<c>_bellows_template.png as rows*cols grey bytes (L3Localizer.cpp:294-295); NULL clears it
  * ("template not loadable", :297-301). */
