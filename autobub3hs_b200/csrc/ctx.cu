@@ -214,6 +214,20 @@ extern "C" int abub_event_submit_cam(abub_ctx* ctx, int slot, int cam, int nfram
     return push_nframes(ctx, slot);
 }
 
+// one frame, from its region of the pinned staging buffer (asynchronous)
+extern "C" int abub_event_upload_frame(abub_ctx* ctx, int slot, int cam, int frame) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && cam >= 0 && cam < ctx->ncams && frame >= 0 && frame < ctx->max_frames,
+                 "slot/cam/frame");
+    cudaSetDevice(ctx->device);
+    abub_slot_state& s = ctx->slots[slot];
+    ABUB_REQUIRE(ctx, s.h_pinned != nullptr, "slot has no pinned buffer (call abub_pinned_acquire)");
+    const size_t off = ((size_t)cam * ctx->max_frames + frame) * ctx->npix;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(s.d_frames + off, s.h_pinned + off, ctx->npix, cudaMemcpyHostToDevice, ctx->stream));
+    s.hist_valid = false;
+    return ABUB_OK;
+}
+
 extern "C" int abub_event_device_ptr(abub_ctx* ctx, int slot, uint8_t** dev_ptr) {
     if (!ctx) return ABUB_E_INVALID;
     ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && dev_ptr, "abub_event_device_ptr");

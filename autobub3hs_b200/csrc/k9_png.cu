@@ -34,24 +34,53 @@ struct WarpTables {
     uint8_t len[320];                      // code lengths being read
 };
 
+// Bit reader shared by the warp.  The compressed stream is read one 128-byte line at a time: lane i holds word i of
+// the current line (one coalesced load per 1024 bits) and of the next line (issued a whole line ahead, so its latency
+// is never waited for); a refill broadcasts the next word with one SHFL.  All fields are warp-uniform except the two
+// line registers.
 struct Bits {
-    const uint8_t* p;
-    uint32_t pos, n;
+    const uint32_t* w;      // stream as 32-bit words (the frame region is 16-byte aligned)
+    uint32_t nwords;        // words that may be read (stream length rounded up)
+    uint32_t line;          // index of the current 32-word line
+    int widx;               // next word of the line to take
+    uint32_t cur, nxt;      // this lane's word of the current / next line
     uint64_t buf;
     int cnt;
     bool overrun;
 };
 
-__device__ __forceinline__ void refill(Bits& b) {          // keep at least 56 bits when input remains
-    while (b.cnt <= 56) {
-        uint64_t v = 0;
-        if (b.pos < b.n) v = __ldg(b.p + b.pos);
-        else if (b.pos > b.n + 8) b.overrun = true;
-        b.pos++;
-        b.buf |= v << b.cnt;
-        b.cnt += 8;
+__device__ __forceinline__ uint32_t bits_load(const Bits& b, uint32_t line, int lane) {
+    const uint32_t i = line * 32u + (uint32_t)lane;
+    return i < b.nwords ? __ldg(b.w + i) : 0u;
+}
+__device__ __forceinline__ void bits_init(Bits& b, const uint8_t* p, uint32_t nbytes, uint32_t bytepos, int lane) {
+    b.w = reinterpret_cast<const uint32_t*>(p);
+    b.nwords = (nbytes + 3u) >> 2;
+    const uint32_t wpos = bytepos >> 2;
+    b.line = wpos >> 5;
+    b.widx = (int)(wpos & 31u);
+    b.cur = bits_load(b, b.line, lane);
+    b.nxt = bits_load(b, b.line + 1, lane);
+    b.buf = 0;
+    b.cnt = 0;
+    b.overrun = false;
+}
+__device__ __forceinline__ void refill(Bits& b, int lane) {     // afterwards at least 33 bits are present
+    if (b.cnt <= 32) {
+        const uint32_t wv = __shfl_sync(0xffffffffu, b.cur, b.widx);
+        b.buf |= (uint64_t)wv << b.cnt;
+        b.cnt += 32;
+        if (++b.widx == 32) {
+            b.widx = 0;
+            b.line++;
+            b.cur = b.nxt;
+            b.nxt = bits_load(b, b.line + 1, lane);
+            if (b.line * 32u > b.nwords + 32u) b.overrun = true;
+        }
     }
 }
+// byte offset in the stream of the first bit not yet consumed (call only when cnt is a multiple of 8)
+__device__ __forceinline__ uint32_t bits_bytepos(const Bits& b) { return (b.line * 32u + (uint32_t)b.widx) * 4u - (uint32_t)(b.cnt >> 3); }
 __device__ __forceinline__ uint32_t take(Bits& b, int n) {  // n <= 32, bits must be present
     const uint32_t v = (uint32_t)(b.buf & ((1ull << n) - 1ull));
     b.buf >>= n;
@@ -148,30 +177,33 @@ __global__ void __launch_bounds__(32 * K9_WARPS) k9_inflate_kernel(const PngDev*
     const PngDev J = jobs[job];
     uint8_t* const out = J.filt;
     Bits b;
-    b.p = J.z; b.n = J.zlen; b.pos = 0; b.buf = 0; b.cnt = 0; b.overrun = false;
+    bits_init(b, J.z, J.zlen, 0, lane);
     int st = 0;
     uint32_t op = 0;
-    refill(b);
+    refill(b, lane);
     {   // zlib header: CM = 8, no preset dictionary, header check
         const uint32_t cmf = take(b, 8), flg = take(b, 8);
         if ((cmf & 15u) != 8u || ((cmf << 8) | flg) % 31u != 0u || (flg & 32u)) st = 1;
     }
     bool last = false;
     while (!st && !last) {
-        refill(b);
+        refill(b, lane);
         last = take(b, 1) != 0;
         const uint32_t type = take(b, 2);
         if (type == 0) {                                   // stored
             take(b, b.cnt & 7);
-            refill(b);
+            refill(b, lane);
             const uint32_t len = take(b, 16), nlen = take(b, 16);
             if ((len ^ 0xFFFFu) != nlen) { st = 2; break; }
-            // the bit buffer holds whole bytes now: rewind to the byte position
-            const uint32_t start = b.pos - (uint32_t)(b.cnt >> 3);
-            if (start + len > b.n || op + len > out_len) { st = 2; break; }
-            for (uint32_t i = lane; i < len; i += 32) out[op + i] = __ldg(b.p + start + i);
+            // the bit buffer holds whole bytes now: continue at the byte position
+            const uint32_t start = bits_bytepos(b);
+            if (start + len > J.zlen || op + len > out_len) { st = 2; break; }
+            for (uint32_t i = lane; i < len; i += 32) out[op + i] = __ldg(J.z + start + i);
             op += len;
-            b.pos = start + len; b.buf = 0; b.cnt = 0;
+            const uint32_t np = start + len;
+            bits_init(b, J.z, J.zlen, np, lane);
+            refill(b, lane);
+            take(b, 8 * (int)(np & 3u));                  // bytes of the first word that belong to the stored data
             __syncwarp();
             continue;
         }
@@ -190,7 +222,7 @@ __global__ void __launch_bounds__(32 * K9_WARPS) k9_inflate_kernel(const PngDev*
             for (int i = lane; i < 19; i += 32) T.len[i] = 0;
             __syncwarp();
             for (int i = 0; i < hclen; i++) {
-                refill(b);
+                refill(b, lane);
                 const uint32_t v = take(b, 3);
                 if (lane == 0) T.len[c_clen_order[i]] = (uint8_t)v;
             }
@@ -200,7 +232,7 @@ __global__ void __launch_bounds__(32 * K9_WARPS) k9_inflate_kernel(const PngDev*
             __syncwarp();
             int i = 0, prev = 0;
             while (i < hlit + hdist) {
-                refill(b);
+                refill(b, lane);
                 const int s = decode_sym(b, T.dist, 7, T.dist_cnt, T.dist_sym);
                 if (s < 0) { st = 3; break; }
                 if (s < 16) {
@@ -235,7 +267,40 @@ __global__ void __launch_bounds__(32 * K9_WARPS) k9_inflate_kernel(const PngDev*
         __syncwarp();
         // ---- symbols of the block ----
         for (;;) {
-            refill(b);
+            refill(b, lane);
+#ifndef ABUB_K9_SCALAR
+            {   // ---- literal run.  Lane j decodes the code that WOULD start at bit j of the window; the codes that really
+                // start there are the chain 0 -> 0+len(0) -> ..., found by pointer doubling over the warp (REDUX + SHFL per
+                // round).  Every literal on the chain is stored by its own lane; the chain stops at the first length code,
+                // end-of-block, long (> TB_LIT bits) code or at the end of the window, where the one-symbol path takes over.
+                const uint32_t x = __funnelshift_r((uint32_t)b.buf, (uint32_t)(b.buf >> 32), lane);
+                const uint32_t e = T.lit[x & ((1u << TB_LIT) - 1u)];
+                const int l = (int)(e & 15u);
+                const bool lit = l != 0 && e < (256u << 4) && lane + l <= b.cnt;
+                const int cons = lit ? lane + l : lane;             // bits consumed if the chain ends at this lane
+                int succ = cons < 32 && lit ? cons : 32;             // 32: no successor inside the window
+                uint32_t M = 1u;
+#pragma unroll
+                for (int k = 0; k < 5; k++) {
+                    const uint32_t add = __reduce_or_sync(0xffffffffu, (((M >> lane) & 1u) && succ < 32) ? (1u << succ) : 0u);
+                    if ((add & ~M) == 0u) break;
+                    M |= add;
+                    const int t = __shfl_sync(0xffffffffu, succ, succ & 31);
+                    succ = succ < 32 ? t : 32;
+                }
+                const uint32_t Mlit = M & __ballot_sync(0xffffffffu, lit);
+                const int last_lane = 31 - __clz((int)M);
+                const int used = __shfl_sync(0xffffffffu, cons, last_lane);
+                const uint32_t n = (uint32_t)__popc(Mlit);
+                if (op + n > out_len) { st = 4; break; }
+                if ((Mlit >> lane) & 1u) out[op + (uint32_t)__popc(Mlit & ((1u << lane) - 1u))] = (uint8_t)(e >> 4);
+                op += n;
+                b.buf >>= used;
+                b.cnt -= used;
+                if (used > last_lane) continue;                      // ran off the window on a literal: next window
+                refill(b, lane);
+            }
+#endif
             const int s = decode_sym(b, T.lit, TB_LIT, T.lit_cnt, T.lit_sym);
             if (s < 256) {
                 if (s < 0) { st = 3; break; }
@@ -247,9 +312,9 @@ __global__ void __launch_bounds__(32 * K9_WARPS) k9_inflate_kernel(const PngDev*
             if (s == 256) break;
             if (s > 285) { st = 3; break; }
             const uint32_t len = c_len_base[s - 257] + take(b, c_len_extra[s - 257]);
+            refill(b, lane);                                // 33 bits: distance code (<= 15) + extra bits (<= 13)
             const int ds = decode_sym(b, T.dist, TB_DIST, T.dist_cnt, T.dist_sym);
             if (ds < 0 || ds > 29) { st = 3; break; }
-            refill(b);
             const uint32_t dist = c_dist_base[ds] + take(b, c_dist_extra[ds]);
             if (dist > op || op + len > out_len) { st = 4; break; }
             __syncwarp();                                   // literals stored by lane 0 become visible to the copy
@@ -371,6 +436,7 @@ extern "C" int abub_event_decode_png(abub_ctx* ctx, const abub_png_job* jobs, in
         ABUB_REQUIRE(ctx, j.slot >= 0 && j.slot < ctx->max_slots && j.cam >= 0 && j.cam < ctx->ncams && j.frame >= 0 &&
                               j.frame < ctx->max_frames, "png job slot/cam/frame");
         ABUB_REQUIRE(ctx, j.zlen >= 2 && (size_t)j.zlen <= ctx->npix, "png job: stream longer than a frame");
+        ABUB_REQUIRE(ctx, ctx->npix % 4 == 0, "on-device PNG decode needs rows*cols to be a multiple of 4 (word-aligned frame regions)");
         ABUB_REQUIRE(ctx, ctx->slots[j.slot].h_pinned != nullptr, "slot has no pinned buffer (call abub_pinned_acquire)");
     }
     if (n > a->cap) {

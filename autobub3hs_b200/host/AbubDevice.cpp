@@ -160,23 +160,123 @@ void AbubDevice::LoadCamera(int slot, int cam, Parser* parser, const std::string
     st.loaded[cam] = true;
 }
 
+void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const std::vector<std::string>& events) {
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
+    struct Item { int slot, cam, frame; const std::string* event; std::string name; char state; uint32_t zlen; };   // state: 0 bad, 1 host-decoded, 2 device job
+    std::vector<Item> items;
+    std::vector<std::vector<int>> ncam(slots.size(), std::vector<int>(ncams_, -1));      // frames per (event, cam); -1 = not staged here
+    for (size_t e = 0; e < events.size(); e++)
+        for (int cam = 0; cam < ncams_; cam++) {
+            AbubSlot& st = slots_[slots[e]];
+            if (st.loaded[cam]) continue;
+            std::vector<std::string> frames;
+            parser->ParseAndSortFramesInFolder(events[e], cam, frames);
+            if ((int)frames.size() > max_frames_) continue;                // the analyzer reports the capacity problem (-6)
+            ncam[e][cam] = (int)frames.size();
+            for (int f = 0; f < (int)frames.size(); f++) items.push_back(Item{slots[e], cam, f, &events[e], frames[f], 0, 0});
+        }
+    if (!ctx_) {                                                           // size the context from the first readable header
+        std::vector<uint8_t> enc;
+        for (size_t i = 0; i < items.size() && !ctx_; i++) {
+            int r, c;
+            if (parser->GetImageBytes(*items[i].event, items[i].name, enc) != parser->FailureCode() && !enc.empty() &&
+                abubcodec::peek_size(enc.data(), enc.size(), &r, &c))
+                Context(r, c);
+        }
+        if (!ctx_) return;                                                 // nothing decodable: the analyzers report it
+    }
+    const size_t npix = (size_t)rows_ * cols_;
+    std::map<int, uint8_t*> pin;
+    for (int s : slots) {
+        uint8_t* p = nullptr;
+        Check(abub_pinned_acquire(ctx_, s, &p), "abub_pinned_acquire");
+        pin[s] = p;
+    }
+    const double t1 = now();
+    const bool device_png = (npix % 4 == 0) && !getenv("ABUB_PNG_ON_HOST");
+#pragma omp parallel for schedule(dynamic, 1)
+    for (long i = 0; i < (long)items.size(); i++) {
+        Item& it = items[i];
+        uint8_t* region = pin[it.slot] + ((size_t)it.cam * max_frames_ + it.frame) * npix;
+        std::vector<uint8_t> enc;
+        if (parser->GetImageBytes(*it.event, it.name, enc) == parser->FailureCode() || enc.empty()) { memset(region, 0, npix); continue; }
+        if (device_png) {
+            const size_t zl = abubcodec::png_gray8_stream(enc.data(), enc.size(), rows_, cols_, region, npix);
+            if (zl >= 2) { it.state = 2; it.zlen = (uint32_t)zl; continue; }
+        }
+        if (abubcodec::decode_into(enc.data(), enc.size(), region, rows_, cols_)) it.state = 1;
+        else memset(region, 0, npix);
+    }
+    const double t2 = now();
+    // host-decoded cameras go up whole (their device-decoded frames carry compressed bytes for the moment) ...
+    std::vector<abub_png_job> jobs;
+    std::vector<size_t> job_item;
+    std::map<std::pair<int, int>, bool> host_cam;
+    for (size_t i = 0; i < items.size(); i++) {
+        if (items[i].state == 2) { jobs.push_back(abub_png_job{items[i].slot, items[i].cam, items[i].frame, items[i].zlen}); job_item.push_back(i); }
+        else host_cam[{items[i].slot, items[i].cam}] = true;
+    }
+    for (size_t e = 0; e < events.size(); e++)
+        for (int cam = 0; cam < ncams_; cam++) {
+            if (ncam[e][cam] < 0) continue;
+            if (host_cam.count({slots[e], cam})) Check(abub_event_submit_cam(ctx_, slots[e], cam, ncam[e][cam]), "abub_event_submit_cam");
+        }
+    // ... then the PNG streams are sent and decoded in place
+    std::vector<int> okv(jobs.size(), 0);
+    if (!jobs.empty()) Check(abub_event_decode_png(ctx_, jobs.data(), (int)jobs.size(), okv.data()), "abub_event_decode_png");
+    for (size_t j = 0; j < jobs.size(); j++) {
+        Item& it = items[job_item[j]];
+        if (okv[j]) { it.state = 1; n_gpu_decoded++; continue; }
+        // the device rejected the stream: let the host decoder have the last word on this frame
+        std::vector<uint8_t> enc;
+        uint8_t* region = pin[it.slot] + ((size_t)it.cam * max_frames_ + it.frame) * npix;
+        it.state = 0;
+        if (parser->GetImageBytes(*it.event, it.name, enc) != parser->FailureCode() && !enc.empty() &&
+            abubcodec::decode_into(enc.data(), enc.size(), region, rows_, cols_)) {
+            it.state = 1;
+            Check(abub_event_upload_frame(ctx_, it.slot, it.cam, it.frame), "abub_event_upload_frame");
+        }
+    }
+    for (size_t e = 0; e < events.size(); e++) {
+        AbubSlot& st = slots_[slots[e]];
+        int nf[8] = {0};
+        for (int cam = 0; cam < ncams_; cam++) {
+            if (ncam[e][cam] >= 0) {
+                st.nframes[cam] = ncam[e][cam];
+                st.loaded[cam] = true;
+                st.bad[cam].clear();
+            }
+            nf[cam] = st.nframes[cam];
+        }
+        Check(abub_event_set_nframes(ctx_, slots[e], nf), "abub_event_set_nframes");
+    }
+    for (const Item& it : items) {
+        if (it.state == 0) slots_[it.slot].bad[it.cam].push_back(it.frame);
+        else if (it.zlen == 0) n_cpu_decoded++;
+    }
+    const double t3 = now();
+    t_read += t1 - t0; t_decode += t2 - t1; t_upload += t3 - t2;
+}
+
 std::vector<int> AbubDevice::PrefetchEvents(Parser* parser, const std::vector<std::string>& keys, const std::vector<std::string>& events,
                                             const int* training_set_sizes) {
     std::lock_guard<std::recursive_mutex> g(mu_);
     std::vector<int> out;
-    for (size_t e = 0; e < events.size(); e++) {
-        const std::string& ev = events[e];
-        const int s = AcquireSlot(keys[e]);
-        out.push_back(s);
-        for (int cam = 0; cam < ncams_; cam++) {
-            std::vector<std::string> frames;
-            parser->ParseAndSortFramesInFolder(ev, cam, frames);
-            try {
-                LoadCamera(s, cam, parser, ev, frames);
-            } catch (const AbubError&) {
-                // left unloaded: the analyzer of this camera will hit the same error and report -6
+    for (size_t e = 0; e < events.size(); e++) out.push_back(AcquireSlot(keys[e]));
+    if (getenv("ABUB_HOST_DECODE")) {
+        for (size_t e = 0; e < events.size(); e++)
+            for (int cam = 0; cam < ncams_; cam++) {
+                std::vector<std::string> frames;
+                parser->ParseAndSortFramesInFolder(events[e], cam, frames);
+                try {
+                    LoadCamera(out[e], cam, parser, events[e], frames);
+                } catch (const AbubError&) {
+                    // left unloaded: the analyzer of this camera will hit the same error and report -6
+                }
             }
-        }
+    } else {
+        StageBatch(parser, out, events);
     }
     // one K1 launch per contiguous slot range
     std::vector<int> sorted(out);

@@ -88,6 +88,8 @@ public:
     const Image8* Mask(int cam, bool bellows, const std::string& mask_dir);
 
     void Shutdown();
+    // Frames decoded on the device so far (PNG, K9) / on the host cores.
+    long n_gpu_decoded = 0, n_cpu_decoded = 0;
 
     // wall-clock seconds spent in the ingest stages (printed by abub3hs when ABUB_TIMING is set)
     double t_read = 0, t_decode = 0, t_upload = 0, t_hist = 0, t_scan = 0, t_loc = 0;
@@ -98,6 +100,9 @@ private:
     abub_ctx* ctx_ = nullptr;
     std::recursive_mutex mu_;
     std::vector<AbubSlot> slots_;
+    // stages every camera of the given (slot, event) pairs: all frames are read on all cores; 8-bit grey PNG frames are
+    // inflated and unfiltered on the device (abub_event_decode_png), anything else is decoded on the host
+    void StageBatch(Parser* parser, const std::vector<int>& slots, const std::vector<std::string>& events);
     std::map<std::string, int> by_key_;
     std::map<std::string, bool> templates_;     // "<mask dir>|<cam>" -> loadable
     std::map<std::string, Image8> masks_;       // "<mask dir>|<cam>|<bellows>" -> image (empty = unreadable)

@@ -95,6 +95,12 @@ struct PngInfo {
     int channels() const { return ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : 4; }
 };
 
+// libpng refuses a file whose critical chunk fails its CRC (cv2.imread then returns an empty Mat); same here, which also
+// makes the compressed stream trustworthy for the device decoder (K9 does not compute the zlib Adler-32).
+inline bool png_chunk_crc_ok(const uint8_t* chunk, uint32_t len) {
+    return (uint32_t)crc32(crc32(0L, Z_NULL, 0), chunk + 4, len + 4) == rd32be(chunk + 8 + len);
+}
+
 bool png_header(const uint8_t* b, size_t n, PngInfo& h) {
     if (n < 33 || memcmp(b, kPngSig, 8) != 0) return false;
     if (rd32be(b + 8) != 13 || memcmp(b + 12, "IHDR", 4) != 0) return false;
@@ -126,7 +132,7 @@ bool png_decode(const uint8_t* b, size_t n, const PngInfo& h, Sink& s) {
         const uint8_t* type = b + pos + 4;
         if (pos + 12 + (size_t)len > n) return false;
         const uint8_t* d = b + pos + 8;
-        if (!memcmp(type, "IDAT", 4)) z.insert(z.end(), d, d + len);
+        if (!memcmp(type, "IDAT", 4)) { if (!png_chunk_crc_ok(b + pos, len)) return false; z.insert(z.end(), d, d + len); }
         else if (!memcmp(type, "PLTE", 4)) { for (uint32_t i = 0; i < len / 3 && i < 256; i++) memcpy(pal[i], d + 3 * i, 3); }
         else if (!memcmp(type, "IEND", 4)) end = true;
         pos += 12 + (size_t)len;
@@ -221,6 +227,27 @@ bool peek_size(const uint8_t* buf, size_t n, int* rows, int* cols) {
     if (bmp_header(buf, n, bh)) { *rows = bh.height; *cols = bh.width; return true; }
     if (png_header(buf, n, ph)) { *rows = ph.height; *cols = ph.width; return true; }
     return false;
+}
+
+size_t png_gray8_stream(const uint8_t* b, size_t n, int rows, int cols, uint8_t* dst, size_t cap) {
+    PngInfo h;
+    if (!png_header(b, n, h)) return 0;
+    if (h.ctype != 0 || h.depth != 8 || h.interlace != 0 || h.width != cols || h.height != rows) return 0;
+    size_t pos = 8, zl = 0;
+    while (pos + 12 <= n) {
+        const uint32_t len = rd32be(b + pos);
+        const uint8_t* type = b + pos + 4;
+        if (pos + 12 + (size_t)len > n) return 0;
+        if (!memcmp(type, "IDAT", 4)) {
+            if (zl + len > cap || !png_chunk_crc_ok(b + pos, len)) return 0;
+            memcpy(dst + zl, b + pos + 8, len);
+            zl += len;
+        } else if (!memcmp(type, "IEND", 4)) {
+            break;
+        }
+        pos += 12 + (size_t)len;
+    }
+    return zl;
 }
 
 bool read_file(const std::string& path, std::vector<uint8_t>& out) {

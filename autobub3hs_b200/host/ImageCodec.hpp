@@ -21,6 +21,10 @@ bool peek_size(const uint8_t* buf, size_t n, int* rows, int* cols);
 bool decode_into(const uint8_t* buf, size_t n, uint8_t* dst, int rows, int cols);
 
 bool read_file(const std::string& path, std::vector<uint8_t>& out);
+// For the on-device decoder (abub_event_decode_png): when buf is an 8-bit greyscale, non-interlaced PNG of exactly
+// rows x cols, copies its zlib stream (the concatenated IDAT payloads) to dst (capacity cap) and returns its length;
+// 0 when the file is anything else or does not fit.
+size_t png_gray8_stream(const uint8_t* buf, size_t n, int rows, int cols, uint8_t* dst, size_t cap);
 
 // Minimal writers (8-bit gray): used by the tests and the synthetic-run generator.
 bool write_bmp_gray(const std::string& path, const uint8_t* px, int rows, int cols);

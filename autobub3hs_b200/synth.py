@@ -269,15 +269,31 @@ def write_png8(path: str, img: np.ndarray) -> None:
                 + chunk(b"IDAT", zlib.compress(raw, 6)) + chunk(b"IEND", b""))
 
 
-def write_run(run: SyntheticRun, data_dir: str, mask_dir: Optional[str] = None) -> str:
-    """Writes ``<data_dir>/<run>/<ev>/Images/cam{c}_image{30+f}.bmp`` (+ masks) and returns the run dir."""
+def write_run(run: SyntheticRun, data_dir: str, mask_dir: Optional[str] = None, fmt: str = "bmp") -> str:
+    """Writes ``<data_dir>/<run>/<ev>/Images/cam{c}_image{30+f}.bmp`` (+ masks) and returns the run dir.
+    ``fmt="png"``: 8-bit grey PNG frames instead (adaptive row filters when cv2 is there to encode them)."""
     rdir = os.path.join(data_dir, run.run_id)
+    encode = None
+    if fmt == "png":
+        try:
+            import cv2
+            encode = lambda img: cv2.imencode(".png", img)[1].tobytes()
+        except ImportError:
+            encode = None
     for evn, ev in zip(run.event_numbers, run.events):
         idir = os.path.join(rdir, str(evn), "Images")
         os.makedirs(idir, exist_ok=True)
         for c, stack in enumerate(ev):
             for f in range(len(stack)):
-                write_bmp8(os.path.join(idir, f"cam{c}_image{run.frame_offset + f}.bmp"), stack[f])
+                if fmt == "png":
+                    path = os.path.join(idir, f"cam{c}_image{run.frame_offset + f}.png")
+                    if encode:
+                        with open(path, "wb") as fh:
+                            fh.write(encode(np.ascontiguousarray(stack[f])))
+                    else:
+                        write_png8(path, stack[f])
+                else:
+                    write_bmp8(os.path.join(idir, f"cam{c}_image{run.frame_offset + f}.bmp"), stack[f])
     if mask_dir:
         os.makedirs(mask_dir, exist_ok=True)
         for c in range(len(run.cam_masks)):

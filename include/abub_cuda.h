@@ -83,6 +83,8 @@ int abub_event_upload(abub_ctx* ctx, int slot, int cam, const uint8_t* frames, i
  * asynchronous H2D of its first `nframes` frames on the ctx stream.  The staging region must stay untouched until the
  * next synchronising call (abub_sync, abub_trigger_results, ...). */
 int abub_event_submit_cam(abub_ctx* ctx, int slot, int cam, int nframes);
+/* Same for a single frame (its region of the staging buffer); the frame count of the camera is not changed. */
+int abub_event_upload_frame(abub_ctx* ctx, int slot, int cam, int frame);
 /* Device address of the slot's [cam][frame][rows*cols] stack (for producers that
  * already live on the device) and the matching frame counts. */
 int abub_event_device_ptr(abub_ctx* ctx, int slot, uint8_t** dev_ptr);

@@ -82,6 +82,52 @@ def test_tma_pitch_raw_png_and_zip(abub3hs, tma_run, tmp_path):
     assert _run(abub3hs, str(zdir), str(tmp_path / "out_zip"), str(tmp_path / "masks"), ["-z", "--batch", "4"]) == gold
 
 
+def test_png_frames_decoded_on_device(abub3hs, tma_run, tmp_path):
+    """Row f-2: 8-bit grey PNG frames are inflated and unfiltered on the device (K9); frames the device path does not
+    take (RGB PNG, a BMP among PNGs) or rejects (truncated stream) go through the host decoder, with the same result as
+    ABUB_HOST_DECODE=1 and as the oracle on the decoded pixels."""
+    import cv2
+    from autobub3hs_b200 import synth
+    run, gold = tma_run
+    synth.write_run(run, str(tmp_path / "data"), str(tmp_path / "masks"), fmt="png")
+
+    def go(out, env=None):
+        os.makedirs(out, exist_ok=True)
+        r = subprocess.run([abub3hs, "-D", "40l-19", "-d", str(tmp_path / "data"), "-r", run.run_id, "-o", out, "-c", str(tmp_path / "masks"),
+                            "--batch", "4"], capture_output=True, text=True, env=dict(os.environ, ABUB_TIMING="1", **(env or {})))
+        assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+        dec = [l for l in r.stderr.splitlines() if l.startswith("ABUB_DECODE")][-1]
+        n_dev, n_host = int(dec.split()[6].rstrip(",")), int(dec.split()[-1])
+        return open(os.path.join(out, f"abub3hs_{run.run_id}.txt")).read(), n_dev, n_host
+
+    text, n_dev, n_host = go(str(tmp_path / "o1"))
+    assert text == gold
+    nframes = sum(len(stack) for ev in run.events for stack in ev)
+    assert n_dev == nframes and n_host == 0
+    text, n_dev, n_host = go(str(tmp_path / "o2"), {"ABUB_HOST_DECODE": "1"})
+    assert text == gold and n_dev == 0
+    # event 0: cam 1 frame 3 as an RGB PNG (same grey values), cam 2 frame 5 as the tail of a truncated file
+    idir = tmp_path / "data" / run.run_id / str(run.event_numbers[0]) / "Images"
+    f3 = idir / f"cam1_image{run.frame_offset + 3}.png"
+    cv2.imwrite(str(f3), cv2.cvtColor(run.events[0][1][3], cv2.COLOR_GRAY2BGR))
+    f5 = idir / f"cam2_image{run.frame_offset + 5}.png"
+    blob = f5.read_bytes()
+    f5.write_bytes(blob[: len(blob) * 2 // 3])
+    # event 1: a flipped byte in the compressed data of cam 0 frame 2 (chunk CRC fails -> unreadable, as with libpng)
+    f2 = tmp_path / "data" / run.run_id / str(run.event_numbers[1]) / "Images" / f"cam0_image{run.frame_offset + 2}.png"
+    blob = bytearray(f2.read_bytes())
+    blob[len(blob) // 2] ^= 0x10
+    f2.write_bytes(bytes(blob))
+    t_dev, n_dev, n_host = go(str(tmp_path / "o3"))
+    t_host, _, _ = go(str(tmp_path / "o4"), {"ABUB_HOST_DECODE": "1"})
+    assert t_dev == t_host
+    assert n_dev == nframes - 3 and n_host >= 1
+    # events 2.. are untouched
+    touched = {str(run.event_numbers[0]), str(run.event_numbers[1])}
+    rest = lambda t: [l for l in t.splitlines() if l.split()[:1] == [run.run_id] and l.split()[1] not in touched]
+    assert rest(t_dev) == rest(gold)
+
+
 def test_unreadable_run_is_minus5_and_bad_training_is_minus7(abub3hs, tmp_path):
     from autobub3hs_b200 import synth
     import oracle.cv2_oracle as o

@@ -87,7 +87,7 @@ def test_cv2_encoded_frames(capi):
 @pytest.mark.parametrize("ftypes", [(0,), (1,), (2,), (3,), (4,), (0, 1, 2, 3, 4), (4, 3, 1)])
 @pytest.mark.parametrize("mode", ["default", "stored", "fixed", "rle"])
 def test_filters_and_block_types(capi, ftypes, mode):
-    rows, cols = 70, 133                     # odd width: unaligned rows
+    rows, cols = 70, 134                     # scanlines of 135 bytes: no row starts aligned
     img = synth_frame(rows, cols, 11 + len(ftypes))
     raw = filter_rows(img, ftypes)
     if mode == "stored":

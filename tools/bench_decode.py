@@ -23,6 +23,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--events", type=int, default=6)
     ap.add_argument("--batch", type=int, default=6)
+    ap.add_argument("--format", choices=["bmp", "png"], default="bmp",
+                    help="png: frames are inflated and unfiltered on the device (K9); with --host-decode on the host cores")
+    ap.add_argument("--host-decode", action="store_true", help="ABUB_HOST_DECODE=1: every frame decoded on the host cores")
     ap.add_argument("--dir", default=None, help="scratch directory (default: a temporary one, removed afterwards)")
     args = ap.parse_args()
     from autobub3hs_b200 import synth
@@ -32,7 +35,7 @@ def main():
         t0 = time.perf_counter()
         classes = ["normal", "multi", "notrigger", "normal", "flicker", "highnoise"]
         run = synth.make_run(args.events, classes)
-        synth.write_run(run, os.path.join(tmp, "data"), os.path.join(tmp, "masks"))
+        synth.write_run(run, os.path.join(tmp, "data"), os.path.join(tmp, "masks"), fmt=args.format)
         t_write = time.perf_counter() - t0
         nbytes = sum(os.path.getsize(os.path.join(dp, f)) for dp, _, fs in os.walk(os.path.join(tmp, "data")) for f in fs)
         exe = os.path.join(ROOT, "autobub3hs_b200", "host", "abub3hs")
@@ -40,15 +43,19 @@ def main():
                "-c", os.path.join(tmp, "masks"), "--batch", str(args.batch)]
         os.makedirs(os.path.join(tmp, "out"), exist_ok=True)
         best = None
+        env = dict(os.environ, ABUB_TIMING="1")
+        if args.host_decode:
+            env["ABUB_HOST_DECODE"] = "1"
         for _ in range(2):                                   # second pass: files in the page cache
             t0 = time.perf_counter()
-            r = subprocess.run(cmd, capture_output=True, text=True, env=dict(os.environ, ABUB_TIMING="1"))
+            r = subprocess.run(cmd, capture_output=True, text=True, env=env)
             dt = time.perf_counter() - t0
             if r.returncode != 0:
                 print(r.stdout[-2000:], r.stderr[-2000:], file=sys.stderr)
                 sys.exit(1)
             best = dt if best is None else min(best, dt)
         timing = [l for l in r.stderr.splitlines() if l.startswith("ABUB_TIMING")]
+        decoded = [l for l in r.stderr.splitlines() if l.startswith("ABUB_DECODE")]
         steady = None
         if timing:
             import re
@@ -57,7 +64,8 @@ def main():
                 t = float(m.group(1)) - float(m.group(2)) + float(m.group(3)) + float(m.group(4))
                 steady = args.events / t if t > 0 else None
         rows = open(os.path.join(tmp, "out", f"abub3hs_{run.run_id}.txt")).read().count("\n")
-        print(json.dumps({"stage": "abub3hs from BMP files (training + detect, decode on host cores)", "events": args.events,
+        print(json.dumps({"stage": f"abub3hs from {args.format.upper()} files (training + detect)" + (" host decode" if args.host_decode else ""),
+                          "decoded": decoded[-1] if decoded else None, "events": args.events,
                           "seconds": best, "events_per_s": args.events / best, "file_GB": nbytes / 1e9,
                           "file_GBps": nbytes / best / 1e9, "host_cores": len(os.sched_getaffinity(0)), "output_rows": rows,
                           "synth_write_seconds": t_write, "detect_steady_events_per_s": steady, "phases": timing[-1] if timing else None,

@@ -25,6 +25,8 @@ def main():
     ap.add_argument("--events", type=int, default=32)
     ap.add_argument("--train-events", type=int, default=200)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--png-events", type=int, default=8, help="events of the PNG decode stage (0 = skip)")
+    ap.add_argument("--only-png", action="store_true", help="only the PNG decode stage")
     args = ap.parse_args()
     import torch
     from autobub3hs_b200 import capi, synth
@@ -45,84 +47,131 @@ def main():
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0) if os.path.exists(
         os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
 
-    # ---- trainer: the ring of E resident events is reused until --train-events have been added ----
-    best = None
-    t_gate = t_fin = 0.0
-    for _ in range(args.reps):
-        tg = tf = 0.0
-        for c in range(B.NCAMS):
-            ctx.train_begin(c)
-            t0 = time.perf_counter()
-            for i0 in range(0, args.train_events, E):
-                ctx.train_add_slots(c, [i % E for i in range(i0, min(i0 + E, args.train_events))])
-            t1 = time.perf_counter()
-            _, _, n, st = ctx.train_finish(c)
-            t2 = time.perf_counter()
-            assert st == 0
-            ctx.set_background_from_training(c)
-            tg += t1 - t0
-            tf += t2 - t1
-        if best is None or tg + tf < best:
-            best, t_gate, t_fin = tg + tf, tg, tf
-    byt_gate = B.NCAMS * args.train_events * 2 * B.NPIX
-    byt_fin = B.NCAMS * (n * B.NPIX + 2 * B.NPIX)
-    byt = byt_gate + byt_fin                                    # gate reads + Welford reads + planes
-    print(json.dumps({"stage": "trainer", "train_events": args.train_events, "kept_frames_per_cam": n, "seconds": best,
-                      "algorithmic_GB": byt / 1e9, "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak,
-                      "gate_seconds": t_gate, "gate_GBps": byt_gate / t_gate / 1e9,
-                      "welford_seconds": t_fin, "welford_GBps": byt_fin / t_fin / 1e9,
-                      "note": "gate: batched K3 over resident slots + one device copy per kept pair (parking); "
-                              "welford: K4 + read-back of the two planes"}))
+    if not args.only_png:
+        # ---- trainer: the ring of E resident events is reused until --train-events have been added ----
+        best = None
+        t_gate = t_fin = 0.0
+        for _ in range(args.reps):
+            tg = tf = 0.0
+            for c in range(B.NCAMS):
+                ctx.train_begin(c)
+                t0 = time.perf_counter()
+                for i0 in range(0, args.train_events, E):
+                    ctx.train_add_slots(c, [i % E for i in range(i0, min(i0 + E, args.train_events))])
+                t1 = time.perf_counter()
+                _, _, n, st = ctx.train_finish(c)
+                t2 = time.perf_counter()
+                assert st == 0
+                ctx.set_background_from_training(c)
+                tg += t1 - t0
+                tf += t2 - t1
+            if best is None or tg + tf < best:
+                best, t_gate, t_fin = tg + tf, tg, tf
+        byt_gate = B.NCAMS * args.train_events * 2 * B.NPIX
+        byt_fin = B.NCAMS * (n * B.NPIX + 2 * B.NPIX)
+        byt = byt_gate + byt_fin                                    # gate reads + Welford reads + planes
+        print(json.dumps({"stage": "trainer", "train_events": args.train_events, "kept_frames_per_cam": n, "seconds": best,
+                          "algorithmic_GB": byt / 1e9, "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak,
+                          "gate_seconds": t_gate, "gate_GBps": byt_gate / t_gate / 1e9,
+                          "welford_seconds": t_fin, "welford_GBps": byt_fin / t_fin / 1e9,
+                          "note": "gate: batched K3 over resident slots + one device copy per kept pair (parking); "
+                                  "welford: K4 + read-back of the two planes"}))
 
-    # ---- trigger + localizer ----
-    ctx.trigger_hist(0, E)
-    ctx.trigger_scan(0, E)
-    trig, status, lt, _ = ctx.trigger_results(0, E, want_sig=False)
-    items = []
-    for s in range(E):
-        for c in range(B.NCAMS):
-            if status[s, c] == 0:
-                t = int(trig[s, c])
-                items.append((s, c, t, max(0, t - 2), int(lt[s, c]), glue.n_post_frames(t, B.NFRAMES)))
-    nplanes = sum(3 + it[5] + 2 for it in items)
-    best = None
-    _, _, nblobs, bufs = ctx.localize_batch_raw(items, cap=1 << 18)
-    for _ in range(args.reps):
-        t0 = time.perf_counter()
-        ctx.localize_batch_raw(items, cap=1 << 18, buffers=bufs)
-        dt = time.perf_counter() - t0
-        best = dt if best is None else min(best, dt)
-    byt = nplanes * B.NPIX
-    print(json.dumps({"stage": "localizer", "items": len(items), "frames": sum(it[5] + 1 for it in items), "blobs": nblobs,
-                      "seconds": best, "items_per_s": len(items) / best, "algorithmic_GB": byt / 1e9,
-                      "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak}))
-
-    best = None
-    for _ in range(args.reps):
-        t0 = time.perf_counter()
+        # ---- trigger + localizer ----
         ctx.trigger_hist(0, E)
         ctx.trigger_scan(0, E)
-        ctx.trigger_results(0, E, want_sig=False)
-        ctx.localize_batch_raw(items, cap=1 << 18, buffers=bufs)
-        dt = time.perf_counter() - t0
-        best = dt if best is None else min(best, dt)
-    byt = E * B.NCAMS * B.K1_BYTES_PER_EVENT_CAM + nplanes * B.NPIX
-    print(json.dumps({"stage": "recon (K1+K2+K5-K7, resident)", "events": E, "seconds": best, "events_per_s": E / best,
-                      "algorithmic_GB": byt / 1e9, "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak}))
-    # ---- bellows veto: TrackAFeature at full size (a14; rare branch, timed for completeness) ----
-    pat, _ = synth.make_bellows_object(1, B.ROWS, B.COLS)
-    ctx.set_bellows_template(1, pat)
-    ctx.bellows_track(0, 1, 0)
-    best = None
-    for _ in range(args.reps):
-        t0 = time.perf_counter()
+        trig, status, lt, _ = ctx.trigger_results(0, E, want_sig=False)
+        items = []
+        for s in range(E):
+            for c in range(B.NCAMS):
+                if status[s, c] == 0:
+                    t = int(trig[s, c])
+                    items.append((s, c, t, max(0, t - 2), int(lt[s, c]), glue.n_post_frames(t, B.NFRAMES)))
+        nplanes = sum(3 + it[5] + 2 for it in items)
+        best = None
+        _, _, nblobs, bufs = ctx.localize_batch_raw(items, cap=1 << 18)
+        for _ in range(args.reps):
+            t0 = time.perf_counter()
+            ctx.localize_batch_raw(items, cap=1 << 18, buffers=bufs)
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        byt = nplanes * B.NPIX
+        print(json.dumps({"stage": "localizer", "items": len(items), "frames": sum(it[5] + 1 for it in items), "blobs": nblobs,
+                          "seconds": best, "items_per_s": len(items) / best, "algorithmic_GB": byt / 1e9,
+                          "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak}))
+
+        best = None
+        for _ in range(args.reps):
+            t0 = time.perf_counter()
+            ctx.trigger_hist(0, E)
+            ctx.trigger_scan(0, E)
+            ctx.trigger_results(0, E, want_sig=False)
+            ctx.localize_batch_raw(items, cap=1 << 18, buffers=bufs)
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        byt = E * B.NCAMS * B.K1_BYTES_PER_EVENT_CAM + nplanes * B.NPIX
+        print(json.dumps({"stage": "recon (K1+K2+K5-K7, resident)", "events": E, "seconds": best, "events_per_s": E / best,
+                          "algorithmic_GB": byt / 1e9, "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak}))
+        # ---- bellows veto: TrackAFeature at full size (a14; rare branch, timed for completeness) ----
+        pat, _ = synth.make_bellows_object(1, B.ROWS, B.COLS)
+        ctx.set_bellows_template(1, pat)
         ctx.bellows_track(0, 1, 0)
-        dt = time.perf_counter() - t0
-        best = dt if best is None else min(best, dt)
-    macs = (B.ROWS - pat.shape[0] + 1) * (B.COLS - pat.shape[1] + 1) * pat.shape[0] * pat.shape[1]
-    print(json.dumps({"stage": "bellows TrackAFeature (K8, one frame)", "template": list(pat.shape), "seconds": best,
-                      "u8_MACs": macs, "TMAC_per_s": macs / best / 1e12,
-                      "note": "exact integer CCORR_NORMED numerators with dp4a; includes window sums, min/max/argmax and the read-back"}))
+        best = None
+        for _ in range(args.reps):
+            t0 = time.perf_counter()
+            ctx.bellows_track(0, 1, 0)
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        macs = (B.ROWS - pat.shape[0] + 1) * (B.COLS - pat.shape[1] + 1) * pat.shape[0] * pat.shape[1]
+        print(json.dumps({"stage": "bellows TrackAFeature (K8, one frame)", "template": list(pat.shape), "seconds": best,
+                          "u8_MACs": macs, "TMAC_per_s": macs / best / 1e12,
+                          "note": "exact integer CCORR_NORMED numerators with dp4a; includes window sums, min/max/argmax and the read-back"}))
+    # ---- K9: on-device PNG decode of a staged batch (8(f)-2) ----
+    if args.png_events > 0:
+        import cv2
+        import struct
+
+        def idat(png):
+            pos, z = 8, b""
+            while pos + 12 <= len(png):
+                n = struct.unpack(">I", png[pos:pos + 4])[0]
+                if png[pos + 4:pos + 8] == b"IDAT":
+                    z += png[pos + 8:pos + 8 + n]
+                pos += 12 + n
+            return z
+
+        pe = min(args.png_events, E)
+        ring = []
+        t_cpu = []
+        for i in range(8):
+            frame = B.slot_tensor(torch, ctx, i % E)[i % B.NCAMS, (5 * i) % B.NFRAMES].cpu().numpy()
+            enc = cv2.imencode(".png", frame)[1]
+            t0 = time.perf_counter()
+            dec = cv2.imdecode(enc, cv2.IMREAD_GRAYSCALE)
+            t_cpu.append(time.perf_counter() - t0)
+            assert np.array_equal(dec, frame)
+            ring.append((idat(enc.tobytes()), frame))
+        jobs = [(s, c, f, ring[(s + c + f) % 8][0]) for s in range(pe) for c in range(B.NCAMS) for f in range(B.NFRAMES)]
+        zbytes = sum(len(j[3]) for j in jobs)
+        okv = ctx.decode_png(jobs)                       # warm-up (allocations), also fills the pinned regions
+        assert okv.all()
+        dev = ctx.download_frames(0)
+        assert np.array_equal(dev[1, 3], ring[(0 + 1 + 3) % 8][1])
+        arr = (capi.PngJob * len(jobs))(*[capi.PngJob(s, c, f, len(z)) for (s, c, f, z) in jobs])
+        okc = (capi.C.c_int * len(jobs))()
+        best = None
+        for _ in range(args.reps):
+            t0 = time.perf_counter()
+            ctx._ck(ctx.lib.abub_event_decode_png(ctx.h, arr, len(jobs), okc), "abub_event_decode_png")
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+        cpu_ms = 1e3 * float(np.median(t_cpu))
+        ncores = len(os.sched_getaffinity(0))
+        print(json.dumps({"stage": "PNG decode on the device (K9: H2D of the compressed bytes + inflate + unfilter)", "events": pe,
+                          "frames": len(jobs), "seconds": best, "events_per_s": pe / best, "frames_per_s": len(jobs) / best,
+                          "compressed_GB": zbytes / 1e9, "pixels_GB": len(jobs) * B.NPIX / 1e9,
+                          "cv2_imdecode_ms_per_frame_one_core": cpu_ms, "host_cores": ncores,
+                          "host_events_per_s_all_cores": ncores / (cpu_ms * 1e-3) / (B.NCAMS * B.NFRAMES)}))
     ctx.close()
 
 
