@@ -44,6 +44,7 @@ struct Bits {
     uint32_t line;          // index of the current 32-word line
     int widx;               // next word of the line to take
     uint32_t cur, nxt;      // this lane's word of the current / next line
+    uint32_t pre;           // word widx of the current line, already broadcast (keeps the SHFL off the refill's critical path)
     uint64_t buf;
     int cnt;
     bool overrun;
@@ -61,14 +62,14 @@ __device__ __forceinline__ void bits_init(Bits& b, const uint8_t* p, uint32_t nb
     b.widx = (int)(wpos & 31u);
     b.cur = bits_load(b, b.line, lane);
     b.nxt = bits_load(b, b.line + 1, lane);
+    b.pre = __shfl_sync(0xffffffffu, b.cur, b.widx);
     b.buf = 0;
     b.cnt = 0;
     b.overrun = false;
 }
 __device__ __forceinline__ void refill(Bits& b, int lane) {     // afterwards at least 33 bits are present
     if (b.cnt <= 32) {
-        const uint32_t wv = __shfl_sync(0xffffffffu, b.cur, b.widx);
-        b.buf |= (uint64_t)wv << b.cnt;
+        b.buf |= (uint64_t)b.pre << b.cnt;
         b.cnt += 32;
         if (++b.widx == 32) {
             b.widx = 0;
@@ -77,6 +78,7 @@ __device__ __forceinline__ void refill(Bits& b, int lane) {     // afterwards at
             b.nxt = bits_load(b, b.line + 1, lane);
             if (b.line * 32u > b.nwords + 32u) b.overrun = true;
         }
+        b.pre = __shfl_sync(0xffffffffu, b.cur, b.widx);
     }
 }
 // byte offset in the stream of the first bit not yet consumed (call only when cnt is a multiple of 8)
@@ -269,23 +271,27 @@ __global__ void __launch_bounds__(32 * K9_WARPS) k9_inflate_kernel(const PngDev*
         for (;;) {
             refill(b, lane);
 #ifndef ABUB_K9_SCALAR
-            {   // ---- literal run.  Lane j decodes the code that WOULD start at bit j of the window; the codes that really
-                // start there are the chain 0 -> 0+len(0) -> ..., found by pointer doubling over the warp (REDUX + SHFL per
-                // round).  Every literal on the chain is stored by its own lane; the chain stops at the first length code,
-                // end-of-block, long (> TB_LIT bits) code or at the end of the window, where the one-symbol path takes over.
+            {   // ---- literal run.  Lane j decodes the codes that WOULD start at bit j of the window (two of them, so that it knows
+                // its 2-hop successor without talking to anyone); the codes that really start there are the chain
+                // 0 -> 0+len(0) -> ..., marked by pointer doubling over the warp (one REDUX per round, the SHFL that squares the
+                // successor map runs beside it).  Every literal on the chain is stored by its own lane; the chain stops at
+                // the first length code, end-of-block, long (> TB_LIT bits) code or at the end of the window, where the
+                // one-symbol path takes over.
                 const uint32_t x = __funnelshift_r((uint32_t)b.buf, (uint32_t)(b.buf >> 32), lane);
                 const uint32_t e = T.lit[x & ((1u << TB_LIT) - 1u)];
                 const int l = (int)(e & 15u);
                 const bool lit = l != 0 && e < (256u << 4) && lane + l <= b.cnt;
                 const int cons = lit ? lane + l : lane;             // bits consumed if the chain ends at this lane
-                int succ = cons < 32 && lit ? cons : 32;             // 32: no successor inside the window
-                uint32_t M = 1u;
-#pragma unroll
-                for (int k = 0; k < 5; k++) {
-                    const uint32_t add = __reduce_or_sync(0xffffffffu, (((M >> lane) & 1u) && succ < 32) ? (1u << succ) : 0u);
-                    if ((add & ~M) == 0u) break;
-                    M |= add;
+                const int s1 = (lit && cons < 32) ? cons : 32;       // successor; 32: none inside the window
+                const uint32_t e2 = T.lit[(uint32_t)(b.buf >> cons) & ((1u << TB_LIT) - 1u)];
+                const int p2 = s1 + (int)(e2 & 15u);
+                int succ = (s1 < 32 && (e2 & 15u) != 0u && e2 < (256u << 4) && p2 <= b.cnt && p2 < 32) ? p2 : 32;   // 2 hops
+                const uint32_t term = __ballot_sync(0xffffffffu, s1 >= 32);          // where a chain would end
+                const int h1 = __shfl_sync(0xffffffffu, s1, 0);
+                uint32_t M = 1u | (h1 < 32 ? 1u << h1 : 0u);
+                while (!(M & term)) {                                // the chain from 0 ends at exactly one such lane
                     const int t = __shfl_sync(0xffffffffu, succ, succ & 31);
+                    M |= __reduce_or_sync(0xffffffffu, (((M >> lane) & 1u) && succ < 32) ? (1u << succ) : 0u);
                     succ = succ < 32 ? t : 32;
                 }
                 const uint32_t Mlit = M & __ballot_sync(0xffffffffu, lit);
