@@ -20,7 +20,7 @@ ABUB_MAX_TRACK = 10
 EXPORTS = [
     "abub_ctx_create", "abub_ctx_destroy", "abub_last_error", "abub_sync", "abub_stream",
     "abub_set_background", "abub_set_background_from_training",
-    "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_submit_cam", "abub_event_upload_frame", "abub_event_decode_png", "abub_event_device_ptr",
+    "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_submit_cam", "abub_event_upload_frame", "abub_set_trigger_metric", "abub_event_decode_png", "abub_event_device_ptr",
     "abub_event_set_nframes",
     "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_hist_write", "abub_trigger_scan", "abub_trigger_results", "abub_trigger", "abub_trigger_stream",
     "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_add_slots",
@@ -97,6 +97,7 @@ def load() -> C.CDLL:
     lib.abub_train_add_slot.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float), ip]
     lib.abub_event_submit_cam.argtypes = [vp, C.c_int, C.c_int, C.c_int]
     lib.abub_event_upload_frame.argtypes = [vp, C.c_int, C.c_int, C.c_int]
+    lib.abub_set_trigger_metric.argtypes = [vp, C.c_int, C.c_float]
     lib.abub_event_decode_png.argtypes = [vp, C.POINTER(PngJob), C.c_int, ip]
     lib.abub_train_add_slots.argtypes = [vp, C.c_int, ip, C.c_int, C.POINTER(C.c_float), ip]
     lib.abub_train_add_events.argtypes = [vp, C.c_int, u8p, C.c_int, C.POINTER(C.c_float), ip]
@@ -250,6 +251,12 @@ class Context:
         h = np.zeros((self.max_frames, 256), np.uint32)
         h[:hist.shape[0]] = hist
         self._ck(self.lib.abub_trigger_hist_write(self.h, slot, cam, _p(h), nframes), "abub_trigger_hist_write")
+
+    METRICS = {"significance": 0, "entropy": 1, "entropy_significance": 2}
+
+    def set_trigger_metric(self, metric: str = "significance", threshold: float = 0.0) -> None:
+        """Which quantity the trigger thresholds (AnalyzerUnit.cpp:226-228); threshold <= 0: the reference's value."""
+        self._ck(self.lib.abub_set_trigger_metric(self.h, self.METRICS[metric], float(threshold)), "abub_set_trigger_metric")
 
     def trigger_scan(self, slot_first: int = 0, nslots: int = 1, start_frames: Optional[np.ndarray] = None) -> None:
         st = None if start_frames is None else np.ascontiguousarray(start_frames, dtype=np.int32)

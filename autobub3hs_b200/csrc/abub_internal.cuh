@@ -65,6 +65,8 @@ struct abub_ctx {
     int*      d_avail = nullptr;    // [slot][cam] frames resident so far (abub_trigger_stream)
     int*      d_trig = nullptr;     // [slot][cam] x {trig,status,loc_thres,scanned}
     double*   d_sig = nullptr;      // [slot][cam][frame]
+    int       trig_metric = 0;      // ABUB_METRIC_* used by K2 (abub_set_trigger_metric)
+    float     trig_thr = 3.5f;      // entropyThreshold before the TrainingSetSize < 6 scaling (AnalyzerUnit.cpp:140-142)
     int*      d_tss = nullptr;      // [cam] TrainingSetSize
     uint32_t** d_k32_ptrs = nullptr;  // [cam] device array of K32 plane pointers
     uint8_t**  d_slot_ptrs = nullptr; // [slot] device array of slot base pointers

@@ -63,11 +63,46 @@ __device__ double significance(const uint32_t* __restrict__ Hrow, WarpScratch* w
     return sig;
 }
 
+// The two trigger variants the reference keeps next to the significance (commented alternatives at AnalyzerUnit.cpp:226-227,
+// :290-291): AnalyzerUnit::calculateEntropyFrame (:386-423), the Shannon entropy of the 128-bin histogram of the
+// ProcessFrame output -- bins of width 2, i.e. pairs of the K1 table -- with p = count * (float)(1/N) and
+// E -= p*log2(p) accumulated in float in bin order (lane 0).  Returns the float entropy on all lanes.
+__device__ float entropy128(const uint32_t* __restrict__ Hrow, WarpScratch* ws, float scale, int lane) {
+    float* t = reinterpret_cast<float*>(ws->term);
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const int k = q * 32 + lane;
+        const uint2 c2 = *reinterpret_cast<const uint2*>(Hrow + 2 * k);
+        const float p = __fmul_rn((float)(c2.x + c2.y), scale);
+        t[k] = p != 0.0f ? __fmul_rn(p, (float)log2((double)p)) : 0.0f;
+    }
+    __syncwarp();
+    float e = 0.0f;
+    if (lane == 0)
+        for (int k = 0; k < 128; k++) e = __fsub_rn(e, t[k]);
+    e = __shfl_sync(0xffffffffu, e, 0);
+    __syncwarp();
+    return e;
+}
+
+// AnalyzerUnit::calculateEntropySignificance (:425-433) on running sums: CalcMean / CalcStdDev add the stored
+// entropies in push order, which is what a running sum does.
+struct EntropyHistory {
+    double s1 = 0.0, s2 = 0.0;
+    int n = 0;
+    __device__ void push(double e) { s1 = __dadd_rn(s1, e); s2 = __dadd_rn(s2, __dmul_rn(e, e)); n++; }
+    __device__ double z(double e) const {
+        const double mean = __ddiv_rn(s1, (double)n);
+        const double sd = __dsqrt_rn(__dsub_rn(__ddiv_rn(s2, (double)n), __dmul_rn(mean, mean)));
+        return __ddiv_rn(__dsub_rn(e, mean), sd);
+    }
+};
+
 __global__ void __launch_bounds__(32 * K2_WARPS)
 k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict__ nframes,
                        const int* __restrict__ start, const int* __restrict__ tss_cam,
                        int* __restrict__ result, double* __restrict__ sig_out, int slot_first, int nslots,
-                       int ncams, int max_frames, const int* __restrict__ avail) {
+                       int ncams, int max_frames, const int* __restrict__ avail, int metric, float thr0, float inv_npix) {
     __shared__ WarpScratch scratch[K2_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int item = blockIdx.x * K2_WARPS + warp;
@@ -92,9 +127,12 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
     }
     int s = start[sc];
     if (s < 1) s = 1;                                             // :163
-    float thr = 3.5f;                                             // :142
+    float thr = thr0;                                             // :140-142 (3.5 for the significance)
     if (tss < 6) thr = (float)((double)thr * (5 / 3.5));          // :185-188
     // history of frames 1..s-1 (empty when s == 1, :165-169)
+    EntropyHistory eh;
+    if (metric == ABUB_METRIC_ENTROPY_SIGNIFICANCE)
+        for (int f = 1; f < s && f < nf; f++) eh.push((double)entropy128(H + (size_t)f * 256, ws, inv_npix, lane));
 #pragma unroll
     for (int q = 0; q < 8; q++) {
         const int b = q * 32 + lane;
@@ -113,22 +151,30 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
     for (int i = s; i < nf; i++) {                                // :191
         if (i >= av) { status = ABUB_STATUS_PENDING; break; }
         const uint32_t* Hi = H + (size_t)i * 256;
+        double sg;
+        if (metric == ABUB_METRIC_SIGNIFICANCE) {
 #pragma unroll
-        for (int q = 0; q < 8; q++) {                             // store = true (:461)
-            const int b = q * 32 + lane;
-            const uint32_t c = Hi[b];
-            ws->s1[b] += (double)c;
-            ws->s2[b] += wrapsq(c);
+            for (int q = 0; q < 8; q++) {                         // store = true (:461)
+                const int b = q * 32 + lane;
+                const uint32_t c = Hi[b];
+                ws->s1[b] += (double)c;
+                ws->s2[b] += wrapsq(c);
+            }
+            __syncwarp();
+            int fo, madc;
+            sg = significance(Hi, ws, i, lane, &fo, &madc);       // :228
+            int lt = max(fo - 1, madc - 1);                       // :487-491
+            if (lt < 2) lt = 2;
+            if (lt > 3 || tss < 6) lt = 3;
+            loc_thres = lt;
+        } else {
+            const double e = (double)entropy128(Hi, ws, inv_npix, lane);   // :226 / :227
+            if (metric == ABUB_METRIC_ENTROPY_SIGNIFICANCE) { eh.push(e); sg = eh.z(e); }
+            else sg = e;
+            loc_thres = 3;                                        // never updated on these paths (:29)
         }
-        __syncwarp();
-        int fo, madc;
-        const double sg = significance(Hi, ws, i, lane, &fo, &madc);   // :228
         scanned++;
         if (lane == 0) so[i] = sg;
-        int lt = max(fo - 1, madc - 1);                           // :487-491
-        if (lt < 2) lt = 2;
-        if (lt > 3 || tss < 6) lt = 3;
-        loc_thres = lt;
         float single = (float)sg;
         if (single > thr && i >= 2) {                             // :254
             if (i != nf - 1) {                                    // :261
@@ -136,8 +182,14 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
                 for (int ii = 1; ii <= 2 && ii + i < nf; ii++) {  // :282
                     if (i + ii >= av) { status = ABUB_STATUS_PENDING; break; }
                     int fo2, madc2;
-                    const double s2v = significance(H + (size_t)(i + ii) * 256, ws, i, lane, &fo2, &madc2);
-                    single = (float)s2v;                          // :292  (store = false)
+                    double s2v;                                   // :290-292  (store = false)
+                    if (metric == ABUB_METRIC_SIGNIFICANCE) {
+                        s2v = significance(H + (size_t)(i + ii) * 256, ws, i, lane, &fo2, &madc2);
+                    } else {
+                        const double e2 = (double)entropy128(H + (size_t)(i + ii) * 256, ws, inv_npix, lane);
+                        s2v = metric == ABUB_METRIC_ENTROPY_SIGNIFICANCE ? eh.z(e2) : e2;
+                    }
+                    single = (float)s2v;
                     const double lhs = __dadd_rn(__ddiv_rn((double)single, __dmul_rn(__ddiv_rn((double)thr, 3.5), 5.0)),
                                                  __ddiv_rn((double)single, max_so_far));
                     if (lhs <= 3.0) break;                        // :296
@@ -159,7 +211,16 @@ int abub_k2_launch_avail(abub_ctx* ctx, int slot_first, int nslots, const int* d
     const int items = nslots * ctx->ncams;
     k2_trigger_scan_kernel<<<(items + K2_WARPS - 1) / K2_WARPS, 32 * K2_WARPS, 0, ctx->stream>>>(
         ctx->d_hist, ctx->d_nframes, ctx->d_start, ctx->d_tss, ctx->d_trig, ctx->d_sig, slot_first, nslots,
-        ctx->ncams, ctx->max_frames, d_avail);
+        ctx->ncams, ctx->max_frames, d_avail, ctx->trig_metric, ctx->trig_thr, (float)(1.0 / (double)ctx->npix));
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    return ABUB_OK;
+}
+
+extern "C" int abub_set_trigger_metric(abub_ctx* ctx, int metric, float threshold) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, metric >= ABUB_METRIC_SIGNIFICANCE && metric <= ABUB_METRIC_ENTROPY_SIGNIFICANCE, "trigger metric");
+    static const float kDefault[3] = {3.5f, 8e-5f, 1.9f};        // AnalyzerUnit.cpp:142, :140, :141
+    ctx->trig_metric = metric;
+    ctx->trig_thr = threshold > 0.0f ? threshold : kDefault[metric];
     return ABUB_OK;
 }

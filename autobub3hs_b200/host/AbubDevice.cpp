@@ -43,6 +43,8 @@ abub_ctx* AbubDevice::Context(int rows, int cols) {
                         " -- this build has no CPU path");
     }
     ctx_ = c; rows_ = rows; cols_ = cols;
+    if (trigger_metric_ != ABUB_METRIC_SIGNIFICANCE || trigger_threshold_ > 0.f)
+        Check(abub_set_trigger_metric(ctx_, trigger_metric_, trigger_threshold_), "abub_set_trigger_metric");
     return ctx_;
 }
 

@@ -49,6 +49,9 @@ public:
     static AbubDevice& Get();
 
     void Configure(int device, int ncams, int max_frames, int max_slots);
+    // Which of the reference's three trigger quantities K2 thresholds (AnalyzerUnit.cpp:226-228; ABUB_METRIC_*); call before
+    // the first frame is staged.  threshold <= 0: the reference's value for the metric (:140-142).
+    void SetTriggerMetric(int metric, float threshold) { trigger_metric_ = metric; trigger_threshold_ = threshold; }
     bool configured() const { return ncams_ > 0; }
     int ncams() const { return ncams_; }
     int max_frames() const { return max_frames_; }
@@ -103,6 +106,8 @@ private:
     // stages every camera of the given (slot, event) pairs: all frames are read on all cores; 8-bit grey PNG frames are
     // inflated and unfiltered on the device (abub_event_decode_png), anything else is decoded on the host
     void StageBatch(Parser* parser, const std::vector<int>& slots, const std::vector<std::string>& events);
+    int trigger_metric_ = 0;
+    float trigger_threshold_ = 0.f;
     std::map<std::string, int> by_key_;
     std::map<std::string, bool> templates_;     // "<mask dir>|<cam>" -> loadable
     std::map<std::string, Image8> masks_;       // "<mask dir>|<cam>|<bellows>" -> image (empty = unreadable)

@@ -1,5 +1,9 @@
 #include "PICOFormatWriterV4.hpp"
 
+#include <charconv>
+#include <cmath>
+#include <cstdio>
+
 #include <fstream>
 
 #include "CommonParameters.h"
@@ -53,11 +57,39 @@ void OutputWriter::stageCameraOutputError(int camera, int error, int event) {
     AllBubbleData[camera]->event = event;
 }
 
-void OutputWriter::formEachBubbleOutput(int camera, int& ibubImageStart, int nBubTotal) {
-    std::stringstream& o = _StreamOutput;
-    o.clear();
-    o.precision(2);
-    o.setf(std::ios::fixed, std::ios::floatfield);
+// Field sink of the batch formatter: what `stream << value` prints under precision(2) + fixed, produced with
+// std::to_chars.  Integers: shortest decimal.  Floating point: the value as a double with two decimals, correctly rounded
+// (what "%.2f" prints); non-finite values are left to snprintf so that "nan" / "-nan" / "inf" come out as the C library
+// spells them.
+namespace {
+struct FastSink {
+    std::string& s;
+    explicit FastSink(std::string& dst) : s(dst) {}
+    FastSink& operator<<(const char* t) { s.append(t); return *this; }
+    FastSink& operator<<(const std::string& t) { s.append(t); return *this; }
+    FastSink& operator<<(int v) {
+        char buf[16];
+        auto r = std::to_chars(buf, buf + sizeof(buf), v);
+        s.append(buf, r.ptr);
+        return *this;
+    }
+    FastSink& operator<<(double v) {
+        char buf[64];
+        if (std::isfinite(v)) {
+            auto r = std::to_chars(buf, buf + sizeof(buf), v, std::chars_format::fixed, 2);
+            if (r.ec == std::errc()) { s.append(buf, r.ptr); return *this; }
+        }
+        char big[400];
+        const int n = snprintf(big, sizeof(big), "%.2f", v);
+        s.append(big, (size_t)n);
+        return *this;
+    }
+    FastSink& operator<<(float v) { return *this << (double)v; }
+};
+}  // namespace
+
+template <class Sink>
+void OutputWriter::formRows(Sink& o, int camera, int& ibubImageStart, int nBubTotal) const {
     const BubbleData* wd = AllBubbleData[camera];
     const int nt = NumFramesBubbleTrack;
     const char* sep = "  ";
@@ -98,6 +130,43 @@ void OutputWriter::formEachBubbleOutput(int camera, int& ibubImageStart, int nBu
         o << "1  \n";
     }
     ibubImageStart += (int)wd->BubbleObjectData.size();
+}
+
+void OutputWriter::formEachBubbleOutput(int camera, int& ibubImageStart, int nBubTotal) {
+    std::stringstream& o = _StreamOutput;
+    o.clear();
+    o.precision(2);
+    o.setf(std::ios::fixed, std::ios::floatfield);
+    formRows(o, camera, ibubImageStart, nBubTotal);
+}
+
+void OutputWriter::appendCameraOutput(std::string& dst) {
+    int ibubImageStart = 1;
+    int nBubTotal = 0;
+    for (int i = 0; i < NumCams; i++)
+        nBubTotal += AllBubbleData[i]->StatusCode != 0 ? 0 : (int)AllBubbleData[i]->BubbleObjectData.size();
+    FastSink sink(dst);
+    for (int i = 0; i < NumCams; i++) formRows(sink, i, ibubImageStart, nBubTotal);
+}
+
+void OutputWriter::appendToFile(const std::string& file, const std::string& rows) {
+    std::ofstream f(file, std::fstream::out | std::fstream::app);
+    f.write(rows.data(), (std::streamsize)rows.size());
+}
+
+std::string OutputWriter::formatValueFast(double v) {
+    std::string s;
+    FastSink k(s);
+    k << v;
+    return s;
+}
+
+std::string OutputWriter::formatValueStream(double v) {
+    std::stringstream o;
+    o.precision(2);
+    o.setf(std::ios::fixed, std::ios::floatfield);
+    o << v;
+    return o.str();
 }
 
 std::string OutputWriter::formatCameraOutput(void) {

@@ -36,11 +36,21 @@ public:
     void stageCameraOutput(std::vector<bubble*> BubbleRectIn, int camera, int frame0, int event);
     void stageCameraOutputError(int camera, int error, int event);
     void formEachBubbleOutput(int camera, int& ibubImageStart, int nBubTotal);
+    template <class Sink> void formRows(Sink& o, int camera, int& ibubImageStart, int nBubTotal) const;
     void writeCameraOutput(void);
 
     /* the staged rows of this event as text, without touching the file (multi-GPU ranks buffer their
      * event range and rank 0 concatenates in event order = the omp ordered file order) */
     std::string formatCameraOutput(void);
+    /* SURVEY 8(f)-3, batch form: the same rows appended to `dst` by a to_chars formatter (no iostream, no locale, no
+     * file access).  A driver formats every event of a staged batch into one buffer and opens/appends/closes the
+     * output once per batch instead of once per event (PICOFormatWriterV4.cpp:299-301). */
+    void appendCameraOutput(std::string& dst);
+    /* open / append / close, once for however many events `rows` holds */
+    static void appendToFile(const std::string& file, const std::string& rows);
+    /* the two formatters on one value, for the self-test */
+    static std::string formatValueFast(double v);
+    static std::string formatValueStream(double v);
     static std::string headerText(void);
     const std::string& fileName() const { return abubOutFilename; }
 };

@@ -88,12 +88,14 @@ static std::string usage() {
            "  --device = Int\t\tCUDA device ordinal (default 0, or the rank with --world)\n"
            "  --batch = Int\t\t\tevents staged on the GPU at once (default 8; 282 MB of HBM each at 4x40 frames of 1680x1050)\n"
            "  --max_frames = Int\t\tframes per camera a slot can hold (default: what the first events hold, at least 40)\n"
+           "  --trigger_metric = Str	significance (default) | entropy | entropy_significance: which of the three lines of\n"
+           "\t\t\t\tAnalyzerUnit.cpp:226-228 is the live one; --trigger_threshold = Float overrides its entropyThreshold\n"
            "  --rank/--world = Int\t\tone process per GPU: this process handles a contiguous range of the events\n"
            "  --nccl_id = File\t\tfile through which rank 0 publishes the NCCL id (default <out_dir>/.abub3hs_<run>.ncclid)\n";
 }
 
 struct Options {
-    std::string dataLoc, run_number, out_dir, mask_dir, data_series, nccl_id;
+    std::string dataLoc, run_number, out_dir, mask_dir, data_series, nccl_id, trigger_metric = "significance", trigger_threshold = "0";
     int event_user = -1, debug_mode = 0, device = -1, batch = 8, max_frames = 0, rank = 0, world = 1;
     bool zipped = false, mask_check = false, help = false;
 };
@@ -127,6 +129,8 @@ static bool parse_args(int argc, char** argv, Options& o) {
         else if (a == "--device") ok = need_int(o.device);
         else if (a == "--batch") ok = need_int(o.batch);
         else if (a == "--max_frames") ok = need_int(o.max_frames);
+        else if (a == "--trigger_metric") ok = need(o.trigger_metric);
+        else if (a == "--trigger_threshold") ok = need(o.trigger_threshold);
         else if (a == "--rank") ok = need_int(o.rank);
         else if (a == "--world") ok = need_int(o.world);
         else if (a == "--nccl_id") ok = need(o.nccl_id);
@@ -211,6 +215,11 @@ int main(int argc, char** argv) {
     void* nccl = nullptr;
     try {
         AbubDevice::Get().Configure(opt.device >= 0 ? opt.device : opt.rank, numCams, max_frames, batch);
+        const int metric = opt.trigger_metric == "significance" ? ABUB_METRIC_SIGNIFICANCE
+                         : opt.trigger_metric == "entropy" ? ABUB_METRIC_ENTROPY
+                         : opt.trigger_metric == "entropy_significance" ? ABUB_METRIC_ENTROPY_SIGNIFICANCE : -1;
+        if (metric < 0) throw std::runtime_error("--trigger_metric: significance | entropy | entropy_significance");
+        AbubDevice::Get().SetTriggerMetric(metric, (float)atof(opt.trigger_threshold.c_str()));
     } catch (std::exception& e) {
         std::cerr << e.what() << std::endl;
         return -5;
@@ -291,6 +300,7 @@ int main(int argc, char** argv) {
             std::cout << e.what() << std::endl;       /* the analyzers will meet the same problem and report -6 */
         }
         T_stage += wall() - ts0;
+        std::string batch_rows;
         for (size_t ci = 0; ci < chunk.size(); ci++) {
             const std::string& ev = chunk[ci];
             OutputWriter* EventOutput = new OutputWriter(out_dir, run_number, frameOffset, numCams);
@@ -308,16 +318,17 @@ int main(int argc, char** argv) {
             }
             const double ta1 = wall();
             T_analyze += ta1 - ta0;
-            /* write and commit after each event, so in the event of a crash it is not lost (:379-383) */
-            const std::string rows = EventOutput->formatCameraOutput();
-            std::ofstream f(part_name, std::fstream::out | std::fstream::app);
-            f << rows;
-            f.close();
+            /* rows of the event go to the batch buffer; the file is opened, appended and closed once per staged batch
+             * (the reference commits after each event, :379-383 -- here a crash loses at most the batch in flight) */
+            EventOutput->appendCameraOutput(batch_rows);
             delete EventOutput;
             for (int icam = 0; icam < numCams; icam++) delete Analyzers[icam];
             AbubDevice::Get().ReleaseSlot(keys[ci]);
             T_write += wall() - ta1;
         }
+        const double tw0 = wall();
+        OutputWriter::appendToFile(part_name, batch_rows);
+        T_write += wall() - tw0;
     }
     printf("run complete.\n");
     if (getenv("ABUB_TIMING")) {

@@ -4,6 +4,9 @@
 //   host_tool raw-events <run_dir/>                               RawParser::GetEventDirLists
 //   host_tool zip-list <run.zip> <event> <cam> | zip-events <run.zip> | zip-get <run.zip> <event> <frame> <out.raw>
 //   host_tool writer-selftest <out_dir/>         fixed bubble lists through OutputWriter (header + rows)
+#include <chrono>
+#include <cstring>
+#include <cstdint>
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -107,11 +110,86 @@ int main(int argc, char** argv) {
             w.stageCameraOutputError(2, -3, 3);            // cam 2: no trigger
             std::vector<bubble*> none;
             w.stageCameraOutput(none, 3, 5, 3);            // cam 3: empty list stages -1
+            std::string fast;
+            w.appendCameraOutput(fast);                    // batch formatter (to_chars) must print the same bytes
+            if (fast != w.formatCameraOutput()) { printf("BATCH FORMATTER DIFFERS\n%s", fast.c_str()); return 1; }
             w.writeCameraOutput();
             for (int c = 0; c < 4; c++) w.stageCameraOutputError(c, -7, 4);
+            fast.clear();
+            w.appendCameraOutput(fast);
+            if (fast != w.formatCameraOutput()) { printf("BATCH FORMATTER DIFFERS\n%s", fast.c_str()); return 1; }
             w.writeCameraOutput();
             printf("%s\n", w.fileName().c_str());
             return 0;
+        }
+        if (cmd == "writer-bench" && argc == 4) {
+            // events/s of the per-event path (format with iostream, open/append/close per event: PICOFormatWriterV4.cpp:287-302)
+            // and of the batch path (to_chars into one buffer, one append) on an event with 2 tracked bubbles per camera
+            const int nev = atoi(argv[3]);
+            std::vector<bubble*> bl;
+            for (int c = 0; c < 8; c++) {
+                bubble* b = new bubble(frame(100 + c, 50, 4, 3, 7.5, 101.256f + c, 51.5f));
+                for (int k = 1; k <= 10; k++) {
+                    b->lockThisIteration = false;
+                    *b << frame(100 + c, 50 - k, 4 + k, 3 + k, 7.5 + 2.1 * k, 101.3f + c, 51.5f - 1.25f * k);
+                }
+                bl.push_back(b);
+            }
+            auto stage = [&](OutputWriter& w, int ev) {
+                for (int c = 0; c < 4; c++) w.stageCameraOutput(std::vector<bubble*>{bl[2 * c], bl[2 * c + 1]}, c, 17, ev);
+            };
+            auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+            const std::string dir = argv[2];
+            double t0 = now();
+            {
+                OutputWriter w(dir, "per_event", 30, 4);
+                w.writeHeader();
+                for (int ev = 0; ev < nev; ev++) { stage(w, ev); w.writeCameraOutput(); }
+            }
+            const double t_event = now() - t0;
+            t0 = now();
+            {
+                OutputWriter w(dir, "batch", 30, 4);
+                w.writeHeader();
+                std::string rows;
+                for (int ev = 0; ev < nev; ev++) {
+                    stage(w, ev);
+                    w.appendCameraOutput(rows);
+                    if ((ev + 1) % 1024 == 0) { OutputWriter::appendToFile(w.fileName(), rows); rows.clear(); }
+                }
+                OutputWriter::appendToFile(w.fileName(), rows);
+            }
+            const double t_batch = now() - t0;
+            printf("{\"events\": %d, \"per_event_events_per_s\": %.0f, \"batch_events_per_s\": %.0f}\n", nev, nev / t_event, nev / t_batch);
+            return 0;
+        }
+        if (cmd == "format-fuzz" && argc == 3) {
+            // the two value formatters on random floats (as double, the promotion `stream << float` does), on halves of the
+            // last printed digit, on huge/tiny/non-finite values
+            const long n = atol(argv[2]);
+            uint64_t x = 0x9E3779B97F4A7C15ull;
+            long bad = 0;
+            auto check = [&](double v) {
+                if (OutputWriter::formatValueFast(v) != OutputWriter::formatValueStream(v)) {
+                    if (bad++ < 5) printf("%a: fast '%s' stream '%s'\n", v, OutputWriter::formatValueFast(v).c_str(), OutputWriter::formatValueStream(v).c_str());
+                }
+            };
+            for (long i = 0; i < n; i++) {
+                x ^= x << 13; x ^= x >> 7; x ^= x << 17;
+                uint32_t bits = (uint32_t)(x >> 17);
+                float f;
+                memcpy(&f, &bits, 4);
+                check((double)f);                                           // any float, incl. NaN/inf/denormals
+                check((double)(float)((int)(x % 400000) - 200000) / 8.0);  // multiples of 0.125 -> ties at the 3rd decimal
+                check((double)(float)(((int)(x % 4000000) - 2000000) * 0.005f));
+                check(((double)(int64_t)(x % 2000001) - 1000000) / 1000.0);
+            }
+            volatile double z = 0.0;
+            const double special[] = {0.0, -0.0, 0.005, 0.015, 0.025, -0.005, 1e300, -1e300, 1e-300, 3.4028234663852886e38,
+                                      1.0 / z, -1.0 / z, z / z, -(z / z), 0.125, 0.375, 2.675, 1.005};
+            for (double v : special) check(v);
+            printf("%ld values, %ld mismatches\n", 4 * n + (long)(sizeof(special) / sizeof(special[0])), bad);
+            return bad ? 1 : 0;
         }
     } catch (int code) {
         printf("THROW %d\n", code);

@@ -105,6 +105,17 @@ int abub_trigger_hist_write(abub_ctx* ctx, int slot, int cam, const uint32_t* hi
  * start_frames[(slot-slot_first)*ncams+cam] (NULL = 1 everywhere).  A start frame > 1
  * resumes with the history of frames 1..start-1 intact (AnalyzerUnit.cpp:165).  Async. */
 int abub_trigger_scan(abub_ctx* ctx, int slot_first, int nslots, const int* start_frames);
+/* Which per-frame quantity the state machine of abub_trigger_scan / abub_trigger / abub_trigger_stream thresholds.  The
+ * reference compiles ONE of three lines (AnalyzerUnit.cpp:226-228 and :290-292); all three read the same K1 table:
+ *   ABUB_METRIC_SIGNIFICANCE          calculateSignificanceFrame (:435-504), entropyThreshold 3.5 (:142) -- the default;
+ *   ABUB_METRIC_ENTROPY               calculateEntropyFrame (:386-423): 128-bin Shannon entropy in float, threshold 8e-5 (:140);
+ *   ABUB_METRIC_ENTROPY_SIGNIFICANCE  calculateEntropySignificance (:425-433): (E - mean)/sigma over the stored entropies, 1.9 (:141).
+ * threshold <= 0 selects the reference's value for the metric.  On the two entropy paths loc_thres stays 3 (:29) and the
+ * `sig` array of abub_trigger_results holds the metric.  Takes effect at the next scan. */
+#define ABUB_METRIC_SIGNIFICANCE 0
+#define ABUB_METRIC_ENTROPY 1
+#define ABUB_METRIC_ENTROPY_SIGNIFICANCE 2
+int abub_set_trigger_metric(abub_ctx* ctx, int metric, float threshold);
 /* Results of the last scan, D2H (synchronises the stream).  Arrays of nslots*ncams:
  * trig = MatTrigFrame (valid when status 0), status = TriggerFrameIdentificationStatus
  * (0, -3, -9), loc_thres = AnalyzerUnit::loc_thres.  sig (may be NULL) =

@@ -81,10 +81,12 @@ class SignificanceState:
 
     def __init__(self) -> None:
         self.pix_counts: List[List[int]] = [[] for _ in range(256)]
+        self.entropies: List[np.float64] = []    # AnalyzerUnit.hpp:72
         self.loc_thres = 3          # AnalyzerUnit.cpp:29
 
     def clear(self) -> None:        # AnalyzerUnit.cpp:165-169
         self.pix_counts = [[] for _ in range(256)]
+        self.entropies = []
 
 
 def calc_mean(vec: Sequence[int], size: int) -> np.float64:
@@ -207,18 +209,57 @@ class TableSource(FrameSource):
         self.bad = set()
 
 
+# The two alternatives the reference keeps beside the significance (AnalyzerUnit.cpp:226-227, :290-291; one of the three
+# lines is compiled) and the entropyThreshold each one goes with (:140-142).
+TRIGGER_THRESHOLDS = {"significance": 3.5, "entropy": 8e-5, "entropy_significance": 1.9}
+
+
+def calculate_entropy_frame128(h256: np.ndarray, total: int) -> np.float32:
+    """AnalyzerUnit::calculateEntropyFrame (AnalyzerUnit.cpp:386-423) from the 256-bin histogram of the frame: calcHist
+    with 128 bins over [0,256) pairs adjacent grey levels (:392-394, :410); then the arithmetic of the Trainer's copy."""
+    h128 = np.asarray(h256, dtype=np.int64).reshape(128, 2).sum(axis=1)
+    return entropy_from_hist16(h128, total)
+
+
+def calculate_entropy_significance(h256: np.ndarray, total: int, store: bool, st: SignificanceState) -> np.float64:
+    """AnalyzerUnit::calculateEntropySignificance (AnalyzerUnit.cpp:425-433) with CalcMean/CalcStdDev on doubles."""
+    e = F64(calculate_entropy_frame128(h256, total))              # double entropy = (float) :426
+    if store:
+        st.entropies.append(e)                                    # :427-429
+    s = F64(0.0)
+    for v in st.entropies:
+        s = s + v
+    s2 = F64(0.0)
+    for v in st.entropies:
+        s2 = s2 + v * v
+    with np.errstate(all="ignore"):
+        n = F64(len(st.entropies))
+        mean = s / n                                              # :430
+        sigma = np.sqrt(s2 / n - mean * mean)                     # :431
+        return (e - mean) / sigma                                 # :432
+
+
 def find_trigger_frame(src: FrameSource, sigma: np.ndarray, training_set_size: int,
                        startframe: int, st: SignificanceState, mat_trig_frame: int,
                        hp: Optional[HistProvider] = None,
-                       min_eval_frame: int = 2) -> TriggerResult:
-    """AnalyzerUnit.cpp:119-324.  gammaCorrection is a no-op (:329)."""
+                       min_eval_frame: int = 2, metric: str = "significance",
+                       threshold: Optional[float] = None) -> TriggerResult:
+    """AnalyzerUnit.cpp:119-324.  gammaCorrection is a no-op (:329).  `metric` picks which of the lines :226-228 (and
+    :290-292) is the compiled one."""
+    def measure(h, store):
+        if metric == "significance":
+            return calculate_significance(h, total, store, st, training_set_size)
+        if metric == "entropy":
+            return F64(calculate_entropy_frame128(h, total))
+        return calculate_entropy_significance(h, total, store, st)
+
     n = len(src)
     if n < 5:                                                     # :122-126
         return TriggerResult(-9, mat_trig_frame, False, st.loc_thres)
     if hp is None:
         hp = HistProvider(src, sigma)
     total = int(src.frames[0].size)
-    thr = F32(3.5)                                                # :142
+    thr = F32(TRIGGER_THRESHOLDS[metric] if threshold is None else threshold)   # :140-142
     if startframe < 1:
         startframe = 1
     if startframe == 1:                                           # :165-169
@@ -237,7 +278,7 @@ def find_trigger_frame(src: FrameSource, sigma: np.ndarray, training_set_size: i
         if err == -1:                                             # :208-213
             return TriggerResult(-9, trig, False, st.loc_thres, res_sig)
         h = hp.hist(i, prevprev if two else prev)                 # :218
-        sg = calculate_significance(h, total, True, st, training_set_size)          # :228
+        sg = measure(h, True)                                     # :226-228
         single = F32(sg)                                          # float singleEntropy (:146)
         res_sig.append((i, float(sg)))
         if single > thr and i >= min_eval_frame:                  # :254
@@ -247,7 +288,7 @@ def find_trigger_frame(src: FrameSource, sigma: np.ndarray, training_set_size: i
                 ii = 1
                 while ii <= 2 and ii + i < n:                     # :282
                     h2 = hp.hist(i + ii, tpp if two else tp)      # :286
-                    single = F32(calculate_significance(h2, total, False, st, training_set_size))  # :292
+                    single = F32(measure(h2, False))              # :290-292
                     with np.errstate(all="ignore"):
                         lhs = F64(single) / (F64(thr) / 3.5 * 5) + F64(single) / max_so_far
                     if lhs <= 3:                                  # :296
@@ -762,7 +803,8 @@ class CamAnalysis:
 
 
 def any_cam_analysis(src: FrameSource, trained: TrainedData, cam_mask, bellows_mask,
-                     event_number: int, mask_dir_set: bool = True, bellows_template=None) -> CamAnalysis:
+                     event_number: int, mask_dir_set: bool = True, bellows_template=None,
+                     metric: str = "significance", threshold: Optional[float] = None) -> CamAnalysis:
     st = SignificanceState()
     hp = HistProvider(src, trained.sigma)
     bubbles: List[Bubble] = []
@@ -772,7 +814,7 @@ def any_cam_analysis(src: FrameSource, trained: TrainedData, cam_mask, bellows_m
     try:
         while True:
             tr = find_trigger_frame(src, trained.sigma, trained.training_set_size,
-                                    mat_trig + 1, st, mat_trig, hp)       # :88
+                                    mat_trig + 1, st, mat_trig, hp, metric=metric, threshold=threshold)   # :88
             res.triggers.append(tr)
             mat_trig = tr.trig
             ok = ok and tr.ok
@@ -809,7 +851,8 @@ def train_all(run_events: Sequence[Sequence[Optional[np.ndarray]]], ncams: int) 
 
 
 def run_detect(run: str, event_numbers: Sequence[int], run_events, trained: List[TrainedData],
-               cam_masks, bellows_masks, frame_offset: int = 30, bellows_templates=None) -> Tuple[str, list]:
+               cam_masks, bellows_masks, frame_offset: int = 30, bellows_templates=None,
+               metric: str = "significance", threshold: Optional[float] = None) -> Tuple[str, list]:
     """Detect loop of main (AutoBubStart3.cpp:342-388): returns the text appended after
     the header and the per-(event,cam) analysis records."""
     text = []
@@ -821,7 +864,7 @@ def run_detect(run: str, event_numbers: Sequence[int], run_events, trained: List
         for cam in range(ncams):
             a = any_cam_analysis(FrameSource(ev[cam]), trained[cam], cam_masks[cam],
                                  bellows_masks[cam], evn, True,
-                                 None if bellows_templates is None else bellows_templates[cam])
+                                 None if bellows_templates is None else bellows_templates[cam], metric, threshold)
             cams.append(a.out)
             rr.append(a)
         text.append(write_camera_output(run, cams, frame_offset))

@@ -128,6 +128,21 @@ def test_png_frames_decoded_on_device(abub3hs, tma_run, tmp_path):
     assert rest(t_dev) == rest(gold)
 
 
+@pytest.mark.parametrize("metric,thr", [("entropy_significance", None), ("entropy", 0.02)])
+def test_trigger_metric_option(abub3hs, tma_run, tmp_path, metric, thr):
+    """8(f)-4 through the binary: --trigger_metric selects calculateEntropyFrame / calculateEntropySignificance
+    (AnalyzerUnit.cpp:226-227) for the whole run; output text as the oracle's with the same line compiled in."""
+    from autobub3hs_b200 import synth
+    import oracle.cv2_oracle as o
+    run, _ = tma_run
+    trained = o.train_all(run.events, 4)
+    text, _ = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks,
+                           metric=metric, threshold=thr)
+    synth.write_run(run, str(tmp_path / "data"), str(tmp_path / "masks"))
+    extra = ["--trigger_metric", metric] + ([] if thr is None else ["--trigger_threshold", str(thr)])
+    assert _run(abub3hs, str(tmp_path / "data"), str(tmp_path / "out"), str(tmp_path / "masks"), extra) == o.write_header() + text
+
+
 def test_unreadable_run_is_minus5_and_bad_training_is_minus7(abub3hs, tmp_path):
     from autobub3hs_b200 import synth
     import oracle.cv2_oracle as o

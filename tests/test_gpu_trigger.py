@@ -226,3 +226,55 @@ def test_trigger_stream_equals_batch(capi, small_run, small_trained, chunk):
         # the result table is left as abub_trigger_results expects it
         t3, s3, l3, _ = ctx.trigger_results(0, nev, want_sig=False)
         assert np.array_equal(s3, status) and np.array_equal(t3[ok], trig[ok])
+
+
+@pytest.mark.parametrize("metric", ["entropy", "entropy_significance"])
+def test_trigger_entropy_variants(capi, small_run, small_trained, metric):
+    """the two trigger quantities the reference keeps as commented alternatives (AnalyzerUnit.cpp:226-227,
+    :290-291 -> calculateEntropyFrame :386-423, calculateEntropySignificance :425-433), selected with
+    abub_set_trigger_metric on the same K1 table.  Status, trigger frame and loc_thres (3, never updated on these paths)
+    must equal the oracle's, including re-triggers from a later start frame; the float entropy may differ from the
+    host's log2f by an ulp per bin: 1e-6 absolute on the entropy, 1e-3 relative on the z-score built from it."""
+    import oracle.cv2_oracle as o
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    exact = total = 0
+    with capi.Context(rows, cols, ncams=4, max_frames=40, max_slots=1) as ctx:
+        for thr in (None, 0.02 if metric == "entropy" else 3.0):
+            ctx.set_trigger_metric(metric, 0.0 if thr is None else thr)
+            for tss in (12, 4):
+                for c in range(4):
+                    ctx.set_background(c, trained[c].avg, trained[c].sigma, tss)
+                for ev in range(len(run.events)):
+                    for c in range(4):
+                        ctx.event_upload(0, c, run.events[ev][c])
+                    for c in range(4):
+                        fr = run.events[ev][c]
+                        st = o.SignificanceState()
+                        hp = o.HistProvider(o.FrameSource(fr), trained[c].sigma)
+                        mat = 0
+                        for attempt in range(3):
+                            r = o.find_trigger_frame(o.FrameSource(fr), trained[c].sigma, tss, mat + 1, st, mat, hp,
+                                                     metric=metric, threshold=thr)
+                            t, s, l, sig = ctx.trigger(0, c, mat + 1)
+                            assert s == r.status, (metric, thr, tss, ev, c, attempt)
+                            for (i, sv) in r.sig:
+                                g = sig[i]
+                                total += 1
+                                exact += (sv == g) or (np.isnan(sv) and np.isnan(g))
+                                if np.isnan(sv) or np.isinf(sv):
+                                    assert np.isnan(g) or g == sv or (np.isinf(g) and np.isinf(sv)), (i, sv, g)
+                                elif metric == "entropy":
+                                    assert abs(g - sv) <= 1e-6, (i, sv, g)
+                                else:
+                                    assert abs(g - sv) <= 1e-3 * max(1.0, abs(sv)), (i, sv, g)
+                            if r.status != -9:
+                                assert l == 3
+                            if r.status != 0:
+                                break
+                            assert t == r.trig
+                            mat = r.trig
+        ctx.set_trigger_metric("significance")
+    # an entropy that differs in its last bit shifts every later z-score of that camera a little: only the plain entropy is
+    # expected to be bit-equal most of the time
+    assert total > 0 and (metric != "entropy" or exact >= 0.9 * total), (exact, total)

@@ -121,10 +121,19 @@ def test_zip_parser(tool, tmp_path, compression):
     assert subprocess.run([tool, "zip-events", str(tmp_path / "nope")], capture_output=True, text=True).stdout.strip() == "THROW -10"
 
 
+def test_batch_formatter_prints_what_the_stream_prints(tool):
+    """SURVEY 8(f)-3: the to_chars formatter of OutputWriter::appendCameraOutput against `stream << value` under
+    fixed / precision(2) on 2M values (random floats of every class, ties at the last digit, non-finite)."""
+    r = subprocess.run([tool, "format-fuzz", "500000"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-1500:]
+    assert "0 mismatches" in r.stdout
+
+
 def test_output_writer_matches_oracle(tool, tmp_path):
     import oracle.cv2_oracle as o
     F32 = np.float32
     r = subprocess.run([tool, "writer-selftest", str(tmp_path) + "/"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-1500:]          # includes: batch formatter == stream formatter on these rows
     text = open(r.stdout.strip()).read()
 
     def frame(x, y, w, h, area, cx, cy):
