@@ -251,3 +251,37 @@ def test_bellows_helpers():
     for bad in ((45, 5, 20, 11), (-1, 0, 5, 5), (0, 0, 0, 5)):
         with pytest.raises(ValueError):
             o.process_frame_roi(a, b, s, bad)
+
+
+def test_entropy_trigger_variants_known_answers():
+    """calculateEntropyFrame (AnalyzerUnit.cpp:386-423) on histograms with closed-form entropies, the pairing of the
+    256-bin table into 128 bins, and calculateEntropySignificance (:425-433) on a hand-computed history."""
+    import oracle.cv2_oracle as o
+    h = np.zeros(256, np.int64)
+    h[0] = 1 << 20
+    assert o.calculate_entropy_frame128(h, 1 << 20) == 0.0                 # one bin: p = 1
+    h[:] = 0
+    h[0] = h[1] = 1 << 19                                                   # grey 0 and 1 share bin 0
+    assert o.calculate_entropy_frame128(h, 1 << 20) == 0.0
+    h[:] = 0
+    h[0] = h[2] = 1 << 19                                                   # two bins of 1/2
+    assert o.calculate_entropy_frame128(h, 1 << 20) == 1.0
+    h[:] = 1 << 12                                                          # uniform: log2(128)
+    assert o.calculate_entropy_frame128(h, 256 << 12) == 7.0
+    # against cv2.calcHist with 128 bins on an image
+    import cv2
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 40, (120, 200)).astype(np.uint8)
+    h128 = cv2.calcHist([img], [0], None, [128], [0, 256]).reshape(128)
+    assert np.array_equal(h128, o.hist256(img).reshape(128, 2).sum(axis=1))
+    # z-score: entropies 0, 1, 1 -> mean 2/3, sigma sqrt(2/3 - 4/9)
+    st = o.SignificanceState()
+    one = np.zeros(256, np.int64); one[0] = 1 << 20
+    two = np.zeros(256, np.int64); two[0] = two[2] = 1 << 19
+    with np.errstate(all="ignore"):
+        assert np.isnan(o.calculate_entropy_significance(one, 1 << 20, True, st))      # 0/0 on the first frame
+    o.calculate_entropy_significance(two, 1 << 20, True, st)
+    z = o.calculate_entropy_significance(two, 1 << 20, True, st)
+    assert abs(z - (1 - 2 / 3) / np.sqrt(2 / 3 - 4 / 9)) < 1e-12
+    z2 = o.calculate_entropy_significance(one, 1 << 20, False, st)                      # store = false: history unchanged
+    assert len(st.entropies) == 3 and abs(z2 - (0 - 2 / 3) / np.sqrt(2 / 3 - 4 / 9)) < 1e-12
