@@ -254,7 +254,7 @@ def run_ours(args, rank, world, local_rank):
     for s in range(B):
         es = synth.make_event_spec(rank * 100000 + s, classes[s], cam_masks, bellows, seed=11)
         specs.append(es)
-        fill_slot(torch, slot_tensor(torch, ctx, s), bgs, es.bubbles, gen)
+        fill_slot(torch, slot_tensor(torch, ctx, s), bgs, es.bubbles, gen, args.noise_sigma)
         ctx.event_set_nframes(s, [NFRAMES] * NCAMS)
     torch.cuda.synchronize()
     t_gen = time.perf_counter() - t_gen
@@ -396,7 +396,7 @@ def run_ours(args, rank, world, local_rank):
         "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": WORKLOAD, "events_per_step": B, "l2": "inputs (35 GB/step at 125 events) exceed L2; no flush",
-                   "event_mix": "90% normal (1-3 bubbles), 5% multi (>=20), 5% no-trigger; noise sigma 2.0",
+                   "event_mix": f"90% normal (1-3 bubbles), 5% multi (>=20), 5% no-trigger; noise sigma {args.noise_sigma}",
                    "train_events": n_train, "generated_on": "device (torch RNG), seconds=%.1f" % t_gen},
         "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": sent_total[0] * NPIX // e2e_steps,
                 "d2h_bytes_per_step": Be * NCAMS * 16 * (1 if args.e2e_mode == "full" else (NFRAMES + args.e2e_chunk - 1) // args.e2e_chunk),
@@ -437,6 +437,8 @@ def main():
     ap.add_argument("--cpu-events", type=int, default=8)
     ap.add_argument("--ref-events", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--noise-sigma", type=float, default=2.0,
+                    help="camera noise of the synthetic frames (grey levels); 2.0 is the workload of the headline number")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
