@@ -197,33 +197,43 @@ void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const
     }
     const double t1 = now();
     const bool device_png = (npix % 4 == 0) && !getenv("ABUB_PNG_ON_HOST");
-#pragma omp parallel for schedule(dynamic, 1)
-    for (long i = 0; i < (long)items.size(); i++) {
-        Item& it = items[i];
-        uint8_t* region = pin[it.slot] + ((size_t)it.cam * max_frames_ + it.frame) * npix;
-        std::vector<uint8_t> enc;
-        if (parser->GetImageBytes(*it.event, it.name, enc) == parser->FailureCode() || enc.empty()) { memset(region, 0, npix); continue; }
-        if (device_png) {
-            const size_t zl = abubcodec::png_gray8_stream(enc.data(), enc.size(), rows_, cols_, region, npix);
-            if (zl >= 2) { it.state = 2; it.zlen = (uint32_t)zl; continue; }
-        }
-        if (abubcodec::decode_into(enc.data(), enc.size(), region, rows_, cols_)) it.state = 1;
-        else memset(region, 0, npix);
-    }
-    const double t2 = now();
-    // host-decoded cameras go up whole (their device-decoded frames carry compressed bytes for the moment) ...
+    // One event at a time: its frames are read and decoded on all cores, then the cameras that hold host-decoded frames go
+    // up asynchronously while the next event is being decoded (their device-decoded frames carry compressed bytes for the
+    // moment).  PNG streams are collected for one decode call over the whole batch (the inflate kernel wants many frames).
     std::vector<abub_png_job> jobs;
     std::vector<size_t> job_item;
-    std::map<std::pair<int, int>, bool> host_cam;
-    for (size_t i = 0; i < items.size(); i++) {
-        if (items[i].state == 2) { jobs.push_back(abub_png_job{items[i].slot, items[i].cam, items[i].frame, items[i].zlen}); job_item.push_back(i); }
-        else host_cam[{items[i].slot, items[i].cam}] = true;
-    }
-    for (size_t e = 0; e < events.size(); e++)
-        for (int cam = 0; cam < ncams_; cam++) {
-            if (ncam[e][cam] < 0) continue;
-            if (host_cam.count({slots[e], cam})) Check(abub_event_submit_cam(ctx_, slots[e], cam, ncam[e][cam]), "abub_event_submit_cam");
+    double t_dec = 0, t_up = 0;
+    size_t i0 = 0;
+    for (size_t e = 0; e < events.size(); e++) {
+        size_t i1 = i0;
+        while (i1 < items.size() && items[i1].event == &events[e]) i1++;
+        const double ta = now();
+#pragma omp parallel for schedule(dynamic, 1)
+        for (long i = (long)i0; i < (long)i1; i++) {
+            Item& it = items[i];
+            uint8_t* region = pin[it.slot] + ((size_t)it.cam * max_frames_ + it.frame) * npix;
+            static thread_local std::vector<uint8_t> enc;          // reused: no fresh 1.8 MB mapping per frame
+            if (parser->GetImageBytes(*it.event, it.name, enc) == parser->FailureCode() || enc.empty()) { memset(region, 0, npix); continue; }
+            if (device_png) {
+                const size_t zl = abubcodec::png_gray8_stream(enc.data(), enc.size(), rows_, cols_, region, npix);
+                if (zl >= 2) { it.state = 2; it.zlen = (uint32_t)zl; continue; }
+            }
+            if (abubcodec::decode_into(enc.data(), enc.size(), region, rows_, cols_)) it.state = 1;
+            else memset(region, 0, npix);
         }
+        const double tb = now();
+        bool host_cam[8] = {false};
+        for (size_t i = i0; i < i1; i++) {
+            if (items[i].state == 2) { jobs.push_back(abub_png_job{items[i].slot, items[i].cam, items[i].frame, items[i].zlen}); job_item.push_back(i); }
+            else host_cam[items[i].cam] = true;
+        }
+        for (int cam = 0; cam < ncams_; cam++)
+            if (ncam[e][cam] >= 0 && host_cam[cam]) Check(abub_event_submit_cam(ctx_, slots[e], cam, ncam[e][cam]), "abub_event_submit_cam");
+        t_dec += tb - ta;
+        t_up += now() - tb;
+        i0 = i1;
+    }
+    const double t2 = t1 + t_dec;
     // ... then the PNG streams are sent and decoded in place
     std::vector<int> okv(jobs.size(), 0);
     if (!jobs.empty()) Check(abub_event_decode_png(ctx_, jobs.data(), (int)jobs.size(), okv.data()), "abub_event_decode_png");
@@ -259,6 +269,7 @@ void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const
     }
     const double t3 = now();
     t_read += t1 - t0; t_decode += t2 - t1; t_upload += t3 - t2;
+    (void)t_up;
 }
 
 std::vector<int> AbubDevice::PrefetchEvents(Parser* parser, const std::vector<std::string>& keys, const std::vector<std::string>& events,

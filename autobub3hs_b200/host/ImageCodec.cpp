@@ -73,9 +73,12 @@ bool bmp_decode(const uint8_t* b, size_t n, const BmpInfo& h, Sink& s) {
             gray_pal[i] = bgr2gray(e[0], e[1], e[2]);
         }
     }
+    bool identity = h.bpp == 8;                         // the usual greyscale palette: rows are copied as they are
+    for (int i = 0; identity && i < 256; i++) identity = i < (int)h.pal_n ? gray_pal[i] == i : false;
     for (int y = 0; y < h.height; y++) {
         const uint8_t* src = b + h.data_off + stride * (h.top_down ? y : h.height - 1 - y);
         uint8_t* dst = s.px + (size_t)y * s.cols;
+        if (identity) { memcpy(dst, src, (size_t)h.width); continue; }
         switch (h.bpp) {
             case 8:  for (int x = 0; x < h.width; x++) dst[x] = gray_pal[src[x]]; break;
             case 4:  for (int x = 0; x < h.width; x++) dst[x] = gray_pal[(src[x >> 1] >> ((x & 1) ? 0 : 4)) & 15]; break;
