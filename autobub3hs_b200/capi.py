@@ -22,7 +22,7 @@ EXPORTS = [
     "abub_set_background", "abub_set_background_from_training",
     "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_submit_cam", "abub_event_upload_frame", "abub_set_trigger_metric", "abub_event_decode_png", "abub_event_device_ptr",
     "abub_event_set_nframes",
-    "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_hist_write", "abub_trigger_scan", "abub_trigger_results", "abub_trigger", "abub_trigger_stream",
+    "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_hist_write", "abub_trigger_scan", "abub_trigger_results", "abub_trigger", "abub_trigger_stream", "abub_trigger_early",
     "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_add_slots",
     "abub_train_add_events", "abub_train_finish", "abub_selftest_fdiv", "abub_k4_fdiv1_max",
     "abub_train_partials", "abub_train_allreduce", "abub_train_finish_partials", "abub_train_finish_allreduced",
@@ -92,6 +92,7 @@ def load() -> C.CDLL:
     lib.abub_trigger_results.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp]
     lib.abub_trigger.argtypes = [vp, C.c_int, C.c_int, C.c_int, ip, ip, ip, vp]
     lib.abub_trigger_stream.argtypes = [vp, C.c_int, C.c_int, ip, C.c_int, vp, vp, vp, vp]
+    lib.abub_trigger_early.argtypes = [vp, C.c_int, C.c_int, C.c_int]
     lib.abub_train_begin.argtypes = [vp, C.c_int]
     lib.abub_train_add_event.argtypes = [vp, C.c_int, u8p, C.POINTER(C.c_float), ip]
     lib.abub_train_add_slot.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float), ip]
@@ -349,6 +350,11 @@ class Context:
         self._ck(self.lib.abub_trigger_stream(self.h, slot_first, nslots, nf, chunk_frames, *[_p(o) for o in out]),
                  "abub_trigger_stream")
         return tuple(out)
+
+    def trigger_early(self, slot_first: int, nslots: int, chunk_frames: int = 6) -> None:
+        """Resident FindTriggerFrame with the reference's early exit (K1 in rounds of chunk_frames frame pairs, decided
+        cameras drop out); asynchronous, results through trigger_results."""
+        self._ck(self.lib.abub_trigger_early(self.h, slot_first, nslots, chunk_frames), "abub_trigger_early")
 
     # ---- multi-GPU (one process per GPU) ----
     def nccl_comm_create(self, id_file: str, rank: int, world: int) -> int:

@@ -118,6 +118,8 @@ int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots);
 // ABUB_STATUS_PENDING
 int abub_k2_launch_avail(abub_ctx* ctx, int slot_first, int nslots, const int* d_avail);
 #define ABUB_STATUS_PENDING (-100)
+// abub_trigger_early: d_avail (and d_start on the first round) of the range for the next round of frames
+int abub_k2_next_avail(abub_ctx* ctx, int slot_first, int nslots, int next, bool first_round);
 // K3/K4 (k34_trainer.cu)
 int abub_k3_gate_hist16(abub_ctx* ctx, const uint8_t* d_f0, const uint8_t* d_f1, uint32_t* d_hist16);
 int abub_k3_gate_batch(abub_ctx* ctx, const uint8_t* const* d_pairs, int n, uint32_t* d_hist16);

@@ -482,6 +482,38 @@ extern "C" int abub_trigger_stream(abub_ctx* ctx, int slot_first, int nslots, co
     return ABUB_OK;
 }
 
+// Resident form of the early exit: the frames are in HBM already, so nothing is gained on the link, but the reference
+// stops computing ProcessFrame at the trigger (AnalyzerUnit.cpp:297-300) and so does this call: K1 runs on
+// chunk_frames frame pairs at a time, K2 after every round, and a (slot,cam) whose search is decided drops out of the
+// following rounds.  No host round trip between the rounds: the per-camera frame limits are updated on the device.
+extern "C" int abub_trigger_early(abub_ctx* ctx, int slot_first, int nslots, int chunk_frames) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot_first >= 0 && nslots >= 1 && slot_first + nslots <= ctx->max_slots, "slot range");
+    ABUB_REQUIRE(ctx, chunk_frames >= 1, "chunk_frames");
+    int rc = require_backgrounds(ctx);
+    if (rc) return rc;
+    cudaSetDevice(ctx->device);
+    int nf_max = 0;
+    for (int s = slot_first; s < slot_first + nslots; s++) {
+        for (int c = 0; c < ctx->ncams; c++) nf_max = ctx->slots[s].nframes[c] > nf_max ? ctx->slots[s].nframes[c] : nf_max;
+        ctx->slots[s].hist_valid = false;                         // the tables stop where the searches stopped
+    }
+    // nothing can be decided on fewer than 5 frames (candidate at i >= 2 plus two look-ahead frames)
+    int lo = 0, hi = chunk_frames < 5 ? 5 : chunk_frames;
+    bool first = true;
+    do {
+        if (hi > nf_max) hi = nf_max;
+        if ((rc = abub_k2_next_avail(ctx, slot_first, nslots, hi, first))) return rc;
+        if ((rc = abub_k1_launch_trigger_range(ctx, slot_first, nslots, lo, hi, ctx->d_avail, first))) return rc;
+        if ((rc = abub_k2_launch_avail(ctx, slot_first, nslots, ctx->d_avail))) return rc;
+        first = false;
+        lo = hi;
+        hi += chunk_frames;
+    } while (lo < nf_max);
+    if (nf_max == 0) return abub_k2_launch(ctx, slot_first, nslots);      // status -9 everywhere
+    return ABUB_OK;
+}
+
 // ---- single-frame parity tap --------------------------------------------------------
 extern "C" int abub_process_frame(abub_ctx* ctx, int cam, const uint8_t* work, const uint8_t* prev, uint8_t* diff,
                                   uint32_t* hist) {

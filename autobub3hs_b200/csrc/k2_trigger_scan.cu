@@ -203,7 +203,30 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
     if (lane == 0) { res[0] = trig; res[1] = status; res[2] = loc_thres; res[3] = scanned; }
 }
 
+// Resident early exit (abub_trigger_early): frames a camera may look at in the next round -- none once its search is
+// decided, the next boundary while K2 reports that it needs more frames.  first round: result == nullptr.
+__global__ void k2_next_avail_kernel(const int* __restrict__ result, const int* __restrict__ nframes, int* __restrict__ avail,
+                                     int* __restrict__ start, int first, int n, int next) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int sc = first + i;
+    if (result == nullptr) {
+        start[sc] = 1;
+        avail[sc] = max(1, min(next, nframes[sc]));       // >= 1: K2 must still report -9 for a camera without frames
+    } else {
+        avail[sc] = (result[sc * 4 + 1] == ABUB_STATUS_PENDING) ? min(next, nframes[sc]) : 0;
+    }
+}
+
 }  // namespace
+
+int abub_k2_next_avail(abub_ctx* ctx, int slot_first, int nslots, int next, bool first_round) {
+    const int n = nslots * ctx->ncams;
+    k2_next_avail_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(first_round ? nullptr : ctx->d_trig, ctx->d_nframes, ctx->d_avail,
+                                                                     ctx->d_start, slot_first * ctx->ncams, n, next);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    return ABUB_OK;
+}
 
 int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots) { return abub_k2_launch_avail(ctx, slot_first, nslots, nullptr); }
 

@@ -309,6 +309,32 @@ def run_ours(args, rank, world, local_rank):
     trig, status, lt, _ = ctx.trigger_results(0, B, want_sig=False)
     value = world * B * args.steps / (ms_total * 1e-3)
 
+    # ---- the same batch with the reference's early exit (abub_trigger_early): extra key, not the headline ----
+    early = None
+    if args.early_chunk > 0:
+        ctx.trigger_early(0, B, args.early_chunk)
+        t_e, s_e, l_e, _ = ctx.trigger_results(0, B, want_sig=False)
+        ok = status == 0
+        if not (np.array_equal(s_e, status) and np.array_equal(t_e[ok], trig[ok]) and np.array_equal(l_e[status != -9], lt[status != -9])):
+            raise SystemExit("abub_trigger_early disagrees with the full-table trigger path")
+        n_e = max(1, min(args.steps, 8))
+        ee0 = torch.cuda.Event(enable_timing=True)
+        ee1 = torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        ee0.record(stream)
+        for _ in range(n_e):
+            ctx.trigger_early(0, B, args.early_chunk)
+        ee1.record(stream)
+        torch.cuda.synchronize()
+        ms_e = ee0.elapsed_time(ee1) / n_e
+        ch = args.early_chunk
+        need = np.where(ok, np.minimum(trig + 3, NFRAMES), NFRAMES)
+        bounds = np.minimum(NFRAMES, np.maximum(5, -(-need // ch) * ch))
+        early = {"value": B / (ms_e * 1e-3), "unit": "events/s (this rank)", "ms_per_step": ms_e, "chunk_frames": ch,
+                 "frame_pairs_computed_frac": float((bounds - 1).sum() / (B * NCAMS * (NFRAMES - 1))),
+                 "note": "K1 in rounds of chunk_frames frame pairs, K2 after every round, decided cameras drop out "
+                         "(AnalyzerUnit.cpp:297-300); results equal to the full-table path"}
+
     # ---- end-to-end through the C ABI from pinned host buffers ----
     Be = min(args.e2e_events, B)
     nf = [NFRAMES] * NCAMS
@@ -416,6 +442,7 @@ def run_ours(args, rank, world, local_rank):
         "cpu_baseline": cpu,
         "clocks": clk.summary(),
         "triggered_fraction": float((status == 0).mean()),
+        "early_exit": early,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -434,6 +461,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--e2e-mode", default="stream", choices=["stream", "full"])
     ap.add_argument("--e2e-chunk", type=int, default=4)
+    ap.add_argument("--early-chunk", type=int, default=6, help="frame pairs per round of abub_trigger_early (0 = skip)")
     ap.add_argument("--cpu-events", type=int, default=8)
     ap.add_argument("--ref-events", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -136,6 +136,13 @@ int abub_trigger(abub_ctx* ctx, int slot, int cam, int start_frame, int* trig, i
  * The frames that were not sent are not resident: upload the slot before calling abub_localize on it. */
 int abub_trigger_stream(abub_ctx* ctx, int slot_first, int nslots, const int* nframes, int chunk_frames,
                         int* trig, int* status, int* loc_thres, int* frames_sent);
+/* Resident form of the same early exit (frames already in HBM, frame counts set by abub_event_submit / _upload /
+ * _set_nframes): K1 over chunk_frames frame pairs at a time, K2 after every round, and a (slot,cam) whose search is
+ * decided takes no part in the following rounds -- the reference stops computing ProcessFrame at the trigger
+ * (AnalyzerUnit.cpp:297-300).  Start frame 1.  Async; read the results with abub_trigger_results (sig holds the
+ * frames that were evaluated).  The histogram tables of the range are left partial: abub_trigger / abub_trigger_hist
+ * rebuild them when a later call needs them (a re-trigger from start_frame > 1). */
+int abub_trigger_early(abub_ctx* ctx, int slot_first, int nslots, int chunk_frames);
 
 /* ---- training: Trainer::MakeAvgSigmaImage (Trainer.cpp:221-331) ----------------- */
 int abub_train_begin(abub_ctx* ctx, int cam);

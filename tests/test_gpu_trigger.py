@@ -228,6 +228,46 @@ def test_trigger_stream_equals_batch(capi, small_run, small_trained, chunk):
         assert np.array_equal(s3, status) and np.array_equal(t3[ok], trig[ok])
 
 
+@pytest.mark.parametrize("chunk", [1, 4, 6, 40])
+def test_trigger_early_equals_batch(capi, small_run, small_trained, chunk):
+    """abub_trigger_early (resident frames, K1 in rounds of `chunk` frame pairs, decided cameras drop out of the later
+    rounds: the reference's return at the trigger, AnalyzerUnit.cpp:297-300) returns exactly what the full-table path
+    returns, leaves the significance of every evaluated frame, and a later abub_trigger rebuilds the table."""
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    nev = len(run.events)
+    with capi.Context(rows, cols, ncams=4, max_frames=40, max_slots=nev) as ctx:
+        for c in range(4):
+            ctx.set_background(c, trained[c].avg, trained[c].sigma, trained[c].training_set_size)
+        for ev in range(nev):
+            for c in range(4):
+                ctx.event_upload(ev, c, run.events[ev][c])
+        ctx.trigger_hist(0, nev)
+        ctx.trigger_scan(0, nev)
+        trig, status, lt, sig = ctx.trigger_results(0, nev)
+        ctx.trigger_early(0, nev, chunk)
+        t2, s2, l2, sig2 = ctx.trigger_results(0, nev)
+        assert np.array_equal(s2, status)
+        ok = status == 0
+        assert ok.any() and (status == -3).any() and (status == -9).any()
+        assert np.array_equal(t2[ok], trig[ok])
+        live = status != -9
+        assert np.array_equal(l2[live], lt[live])
+        for ev in range(nev):
+            for c in range(4):
+                upto = trig[ev, c] + 1 if status[ev, c] == 0 else (len(run.events[ev][c]) if status[ev, c] == -3 else 0)
+                assert np.array_equal(sig2[ev, c, :upto], sig[ev, c, :upto], equal_nan=True), (ev, c)
+        # the partial tables are not mistaken for full ones: a re-trigger after the first trigger sees every frame
+        ev, c = [int(v[0]) for v in np.nonzero(ok)]
+        again = ctx.trigger(ev, c, int(trig[ev, c]) + 1)
+        ctx.trigger_hist(0, nev)
+        st = np.ones((nev, 4), np.int32)
+        st[ev, c] = trig[ev, c] + 1
+        ctx.trigger_scan(0, nev, st)
+        t3, s3, l3, _ = ctx.trigger_results(0, nev, want_sig=False)
+        assert again[1] == s3[ev, c] and (again[1] != 0 or again[0] == t3[ev, c])
+
+
 @pytest.mark.parametrize("metric", ["entropy", "entropy_significance"])
 def test_trigger_entropy_variants(capi, small_run, small_trained, metric):
     """the two trigger quantities the reference keeps as commented alternatives (AnalyzerUnit.cpp:226-227,
