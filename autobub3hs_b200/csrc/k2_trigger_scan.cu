@@ -30,11 +30,21 @@ __device__ __forceinline__ double wrapsq(uint32_t c) { return (double)(int32_t)(
 __device__ double significance(const uint32_t* __restrict__ Hrow, WarpScratch* ws, int n, int lane,
                                int* first_over, int* max_adc) {
     int maxbin = 0;
+    uint32_t cus[8];
 #pragma unroll
     for (int q = 0; q < 8; q++) {
+        cus[q] = Hrow[q * 32 + lane];
+        if (cus[q]) maxbin = q * 32 + lane;
+    }
+    maxbin = __reduce_max_sync(0xffffffffu, maxbin);
+    // the running sum below stops at the last occupied bin of THIS frame (pix_rem reaches 0 there, :470/:493), so the
+    // z-scores of higher bins are never read: skip their fp64 divisions and square roots (typically 7 of the 8 groups)
+    const int qn = maxbin >> 5;
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+        if (q > qn) break;
         const int b = q * 32 + lane;
-        const uint32_t cu = Hrow[b];
-        if (cu) maxbin = b;
+        const uint32_t cu = cus[q];
         const double c = (double)(float)cu;                       // binEntry is float (:459)
         const double mean = __ddiv_rn(ws->s1[b], (double)n);      // CalcMean :514-521
         const double var = __dsub_rn(__ddiv_rn(ws->s2[b], (double)n), __dmul_rn(mean, mean));
@@ -44,7 +54,6 @@ __device__ double significance(const uint32_t* __restrict__ Hrow, WarpScratch* w
         const uint32_t m = __ballot_sync(0xffffffffu, use);
         if (lane == 0) ws->use[q] = m;
     }
-    maxbin = __reduce_max_sync(0xffffffffu, maxbin);
     __syncwarp();
     double sig = 0.0;
     int fo = -1;
