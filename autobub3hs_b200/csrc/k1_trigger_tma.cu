@@ -29,6 +29,8 @@
 //     (bin 0 is a scratch bin) and the true bin 0 is recovered as rows*cols - sum(other bins) by k1_fill_bin0_kernel.
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "abub_internal.cuh"
 
 namespace {
@@ -51,6 +53,8 @@ constexpr int T_B_OFF = ((T_R * T_BW + 127) / 128) * 128;         // frame j-d r
 constexpr int T_K_OFF = 2 * T_B_OFF;                              // K16 rows          (T_R x 544 B)
 constexpr int T_TX_BYTES = T_R * T_BW * 4;                        // bytes one stage receives
 constexpr int T_STAGE_BYTES = ((T_K_OFF + T_R * T_BW * 2 + 127) / 128) * 128;
+constexpr int T_HB_ENTRIES = 64;          // pending histogram entries per warp: < 32 left over + one row of 30 lanes
+constexpr int T_HB_BYTES = T_HB_ENTRIES * 8;
 constexpr int T_MAX_WARPS = 1;            // one warp per CTA: nothing to wait for at the end of a strip, and every
                                           // TMA operand (ring, barrier, coordinates) lives in uniform registers
 constexpr int T_TH_TARGET = 350;          // output rows per strip (4 halo rows per strip)
@@ -119,15 +123,14 @@ __global__ void __launch_bounds__(32 * T_MAX_WARPS, ABUB_K1T_MINCTA)
 k1_trigger_tma_kernel(const CUtensorMap* __restrict__ slot_maps, const CUtensorMap* __restrict__ k16_maps,
                       const int* __restrict__ nframes, const int* __restrict__ tss, uint32_t* __restrict__ hist,
                       int slot_first, int rows, int cols, int ncams, int max_frames, int th, int nxg, int j_first) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
+    extern __shared__ __align__(128) uint8_t smem_raw[];
     const int warp = (T_MAX_WARPS == 1) ? 0 : (int)(threadIdx.x >> 5), lane = threadIdx.x & 31;
     const int wpc = (T_MAX_WARPS == 1) ? 1 : (int)(blockDim.x >> 5);
-    // layout: [ring stages, 128-aligned][hist 256 u32][hit list 64 x 8 B per warp][mbarriers]
-    const uint32_t raw = smem_u32(smem_raw);
-    const uint32_t ring = (raw + 127u) & ~127u;
-    uint8_t* const ring_p = smem_raw + (ring - raw);
+    // layout: [ring stages, 128-aligned][hist 256 u32][pending entries T_HB_ENTRIES x 8 B + counter per warp][mbarriers]
+    const uint32_t ring = smem_u32(smem_raw);
+    uint8_t* const ring_p = smem_raw;
     uint32_t* const sh_hist = reinterpret_cast<uint32_t*>(ring_p + (size_t)wpc * T_S * T_STAGE_BYTES);
-    const uint32_t bars = ring + (uint32_t)wpc * T_S * T_STAGE_BYTES + 1024u + (uint32_t)wpc * 512u + (uint32_t)warp * T_S * 8u;
+    const uint32_t bars = ring + (uint32_t)wpc * T_S * T_STAGE_BYTES + 1024u + (uint32_t)wpc * T_HB_BYTES + (uint32_t)warp * T_S * 8u;
     const uint32_t my_ring = ring + (uint32_t)warp * T_S * T_STAGE_BYTES;
     const uint8_t* const my_ring_p = ring_p + (size_t)warp * T_S * T_STAGE_BYTES;
 
@@ -179,121 +182,105 @@ k1_trigger_tma_kernel(const CUtensorMap* __restrict__ slot_maps, const CUtensorM
 
         int stage = 0;
         uint32_t parity = 0;
-#ifndef ABUB_K1T_DIRECT_HIST
-        uint2* const hbuf = reinterpret_cast<uint2*>(sh_hist + 256) + (size_t)warp * 64;     // 64 entries per warp
-        int hcnt = 0;
+        // Non-zero outputs are rare (about 2.6 lanes of 32 per row on the benchmark's noise): a lane whose 8 packed outputs
+        // are not all zero appends them to a per-warp list (slot from a shared counter), and the list is histogrammed 32
+        // entries at a time -- all eight bytes of an entry are added, zeros included (bin 0 of the shared table is scratch,
+        // the true bin 0 is rows*cols - sum of the others): no branches or predicates in the byte-wise atomics.
+        uint2* const hbuf = reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(sh_hist + 256) + (size_t)warp * T_HB_BYTES);
+        int hcnt = 0;                                  // pending entries (warp-uniform)
         const uint32_t lt_mask = (1u << lane) - 1u;
-#endif
-#pragma unroll 1
-        for (int s = 0; s < nst; s++) {
-            mbar_wait(bars + stage * 8, parity);
-            const uint8_t* st = my_ring_p + stage * T_STAGE_BYTES;
-#pragma unroll
-            for (int r = 0; r < T_R; r++) {
-                const int rl = s * T_R + r;
-                {
-                    const uint2 a = *reinterpret_cast<const uint2*>(st + T_A_OFF + r * T_BW + 8 + lane * 8);
-                    const uint2 b = *reinterpret_cast<const uint2*>(st + T_B_OFF + r * T_BW + 8 + lane * 8);
-                    const uint4 k = *reinterpret_cast<const uint4*>(st + T_K_OFF + r * 2 * T_BW + 16 + lane * 16);
-                    const uint32_t nbx = ~b.x, nby = ~b.y;
-                    uint32_t w[8];
-                    {
-                        const uint32_t x0_ = __byte_perm(a.x, 0, 0x4140) + __byte_perm(nbx, 0, 0x4140);
-                        const uint32_t x1_ = __byte_perm(a.x, 0, 0x4342) + __byte_perm(nbx, 0, 0x4342);
-                        const uint32_t x2_ = __byte_perm(a.y, 0, 0x4140) + __byte_perm(nby, 0, 0x4140);
-                        const uint32_t x3_ = __byte_perm(a.y, 0, 0x4342) + __byte_perm(nby, 0, 0x4342);
-                        w[0] = relu_add_s16x2(x0_, k.x); w[4] = relu_add_s16x2(0x01FE01FEu - x0_, k.x);
-                        w[1] = relu_add_s16x2(x1_, k.y); w[5] = relu_add_s16x2(0x01FE01FEu - x1_, k.y);
-                        w[2] = relu_add_s16x2(x2_, k.z); w[6] = relu_add_s16x2(0x01FE01FEu - x2_, k.z);
-                        w[3] = relu_add_s16x2(x3_, k.w); w[7] = relu_add_s16x2(0x01FE01FEu - x3_, k.w);
-                    }
-                    uint32_t v[8];
-#pragma unroll
-                    for (int i = 0; i < 8; i++) {
-                        const uint32_t p = w[i] + X[i];
-                        const uint32_t q = p + P[i];
-                        const uint32_t rr = q + Q[i];
-                        v[i] = rr + Rr[i];
-                        X[i] = w[i]; P[i] = p; Q[i] = q; Rr[i] = rr;
-                    }
-                    // rows past nloc (tail of the last box) are computed and dropped: keeping the
-                    // state update unconditional lets the cascade registers rotate without moves
-                    if (rl >= 4 && rl < nloc) {
-                        uint32_t Wp[6], Wn[6];
-                        Wp[0] = __shfl_up_sync(0xffffffffu, v[3], 1);
-                        Wn[0] = __shfl_up_sync(0xffffffffu, v[7], 1);
-                        Wp[5] = __shfl_down_sync(0xffffffffu, v[0], 1);
-                        Wn[5] = __shfl_down_sync(0xffffffffu, v[4], 1);
-#pragma unroll
-                        for (int i = 0; i < 4; i++) { Wp[1 + i] = v[i]; Wn[1 + i] = v[4 + i]; }
-                        if (edge_warp) {
-                            // BORDER_REFLECT_101 in x: cols -2,-1 -> 2,1 ; cols, cols+1 -> cols-2, cols-3
-                            if (left_edge)  { Wp[0] = __byte_perm(v[0], v[1], 0x3254); Wn[0] = __byte_perm(v[4], v[5], 0x3254); }
-                            if (right_edge) { Wp[5] = __byte_perm(v[2], v[3], 0x3254); Wn[5] = __byte_perm(v[6], v[7], 0x3254); }
-                        }
-                        uint32_t Hp[4], Hn[4];
-                        k1t_hpass(Wp, Hp);
-                        k1t_hpass(Wn, Hn);
-                        const uint32_t z = ((Hp[0] | Hp[1] | Hp[2]) | (Hp[3] | Hn[0] | Hn[1]) | (Hn[2] | Hn[3])) & 0xFF00FF00u;
-#ifdef ABUB_K1T_DIRECT_HIST
-                        if (z != 0 && out_lane) {
-                            const uint32_t p03 = __byte_perm(Hp[0], Hp[1], 0x7531), n03 = __byte_perm(Hn[0], Hn[1], 0x7531);
-                            const uint32_t p47 = __byte_perm(Hp[2], Hp[3], 0x7531), n47 = __byte_perm(Hn[2], Hn[3], 0x7531);
-                            const uint32_t o03 = __vabsdiffu4(p03, n03), o47 = __vabsdiffu4(p47, n47);
-#pragma unroll
-                            for (int c = 0; c < 4; c++) {
-                                atomicAdd(&sh_hist[__byte_perm(o03, 0, 0x4440 + c)], 1u);
-                                atomicAdd(&sh_hist[__byte_perm(o47, 0, 0x4440 + c)], 1u);
-                            }
-                        }
-#else
-                        // Lanes whose 8 outputs may be non-zero (about 2.6 of 32 per row on the benchmark's noise) append
-                        // their packed outputs to a per-warp list in shared memory; the list is histogrammed 32 entries at
-                        // a time, so the eight byte-wise atomics are issued once per 32 hit lanes instead of once per row.
-                        const bool hit = (z != 0) && out_lane;
-                        const uint32_t hm = __ballot_sync(0xffffffffu, hit);
-                        if (hm) {
-                            // P = byte 1 / byte 3 of each word
-                            const uint32_t p03 = __byte_perm(Hp[0], Hp[1], 0x7531), n03 = __byte_perm(Hn[0], Hn[1], 0x7531);
-                            const uint32_t p47 = __byte_perm(Hp[2], Hp[3], 0x7531), n47 = __byte_perm(Hn[2], Hn[3], 0x7531);
-                            if (hit) hbuf[hcnt + __popc(hm & lt_mask)] = make_uint2(__vabsdiffu4(p03, n03), __vabsdiffu4(p47, n47));
-                            hcnt += __popc(hm);
-                            if (hcnt >= 32) {
-                                __syncwarp();
-                                const uint2 e = hbuf[lane];
-                                // all eight bytes go to the histogram, zeros included: bin 0 of the shared table is scratch
-                                // (the real bin 0 is rows*cols - sum of the others): no branches, no predicates
-#pragma unroll
-                                for (int c = 0; c < 4; c++) {
-                                    atomicAdd(&sh_hist[__byte_perm(e.x, 0, 0x4440 + c)], 1u);
-                                    atomicAdd(&sh_hist[__byte_perm(e.y, 0, 0x4440 + c)], 1u);
-                                }
-                                hcnt -= 32;
-                                const uint2 mv = hbuf[32 + lane];
-                                __syncwarp();
-                                if (lane < hcnt) hbuf[lane] = mv;
-                            }
-                        }
-#endif
-                    }
-                }
-            }
-            __syncwarp();
-            if (lane == 0 && s + T_S < nst)
-                k1t_issue(smap, kmap, my_ring + stage * T_STAGE_BYTES, bars + stage * 8, s + T_S, y0, xe, za, zb);
-            if (++stage == T_S) { stage = 0; parity ^= 1u; }
-        }
-#ifndef ABUB_K1T_DIRECT_HIST
-        __syncwarp();
-        {
-            const uint2 e = (lane < hcnt) ? hbuf[lane] : make_uint2(0u, 0u);
+        auto hist32 = [&](const uint2 e) {
 #pragma unroll
             for (int c = 0; c < 4; c++) {
                 atomicAdd(&sh_hist[__byte_perm(e.x, 0, 0x4440 + c)], 1u);
                 atomicAdd(&sh_hist[__byte_perm(e.y, 0, 0x4440 + c)], 1u);
             }
+        };
+        // 32 pending entries go to the histogram, the rest (< 32) moves to the front
+        auto drain = [&]() {
+            __syncwarp();
+            hist32(hbuf[lane]);
+            hcnt -= 32;
+            const uint2 mv = hbuf[32 + lane];
+            __syncwarp();
+            if (lane < hcnt) hbuf[lane] = mv;
+        };
+        // one ring stage = T_R image rows.  CHK = the stage may hold rows without an output (the first four rows of the
+        // strip only prime the cascade, rows past nloc are the tail of the last box): interior stages skip the tests.
+        auto do_stage = [&](auto chk, const int s, const uint8_t* const st) {
+            constexpr bool CHK = decltype(chk)::value;
+#pragma unroll
+            for (int r = 0; r < T_R; r++) {
+                const int rl = s * T_R + r;
+                const uint2 a = *reinterpret_cast<const uint2*>(st + T_A_OFF + r * T_BW + 8 + lane * 8);
+                const uint2 b = *reinterpret_cast<const uint2*>(st + T_B_OFF + r * T_BW + 8 + lane * 8);
+                const uint4 k = *reinterpret_cast<const uint4*>(st + T_K_OFF + r * 2 * T_BW + 16 + lane * 16);
+                uint32_t w[8];
+                {
+                    // s16x2 lanes a - b + 255 and b - a + 255 (both lanes >= 0: the 32-bit difference cannot borrow across)
+                    const uint32_t a0 = __byte_perm(a.x, 0, 0x4140), b0 = __byte_perm(b.x, 0, 0x4140);
+                    const uint32_t a1 = __byte_perm(a.x, 0, 0x4342), b1 = __byte_perm(b.x, 0, 0x4342);
+                    const uint32_t a2 = __byte_perm(a.y, 0, 0x4140), b2 = __byte_perm(b.y, 0, 0x4140);
+                    const uint32_t a3 = __byte_perm(a.y, 0, 0x4342), b3 = __byte_perm(b.y, 0, 0x4342);
+                    w[0] = relu_add_s16x2(a0 - b0 + 0x00FF00FFu, k.x); w[4] = relu_add_s16x2(b0 - a0 + 0x00FF00FFu, k.x);
+                    w[1] = relu_add_s16x2(a1 - b1 + 0x00FF00FFu, k.y); w[5] = relu_add_s16x2(b1 - a1 + 0x00FF00FFu, k.y);
+                    w[2] = relu_add_s16x2(a2 - b2 + 0x00FF00FFu, k.z); w[6] = relu_add_s16x2(b2 - a2 + 0x00FF00FFu, k.z);
+                    w[3] = relu_add_s16x2(a3 - b3 + 0x00FF00FFu, k.w); w[7] = relu_add_s16x2(b3 - a3 + 0x00FF00FFu, k.w);
+                }
+                uint32_t v[8];
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const uint32_t p = w[i] + X[i];
+                    const uint32_t q = p + P[i];
+                    const uint32_t rr = q + Q[i];
+                    v[i] = rr + Rr[i];
+                    X[i] = w[i]; P[i] = p; Q[i] = q; Rr[i] = rr;
+                }
+                // rows without an output are computed and dropped: keeping the state update unconditional lets the
+                // cascade registers rotate without moves
+                if (!CHK || (rl >= 4 && rl < nloc)) {
+                    uint32_t Wp[6], Wn[6];
+                    Wp[0] = __shfl_up_sync(0xffffffffu, v[3], 1);
+                    Wn[0] = __shfl_up_sync(0xffffffffu, v[7], 1);
+                    Wp[5] = __shfl_down_sync(0xffffffffu, v[0], 1);
+                    Wn[5] = __shfl_down_sync(0xffffffffu, v[4], 1);
+#pragma unroll
+                    for (int i = 0; i < 4; i++) { Wp[1 + i] = v[i]; Wn[1 + i] = v[4 + i]; }
+                    if (edge_warp) {
+                        // BORDER_REFLECT_101 in x: cols -2,-1 -> 2,1 ; cols, cols+1 -> cols-2, cols-3
+                        if (left_edge)  { Wp[0] = __byte_perm(v[0], v[1], 0x3254); Wn[0] = __byte_perm(v[4], v[5], 0x3254); }
+                        if (right_edge) { Wp[5] = __byte_perm(v[2], v[3], 0x3254); Wn[5] = __byte_perm(v[6], v[7], 0x3254); }
+                    }
+                    uint32_t Hp[4], Hn[4];
+                    k1t_hpass(Wp, Hp);
+                    k1t_hpass(Wn, Hn);
+                    // P = byte 1 / byte 3 of each word
+                    const uint32_t p03 = __byte_perm(Hp[0], Hp[1], 0x7531), n03 = __byte_perm(Hn[0], Hn[1], 0x7531);
+                    const uint32_t p47 = __byte_perm(Hp[2], Hp[3], 0x7531), n47 = __byte_perm(Hn[2], Hn[3], 0x7531);
+                    const uint32_t o03 = __vabsdiffu4(p03, n03), o47 = __vabsdiffu4(p47, n47);
+                    const bool hit = out_lane && (o03 | o47) != 0u;
+                    const uint32_t hm = __ballot_sync(0xffffffffu, hit);
+                    if (hm) {
+                        if (hit) hbuf[hcnt + __popc(hm & lt_mask)] = make_uint2(o03, o47);
+                        hcnt += __popc(hm);
+                        if (hcnt >= 32) drain();
+                    }
+                }
+            }
+        };
+#pragma unroll 1
+        for (int s = 0; s < nst; s++) {
+            mbar_wait(bars + stage * 8, parity);
+            const uint8_t* st = my_ring_p + stage * T_STAGE_BYTES;
+            if (s >= 1 && (s + 1) * T_R <= nloc) do_stage(std::false_type{}, s, st);
+            else do_stage(std::true_type{}, s, st);
+            __syncwarp();       // every lane is done with the stage
+            if (lane == 0 && s + T_S < nst)
+                k1t_issue(smap, kmap, my_ring + stage * T_STAGE_BYTES, bars + stage * 8, s + T_S, y0, xe, za, zb);
+            if (++stage == T_S) { stage = 0; parity ^= 1u; }
         }
-#endif
+        __syncwarp();
+        hist32((lane < hcnt) ? hbuf[lane] : make_uint2(0u, 0u));
     }
     __syncthreads();
     uint32_t* H = hist + (((size_t)slot * ncams + cam) * max_frames + j) * 256;
@@ -390,7 +377,7 @@ int abub_k1_launch_trigger_tma(abub_ctx* ctx, int slot_first, int nslots, int j_
     const int nmain = ctx->rows - 4;              // output rows [2, rows-2)
     const int nstrips = (nmain + T_TH_TARGET - 1) / T_TH_TARGET;
     const int th = (nmain + nstrips - 1) / nstrips;
-    const size_t smem = 128 + (size_t)wpc * T_S * T_STAGE_BYTES + 1024 + (size_t)wpc * 512 + (size_t)wpc * T_S * 8;
+    const size_t smem = (size_t)wpc * T_S * T_STAGE_BYTES + 1024 + (size_t)wpc * T_HB_BYTES + (size_t)wpc * T_S * 8;
     ABUB_CHECK_CUDA(ctx, cudaFuncSetAttribute(k1_trigger_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const CUtensorMap* maps = reinterpret_cast<const CUtensorMap*>(ctx->d_tmaps);
     const int per = 65535 / ctx->ncams;
