@@ -35,7 +35,7 @@ sys.path.insert(0, ROOT)
 ROWS, COLS, NCAMS, NFRAMES = 1050, 1680, 4, 40
 NPIX = ROWS * COLS
 K1_BYTES_PER_EVENT_CAM = (NFRAMES + 1) * NPIX          # every frame once + the sigma plane once
-K1_DRAM_TRAFFIC_125 = 39.514520e9 + 8.572e6             # bytes per 125-event launch, measured (profiles/)
+K1_DRAM_TRAFFIC_125 = 37.733456e9 + 8.645e6             # bytes per 125-event launch, measured (profiles/r1_k1_v6_125ev_full.txt)
 WORKLOAD = "trigger-only: 1000 events x 4 cams x 40 frames, 1050x1680 u8 (BASELINE.json configs[1])"
 
 
@@ -434,7 +434,7 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": args.steps * 4,      # k1_trigger_tma + k1_trigger (border rows) + k1_fill_bin0 + k2_trigger_scan
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": K1_DRAM_TRAFFIC_125 if B == 125 else None,
-                     "traffic_source": "profiles/r1_final_k1_tma_full.txt (ncu --set full, dram read+write of one 125-event launch)",
+                     "traffic_source": "profiles/r1_k1_v6_125ev_full.txt (ncu --set full, dram read+write of one 125-event launch)",
                      "kernel": "k1_trigger_tma_kernel (+ k1_trigger_kernel on the 4 border rows, k1_fill_bin0_kernel)",
                      "ms_per_launch": k1_ms,
                      "algorithmic_bytes_per_launch": k1_bytes,
