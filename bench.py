@@ -384,6 +384,23 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
     e2e_value = world * Be * e2e_steps / (e2e_ms * 1e-3)
+    # what the link does on one large pinned copy (context for e2e, which is bound by it)
+    link_gbs = None
+    try:
+        pin0 = torch.from_numpy(ctx.pinned(0))
+        dst0 = slot_tensor(torch, ctx, 0)
+        lk0 = torch.cuda.Event(enable_timing=True)
+        lk1 = torch.cuda.Event(enable_timing=True)
+        cur = torch.cuda.current_stream()
+        dst0.copy_(pin0, non_blocking=True)
+        lk0.record(cur)
+        for _ in range(4):
+            dst0.copy_(pin0, non_blocking=True)
+        lk1.record(cur)
+        torch.cuda.synchronize()
+        link_gbs = 4 * pin0.numel() / (lk0.elapsed_time(lk1) * 1e-3) / 1e9
+    except Exception:
+        pass
     assert np.array_equal(host_res[1], status[:Be]) and np.array_equal(host_res[0], trig[:Be])
 
     if rank != 0:
@@ -427,6 +444,8 @@ def run_ours(args, rank, world, local_rank):
         "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": sent_total[0] * NPIX // e2e_steps,
                 "d2h_bytes_per_step": Be * NCAMS * 16 * (1 if args.e2e_mode == "full" else (NFRAMES + args.e2e_chunk - 1) // args.e2e_chunk),
                 "events_per_step": Be, "steps": e2e_steps, "mode": args.e2e_mode, "rank0_numa_node": numa_node,
+                "h2d_gbs": sent_total[0] * NPIX / e2e_steps / (e2e_ms / e2e_steps * 1e-3) / 1e9 * 1.0,
+                "h2d_link_gbs_one_large_pinned_copy": link_gbs,
                 "note": ("abub_trigger_stream: host frames in pinned memory, sent %d frames at a time, a camera stops "
                          "receiving frames once its trigger search is decided (the reference's early exit); "
                          "frames_sent/frames_total = %.3f" % (args.e2e_chunk, sent_total[0] / max(1, e2e_steps * Be * NCAMS * NFRAMES)))
