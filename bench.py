@@ -425,6 +425,27 @@ def run_ours(args, rank, world, local_rank):
                          f"one process per (event,camera), early exit at trigger kept; parity mismatches vs GPU: {mism}"}
         if mism:
             raise SystemExit(f"PARITY FAILURE: {mism} (event,camera) results differ from the oracle")
+        # the cv2-free C restatement (oracle/abub_ref.c), one thread: ProcessFrame + calcHist of a few frame pairs of
+        # the same sample, checked against the GPU's histograms of those pairs
+        try:
+            from oracle import cref
+            ctx.trigger_hist(0, 1)               # the streamed / early-exit passes above leave partial tables
+            H_gpu = ctx.trigger_hist_read(0, 0)
+            fr = sample[0][0]
+            n_pairs = 4
+            t0 = time.perf_counter()
+            hs = [cref.hist256(cref.process_frame(fr[j], fr[j - 2], sig_np[0])) for j in range(2, 2 + n_pairs)]
+            dt_c = (time.perf_counter() - t0) / n_pairs
+            bad = sum(0 if np.array_equal(h, H_gpu[2 + i]) else 1 for i, h in enumerate(hs))
+            if bad:
+                raise SystemExit(f"PARITY FAILURE: {bad} histograms differ from the C restatement")
+            cpu["c_port_one_thread"] = {"ms_per_frame_pair": dt_c * 1e3,
+                                        "events_per_s_without_early_exit": 1.0 / (dt_c * NCAMS * (NFRAMES - 1)),
+                                        "sample": f"{n_pairs} frame pairs of event 0, camera 0; histograms equal to the GPU's"}
+        except SystemExit:
+            raise
+        except Exception as e:
+            cpu["c_port_one_thread"] = {"unavailable": repr(e)[:120]}
 
     peaks = {}
     try:
