@@ -20,7 +20,7 @@ ABUB_MAX_TRACK = 10
 EXPORTS = [
     "abub_ctx_create", "abub_ctx_destroy", "abub_last_error", "abub_sync", "abub_stream",
     "abub_set_background", "abub_set_background_from_training",
-    "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_submit_cam", "abub_event_upload_frame", "abub_set_trigger_metric", "abub_event_decode_png", "abub_event_device_ptr",
+    "abub_pinned_acquire", "abub_event_submit", "abub_event_upload", "abub_event_submit_cam", "abub_event_upload_frame", "abub_set_trigger_metric", "abub_event_decode_png", "abub_event_flip_rows", "abub_event_device_ptr",
     "abub_event_set_nframes",
     "abub_trigger_hist", "abub_trigger_hist_read", "abub_trigger_hist_write", "abub_trigger_scan", "abub_trigger_results", "abub_trigger", "abub_trigger_stream", "abub_trigger_early",
     "abub_train_begin", "abub_train_add_event", "abub_train_add_slot", "abub_train_add_slots",
@@ -100,6 +100,7 @@ def load() -> C.CDLL:
     lib.abub_event_upload_frame.argtypes = [vp, C.c_int, C.c_int, C.c_int]
     lib.abub_set_trigger_metric.argtypes = [vp, C.c_int, C.c_float]
     lib.abub_event_decode_png.argtypes = [vp, C.POINTER(PngJob), C.c_int, ip]
+    lib.abub_event_flip_rows.argtypes = [vp, vp, C.c_int]
     lib.abub_train_add_slots.argtypes = [vp, C.c_int, ip, C.c_int, C.POINTER(C.c_float), ip]
     lib.abub_train_add_events.argtypes = [vp, C.c_int, u8p, C.c_int, C.POINTER(C.c_float), ip]
     lib.abub_selftest_fdiv.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
@@ -433,6 +434,12 @@ class Context:
         ok = (C.c_int * n)()
         self._ck(self.lib.abub_event_decode_png(self.h, arr, n, ok), "abub_event_decode_png")
         return np.array([ok[i] for i in range(n)], dtype=bool)
+
+    def event_flip_rows(self, refs) -> None:
+        """refs: (slot, cam, frame) of resident frames whose rows are stored bottom-up (BMP pixel arrays read as
+        they lie in the file); turned over in place on the device."""
+        a = np.ascontiguousarray(np.asarray(refs, dtype=np.int32).reshape(-1, 3))
+        self._ck(self.lib.abub_event_flip_rows(self.h, _p(a), len(a)), "abub_event_flip_rows")
 
     # ---- bellows veto ----
     def set_bellows_template(self, cam: int, templ: Optional[np.ndarray]) -> None:

@@ -165,7 +165,7 @@ void AbubDevice::LoadCamera(int slot, int cam, Parser* parser, const std::string
 void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const std::vector<std::string>& events) {
     auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t0 = now();
-    struct Item { int slot, cam, frame; const std::string* event; std::string name; char state; uint32_t zlen; };   // state: 0 bad, 1 host-decoded, 2 device job
+    struct Item { int slot, cam, frame; const std::string* event; std::string name; char state; uint32_t zlen; };   // state: 0 bad, 1 host-decoded, 2 device PNG job, 3 BMP pixel array read as stored (rows to be turned over on the device)
     std::vector<Item> items;
     std::vector<std::vector<int>> ncam(slots.size(), std::vector<int>(ncams_, -1));      // frames per (event, cam); -1 = not staged here
     for (size_t e = 0; e < events.size(); e++)
@@ -197,6 +197,10 @@ void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const
     }
     const double t1 = now();
     const bool device_png = (npix % 4 == 0) && !getenv("ABUB_PNG_ON_HOST");
+    // 8-bit BMP frames (what the DAQ writes in raw mode): the pixel array goes from the file into the pinned region with
+    // one positional read and the bottom-up row order is undone on the device after the upload
+    const bool device_flip = (cols_ % 4 == 0) && !getenv("ABUB_BMP_ON_HOST");
+    std::vector<abub_frame_ref> flips;
     // One event at a time: its frames are read and decoded on all cores, then the cameras that hold host-decoded frames go
     // up asynchronously while the next event is being decoded (their device-decoded frames carry compressed bytes for the
     // moment).  PNG streams are collected for one decode call over the whole batch (the inflate kernel wants many frames).
@@ -212,6 +216,10 @@ void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const
         for (long i = (long)i0; i < (long)i1; i++) {
             Item& it = items[i];
             uint8_t* region = pin[it.slot] + ((size_t)it.cam * max_frames_ + it.frame) * npix;
+            if (device_flip) {
+                bool bottom_up = false;
+                if (parser->ReadGray8BmpPixels(*it.event, it.name, rows_, cols_, region, &bottom_up)) { it.state = bottom_up ? 3 : 1; continue; }
+            }
             static thread_local std::vector<uint8_t> enc;          // reused: no fresh 1.8 MB mapping per frame
             if (parser->GetImageBytes(*it.event, it.name, enc) == parser->FailureCode() || enc.empty()) { memset(region, 0, npix); continue; }
             if (device_png) {
@@ -229,6 +237,10 @@ void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const
         }
         for (int cam = 0; cam < ncams_; cam++)
             if (ncam[e][cam] >= 0 && host_cam[cam]) Check(abub_event_submit_cam(ctx_, slots[e], cam, ncam[e][cam]), "abub_event_submit_cam");
+        flips.clear();
+        for (size_t i = i0; i < i1; i++)
+            if (items[i].state == 3) flips.push_back(abub_frame_ref{items[i].slot, items[i].cam, items[i].frame});
+        if (!flips.empty()) Check(abub_event_flip_rows(ctx_, flips.data(), (int)flips.size()), "abub_event_flip_rows");   // after the uploads, same stream
         t_dec += tb - ta;
         t_up += now() - tb;
         i0 = i1;

@@ -34,6 +34,16 @@ public:
     // the pinned staging buffer of a device slot (abub_pinned_acquire).  Same return convention as
     // GetImage of the concrete class.
     virtual int GetImageBytes(std::string EventID, std::string FrameName, std::vector<uint8_t>& Bytes) = 0;
+    // Not in the reference: fast path for the DAQ's raw frames.  When the frame is an uncompressed 8-bit BMP of exactly
+    // rows x cols with the identity grey palette (and cols % 4 == 0, so that the file's row pitch is cols), its pixel
+    // array is read with one positional read into dst (rows*cols bytes, e.g. the pinned staging region) in FILE order and
+    // *bottom_up says whether the rows still have to be turned over (abub_event_flip_rows does that on the device).
+    // false = not such a file / not supported by this parser: use GetImageBytes + decode.
+    virtual bool ReadGray8BmpPixels(const std::string& EventID, const std::string& FrameName, int rows, int cols, uint8_t* dst,
+                                    bool* bottom_up) {
+        (void)EventID; (void)FrameName; (void)rows; (void)cols; (void)dst; (void)bottom_up;
+        return false;
+    }
     // value GetImage returns for "could not produce this frame"
     virtual int FailureCode() const = 0;
 };

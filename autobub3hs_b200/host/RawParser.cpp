@@ -1,6 +1,9 @@
 // RawParser (reference: ParseFolder/RawParser.cpp:28-157) on std::filesystem / std::regex instead of Boost.
 #include "RawParser.hpp"
 
+#include <fcntl.h>
+#include <unistd.h>
+
 #include <algorithm>
 #include <filesystem>
 #include <regex>
@@ -33,6 +36,41 @@ std::string RawParser::FramePath(const std::string& EventID, const std::string& 
 
 int RawParser::GetImageBytes(std::string EventID, std::string FrameName, std::vector<uint8_t>& Bytes) {
     return abubcodec::read_file(FramePath(EventID, FrameName), Bytes) ? 1 : 0;
+}
+
+// One open, one 1078-byte read (file header, info header, palette) and one positional read of the pixel array straight
+// into the caller's buffer: no intermediate copy of the file and no row copies.
+bool RawParser::ReadGray8BmpPixels(const std::string& EventID, const std::string& FrameName, int rows, int cols, uint8_t* dst,
+                                   bool* bottom_up) {
+    if ((cols & 3) != 0) return false;
+    const int fd = ::open(FramePath(EventID, FrameName).c_str(), O_RDONLY | O_CLOEXEC);
+    if (fd < 0) return false;
+    uint8_t h[14 + 40 + 1024];
+    bool ok = ::pread(fd, h, sizeof(h), 0) == (ssize_t)sizeof(h) && h[0] == 'B' && h[1] == 'M';
+    auto rd32 = [&h](int o) { return (uint32_t)h[o] | ((uint32_t)h[o + 1] << 8) | ((uint32_t)h[o + 2] << 16) | ((uint32_t)h[o + 3] << 24); };
+    uint32_t off = 0;
+    if (ok) {
+        off = rd32(10);
+        const int32_t hh = (int32_t)rd32(22);
+        const uint32_t pal_n = rd32(46);
+        ok = rd32(14) == 40 && (int32_t)rd32(18) == cols && (hh == rows || hh == -rows) && (h[28] | (h[29] << 8)) == 8 &&
+             rd32(30) == 0 && (pal_n == 0 || pal_n == 256) && off >= sizeof(h);
+        *bottom_up = hh > 0;
+        // identity grey palette: entry i = (i, i, i, x)
+        for (int i = 0; ok && i < 256; i++) ok = h[54 + 4 * i] == i && h[55 + 4 * i] == i && h[56 + 4 * i] == i;
+    }
+    if (ok) {
+        const size_t n = (size_t)rows * cols;
+        size_t got = 0;
+        while (got < n) {
+            const ssize_t r = ::pread(fd, dst + got, n - got, (off_t)off + (off_t)got);
+            if (r <= 0) break;
+            got += (size_t)r;
+        }
+        ok = got == n;
+    }
+    ::close(fd);
+    return ok;
 }
 
 // RawParser.cpp:34-47: cv::imread(path, 0); returns !Image.empty()

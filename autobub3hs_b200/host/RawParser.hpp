@@ -15,6 +15,8 @@ public:
     void GetEventDirLists(std::vector<std::string>& EventList) override;
     void GetFileLists(const char* EventFolder, std::vector<std::string>& FileList, const char* camera_out_name) override;
     void ParseAndSortFramesInFolder(std::string EventID, int Camera, std::vector<std::string>& Contents) override;
+    bool ReadGray8BmpPixels(const std::string& EventID, const std::string& FrameName, int rows, int cols, uint8_t* dst,
+                            bool* bottom_up) override;
 
 private:
     std::string FramePath(const std::string& EventID, const std::string& FrameName) const;

@@ -205,6 +205,16 @@ typedef struct abub_png_job {
 } abub_png_job;
 int abub_event_decode_png(abub_ctx* ctx, const abub_png_job* jobs, int n, int* ok);
 
+/* 8-bit BMP frames keep their rows bottom-up in the file.  The caller reads the pixel array of such a file straight
+ * into the frame's pinned region (one positional read, no row copies on the host; what cv::imread does for these
+ * files behind Parser::GetImage, RawParser.cpp:34-47, is a row-by-row copy), sends it with the usual upload calls and
+ * then has the rows of those frames turned over in place in HBM.  Async on the ctx stream: enqueue it after the
+ * uploads of the frames it names.  Requires cols % 4 == 0 (the BMP row pitch equals cols then). */
+typedef struct abub_frame_ref {
+    int32_t slot, cam, frame;
+} abub_frame_ref;
+int abub_event_flip_rows(abub_ctx* ctx, const abub_frame_ref* frames, int n);
+
 /* ---- bellows veto: L3Localizer.cpp:292-390 (taken when every genesis contour lies in the bellows mask) ---- */
 /* The camera's cam<c>_bellows_template.png as rows*cols grey bytes (L3Localizer.cpp:294-295); NULL clears it
  * ("template not loadable", :297-301). */

@@ -128,3 +128,24 @@ def test_full_size_frames_and_corrupt_stream(capi):
         if not okv[1]:
             assert not dev[1].any()            # undecodable frames are zero-filled
         assert not dev[2].any()
+
+
+@pytest.mark.parametrize("shape", [(7, 12), (70, 136), (1050, 1680)])
+def test_bmp_pixel_arrays_turned_over_on_device(capi, shape):
+    """abub_event_flip_rows: frames uploaded in BMP file order (bottom-up) come out as cv::imread returns them; frames
+    not named keep their rows (odd and even row counts, the full-size frame)."""
+    rows, cols = shape
+    rng = np.random.default_rng(rows + cols)
+    fr = rng.integers(0, 256, (2, 5, rows, cols)).astype(np.uint8)
+    with capi.Context(rows, cols, 2, 5, max_slots=2) as ctx:
+        flipped = [(1, 0, 0), (1, 1, 3), (1, 1, 4), (0, 0, 2)]
+        for slot in range(2):
+            for c in range(2):
+                up = fr[c].copy()
+                for (s_, c_, f_) in flipped:
+                    if s_ == slot and c_ == c:
+                        up[f_] = fr[c, f_, ::-1]
+                ctx.event_upload(slot, c, up)
+        ctx.event_flip_rows(flipped)
+        for slot in range(2):
+            assert np.array_equal(ctx.download_frames(slot), fr), slot
