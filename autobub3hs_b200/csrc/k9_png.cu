@@ -485,10 +485,13 @@ extern "C" int abub_event_decode_png(abub_ctx* ctx, const abub_png_job* jobs, in
 
 // ---- bottom-up BMP pixel arrays: rows turned over in place ---------------------------------------------------------
 namespace {
+constexpr int FLIP_REFS = 256;                     // frame references per launch: they travel as a kernel argument (3 KB),
+struct FlipRefs { abub_frame_ref r[FLIP_REFS]; };  // so the call needs no device buffer, no copy and no synchronisation
+
 // grid: x = chunks of a frame's upper half, y = frame.  One thread swaps 4 bytes of row r with 4 bytes of row rows-1-r.
-__global__ void __launch_bounds__(256) k9_flip_rows_kernel(uint8_t* const* __restrict__ slot_ptrs, const abub_frame_ref* __restrict__ refs,
-                                                           int rows, int cols, int ncams, int max_frames) {
-    const abub_frame_ref f = refs[blockIdx.y];
+__global__ void __launch_bounds__(256) k9_flip_rows_kernel(uint8_t* const* __restrict__ slot_ptrs, const __grid_constant__ FlipRefs refs,
+                                                           int rows, int cols, int max_frames) {
+    const abub_frame_ref f = refs.r[blockIdx.y];
     uint32_t* const img = reinterpret_cast<uint32_t*>(slot_ptrs[f.slot] + ((size_t)f.cam * max_frames + f.frame) * ((size_t)rows * cols));
     const int wpr = cols >> 2;                                   // words per row
     const int half = rows >> 1;
@@ -507,21 +510,16 @@ extern "C" int abub_event_flip_rows(abub_ctx* ctx, const abub_frame_ref* frames,
     if (!ctx) return ABUB_E_INVALID;
     ABUB_REQUIRE(ctx, n >= 0 && (frames || n == 0), "abub_event_flip_rows");
     ABUB_REQUIRE(ctx, (ctx->cols & 3) == 0, "abub_event_flip_rows needs cols % 4 == 0");
-    if (n == 0) return ABUB_OK;
     for (int i = 0; i < n; i++)
         ABUB_REQUIRE(ctx, frames[i].slot >= 0 && frames[i].slot < ctx->max_slots && frames[i].cam >= 0 && frames[i].cam < ctx->ncams &&
                               frames[i].frame >= 0 && frames[i].frame < ctx->max_frames, "frame reference out of range");
     cudaSetDevice(ctx->device);
-    abub_frame_ref* d_refs = nullptr;
-    ABUB_CHECK_CUDA(ctx, cudaMallocAsync(&d_refs, (size_t)n * sizeof(abub_frame_ref), ctx->stream));
-    // pageable source: the copy is staged before the call returns
-    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(d_refs, frames, (size_t)n * sizeof(abub_frame_ref), cudaMemcpyHostToDevice, ctx->stream));
-    for (int i0 = 0; i0 < n; i0 += 65535) {
-        const int cnt = n - i0 < 65535 ? n - i0 : 65535;
-        k9_flip_rows_kernel<<<dim3(32, cnt), 256, 0, ctx->stream>>>(ctx->d_slot_ptrs, d_refs + i0, ctx->rows, ctx->cols, ctx->ncams,
-                                                                    ctx->max_frames);
+    FlipRefs refs;
+    for (int i0 = 0; i0 < n; i0 += FLIP_REFS) {
+        const int cnt = n - i0 < FLIP_REFS ? n - i0 : FLIP_REFS;
+        memcpy(refs.r, frames + i0, (size_t)cnt * sizeof(abub_frame_ref));
+        k9_flip_rows_kernel<<<dim3(32, cnt), 256, 0, ctx->stream>>>(ctx->d_slot_ptrs, refs, ctx->rows, ctx->cols, ctx->max_frames);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
-    ABUB_CHECK_CUDA(ctx, cudaFreeAsync(d_refs, ctx->stream));
     return ABUB_OK;
 }

@@ -50,9 +50,7 @@ ZipParser::~ZipParser() {
 
 ZipParser* ZipParser::clone() {
     ZipParser* other = new ZipParser(RunFolder, ImageFolder, ImageFormat);
-    other->FileContents = FileContents;
-    other->ImageNames = ImageNames;
-    other->ImageLocs = ImageLocs;
+    if (!idx->FileContents.empty()) other->idx = idx;        // built: shared, read-only from here on
     return other;
 }
 
@@ -106,10 +104,10 @@ void ZipParser::BuildFileList() {
             }
             x += 4 + sz;
         }
-        FileContents.push_back(name);
+        idx->FileContents.push_back(name);
         if (std::regex_match(name, m, re)) {
-            ImageNames[m[1].str()][m[2].str()] = name;
-            ImageLocs[m[1].str()][m[2].str()] = loc;
+            idx->ImageNames[m[1].str()][m[2].str()] = name;
+            idx->ImageLocs[m[1].str()][m[2].str()] = loc;
         }
         p += 46 + nlen + xlen + clen;
     }
@@ -135,9 +133,9 @@ bool ZipParser::ReadEntry(const ZipEntryLoc& loc, std::vector<uint8_t>& out) {
 }
 
 int ZipParser::GetImageBytes(std::string EventID, std::string FrameName, std::vector<uint8_t>& Bytes) {
-    if (FileContents.size() == 0) BuildFileList();
-    auto ev = ImageLocs.find(EventID);
-    if (ev == ImageLocs.end()) return -1;
+    if (idx->FileContents.size() == 0) BuildFileList();
+    auto ev = idx->ImageLocs.find(EventID);
+    if (ev == idx->ImageLocs.end()) return -1;
     auto fr = ev->second.find(FrameName);
     if (fr == ev->second.end()) return -1;
     return ReadEntry(fr->second, Bytes) ? 1 : -1;
@@ -159,19 +157,19 @@ void ZipParser::GetFileLists(const char*, std::vector<std::string>&, const char*
 
 // ZipParser.cpp:248-283: directory entries "^.*/(\d+)/$"
 void ZipParser::GetEventDirLists(std::vector<std::string>& EventList) {
-    if (FileContents.size() == 0) BuildFileList();
+    if (idx->FileContents.size() == 0) BuildFileList();
     const std::regex expression("^.*/(\\d+)/$");
     std::smatch what;
-    for (const std::string& name : FileContents)
+    for (const std::string& name : idx->FileContents)
         if (std::regex_match(name, what, expression)) EventList.push_back(what[1].str());
 }
 
 // ZipParser.cpp:286-315
 void ZipParser::ParseAndSortFramesInFolder(std::string EventID, int camera, std::vector<std::string>& Contents) {
-    if (FileContents.size() == 0) BuildFileList();
+    if (idx->FileContents.size() == 0) BuildFileList();
     const std::regex re("cam" + std::to_string(camera) + ".*image.*(png|bmp)");
-    auto ev = ImageNames.find(EventID);
-    if (ev != ImageNames.end())
+    auto ev = idx->ImageNames.find(EventID);
+    if (ev != idx->ImageNames.end())
         for (const auto& entry : ev->second)
             if (std::regex_match(entry.first, re)) Contents.push_back(entry.first);
     std::sort(Contents.begin(), Contents.end());

@@ -8,6 +8,7 @@
 #include <stdio.h>
 
 #include <map>
+#include <memory>
 
 #include "Parser.hpp"
 
@@ -32,10 +33,16 @@ private:
     void BuildFileList();
     bool ReadEntry(const ZipEntryLoc& loc, std::vector<uint8_t>& out);
 
+    // The central-directory index is immutable once built and shared by the clones made after that (the reference
+    // copies the lists into every clone, ZipParser.cpp: one copy per analyzer, i.e. per event and camera -- with 1.6 M
+    // entries in a 10,000-event archive that copy alone would dominate the host side).
+    struct Index {
+        std::vector<std::string> FileContents;                                  // every entry name
+        std::map<std::string, std::map<std::string, std::string>> ImageNames;   // [event][frame] -> entry name
+        std::map<std::string, std::map<std::string, ZipEntryLoc>> ImageLocs;    // [event][frame] -> location
+    };
     FILE* fp = nullptr;
-    std::vector<std::string> FileContents;                                  // every entry name
-    std::map<std::string, std::map<std::string, std::string>> ImageNames;   // [event][frame] -> entry name
-    std::map<std::string, std::map<std::string, ZipEntryLoc>> ImageLocs;    // [event][frame] -> location
+    std::shared_ptr<Index> idx = std::make_shared<Index>();
 };
 
 #endif
