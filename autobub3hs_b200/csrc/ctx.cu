@@ -147,9 +147,18 @@ extern "C" int abub_set_background_from_training(abub_ctx* ctx, int cam) {
 // ---- event frames -----------------------------------------------------------------
 static size_t slot_bytes(const abub_ctx* ctx) { return (size_t)ctx->ncams * ctx->max_frames * ctx->npix; }
 
+// The frame counts travel as a kernel argument: a cudaMemcpyAsync from pageable memory may wait for the stream, and this
+// call sits between the large uploads of the staging loop.
+struct NframesArg { int n[ABUB_MAX_CAMS]; };
+__global__ void set_nframes_kernel(int* __restrict__ dst, const NframesArg a, int ncams) {
+    if ((int)threadIdx.x < ncams) dst[threadIdx.x] = a.n[threadIdx.x];
+}
+
 static int push_nframes(abub_ctx* ctx, int slot) {
-    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_nframes + (size_t)slot * ctx->ncams, ctx->slots[slot].nframes,
-                                         ctx->ncams * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    NframesArg a;
+    for (int c = 0; c < ABUB_MAX_CAMS; c++) a.n[c] = ctx->slots[slot].nframes[c];
+    set_nframes_kernel<<<1, 32, 0, ctx->stream>>>(ctx->d_nframes + (size_t)slot * ctx->ncams, a, ctx->ncams);
+    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     ctx->slots[slot].hist_valid = false;
     return ABUB_OK;
 }
