@@ -412,14 +412,17 @@ extern "C" int abub_trigger_stream(abub_ctx* ctx, int slot_first, int nslots, co
         ABUB_CHECK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->ev_stream, 0));
     }
     // read-backs must be asynchronous for the two groups to overlap: pinned result table
-    if (ctx->h_raw_cap < n * 4) {
+    if (ctx->h_raw_cap < n * 5) {
         if (ctx->h_raw) cudaFreeHost(ctx->h_raw);
         ctx->h_raw = nullptr;
         ctx->h_raw_cap = 0;
-        ABUB_CHECK_CUDA(ctx, cudaHostAlloc((void**)&ctx->h_raw, n * 4 * sizeof(int), cudaHostAllocDefault));
-        ctx->h_raw_cap = n * 4;
+        ABUB_CHECK_CUDA(ctx, cudaHostAlloc((void**)&ctx->h_raw, n * 5 * sizeof(int), cudaHostAllocDefault));
+        ctx->h_raw_cap = n * 5;
     }
     int* const raw = ctx->h_raw;
+    // the per-camera frame limits go up from pinned memory too: a copy from pageable memory would make the host wait
+    // for the frames it has just queued on that stream
+    int* const avail_pin = ctx->h_raw + n * 4;
     bool pending[2] = {false, false};                             // results of the group's last chunk not read yet
     bool active[2] = {true, ngroups == 2};
     cudaStream_t const main_stream = ctx->stream;
@@ -460,7 +463,8 @@ extern "C" int abub_trigger_stream(abub_ctx* ctx, int slot_first, int nslots, co
             }
             if (!any) { active[g] = false; continue; }
             const size_t o = (size_t)gfirst[g] * nc, cnt = (size_t)gcount[g] * nc;
-            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(d_av + o, avail.data() + o, cnt * sizeof(int), cudaMemcpyHostToDevice, st_g));
+            memcpy(avail_pin + o, avail.data() + o, cnt * sizeof(int));     // the group's previous copy was harvested above
+            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(d_av + o, avail_pin + o, cnt * sizeof(int), cudaMemcpyHostToDevice, st_g));
             ctx->stream = st_g;                                   // the launchers enqueue on ctx->stream
             rc = abub_k1_launch_trigger_range(ctx, slot_first + gfirst[g], gcount[g], lo, hi, ctx->d_avail, false);
             if (!rc) rc = abub_k2_launch_avail(ctx, slot_first + gfirst[g], gcount[g], ctx->d_avail);
