@@ -235,12 +235,16 @@ void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const
             if (items[i].state == 2) { jobs.push_back(abub_png_job{items[i].slot, items[i].cam, items[i].frame, items[i].zlen}); job_item.push_back(i); }
             else host_cam[items[i].cam] = true;
         }
+        const double ts0 = now();
         for (int cam = 0; cam < ncams_; cam++)
             if (ncam[e][cam] >= 0 && host_cam[cam]) Check(abub_event_submit_cam(ctx_, slots[e], cam, ncam[e][cam]), "abub_event_submit_cam");
+        const double ts1 = now();
+        t_submit += ts1 - ts0;
         flips.clear();
         for (size_t i = i0; i < i1; i++)
             if (items[i].state == 3) flips.push_back(abub_frame_ref{items[i].slot, items[i].cam, items[i].frame});
         if (!flips.empty()) Check(abub_event_flip_rows(ctx_, flips.data(), (int)flips.size()), "abub_event_flip_rows");   // after the uploads, same stream
+        t_flip += now() - ts1;
         t_dec += tb - ta;
         t_up += now() - tb;
         i0 = i1;
@@ -281,7 +285,7 @@ void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const
     }
     const double t3 = now();
     t_read += t1 - t0; t_decode += t2 - t1; t_upload += t3 - t2;
-    (void)t_up;
+    t_tail += (t3 - t2) - t_up;
 }
 
 std::vector<int> AbubDevice::PrefetchEvents(Parser* parser, const std::vector<std::string>& keys, const std::vector<std::string>& events,

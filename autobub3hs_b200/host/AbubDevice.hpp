@@ -96,6 +96,7 @@ public:
 
     // wall-clock seconds spent in the ingest stages (printed by abub3hs when ABUB_TIMING is set)
     double t_read = 0, t_decode = 0, t_upload = 0, t_hist = 0, t_scan = 0, t_loc = 0;
+    double t_submit = 0, t_flip = 0, t_tail = 0;     // parts of t_upload: upload calls, row-flip calls, end of StageBatch
 
 private:
     AbubDevice() {}

@@ -335,6 +335,7 @@ int main(int argc, char** argv) {
         AbubDevice& d = AbubDevice::Get();
         fprintf(stderr, "ABUB_TIMING train %.3f s | detect: stage %.3f s (setup %.3f read+decode %.3f upload %.3f K1 %.3f K2 %.3f localizer %.3f) analyze %.3f s write %.3f s\n",
                 T_train1 - T_train0, T_stage, d.t_read, d.t_decode, d.t_upload, d.t_hist, d.t_scan, d.t_loc, T_analyze, T_write);
+        fprintf(stderr, "ABUB_UPLOAD upload = submit calls %.3f + flip calls %.3f + end of staging %.3f s\n", d.t_submit, d.t_flip, d.t_tail);
         fprintf(stderr, "ABUB_DECODE frames decoded on the device %ld, on the host %ld\n", d.n_gpu_decoded, d.n_cpu_decoded);
     }
 

@@ -56,6 +56,7 @@ def main():
             best = dt if best is None else min(best, dt)
         timing = [l for l in r.stderr.splitlines() if l.startswith("ABUB_TIMING")]
         decoded = [l for l in r.stderr.splitlines() if l.startswith("ABUB_DECODE")]
+        upload = [l for l in r.stderr.splitlines() if l.startswith("ABUB_UPLOAD")]
         steady = None
         if timing:
             import re
@@ -68,7 +69,7 @@ def main():
                           "decoded": decoded[-1] if decoded else None, "events": args.events,
                           "seconds": best, "events_per_s": args.events / best, "file_GB": nbytes / 1e9,
                           "file_GBps": nbytes / best / 1e9, "host_cores": len(os.sched_getaffinity(0)), "output_rows": rows,
-                          "synth_write_seconds": t_write, "detect_steady_events_per_s": steady, "phases": timing[-1] if timing else None,
+                          "synth_write_seconds": t_write, "detect_steady_events_per_s": steady, "phases": timing[-1] if timing else None, "upload_parts": upload[-1] if upload else None,
                           "note": "events_per_s: whole-program wall clock incl. CUDA context creation, pinned-buffer allocation and the "
                                   "training pass; detect_steady_events_per_s: detect loop without the one-time pinned allocation "
                                   "(read + decode of every frame on the host cores, async H2D, K1/K2/localizer for the batch, "
