@@ -17,6 +17,8 @@ public:
     void ParseAndSortFramesInFolder(std::string EventID, int Camera, std::vector<std::string>& Contents) override;
     bool ReadGray8BmpPixels(const std::string& EventID, const std::string& FrameName, int rows, int cols, uint8_t* dst,
                             bool* bottom_up) override;
+    // regex_match(path, "^.*cam<Camera>.*(png|bmp)") of the reference (RawParser.cpp:145-150), written out
+    static bool FramePathMatches(const std::string& path, int Camera);
 
 private:
     std::string FramePath(const std::string& EventID, const std::string& FrameName) const;

@@ -13,6 +13,7 @@
 #include <string.h>
 
 #include <iostream>
+#include <regex>
 
 #include "ImageCodec.hpp"
 #include "PICOFormatWriterV4.hpp"
@@ -162,6 +163,31 @@ int main(int argc, char** argv) {
             const double t_batch = now() - t0;
             printf("{\"events\": %d, \"per_event_events_per_s\": %.0f, \"batch_events_per_s\": %.0f}\n", nev, nev / t_event, nev / t_batch);
             return 0;
+        }
+        if (cmd == "frame-pattern-fuzz" && argc == 3) {
+            // RawParser::FramePathMatches against the std::regex it replaces, on random strings over an alphabet that
+            // makes near-misses common (prefixes of "cam<N>", the two suffixes, line breaks)
+            const long n = atol(argv[2]);
+            uint64_t x = 0x2545F4914F6CDD1Dull;
+            auto rnd = [&x]() { x ^= x << 13; x ^= x >> 7; x ^= x << 17; return (uint32_t)(x >> 20); };
+            const char alpha[] = "cam0123pngb.m/_\n\r x";
+            long bad = 0, hits = 0;
+            for (int cam = 0; cam < 4; cam++) {
+                const std::regex re("^.*cam" + std::to_string(cam) + ".*(png|bmp)");
+                for (long i = 0; i < n; i++) {
+                    std::string s;
+                    const int len = (int)(rnd() % 14);
+                    for (int k = 0; k < len; k++) s += alpha[rnd() % (sizeof(alpha) - 1)];
+                    if (rnd() % 4 == 0) s = "cam" + std::to_string(rnd() % 4) + s;
+                    if (rnd() % 3 == 0) s += (rnd() % 2) ? "png" : "bmp";
+                    if (rnd() % 5 == 0) s = "/data/run/7/Images/" + s;
+                    const bool a = std::regex_match(s, re), b = RawParser::FramePathMatches(s, cam);
+                    hits += a;
+                    if (a != b && bad++ < 5) printf("'%s' cam %d: regex %d matcher %d\n", s.c_str(), cam, (int)a, (int)b);
+                }
+            }
+            printf("%ld strings, %ld matches, %ld mismatches\n", 4 * n, hits, bad);
+            return bad ? 1 : 0;
         }
         if (cmd == "format-fuzz" && argc == 3) {
             // the two value formatters on random floats (as double, the promotion `stream << float` does), on halves of the

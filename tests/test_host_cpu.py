@@ -121,6 +121,14 @@ def test_zip_parser(tool, tmp_path, compression):
     assert subprocess.run([tool, "zip-events", str(tmp_path / "nope")], capture_output=True, text=True).stdout.strip() == "THROW -10"
 
 
+def test_frame_path_matcher_equals_the_reference_regex(tool):
+    """RawParser::ParseAndSortFramesInFolder selects frames with regex_match(path, "^.*cam<N>.*(png|bmp)")
+    (reference RawParser.cpp:145-150); the written-out matcher must select exactly the same paths."""
+    r = subprocess.run([tool, "frame-pattern-fuzz", "100000"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-1500:]
+    assert " 0 mismatches" in r.stdout and " 0 matches" not in r.stdout
+
+
 def test_batch_formatter_prints_what_the_stream_prints(tool):
     """SURVEY 8(f)-3: the to_chars formatter of OutputWriter::appendCameraOutput against `stream << value` under
     fixed / precision(2) on 2M values (random floats of every class, ties at the last digit, non-finite)."""
