@@ -29,6 +29,7 @@ EXPORTS = [
     "abub_nccl_comm_create", "abub_nccl_comm_destroy", "abub_nccl_barrier",
     "abub_set_bellows_template", "abub_bellows_track", "abub_bellows_map", "abub_localize_bellows",
     "abub_localize", "abub_localize_batch", "abub_localize_binary", "abub_process_frame",
+    "abub_event_submit_range", "abub_launch_count", "abub_profile", "abub_profile_read",
 ]
 
 
@@ -123,10 +124,15 @@ def load() -> C.CDLL:
     lib.abub_localize_bellows.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, fp, fp, C.POINTER(Blob), C.c_int,
                                           ip, ip, ip]
     lib.abub_process_frame.argtypes = [vp, C.c_int, u8p, u8p, u8p, vp]
+    lib.abub_event_submit_range.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.abub_launch_count.argtypes = [vp]
+    lib.abub_profile.argtypes = [vp, C.c_int]
+    lib.abub_profile_read.argtypes = [vp, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
     for name in EXPORTS:
         fn = getattr(lib, name)
-        if name not in ("abub_ctx_destroy", "abub_last_error", "abub_stream"):
+        if name not in ("abub_ctx_destroy", "abub_last_error", "abub_stream", "abub_launch_count"):
             fn.restype = C.c_int
+    lib.abub_launch_count.restype = C.c_longlong
     _lib = lib
     return lib
 
@@ -158,10 +164,40 @@ class Context:
                 self.h = None
             raise AbubError(f"abub_ctx_create rc={rc}: {msg}")
 
+    @classmethod
+    def adopt(cls, handle: int, rows: int, cols: int, ncams: int, max_frames: int, max_slots: int) -> "Context":
+        """Wraps an abub_ctx* owned by someone else (the host library's AbubDevice): close() leaves it alone."""
+        self = cls.__new__(cls)
+        self.lib = load()
+        self.rows, self.cols, self.ncams, self.max_frames, self.max_slots = rows, cols, ncams, max_frames, max_slots
+        self.npix = rows * cols
+        self.h = C.c_void_p(handle)
+        self._borrowed = True
+        return self
+
     def close(self) -> None:
         if getattr(self, "h", None):
-            self.lib.abub_ctx_destroy(self.h)
+            if not getattr(self, "_borrowed", False):
+                self.lib.abub_ctx_destroy(self.h)
             self.h = None
+
+    def launch_count(self) -> int:
+        return int(self.lib.abub_launch_count(self.h))
+
+    def profile(self, enable: bool) -> None:
+        self._ck(self.lib.abub_profile(self.h, 1 if enable else 0), "abub_profile")
+
+    def profile_read(self):
+        """[(name, ms, calls)] per kernel group since profile(True)."""
+        cap = 32
+        names = (C.c_char_p * cap)()
+        ms = (C.c_double * cap)()
+        calls = (C.c_longlong * cap)()
+        n = self.lib.abub_profile_read(self.h, cap, names, ms, calls)
+        return [(names[i].decode(), float(ms[i]), int(calls[i])) for i in range(min(n, cap))]
+
+    def event_submit_range(self, slot: int, cam: int, frame_first: int, nframes: int) -> None:
+        self._ck(self.lib.abub_event_submit_range(self.h, slot, cam, frame_first, nframes), "abub_event_submit_range")
 
     def __enter__(self):
         return self
@@ -486,3 +522,89 @@ class Context:
         hist = np.zeros(256, np.uint32)
         self._ck(self.lib.abub_process_frame(self.h, cam, _p(w), _p(p), _p(diff), _p(hist)), "abub_process_frame")
         return diff, hist
+
+
+# ---------------------------------------------------------------------------------------
+# libabubhost.so: the host C++ classes (Trainer / L3Localizer / OutputWriter, AbubDevice) with the harness entry
+# points of host/ReconDriver.cpp -- the full recon of events produced in memory, through the abub3hs detect loop.
+# ---------------------------------------------------------------------------------------
+HOST_LIB_PATH = os.path.join(_HERE, "host", "libabubhost.so")
+HOST_EXPORTS = ["abubhost_open", "abubhost_begin_run", "abubhost_recon", "abubhost_end_run", "abubhost_close", "abubhost_last_error"]
+_hostlib = None
+
+
+def load_host() -> C.CDLL:
+    global _hostlib
+    if _hostlib is not None:
+        return _hostlib
+    load()                                     # libabub_cuda.so first (same copy for both bindings)
+    if not os.path.exists(HOST_LIB_PATH):
+        raise AbubError(f"{HOST_LIB_PATH} is missing: run `make -C autobub3hs_b200/host`")
+    lib = C.CDLL(HOST_LIB_PATH)
+    ip = C.POINTER(C.c_int)
+    lib.abubhost_open.argtypes = [C.c_int] * 7 + [C.POINTER(C.c_void_p)]
+    lib.abubhost_begin_run.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, ip]
+    lib.abubhost_recon.argtypes = [C.c_int, C.c_int, ip, ip, C.c_int, C.c_int, C.POINTER(C.c_double)]
+    lib.abubhost_end_run.argtypes = []
+    lib.abubhost_close.argtypes = []
+    lib.abubhost_close.restype = None
+    lib.abubhost_last_error.argtypes = []
+    lib.abubhost_last_error.restype = C.c_char_p
+    _hostlib = lib
+    return lib
+
+
+class HostRecon:
+    """The abub3hs detect loop over events whose frames live in device slots / pinned staging buffers.
+    `ctx` is a borrowed Context on the host library's abub_ctx (training, slot pointers, pinned buffers)."""
+
+    STAT_KEYS = ("trigger_s", "trigger_readback_s", "localizer_s", "host_analysis_s", "file_write_s", "frames_sent")
+
+    def __init__(self, rows: int, cols: int, ncams: int = 4, max_frames: int = 40, max_slots: int = 1, device: int = 0,
+                 early_chunk: int = 6):
+        self.hl = load_host()
+        h = C.c_void_p()
+        rc = self.hl.abubhost_open(device, rows, cols, ncams, max_frames, max_slots, early_chunk, C.byref(h))
+        if rc != 0:
+            raise AbubError("abubhost_open: " + self.hl.abubhost_last_error().decode())
+        self.ctx = Context.adopt(h.value, rows, cols, ncams, max_frames, max_slots)
+        self.ncams = ncams
+        self.stats = (C.c_double * 8)()
+
+    def begin_run(self, run_id: str, out_dir: str, mask_dir: str, frame_offset: int, training_set_sizes: Sequence[int]) -> str:
+        tss = (C.c_int * self.ncams)(*[int(v) for v in training_set_sizes])
+        rc = self.hl.abubhost_begin_run(run_id.encode(), out_dir.encode(), (mask_dir or "").encode(), frame_offset, tss)
+        if rc != 0:
+            raise AbubError("abubhost_begin_run: " + self.hl.abubhost_last_error().decode())
+        return os.path.join(out_dir, f"abub3hs_{run_id}.txt")
+
+    def recon(self, slot_first: int, event_numbers: Sequence[int], nframes, pinned: bool = False, chunk_frames: int = 4) -> None:
+        n = len(event_numbers)
+        ev = (C.c_int * n)(*[int(v) for v in event_numbers])
+        nf = np.ascontiguousarray(nframes, dtype=np.int32).reshape(n * self.ncams)
+        rc = self.hl.abubhost_recon(slot_first, n, ev, nf.ctypes.data_as(C.POINTER(C.c_int)), 1 if pinned else 0, chunk_frames,
+                                    self.stats)
+        if rc != 0:
+            raise AbubError("abubhost_recon: " + self.hl.abubhost_last_error().decode())
+
+    def read_stats(self, reset: bool = True) -> dict:
+        d = {k: float(self.stats[i]) for i, k in enumerate(self.STAT_KEYS)}
+        if reset:
+            for i in range(8):
+                self.stats[i] = 0.0
+        return d
+
+    def end_run(self) -> None:
+        self.hl.abubhost_end_run()
+
+    def close(self) -> None:
+        if getattr(self, "ctx", None) is not None:
+            self.ctx.close()
+            self.ctx = None
+            self.hl.abubhost_close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()

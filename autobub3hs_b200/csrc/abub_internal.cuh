@@ -47,7 +47,36 @@ struct abub_slot_state {
     bool hist_valid = false;
 };
 
+// Per-kernel-group device timing (abub_profile / abub_profile_read): CUDA events recorded on the stream a group is
+// launched on, resolved when the table is read.  Off by default (no events are recorded then).
+enum {
+    ABUB_PROF_K1 = 0,   // k1_trigger_tma_kernel + k1_trigger_kernel (border rows) + k1_fill_bin0_kernel
+    ABUB_PROF_K2,       // k2_trigger_scan_kernel (+ k2_next_avail_kernel)
+    ABUB_PROF_K5A,      // localizer genesis frames (ProcessFrame in store mode + TOZERO + histogram)
+    ABUB_PROF_K5B,      // localizer post-trigger frames (k5_post_stream_kernel)
+    ABUB_PROF_K5C,      // k5_otsu_kernel + flag fill
+    ABUB_PROF_K6,       // k6_candidates_*_kernel
+    ABUB_PROF_SORT,     // cub radix sort / scans (library kernels)
+    ABUB_PROF_K7A,      // k7_trace1_kernel
+    ABUB_PROF_K7B,      // k7_trace2_kernel
+    ABUB_PROF_K7C,      // k7_external_kernel + k7_emit_kernel
+    ABUB_PROF_K3,       // k3_gate_*_kernel
+    ABUB_PROF_K4,       // k4_welford*_kernel / partials / finish / fixup
+    ABUB_PROF_N
+};
+struct abub_prof_state {
+    bool on = false;
+    std::vector<cudaEvent_t> pool;
+    size_t used = 0;
+    struct Rec { int id; size_t e0, e1; };
+    std::vector<Rec> recs;
+    double ms[ABUB_PROF_N] = {0};
+    long long calls[ABUB_PROF_N] = {0};
+};
+
 struct abub_ctx {
+    long long n_launches = 0;           // kernels of this library launched so far (ABUB_L at every launch site)
+    abub_prof_state prof;
     int device = 0, rows = 0, cols = 0, ncams = 0, max_frames = 0, max_slots = 0;
     size_t npix = 0;
     cudaStream_t stream = nullptr;
@@ -80,6 +109,32 @@ struct abub_ctx {
     void*     bel = nullptr;        // bellows-veto arena (k8_bellows.cu)
     void*     png = nullptr;        // on-device PNG decode arena (k9_png.cu)
     void*     d_tmaps = nullptr;    // CUtensorMap[2*max_slots + 2*ncams] (k1_trigger_tma.cu); null = TMA path off
+};
+
+#define ABUB_L(ctx) ((void)++(ctx)->n_launches)
+
+// RAII scope around the launches of one kernel group; a no-op unless abub_profile(ctx, 1) was called
+struct abub_prof_scope {
+    abub_ctx* c; int id; size_t e0 = 0; bool live = false;
+    static size_t ev(abub_ctx* c) {
+        abub_prof_state& p = c->prof;
+        if (p.used == p.pool.size()) { cudaEvent_t e; if (cudaEventCreate(&e) != cudaSuccess) return (size_t)-1; p.pool.push_back(e); }
+        return p.used++;
+    }
+    abub_prof_scope(abub_ctx* ctx, int id_) : c(ctx), id(id_) {
+        if (!c->prof.on) return;
+        e0 = ev(c);
+        if (e0 == (size_t)-1) return;
+        cudaEventRecord(c->prof.pool[e0], c->stream);
+        live = true;
+    }
+    ~abub_prof_scope() {
+        if (!live) return;
+        const size_t e1 = ev(c);
+        if (e1 == (size_t)-1) return;
+        cudaEventRecord(c->prof.pool[e1], c->stream);
+        c->prof.recs.push_back({id, e0, e1});
+    }
 };
 
 #define ABUB_CHECK_CUDA(ctx, call)                                                        \

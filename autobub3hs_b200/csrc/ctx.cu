@@ -96,6 +96,7 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     cudaFree((void*)ctx->d_gate_tab); cudaFree(ctx->d_gate_hist);
     cudaFree(ctx->d_tmaps);
     if (ctx->h_raw) cudaFreeHost(ctx->h_raw);
+    for (cudaEvent_t e : ctx->prof.pool) cudaEventDestroy(e);
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     if (ctx->ev_stream) cudaEventDestroy(ctx->ev_stream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -109,6 +110,49 @@ extern "C" int abub_sync(abub_ctx* ctx) {
 }
 
 extern "C" void* abub_stream(abub_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+extern "C" long long abub_launch_count(const abub_ctx* ctx) { return ctx ? ctx->n_launches : 0; }
+
+static const char* const kProfNames[ABUB_PROF_N] = {
+    "K1 k1_trigger_tma_kernel + border rows + bin0", "K2 k2_trigger_scan_kernel", "K5a genesis ProcessFrame (store mode)",
+    "K5b k5_post_stream_kernel", "K5c k5_otsu_kernel + flags", "K6 k6_candidates_seg_kernel", "cub sort/scan (library)",
+    "K7a k7_trace1_kernel", "K7b k7_trace2_kernel", "K7c k7_external_kernel + k7_emit_kernel", "K3 k3_gate_batch_kernel",
+    "K4 k4_welford16_kernel"};
+
+static void prof_resolve(abub_ctx* ctx) {
+    abub_prof_state& p = ctx->prof;
+    for (const auto& r : p.recs) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(p.pool[r.e1]) == cudaSuccess && cudaEventElapsedTime(&ms, p.pool[r.e0], p.pool[r.e1]) == cudaSuccess) {
+            p.ms[r.id] += ms;
+            p.calls[r.id]++;
+        }
+    }
+    p.recs.clear();
+    p.used = 0;
+}
+
+extern "C" int abub_profile(abub_ctx* ctx, int enable) {
+    if (!ctx) return ABUB_E_INVALID;
+    cudaSetDevice(ctx->device);
+    prof_resolve(ctx);
+    for (int i = 0; i < ABUB_PROF_N; i++) { ctx->prof.ms[i] = 0; ctx->prof.calls[i] = 0; }
+    ctx->prof.on = enable != 0;
+    return ABUB_OK;
+}
+
+extern "C" int abub_profile_read(abub_ctx* ctx, int cap, const char** names, double* ms, long long* calls) {
+    if (!ctx) return ABUB_E_INVALID;
+    cudaSetDevice(ctx->device);
+    prof_resolve(ctx);
+    const int n = cap < ABUB_PROF_N ? cap : ABUB_PROF_N;
+    for (int i = 0; i < n; i++) {
+        if (names) names[i] = kProfNames[i];
+        if (ms) ms[i] = ctx->prof.ms[i];
+        if (calls) calls[i] = ctx->prof.calls[i];
+    }
+    return ABUB_PROF_N;
+}
 
 // ---- background -------------------------------------------------------------------
 static int install_background(abub_ctx* ctx, int cam, int tss) {
@@ -157,7 +201,7 @@ __global__ void set_nframes_kernel(int* __restrict__ dst, const NframesArg a, in
 static int push_nframes(abub_ctx* ctx, int slot) {
     NframesArg a;
     for (int c = 0; c < ABUB_MAX_CAMS; c++) a.n[c] = ctx->slots[slot].nframes[c];
-    set_nframes_kernel<<<1, 32, 0, ctx->stream>>>(ctx->d_nframes + (size_t)slot * ctx->ncams, a, ctx->ncams);
+    ABUB_L(ctx), set_nframes_kernel<<<1, 32, 0, ctx->stream>>>(ctx->d_nframes + (size_t)slot * ctx->ncams, a, ctx->ncams);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     ctx->slots[slot].hist_valid = false;
     return ABUB_OK;
@@ -234,6 +278,24 @@ extern "C" int abub_event_upload_frame(abub_ctx* ctx, int slot, int cam, int fra
     const size_t off = ((size_t)cam * ctx->max_frames + frame) * ctx->npix;
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(s.d_frames + off, s.h_pinned + off, ctx->npix, cudaMemcpyHostToDevice, ctx->stream));
     s.hist_valid = false;
+    return ABUB_OK;
+}
+
+// frames [frame_first, frame_first + nframes) of one camera, from their regions of the pinned staging buffer (asynchronous).
+// The frame count of the camera is not changed.
+extern "C" int abub_event_submit_range(abub_ctx* ctx, int slot, int cam, int frame_first, int nframes) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot >= 0 && slot < ctx->max_slots && cam >= 0 && cam < ctx->ncams, "slot/cam");
+    ABUB_REQUIRE(ctx, frame_first >= 0 && nframes >= 0 && frame_first + nframes <= ctx->max_frames, "frame range");
+    cudaSetDevice(ctx->device);
+    abub_slot_state& s = ctx->slots[slot];
+    ABUB_REQUIRE(ctx, s.h_pinned != nullptr, "slot has no pinned buffer (call abub_pinned_acquire)");
+    if (nframes > 0) {
+        const size_t off = ((size_t)cam * ctx->max_frames + frame_first) * ctx->npix;
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(s.d_frames + off, s.h_pinned + off, (size_t)nframes * ctx->npix, cudaMemcpyHostToDevice,
+                                             ctx->stream));
+        s.hist_valid = false;
+    }
     return ABUB_OK;
 }
 

@@ -474,7 +474,7 @@ static inline size_t k1_smem_bytes(int threads) { return (256 + (threads / 32) *
 int abub_k1_build_k32(abub_ctx* ctx, int cam) {
     abub_cam_state& c = ctx->cam[cam];
     const size_t n = ctx->npix;
-    k1_build_k32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(c.d_sigma, c.d_k32, c.d_t8, n);
+    ABUB_L(ctx), k1_build_k32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(c.d_sigma, c.d_k32, c.d_t8, n);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
 }
@@ -493,6 +493,7 @@ int abub_k1_launch_trigger_range(abub_ctx* ctx, int slot_first, int nslots, int 
     if (j_first < 1) j_first = 1;
     if (j_last > ctx->max_frames) j_last = ctx->max_frames;
     if (j_last <= j_first) return ABUB_OK;
+    abub_prof_scope prof(ctx, ABUB_PROF_K1);
     int nstrips, th;
     k1_strips(ctx->rows, &nstrips, &th);
     if (int rc = k1_allow_smem(ctx, k1_trigger_kernel, k1_smem_bytes(threads))) return rc;
@@ -506,13 +507,13 @@ int abub_k1_launch_trigger_range(abub_ctx* ctx, int slot_first, int nslots, int 
         const int ns = (nslots - s0 < per) ? nslots - s0 : per;
         // with the TMA kernel on rows [2, rows-2) this kernel only does the 2+2 border rows
         dim3 grid((tma ? 2 : nstrips) * k1_xgroups(ctx->cols), j_last - j_first, ns * ctx->ncams);
-        k1_trigger_kernel<<<grid, threads, k1_smem_bytes(threads), ctx->stream>>>(
+        ABUB_L(ctx), k1_trigger_kernel<<<grid, threads, k1_smem_bytes(threads), ctx->stream>>>(
             ctx->d_slot_ptrs, d_limit, ctx->d_tss, ctx->d_k32_ptrs, ctx->d_hist, slot_first + s0,
             ctx->rows, ctx->cols, ctx->ncams, ctx->max_frames, tma ? 2 : th, k1_xgroups(ctx->cols), tma ? 1 : 0, j_first);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     const int total_w = nslots * ctx->ncams * ctx->max_frames;
-    k1_fill_bin0_kernel<<<(total_w * 32 + 255) / 256, 256, 0, ctx->stream>>>(
+    ABUB_L(ctx), k1_fill_bin0_kernel<<<(total_w * 32 + 255) / 256, 256, 0, ctx->stream>>>(
         ctx->d_hist, d_limit, slot_first, nslots, ctx->ncams, ctx->max_frames, (uint32_t)ctx->npix, j_first, j_last);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
@@ -530,17 +531,18 @@ int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b,
     k1_strips(ctx->rows, &nstrips, &th);
     if (int rc = k1_allow_smem(ctx, k1_single_kernel, k1_smem_bytes(threads))) return rc;
     const int nxg = k1_xgroups(ctx->cols);
-    k1_single_kernel<<<nstrips * nxg, threads, k1_smem_bytes(threads), ctx->stream>>>(d_a, d_b, d_k32, d_out, d_hist, ctx->rows,
+    ABUB_L(ctx), k1_single_kernel<<<nstrips * nxg, threads, k1_smem_bytes(threads), ctx->stream>>>(d_a, d_b, d_k32, d_out, d_hist, ctx->rows,
                                                                                        ctx->cols, tozero_thres, th, nxg);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     if (d_hist) {
-        k1_fill_bin0_single<<<1, 32, 0, ctx->stream>>>(d_hist, (uint32_t)ctx->npix);
+        ABUB_L(ctx), k1_fill_bin0_single<<<1, 32, 0, ctx->stream>>>(d_hist, (uint32_t)ctx->npix);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     return ABUB_OK;
 }
 
 int abub_k1_launch_genesis_jobs(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs) {
+    abub_prof_scope prof(ctx, ABUB_PROF_K5A);
     const int threads = k1_block_threads(ctx->cols);
     int nstrips, th;
     k1_strips(ctx->rows, &nstrips, &th);
@@ -548,7 +550,7 @@ int abub_k1_launch_genesis_jobs(abub_ctx* ctx, const abub_loc_job* d_jobs, int n
     for (int j0 = 0; j0 < njobs; j0 += 65535) {
         const int nj = (njobs - j0 < 65535) ? njobs - j0 : 65535;
         const int nxg = k1_xgroups(ctx->cols);
-        k1_genesis_jobs_kernel<<<dim3(nstrips * nxg, nj), threads, k1_smem_bytes(threads), ctx->stream>>>(
+        ABUB_L(ctx), k1_genesis_jobs_kernel<<<dim3(nstrips * nxg, nj), threads, k1_smem_bytes(threads), ctx->stream>>>(
             d_jobs + j0, ctx->rows, ctx->cols, th, nxg);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }

@@ -358,7 +358,7 @@ int abub_k1_tma_init(abub_ctx* ctx) {
 int abub_k1_build_k16(abub_ctx* ctx, int cam) {
     abub_cam_state& c = ctx->cam[cam];
     const size_t n = ctx->npix;
-    k1_build_k16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(c.d_sigma, c.d_k16, n);
+    ABUB_L(ctx), k1_build_k16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(c.d_sigma, c.d_k16, n);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
 }
@@ -384,7 +384,7 @@ int abub_k1_launch_trigger_tma(abub_ctx* ctx, int slot_first, int nslots, int j_
     for (int s0 = 0; s0 < nslots; s0 += per) {
         const int ns = (nslots - s0 < per) ? nslots - s0 : per;
         dim3 grid(nstrips * nxg, j_last - j_first, ns * ctx->ncams);
-        k1_trigger_tma_kernel<<<grid, 32 * wpc, smem, ctx->stream>>>(
+        ABUB_L(ctx), k1_trigger_tma_kernel<<<grid, 32 * wpc, smem, ctx->stream>>>(
             maps, maps + ctx->max_slots, d_limit, ctx->d_tss, ctx->d_hist, slot_first + s0, ctx->rows,
             ctx->cols, ctx->ncams, ctx->max_frames, th, nxg, j_first);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());

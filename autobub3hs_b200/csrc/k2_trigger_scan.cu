@@ -231,7 +231,7 @@ __global__ void k2_next_avail_kernel(const int* __restrict__ result, const int* 
 
 int abub_k2_next_avail(abub_ctx* ctx, int slot_first, int nslots, int next, bool first_round) {
     const int n = nslots * ctx->ncams;
-    k2_next_avail_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(first_round ? nullptr : ctx->d_trig, ctx->d_nframes, ctx->d_avail,
+    ABUB_L(ctx), k2_next_avail_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(first_round ? nullptr : ctx->d_trig, ctx->d_nframes, ctx->d_avail,
                                                                      ctx->d_start, slot_first * ctx->ncams, n, next);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
@@ -241,7 +241,8 @@ int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots) { return abub_k2_l
 
 int abub_k2_launch_avail(abub_ctx* ctx, int slot_first, int nslots, const int* d_avail) {
     const int items = nslots * ctx->ncams;
-    k2_trigger_scan_kernel<<<(items + K2_WARPS - 1) / K2_WARPS, 32 * K2_WARPS, 0, ctx->stream>>>(
+    abub_prof_scope prof(ctx, ABUB_PROF_K2);
+    ABUB_L(ctx), k2_trigger_scan_kernel<<<(items + K2_WARPS - 1) / K2_WARPS, 32 * K2_WARPS, 0, ctx->stream>>>(
         ctx->d_hist, ctx->d_nframes, ctx->d_start, ctx->d_tss, ctx->d_trig, ctx->d_sig, slot_first, nslots,
         ctx->ncams, ctx->max_frames, d_avail, ctx->trig_metric, ctx->trig_thr, (float)(1.0 / (double)ctx->npix));
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());

@@ -341,22 +341,23 @@ __global__ void k4_fdiv_check_kernel(int k_first, unsigned long long* __restrict
 
 int abub_k3_gate_hist16(abub_ctx* ctx, const uint8_t* d_f0, const uint8_t* d_f1, uint32_t* d_hist16) {
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_hist16, 0, 16 * sizeof(uint32_t), ctx->stream));
-    k3_gate_hist16_kernel<<<148 * 4, 256, 0, ctx->stream>>>(d_f0, d_f1, d_hist16, ctx->npix);
+    ABUB_L(ctx), k3_gate_hist16_kernel<<<148 * 4, 256, 0, ctx->stream>>>(d_f0, d_f1, d_hist16, ctx->npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
-    k3_fill_bin0<<<1, 1, 0, ctx->stream>>>(d_hist16, (uint32_t)ctx->npix);
+    ABUB_L(ctx), k3_fill_bin0<<<1, 1, 0, ctx->stream>>>(d_hist16, (uint32_t)ctx->npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
 }
 
 int abub_k3_gate_batch(abub_ctx* ctx, const uint8_t* const* d_pairs, int n, uint32_t* d_hist16) {
+    abub_prof_scope prof(ctx, ABUB_PROF_K3);
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_hist16, 0, (size_t)n * 16 * sizeof(uint32_t), ctx->stream));
     // 32 CTAs x 256 threads x 16 B per sweep of one pair; the event index rides on grid.y
     for (int e0 = 0; e0 < n; e0 += 65535) {
         const int ne = n - e0 < 65535 ? n - e0 : 65535;
-        k3_gate_batch_kernel<<<dim3(32, ne), 256, 0, ctx->stream>>>(d_pairs + 2 * (size_t)e0, d_hist16 + 16 * (size_t)e0, ctx->npix);
+        ABUB_L(ctx), k3_gate_batch_kernel<<<dim3(32, ne), 256, 0, ctx->stream>>>(d_pairs + 2 * (size_t)e0, d_hist16 + 16 * (size_t)e0, ctx->npix);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
-    k3_fill_bin0_batch<<<(n + 127) / 128, 128, 0, ctx->stream>>>(d_hist16, n, (uint32_t)ctx->npix);
+    ABUB_L(ctx), k3_fill_bin0_batch<<<(n + 127) / 128, 128, 0, ctx->stream>>>(d_hist16, n, (uint32_t)ctx->npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
 }
@@ -364,27 +365,28 @@ int abub_k3_gate_batch(abub_ctx* ctx, const uint8_t* const* d_pairs, int n, uint
 // d_frame_table holds frames parked by train.cu (cudaMalloc'd chunks, frame stride npix): 16-byte aligned whenever
 // npix is a multiple of 16
 int abub_k4_welford(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint8_t* d_mean, uint8_t* d_sigma) {
+    abub_prof_scope prof(ctx, ABUB_PROF_K4);
     const bool fast = n <= (1 << 24) && ctx->npix % 16 == 0 && (((uintptr_t)d_mean | (uintptr_t)d_sigma) & 15) == 0 &&
                       !getenv("ABUB_K4_GENERIC");
     if (fast) {
         const size_t nvec = ctx->npix / 16;
         const unsigned nb = (unsigned)((nvec + 63) / 64);
         if (n <= ABUB_FDIV1_MAX)
-            k4_welford16_kernel<1><<<nb, 64, 0, ctx->stream>>>(d_frame_table, n, d_mean, d_sigma, nvec);
+            ABUB_L(ctx), k4_welford16_kernel<1><<<nb, 64, 0, ctx->stream>>>(d_frame_table, n, d_mean, d_sigma, nvec);
         else
-            k4_welford16_kernel<2><<<nb, 64, 0, ctx->stream>>>(d_frame_table, n, d_mean, d_sigma, nvec);
+            ABUB_L(ctx), k4_welford16_kernel<2><<<nb, 64, 0, ctx->stream>>>(d_frame_table, n, d_mean, d_sigma, nvec);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
         return ABUB_OK;
     }
     const size_t nthreads = (ctx->npix + 3) / 4;
-    k4_welford_kernel<<<(unsigned)((nthreads + 127) / 128), 128, 0, ctx->stream>>>(d_frame_table, n, d_mean, d_sigma,
+    ABUB_L(ctx), k4_welford_kernel<<<(unsigned)((nthreads + 127) / 128), 128, 0, ctx->stream>>>(d_frame_table, n, d_mean, d_sigma,
                                                                                   ctx->npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
 }
 
 int abub_k4_partials(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint32_t* d_sum, uint64_t* d_sumsq) {
-    k4_partials_kernel<<<(unsigned)((ctx->npix + 255) / 256), 256, 0, ctx->stream>>>(d_frame_table, n, d_sum, d_sumsq,
+    ABUB_L(ctx), k4_partials_kernel<<<(unsigned)((ctx->npix + 255) / 256), 256, 0, ctx->stream>>>(d_frame_table, n, d_sum, d_sumsq,
                                                                                      ctx->npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
@@ -393,7 +395,7 @@ int abub_k4_partials(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, 
 int abub_k4_finish_from_partials(abub_ctx* ctx, const uint32_t* d_sum, const uint64_t* d_sumsq, int n, uint8_t* d_mean,
                                  uint8_t* d_sigma, int* d_nflag, uint8_t* d_flag) {
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_nflag, 0, sizeof(int), ctx->stream));
-    k4_finish_partials_kernel<<<(unsigned)((ctx->npix + 255) / 256), 256, 0, ctx->stream>>>(d_sum, d_sumsq, n, d_mean,
+    ABUB_L(ctx), k4_finish_partials_kernel<<<(unsigned)((ctx->npix + 255) / 256), 256, 0, ctx->stream>>>(d_sum, d_sumsq, n, d_mean,
                                                                                             d_sigma, d_nflag, d_flag,
                                                                                             ctx->npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
@@ -402,7 +404,7 @@ int abub_k4_finish_from_partials(abub_ctx* ctx, const uint32_t* d_sum, const uin
 
 int abub_k4_fixup(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, const uint8_t* d_flag, uint8_t* d_mean,
                   uint8_t* d_sigma) {
-    k4_fixup_kernel<<<(unsigned)((ctx->npix + 255) / 256), 256, 0, ctx->stream>>>(d_frame_table, n, d_flag, d_mean,
+    ABUB_L(ctx), k4_fixup_kernel<<<(unsigned)((ctx->npix + 255) / 256), 256, 0, ctx->stream>>>(d_frame_table, n, d_flag, d_mean,
                                                                                   d_sigma, ctx->npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
@@ -420,8 +422,8 @@ extern "C" int abub_selftest_fdiv(abub_ctx* ctx, int steps, int k_first, int k_l
     ABUB_CHECK_CUDA(ctx, cudaMalloc(&d, 3 * sizeof(unsigned long long)));
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d, 0, 3 * sizeof(unsigned long long), ctx->stream));
     const dim3 grid(148 * 2, (unsigned)(k_last - k_first + 1));
-    if (steps == 1) k4_fdiv_check_kernel<1><<<grid, 256, 0, ctx->stream>>>(k_first, d);
-    else k4_fdiv_check_kernel<2><<<grid, 256, 0, ctx->stream>>>(k_first, d);
+    if (steps == 1) ABUB_L(ctx), k4_fdiv_check_kernel<1><<<grid, 256, 0, ctx->stream>>>(k_first, d);
+    else ABUB_L(ctx), k4_fdiv_check_kernel<2><<<grid, 256, 0, ctx->stream>>>(k_first, d);
     unsigned long long h[3] = {0, 0, 0};
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(h, d, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream);

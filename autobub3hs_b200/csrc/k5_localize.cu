@@ -561,40 +561,49 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_hist, 0, (size_t)njobs * 256 * sizeof(uint32_t), st));
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_npf, 0, (size_t)njobs * sizeof(int), st));
     if ((rc = abub_k1_launch_genesis_jobs(ctx, a->d_jobs, njobs))) return rc;
+    {
+    abub_prof_scope prof(ctx, ABUB_PROF_K5B);
     if ((ctx->cols % 8) == 0 && ctx->cols >= 16) {
         const int nxw = (ctx->cols + 239) / 240, nstrips = (ctx->rows + PS_TH - 1) / PS_TH;
         dim3 grid((nxw * nstrips + PS_WARPS - 1) / PS_WARPS, 1, njobs);
-        k5_post_stream_kernel<<<grid, 32 * PS_WARPS, 0, st>>>(a->d_jobs, ctx->rows, ctx->cols, nxw, nstrips);
+        ABUB_L(ctx), k5_post_stream_kernel<<<grid, 32 * PS_WARPS, 0, st>>>(a->d_jobs, ctx->rows, ctx->cols, nxw, nstrips);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     } else {
         dim3 grid((ctx->cols + PT_W - 1) / PT_W, (ctx->rows + PT_H - 1) / PT_H, njobs);
-        k5_post_kernel<<<grid, 256, 0, st>>>(a->d_jobs, ctx->rows, ctx->cols);
+        ABUB_L(ctx), k5_post_kernel<<<grid, 256, 0, st>>>(a->d_jobs, ctx->rows, ctx->cols);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
+    }
     if (has_prepared) {
-        k5_prepared_kernel<<<dim3(148 * 2, njobs), 256, 0, st>>>(a->d_jobs, npix);
+        ABUB_L(ctx), k5_prepared_kernel<<<dim3(148 * 2, njobs), 256, 0, st>>>(a->d_jobs, npix);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     const int nxw_f = (ctx->cols + 239) / 240;
     const bool stream_k5b = (ctx->cols % 8) == 0 && ctx->cols >= 16;
-    k5_flag_fill_kernel<<<dim3(4, njobs), 256, 0, st>>>(a->d_jobs, (size_t)ctx->rows * nxw_f, stream_k5b ? 0 : 1);
+    {
+    abub_prof_scope prof(ctx, ABUB_PROF_K5C);
+    ABUB_L(ctx), k5_flag_fill_kernel<<<dim3(4, njobs), 256, 0, st>>>(a->d_jobs, (size_t)ctx->rows * nxw_f, stream_k5b ? 0 : 1);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
-    k5_otsu_kernel<<<(njobs + 63) / 64, 64, 0, st>>>(a->d_jobs, a->d_thr, njobs, (uint32_t)npix);
+    ABUB_L(ctx), k5_otsu_kernel<<<(njobs + 63) / 64, 64, 0, st>>>(a->d_jobs, a->d_thr, njobs, (uint32_t)npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
     a->last_njobs = njobs;
 
     int counters[8];
     if (a->cand_cap == 0 && (rc = ensure_cands(ctx, a, 1 << 16))) return rc;
     for (;;) {
         ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_counters, 0, 8 * sizeof(int), st));
+        {
+        abub_prof_scope prof(ctx, ABUB_PROF_K6);
         if ((ctx->cols & 15) == 0 && !getenv("ABUB_K6_DENSE")) {
             const int nseg = ctx->rows * nxw_f;
-            k6_candidates_seg_kernel<<<dim3((nseg + 255) / 256, njobs), 256, 0, st>>>(a->d_jobs, a->d_thr, ctx->rows, ctx->cols, nxw_f,
+            ABUB_L(ctx), k6_candidates_seg_kernel<<<dim3((nseg + 255) / 256, njobs), 256, 0, st>>>(a->d_jobs, a->d_thr, ctx->rows, ctx->cols, nxw_f,
                                                                                      a->d_keys, a->d_counters, a->cand_cap, 0);
         } else {
             const int gx = (int)((npix + 256 * 16 - 1) / (256 * 16));
-            k6_candidates_kernel<<<dim3(gx, njobs), 256, 0, st>>>(a->d_jobs, a->d_thr, ctx->rows, ctx->cols, a->d_keys,
+            ABUB_L(ctx), k6_candidates_kernel<<<dim3(gx, njobs), 256, 0, st>>>(a->d_jobs, a->d_thr, ctx->rows, ctx->cols, a->d_keys,
                                                                  a->d_counters, a->cand_cap, 0);
+        }
         }
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
         ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(counters, a->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
@@ -606,10 +615,16 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     npf_out.assign(njobs, 0);
     if (ncand == 0) return ABUB_OK;
     size_t tmpb = a->cub_tmp_bytes;
-    cub::DeviceRadixSort::SortKeys(a->d_cub_tmp, tmpb, a->d_keys, a->d_keys_alt, ncand, 0, 64, st);
+    {
+        abub_prof_scope prof(ctx, ABUB_PROF_SORT);
+        cub::DeviceRadixSort::SortKeys(a->d_cub_tmp, tmpb, a->d_keys, a->d_keys_alt, ncand, 0, 64, st);
+    }
     const int tb = 64, nb = (ncand + tb - 1) / tb;
-    k7_trace1_kernel<<<nb, tb, 0, st>>>(a->d_keys_alt, ncand, a->d_jobs, a->d_thr, ctx->rows, ctx->cols, 0, a->d_cand,
+    {
+    abub_prof_scope prof(ctx, ABUB_PROF_K7A);
+    ABUB_L(ctx), k7_trace1_kernel<<<nb, tb, 0, st>>>(a->d_keys_alt, ncand, a->d_jobs, a->d_thr, ctx->rows, ctx->cols, 0, a->d_cand,
                                         a->d_scan);
+    }
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     // arena offsets: exclusive scan over ncand+1 entries (the extra entry yields the total)
     ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(a->d_scan + ncand, 0, sizeof(long long), st));
@@ -625,15 +640,21 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     }
     abub_blob* tmp = a->d_blobs;
     abub_blob* ordered = a->d_blobs + a->blob_cap;
-    k7_trace2_kernel<<<nb, tb, 0, st>>>(ncand, a->d_jobs, a->d_thr, ctx->rows, ctx->cols, a->d_cand, a->d_scan, a->d_chain, tmp);
+    {
+    abub_prof_scope prof(ctx, ABUB_PROF_K7B);
+    ABUB_L(ctx), k7_trace2_kernel<<<nb, tb, 0, st>>>(ncand, a->d_jobs, a->d_thr, ctx->rows, ctx->cols, a->d_cand, a->d_scan, a->d_chain, tmp);
+    }
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     int* flags = a->d_iscan;
     int* pos = a->d_iscan + ncand + 1;
-    k7_external_kernel<<<nb, tb, 0, st>>>(ncand, ctx->cols, a->d_cand, a->d_chain, flags);
+    {
+    abub_prof_scope prof7c(ctx, ABUB_PROF_K7C);
+    ABUB_L(ctx), k7_external_kernel<<<nb, tb, 0, st>>>(ncand, ctx->cols, a->d_cand, a->d_chain, flags);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     tmpb = a->cub_tmp_bytes;
     cub::DeviceScan::ExclusiveSum(a->d_cub_tmp, tmpb, flags, pos, ncand, st);
-    k7_emit_kernel<<<nb, tb, 0, st>>>(ncand, a->d_cand, flags, pos, tmp, ordered, a->blob_cap, a->d_npf, a->d_counters);
+    ABUB_L(ctx), k7_emit_kernel<<<nb, tb, 0, st>>>(ncand, a->d_cand, flags, pos, tmp, ordered, a->blob_cap, a->d_npf, a->d_counters);
+    }
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(counters, a->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(npf_out.data(), a->d_npf, njobs * sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -772,7 +793,7 @@ extern "C" int abub_localize_binary(abub_ctx* ctx, int k, uint8_t* out) {
     LocArena* a = arena_of(ctx);
     ABUB_REQUIRE(ctx, out && a && k >= 0 && k < a->last_njobs, "abub_localize_binary: no such frame in the last call");
     cudaSetDevice(ctx->device);
-    k5_binary_kernel<<<(unsigned)((ctx->npix + 255) / 256), 256, 0, ctx->stream>>>(a->d_tz, a->d_thr, k, ctx->d_tmp8[3], ctx->npix);
+    ABUB_L(ctx), k5_binary_kernel<<<(unsigned)((ctx->npix + 255) / 256), 256, 0, ctx->stream>>>(a->d_tz, a->d_thr, k, ctx->d_tmp8[3], ctx->npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(out, ctx->d_tmp8[3], ctx->npix, cudaMemcpyDeviceToHost, ctx->stream));
     ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -314,14 +314,14 @@ static int ncc_map(abub_ctx* ctx, BelArena* a, const abub_cam_state& cs, const u
     }
     if (!a->d_red) ABUB_CHECK_CUDA(ctx, cudaMalloc(&a->d_red, 4 * sizeof(unsigned long long)));
     cudaStream_t st = ctx->stream;
-    k8_sq_h_kernel<<<dim3(((rc + 63) / 64 + 63) / 64, ctx->rows), 64, 0, st>>>(d_img, ctx->rows, ctx->cols, tw, rc, a->d_sqh);
+    ABUB_L(ctx), k8_sq_h_kernel<<<dim3(((rc + 63) / 64 + 63) / 64, ctx->rows), 64, 0, st>>>(d_img, ctx->rows, ctx->cols, tw, rc, a->d_sqh);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
-    k8_sq_v_kernel<<<dim3((rc + 127) / 128, (rr + 31) / 32), 128, 0, st>>>(a->d_sqh, th, rr, rc, a->d_w);
+    ABUB_L(ctx), k8_sq_v_kernel<<<dim3((rc + 127) / 128, (rr + 31) / 32), 128, 0, st>>>(a->d_sqh, th, rr, rc, a->d_w);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     const size_t smem = ncc_smem_bytes(th, tp);
     ABUB_CHECK_CUDA(ctx, cudaFuncSetAttribute(k8_ncc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // templNorm of common_matchTemplate for CCORR_NORMED: sqrt(sum T^2)
-    k8_ncc_kernel<<<dim3((rc + NCC_TX - 1) / NCC_TX, (rr + NCC_TY - 1) / NCC_TY), NCC_THREADS, smem, st>>>(
+    ABUB_L(ctx), k8_ncc_kernel<<<dim3((rc + NCC_TX - 1) / NCC_TX, (rr + NCC_TY - 1) / NCC_TY), NCC_THREADS, smem, st>>>(
         d_img, ctx->rows, ctx->cols, cs.d_templ, th, tp, a->d_w, sqrt(cs.templ_sum2), rr, rc, a->d_map);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     a->rr = rr;
@@ -344,9 +344,9 @@ extern "C" int abub_bellows_track(abub_ctx* ctx, int slot, int cam, int frame, f
     const size_t n = (size_t)a->rr * a->rc;
     const unsigned long long init[4] = {0xFFFFFFFFull, 0, 0, 0};
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(a->d_red, init, sizeof(init), cudaMemcpyHostToDevice, st));
-    k8_minmax_kernel<<<148 * 4, 256, 0, st>>>(a->d_map, n, a->d_red);
+    ABUB_L(ctx), k8_minmax_kernel<<<148 * 4, 256, 0, st>>>(a->d_map, n, a->d_red);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
-    k8_argmax_kernel<<<148 * 4, 256, 0, st>>>(a->d_map, n, a->d_red);
+    ABUB_L(ctx), k8_argmax_kernel<<<148 * 4, 256, 0, st>>>(a->d_map, n, a->d_red);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     unsigned long long red[4];
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(red, a->d_red, sizeof(red), cudaMemcpyDeviceToHost, st));
@@ -445,7 +445,7 @@ extern "C" int abub_localize_bellows(abub_ctx* ctx, int slot, int cam, int trig,
                                     nullptr, -1);
     if (rc_) return rc_;
     const dim3 blk(32, 8), grd((delta_x + 31) / 32, (delta_y + 7) / 8);
-    k8_veto_kernel<<<grd, blk, 0, ctx->stream>>>(a->d_over, cs.d_sigma, ctx->cols, cs.d_templ, th, tw, cs.templ_pitch, itx, ity, ipx,
+    ABUB_L(ctx), k8_veto_kernel<<<grd, blk, 0, ctx->stream>>>(a->d_over, cs.d_sigma, ctx->cols, cs.d_templ, th, tw, cs.templ_pitch, itx, ity, ipx,
                                                 ipy, start_x, start_y, delta_x, delta_y);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return abub_loc_run_prepared(ctx, a->d_over, loc_thres, out, cap, n_out);

@@ -469,12 +469,12 @@ extern "C" int abub_event_decode_png(abub_ctx* ctx, const abub_png_job* jobs, in
     }
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(a->d_jobs, a->h_jobs.data(), (size_t)n * sizeof(PngDev), cudaMemcpyHostToDevice, st));
     const int nb = (n + K9_WARPS - 1) / K9_WARPS;
-    k9_inflate_kernel<<<nb, 32 * K9_WARPS, 0, st>>>(a->d_jobs, n, (uint32_t)flen, a->d_status);
+    ABUB_L(ctx), k9_inflate_kernel<<<nb, 32 * K9_WARPS, 0, st>>>(a->d_jobs, n, (uint32_t)flen, a->d_status);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     const size_t smem = (size_t)K9_WARPS * 2 * ((ctx->cols + 15) & ~15);
     ABUB_REQUIRE(ctx, smem <= 200 * 1024, "frame too wide for the on-device PNG unfilter");
     ABUB_CHECK_CUDA(ctx, cudaFuncSetAttribute(k9_unfilter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k9_unfilter_kernel<<<nb, 32 * K9_WARPS, smem, st>>>(a->d_jobs, n, ctx->rows, ctx->cols, a->d_status);
+    ABUB_L(ctx), k9_unfilter_kernel<<<nb, 32 * K9_WARPS, smem, st>>>(a->d_jobs, n, ctx->rows, ctx->cols, a->d_status);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(a->h_status.data(), a->d_status, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, st));
     ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(st));
@@ -518,7 +518,7 @@ extern "C" int abub_event_flip_rows(abub_ctx* ctx, const abub_frame_ref* frames,
     for (int i0 = 0; i0 < n; i0 += FLIP_REFS) {
         const int cnt = n - i0 < FLIP_REFS ? n - i0 : FLIP_REFS;
         memcpy(refs.r, frames + i0, (size_t)cnt * sizeof(abub_frame_ref));
-        k9_flip_rows_kernel<<<dim3(32, cnt), 256, 0, ctx->stream>>>(ctx->d_slot_ptrs, refs, ctx->rows, ctx->cols, ctx->max_frames);
+        ABUB_L(ctx), k9_flip_rows_kernel<<<dim3(32, cnt), 256, 0, ctx->stream>>>(ctx->d_slot_ptrs, refs, ctx->rows, ctx->cols, ctx->max_frames);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     return ABUB_OK;

@@ -174,10 +174,10 @@ extern "C" int abub_train_finish_allreduced(abub_ctx* ctx, int cam, void* comm, 
         ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_loc, (size_t)F * stride));
         ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_all, (size_t)world * F * stride));
         ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_loc, 0, (size_t)F * stride, ctx->stream));
-        gather_flagged_kernel<<<(F + 127) / 128, 128, 0, ctx->stream>>>(cs.d_table, n_local, d_idx, F, stride, d_loc);
+        ABUB_L(ctx), gather_flagged_kernel<<<(F + 127) / 128, 128, 0, ctx->stream>>>(cs.d_table, n_local, d_idx, F, stride, d_loc);
         nr = ag(d_loc, d_all, (size_t)F * stride, NCCL_U8, comm, ctx->stream);
         if (!nr)
-            fixup_gathered_kernel<<<(F + 127) / 128, 128, 0, ctx->stream>>>(d_all, d_counts, world, d_idx, F, stride, n,
+            ABUB_L(ctx), fixup_gathered_kernel<<<(F + 127) / 128, 128, 0, ctx->stream>>>(d_all, d_counts, world, d_idx, F, stride, n,
                                                                              cs.d_mean, cs.d_sigma);
         cudaError_t e = cudaStreamSynchronize(ctx->stream);
         cudaFree(d_idx); cudaFree(d_nsel); cudaFree(d_tmp); cudaFree(d_loc); cudaFree(d_all);

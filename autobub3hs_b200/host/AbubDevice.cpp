@@ -104,6 +104,23 @@ int AbubDevice::AcquireSlot(const std::string& key) {
     throw AbubError("no free event slot (max_slots = " + std::to_string(max_slots_) + ")");
 }
 
+int AbubDevice::BindSlot(const std::string& key, int slot) {
+    std::lock_guard<std::recursive_mutex> g(mu_);
+    if (slot < 0 || slot >= (int)slots_.size()) throw AbubError("BindSlot: no such slot");
+    auto it = by_key_.find(key);
+    if (it != by_key_.end()) {
+        if (it->second != slot) throw AbubError("BindSlot: event " + key + " is bound to another slot");
+        slots_[slot].refs++;
+        return slot;
+    }
+    if (slots_[slot].refs != 0) throw AbubError("BindSlot: slot " + std::to_string(slot) + " is in use");
+    slots_[slot] = AbubSlot();
+    slots_[slot].key = key;
+    slots_[slot].refs = 1;
+    by_key_[key] = slot;
+    return slot;
+}
+
 void AbubDevice::ReleaseSlot(const std::string& key) {
     std::lock_guard<std::recursive_mutex> g(mu_);
     auto it = by_key_.find(key);
@@ -159,6 +176,7 @@ void AbubDevice::LoadCamera(int slot, int cam, Parser* parser, const std::string
     const double t3 = now();
     t_read += t1 - t0; t_decode += t2 - t1; t_upload += t3 - t2;      // t_read = context sizing + pinned allocation
     st.nframes[cam] = n;
+    st.resident_upto[cam] = n;
     st.loaded[cam] = true;
 }
 
@@ -272,6 +290,7 @@ void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const
         for (int cam = 0; cam < ncams_; cam++) {
             if (ncam[e][cam] >= 0) {
                 st.nframes[cam] = ncam[e][cam];
+                st.resident_upto[cam] = ncam[e][cam];
                 st.loaded[cam] = true;
                 st.bad[cam].clear();
             }
@@ -307,31 +326,66 @@ std::vector<int> AbubDevice::PrefetchEvents(Parser* parser, const std::vector<st
     } else {
         StageBatch(parser, out, events);
     }
-    // one K1 launch per contiguous slot range
+    AnalyzeBatch(out, training_set_sizes);
+    return out;
+}
+
+static inline double wall_now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+void AbubDevice::MarkResident(int slot, const int* nframes, bool in_hbm) {
+    std::lock_guard<std::recursive_mutex> g(mu_);
+    AbubSlot& st = slots_[slot];
+    for (int c = 0; c < ncams_; c++) {
+        st.nframes[c] = nframes[c];
+        st.loaded[c] = true;
+        st.bad[c].clear();
+        st.resident_upto[c] = in_hbm ? nframes[c] : 0;
+        st.trig_valid[c] = st.loc_valid[c] = false;
+    }
+    if (in_hbm) Check(abub_event_set_nframes(ctx_, slot, nframes), "abub_event_set_nframes");
+}
+
+void AbubDevice::EnsureAllResident(int slot) {
+    std::lock_guard<std::recursive_mutex> g(mu_);
+    AbubSlot& st = slots_[slot];
+    for (int c = 0; c < ncams_; c++)
+        if (st.loaded[c] && st.resident_upto[c] < st.nframes[c]) {
+            Check(abub_event_submit_range(ctx_, slot, c, st.resident_upto[c], st.nframes[c] - st.resident_upto[c]), "abub_event_submit_range");
+            st.resident_upto[c] = st.nframes[c];
+        }
+}
+
+// FindTriggerFrame(startframe = 1) of every (event, camera) of the slots, then LocalizeOMatic of every triggered one.
+void AbubDevice::AnalyzeBatch(const std::vector<int>& out, const int* training_set_sizes) {
+    std::lock_guard<std::recursive_mutex> g(mu_);
+    if (!ctx_) return;
     std::vector<int> sorted(out);
     std::sort(sorted.begin(), sorted.end());
-    size_t i = 0;
-    const auto h0 = std::chrono::steady_clock::now();
-    while (ctx_ && i < sorted.size()) {
+    const double h0 = wall_now();
+    // The trigger search of a contiguous slot range.  Default: the resident early exit (abub_trigger_early) -- K1 over
+    // early_chunk_ frame pairs at a time, K2 after every round, decided cameras drop out, as the reference stops calling
+    // ProcessFrame at the trigger (AnalyzerUnit.cpp:297-300).  early_chunk_ = 0: the full table (one K1 launch over all
+    // pairs, then K2).  A re-trigger (startframe > 1) rebuilds the slot's table on demand (abub_trigger).
+    for (size_t i = 0; i < sorted.size();) {
         size_t j = i + 1;
         while (j < sorted.size() && sorted[j] == sorted[j - 1] + 1) j++;
-        Check(abub_trigger_hist(ctx_, sorted[i], (int)(j - i)), "abub_trigger_hist");
+        const int first = sorted[i], ns = (int)(j - i);
+        if (early_chunk_ > 0) {
+            Check(abub_trigger_early(ctx_, first, ns, early_chunk_), "abub_trigger_early");
+        } else {
+            Check(abub_trigger_hist(ctx_, first, ns), "abub_trigger_hist");
+            Check(abub_trigger_scan(ctx_, first, ns, nullptr), "abub_trigger_scan");
+        }
         i = j;
     }
-    if (ctx_) abub_sync(ctx_);
-    const auto h1 = std::chrono::steady_clock::now();
-    t_hist += std::chrono::duration<double>(h1 - h0).count();
-    if (!ctx_) return out;
-
-    // FindTriggerFrame(startframe = 1) of every (event, camera) of the batch: one K2 launch per slot range
-    i = 0;
-    while (i < sorted.size()) {
+    const double h1 = wall_now();
+    t_hist += h1 - h0;
+    for (size_t i = 0; i < sorted.size();) {
         size_t j = i + 1;
         while (j < sorted.size() && sorted[j] == sorted[j - 1] + 1) j++;
         const int first = sorted[i], ns = (int)(j - i);
         std::vector<int> tr(ns * ncams_), stt(ns * ncams_), lt(ns * ncams_);
         std::vector<double> sg((size_t)ns * ncams_ * max_frames_);
-        Check(abub_trigger_scan(ctx_, first, ns, nullptr), "abub_trigger_scan");
         Check(abub_trigger_results(ctx_, first, ns, tr.data(), stt.data(), lt.data(), sg.data()), "abub_trigger_results");
         for (int s = 0; s < ns; s++)
             for (int c = 0; c < ncams_; c++) {
@@ -344,11 +398,75 @@ std::vector<int> AbubDevice::PrefetchEvents(Parser* parser, const std::vector<st
             }
         i = j;
     }
-    const auto h2 = std::chrono::steady_clock::now();
-    t_scan += std::chrono::duration<double>(h2 - h1).count();
-    if (!training_set_sizes) return out;
+    const double h2 = wall_now();
+    t_scan += h2 - h1;
+    if (training_set_sizes) LocalizeBatch(out, training_set_sizes);
+    t_loc += wall_now() - h2;
+}
 
-    // LocalizeOMatic of every triggered (event, camera): one abub_localize_batch
+// Events whose frames wait in the slots' pinned staging buffers (MarkResident(..., false)): abub_trigger_stream sends them
+// chunk by chunk and stops per camera at the decision; what the localizer still needs (up to trig + n_post) follows.
+long long AbubDevice::StreamBatch(const std::vector<int>& out, const int* training_set_sizes, int chunk_frames) {
+    std::lock_guard<std::recursive_mutex> g(mu_);
+    if (!ctx_) return 0;
+    std::vector<int> sorted(out);
+    std::sort(sorted.begin(), sorted.end());
+    long long frames_sent = 0;
+    const double h0 = wall_now();
+    for (size_t i = 0; i < sorted.size();) {
+        size_t j = i + 1;
+        while (j < sorted.size() && sorted[j] == sorted[j - 1] + 1) j++;
+        const int first = sorted[i], ns = (int)(j - i);
+        std::vector<int> nf(ns * ncams_), tr(ns * ncams_), stt(ns * ncams_), lt(ns * ncams_), sent(ns * ncams_);
+        for (int s = 0; s < ns; s++)
+            for (int c = 0; c < ncams_; c++) nf[s * ncams_ + c] = slots_[first + s].nframes[c];
+        Check(abub_trigger_stream(ctx_, first, ns, nf.data(), chunk_frames, tr.data(), stt.data(), lt.data(), sent.data()), "abub_trigger_stream");
+        for (int s = 0; s < ns; s++)
+            for (int c = 0; c < ncams_; c++) {
+                AbubSlot& st = slots_[first + s];
+                const int k = s * ncams_ + c;
+                st.resident_upto[c] = sent[k];
+                frames_sent += sent[k];
+                if (!st.loaded[c] || st.nframes[c] < 5) continue;
+                st.trig[c] = tr[k]; st.trig_status[c] = stt[k]; st.trig_loc_thres[c] = lt[k];
+                st.sig[c].assign(max_frames_, 0.0);          // the streamed search does not read the per-frame values back
+                st.trig_valid[c] = true;
+            }
+        i = j;
+    }
+    const double h1 = wall_now();
+    t_hist += h1 - h0;
+    if (training_set_sizes) {
+        // frames trig+1 .. trig+n_post of every triggered camera (L3Localizer.cpp:770) that the search did not need
+        for (int s : out)
+            for (int c = 0; c < ncams_; c++) {
+                AbubSlot& st = slots_[s];
+                if (!st.trig_valid[c] || st.trig_status[c] != 0 || st.nframes[c] <= 5) continue;
+                const int need = st.trig[c] + NPost(st.trig[c], st.nframes[c]) + 1;
+                if (need > st.resident_upto[c]) {
+                    Check(abub_event_submit_range(ctx_, s, c, st.resident_upto[c], need - st.resident_upto[c]), "abub_event_submit_range");
+                    frames_sent += need - st.resident_upto[c];
+                    st.resident_upto[c] = need;
+                }
+            }
+        LocalizeBatch(out, training_set_sizes);
+    }
+    t_loc += wall_now() - h1;
+    return frames_sent;
+}
+
+int AbubDevice::NPost(int trig, int N) {                         // L3Localizer.cpp:944-954
+    const int kmax = trig < 29 ? ABUB_MAX_TRACK : 39 - trig;
+    int n_post = 0;
+    for (int k = 1; k <= kmax; k++) {
+        if (trig + k >= N) break;
+        n_post++;
+    }
+    return n_post;
+}
+
+// LocalizeOMatic of every triggered (event, camera): one abub_localize_batch
+void AbubDevice::LocalizeBatch(const std::vector<int>& out, const int* training_set_sizes) {
     std::vector<abub_loc_item> items;
     std::vector<std::pair<int, int>> who;
     for (int s : out)
@@ -358,41 +476,33 @@ std::vector<int> AbubDevice::PrefetchEvents(Parser* parser, const std::vector<st
             const int trig = st.trig[c], N = st.nframes[c];
             int pre = trig - (training_set_sizes[c] < 6 ? 1 : 2);                    // L3Localizer.cpp:919-934
             if (pre < 0) pre = 0;
-            const int kmax = trig < 29 ? ABUB_MAX_TRACK : 39 - trig;                 // :944-954
-            int n_post = 0;
-            for (int k = 1; k <= kmax; k++) {
-                if (trig + k >= N) break;
-                n_post++;
-            }
-            items.push_back(abub_loc_item{s, c, trig, pre, st.trig_loc_thres[c], n_post});
+            items.push_back(abub_loc_item{s, c, trig, pre, st.trig_loc_thres[c], NPost(trig, N)});
             who.push_back({s, c});
         }
-    if (!items.empty()) {
-        std::vector<abub_blob> blobs((size_t)1 << 16);
-        std::vector<int> npf(items.size() * (ABUB_MAX_TRACK + 1));
-        int total = 0;
-        for (;;) {
-            const int rc = abub_localize_batch(ctx_, items.data(), (int)items.size(), blobs.data(), (int)blobs.size(), npf.data(), &total);
-            if (rc == ABUB_E_CAPACITY && blobs.size() < ((size_t)1 << 26)) { blobs.resize((size_t)total + 1024); continue; }
-            Check(rc, "abub_localize_batch");
-            break;
-        }
-        size_t off = 0;
-        for (size_t it = 0; it < items.size(); it++) {
-            AbubSlot& st = slots_[who[it].first];
-            const int c = who[it].second;
-            size_t cnt = 0;
-            for (int k = 0; k <= ABUB_MAX_TRACK; k++) {
-                st.loc_npf[c][k] = npf[it * (ABUB_MAX_TRACK + 1) + k];
-                cnt += (size_t)st.loc_npf[c][k];
-            }
-            st.loc_blobs[c].assign(blobs.begin() + off, blobs.begin() + off + cnt);
-            off += cnt;
-            st.loc_trig[c] = items[it].trig; st.loc_pre[c] = items[it].pre_trig; st.loc_thres[c] = items[it].loc_thres;
-            st.loc_npost[c] = items[it].n_post;
-            st.loc_valid[c] = true;
-        }
+    if (items.empty()) return;
+    if (loc_blobs_.size() < ((size_t)1 << 16)) loc_blobs_.resize((size_t)1 << 16);
+    std::vector<int> npf(items.size() * (ABUB_MAX_TRACK + 1));
+    int total = 0;
+    for (;;) {
+        const int rc = abub_localize_batch(ctx_, items.data(), (int)items.size(), loc_blobs_.data(), (int)loc_blobs_.size(), npf.data(), &total);
+        if (rc == ABUB_E_CAPACITY && loc_blobs_.size() < ((size_t)1 << 26)) { loc_blobs_.resize((size_t)total + 1024); continue; }
+        Check(rc, "abub_localize_batch");
+        break;
     }
-    t_loc += std::chrono::duration<double>(std::chrono::steady_clock::now() - h2).count();
-    return out;
+    size_t off = 0;
+    for (size_t it = 0; it < items.size(); it++) {
+        AbubSlot& st = slots_[who[it].first];
+        const int c = who[it].second;
+        size_t cnt = 0;
+        for (int k = 0; k <= ABUB_MAX_TRACK; k++) {
+            st.loc_npf[c][k] = npf[it * (ABUB_MAX_TRACK + 1) + k];
+            cnt += (size_t)st.loc_npf[c][k];
+        }
+        st.loc_blobs[c].assign(loc_blobs_.begin() + off, loc_blobs_.begin() + off + cnt);
+        off += cnt;
+        st.loc_trig[c] = items[it].trig; st.loc_pre[c] = items[it].pre_trig; st.loc_thres[c] = items[it].loc_thres;
+        st.loc_npost[c] = items[it].n_post;
+        st.loc_valid[c] = true;
+    }
 }
+

@@ -33,6 +33,7 @@ struct AbubSlot {
     bool loaded[8] = {false};        // frames of this camera are in HBM
     int nframes[8] = {0};
     std::vector<int> bad[8];         // frame indices that failed to load/decode
+    int resident_upto[8] = {0};      // frames [0, resident_upto) are in HBM (the streamed search stops sending at the decision)
     // results computed for the whole batch by PrefetchEvents (one K2 launch, one localizer call); an analyzer that asks
     // for exactly this work takes it from here instead of launching its own
     bool trig_valid[8] = {false};
@@ -69,6 +70,8 @@ public:
     // Slot of an event (allocated on first request, freed when the last holder releases it).
     int AcquireSlot(const std::string& key);
     void ReleaseSlot(const std::string& key);
+    // Binds an event key to a given slot (whose frames a producer has filled); the slot must be free.
+    int BindSlot(const std::string& key, int slot);
     AbubSlot& slot(int s) { return slots_[s]; }
 
     // Decodes (in parallel over frames) and uploads the frames of one camera of an event into its slot;
@@ -82,6 +85,20 @@ public:
     // batch (the pre-trigger frame offset depends on TrainingSetSize, L3Localizer.cpp:919-934).
     std::vector<int> PrefetchEvents(Parser* parser, const std::vector<std::string>& keys, const std::vector<std::string>& events,
                                     const int* training_set_sizes = nullptr);
+
+    // The device work of a batch whose frames are resident: FindTriggerFrame(1) of every (event, camera), LocalizeOMatic
+    // of every triggered one (when training_set_sizes is given); results land in the slots' caches.
+    void AnalyzeBatch(const std::vector<int>& slots, const int* training_set_sizes);
+    // Same for slots whose frames wait in the pinned staging buffers: frames cross PCIe chunk_frames at a time and only as
+    // far as the search and the localizer need them.  Returns the number of frames sent.
+    long long StreamBatch(const std::vector<int>& slots, const int* training_set_sizes, int chunk_frames);
+    // Declares the frames of a slot present: in_hbm = a producer wrote them to abub_event_device_ptr; otherwise they are
+    // in the pinned staging buffer (abub_pinned_acquire) and StreamBatch / EnsureAllResident send them.
+    void MarkResident(int slot, const int* nframes, bool in_hbm);
+    void EnsureAllResident(int slot);
+    // frame pairs per round of the resident early exit (abub_trigger_early); 0 = full histogram table
+    void SetEarlyChunk(int chunk) { early_chunk_ = chunk; }
+    static int NPost(int trig, int nframes);                 // L3Localizer.cpp:944-954
 
     // cam<c>_bellows_template.png of `mask_dir` (L3Localizer.cpp:294-295), decoded and handed to the device on first
     // use; false when the file cannot be read or decoded ("template not loadable", :297-301).
@@ -107,6 +124,9 @@ private:
     // stages every camera of the given (slot, event) pairs: all frames are read on all cores; 8-bit grey PNG frames are
     // inflated and unfiltered on the device (abub_event_decode_png), anything else is decoded on the host
     void StageBatch(Parser* parser, const std::vector<int>& slots, const std::vector<std::string>& events);
+    void LocalizeBatch(const std::vector<int>& slots, const int* training_set_sizes);
+    std::vector<abub_blob> loc_blobs_;
+    int early_chunk_ = 6;
     int trigger_metric_ = 0;
     float trigger_threshold_ = 0.f;
     std::map<std::string, int> by_key_;

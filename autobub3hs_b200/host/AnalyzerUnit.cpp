@@ -62,6 +62,7 @@ void AnalyzerUnit::FindTriggerFrame(bool nonStopMode, int startframe) {
             trig = st.trig[CameraNumber]; status = st.trig_status[CameraNumber]; lt = st.trig_loc_thres[CameraNumber];
             sig = st.sig[CameraNumber];
         } else {
+            dev.EnsureAllResident(Slot);                  // a streamed batch stopped sending frames at the first decision
             dev.Check(abub_trigger(dev.ctx(), Slot, CameraNumber, startframe, &trig, &status, &lt, sig.data()), "abub_trigger");
         }
     }

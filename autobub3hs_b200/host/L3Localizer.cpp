@@ -189,6 +189,7 @@ void L3Localizer::LocalizeOMatic(std::string) {
             blobs = st.loc_blobs[c];
             for (int k = 0; k <= ABUB_MAX_TRACK; k++) npf[k] = st.loc_npf[c][k];
         } else {
+            dev.EnsureAllResident(Slot);
             for (;;) {
                 const int rc = abub_localize(dev.ctx(), Slot, CameraNumber, MatTrigFrame, preTrigNum, loc_thres, n_post,
                                              blobs.data(), (int)blobs.size(), npf);

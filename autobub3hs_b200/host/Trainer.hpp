@@ -51,6 +51,9 @@ public:
     /* installs TrainedAvgImage/TrainedSigmaImage/TrainingSetSize of this object on the device (no-op when they
      * already are): lets a caller that filled the public fields by hand use the analyzers */
     void InstallOnDevice();
+    /* the planes of this camera are on the device already (abub_set_background / abub_set_background_from_training by
+     * the caller): only the bookkeeping the analyzers read is set */
+    void AdoptDevicePlanes(int training_set_size) { TrainingSetSize = training_set_size; StatusCode = 0; installed = true; }
     int Camera() const { return camera; }
 };
 

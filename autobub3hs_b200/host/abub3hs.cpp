@@ -22,52 +22,13 @@
 #include "L3Localizer.hpp"
 #include "PICOFormatWriterV4.hpp"
 #include "RawParser.hpp"
+#include "ReconDriver.hpp"
 #include <chrono>
 
 #include "Trainer.hpp"
 #include "ZipParser.hpp"
 
 static bool eventNameOrderSort(std::string a, std::string b) { return std::stoi(a) < std::stoi(b); }
-
-static void advance_cursor() {                     // common/UtilityFunctions.cpp:109-115
-    static int pos = 0;
-    static const char cursor[4] = {'/', '-', '\\', '|'};
-    printf("%c\b", cursor[pos]);
-    fflush(stdout);
-    pos = (pos + 1) % 4;
-}
-
-/* the same routine for every camera (AutoBubStart3.cpp:67-125) */
-static int AnyCamAnalysis(std::string EventID, std::string ImgDir, int camera, bool nonStopPref, Trainer** TrainingData,
-                          OutputWriter** P60Output, std::string out_dir, int actualEventNumber, AnalyzerUnit** AGeneric) {
-    OutputWriter* Pico60Writer = *P60Output;
-    AnalyzerUnit* AnalyzerCGeneric = *AGeneric;
-    try {
-        do {
-            AnalyzerCGeneric->FindTriggerFrame(nonStopPref, AnalyzerCGeneric->MatTrigFrame + 1);
-            if (AnalyzerCGeneric->okToProceed) {
-                AnalyzerCGeneric->LocalizeOMatic(out_dir);
-                if (AnalyzerCGeneric->okToProceed) {
-                    Pico60Writer->stageCameraOutput(AnalyzerCGeneric->BubbleList, camera, AnalyzerCGeneric->MatTrigFrame,
-                                                    actualEventNumber);
-                } else {
-                    Pico60Writer->stageCameraOutputError(camera, -8, actualEventNumber);
-                    break;
-                }
-            } else {
-                Pico60Writer->stageCameraOutputError(camera, AnalyzerCGeneric->TriggerFrameIdentificationStatus,
-                                                     actualEventNumber);
-                break;
-            }
-        } while (AnalyzerCGeneric->BubbleList.size() == 0);
-    } catch (std::exception& e) {
-        /* per-camera failure: -6 (a CUDA error inside an event lands here as well) */
-        std::cout << e.what() << '\n';
-        Pico60Writer->stageCameraOutputError(camera, -6, actualEventNumber);
-    }
-    advance_cursor();
-    return 0;
-}
 
 static std::string usage() {
     return "Usage: abub3hs [-hzme] [-D data_series] [-c cam_mask_dir] [--debug code] -d data_dir -r run_ID -o out_dir\n"
@@ -87,6 +48,7 @@ static std::string usage() {
            "GPU arguments (not in the reference):\n"
            "  --device = Int\t\tCUDA device ordinal (default 0, or the rank with --world)\n"
            "  --batch = Int\t\t\tevents staged on the GPU at once (default 8; 282 MB of HBM each at 4x40 frames of 1680x1050)\n"
+           "  --early_chunk = Int\t\tframe pairs per round of the trigger search's early exit (default 6; 0 = all pairs at once)\n"
            "  --max_frames = Int\t\tframes per camera a slot can hold (default: what the first events hold, at least 40)\n"
            "  --trigger_metric = Str	significance (default) | entropy | entropy_significance: which of the three lines of\n"
            "\t\t\t\tAnalyzerUnit.cpp:226-228 is the live one; --trigger_threshold = Float overrides its entropyThreshold\n"
@@ -96,7 +58,7 @@ static std::string usage() {
 
 struct Options {
     std::string dataLoc, run_number, out_dir, mask_dir, data_series, nccl_id, trigger_metric = "significance", trigger_threshold = "0";
-    int event_user = -1, debug_mode = 0, device = -1, batch = 8, max_frames = 0, rank = 0, world = 1;
+    int event_user = -1, debug_mode = 0, device = -1, batch = 8, early_chunk = 6, max_frames = 0, rank = 0, world = 1;
     bool zipped = false, mask_check = false, help = false;
 };
 
@@ -128,6 +90,7 @@ static bool parse_args(int argc, char** argv, Options& o) {
         else if (a == "--debug") ok = need_int(o.debug_mode);
         else if (a == "--device") ok = need_int(o.device);
         else if (a == "--batch") ok = need_int(o.batch);
+        else if (a == "--early_chunk") ok = need_int(o.early_chunk);
         else if (a == "--max_frames") ok = need_int(o.max_frames);
         else if (a == "--trigger_metric") ok = need(o.trigger_metric);
         else if (a == "--trigger_threshold") ok = need(o.trigger_threshold);
@@ -219,6 +182,7 @@ int main(int argc, char** argv) {
                          : opt.trigger_metric == "entropy" ? ABUB_METRIC_ENTROPY
                          : opt.trigger_metric == "entropy_significance" ? ABUB_METRIC_ENTROPY_SIGNIFICANCE : -1;
         if (metric < 0) throw std::runtime_error("--trigger_metric: significance | entropy | entropy_significance");
+        AbubDevice::Get().SetEarlyChunk(opt.early_chunk);
         AbubDevice::Get().SetTriggerMetric(metric, (float)atof(opt.trigger_threshold.c_str()));
     } catch (std::exception& e) {
         std::cerr << e.what() << std::endl;
@@ -280,6 +244,12 @@ int main(int argc, char** argv) {
     /* Detect mode: batches of events staged on the device, rows appended in event order */
     const std::string part_name = out_dir + "abub3hs_" + run_number + ".txt" + (opt.world > 1 ? ".rank" + std::to_string(opt.rank) : "");
     if (opt.world > 1) { std::ofstream trunc(part_name); }
+    /* rows are committed event by event (AutoBubStart3.cpp:379-383); the file stays open between events */
+    std::ofstream part_out(part_name, std::fstream::out | std::fstream::app);
+    DetectRun drun;
+    drun.run_number = run_number; drun.out_dir = out_dir; drun.mask_dir = mask_dir; drun.eventDir = eventDir;
+    drun.imageFolder = "/Images/"; drun.frameOffset = frameOffset; drun.numCams = numCams; drun.debug_mode = debug_mode;
+    drun.nEvents = nEvents; drun.Trainers = &Trainers; drun.FileParser = FileParser;
     for (int b0 = ev_lo; b0 < ev_hi; b0 += batch) {
         const int b1 = std::min(b0 + batch, ev_hi);
         std::vector<std::string> chunk;
@@ -300,36 +270,10 @@ int main(int argc, char** argv) {
             std::cout << e.what() << std::endl;       /* the analyzers will meet the same problem and report -6 */
         }
         T_stage += wall() - ts0;
-        std::string batch_rows;
-        for (size_t ci = 0; ci < chunk.size(); ci++) {
-            const std::string& ev = chunk[ci];
-            OutputWriter* EventOutput = new OutputWriter(out_dir, run_number, frameOffset, numCams);
-            std::string imageDir = eventDir + ev + "/Images/";
-            int actualEventNumber = atoi(ev.c_str());
-            printf("\rProcessing event: %s / %d  ... ", ev.c_str(), nEvents - 1);
-            advance_cursor();
-            std::vector<AnalyzerUnit*> Analyzers;
-            const double ta0 = wall();
-            for (int icam = 0; icam < numCams; icam++) {
-                Parser* tp = FileParser->clone();
-                Analyzers.push_back(new L3Localizer(ev, imageDir, icam, debug_mode / 100 ? false : true, &Trainers[icam], mask_dir, tp));
-                AnyCamAnalysis(ev, imageDir, icam, debug_mode % 10 ? false : true, &Trainers[icam], &EventOutput, out_dir,
-                               actualEventNumber, &Analyzers[icam]);
-            }
-            const double ta1 = wall();
-            T_analyze += ta1 - ta0;
-            /* rows of the event go to the batch buffer; the file is opened, appended and closed once per staged batch
-             * (the reference commits after each event, :379-383 -- here a crash loses at most the batch in flight) */
-            EventOutput->appendCameraOutput(batch_rows);
-            delete EventOutput;
-            for (int icam = 0; icam < numCams; icam++) delete Analyzers[icam];
-            AbubDevice::Get().ReleaseSlot(keys[ci]);
-            T_write += wall() - ta1;
-        }
-        const double tw0 = wall();
-        OutputWriter::appendToFile(part_name, batch_rows);
-        T_write += wall() - tw0;
+        DetectStagedBatch(drun, chunk, keys, part_out);
     }
+    T_analyze = drun.T_analyze; T_write = drun.T_write;
+    part_out.close();
     printf("run complete.\n");
     if (getenv("ABUB_TIMING")) {
         AbubDevice& d = AbubDevice::Get();

@@ -191,7 +191,9 @@ def render_camera(es: EventSpec, cam: int, background: np.ndarray, seed: int = 0
                 bx, by = bx + k * mv[1], by + k * mv[2]
             scene = bg.copy()
             scene[by:by + pat.shape[0], bx:bx + pat.shape[1]] = pat
-        img = scene + rng.standard_normal((rows, cols), dtype=np.float32) * np.float32(es.noise_sigma)
+        img = rng.standard_normal((rows, cols), dtype=np.float32)         # in place from here on: same values as
+        img *= np.float32(es.noise_sigma)                                  # scene + noise * sigma, fewer passes over memory
+        img += scene
         if f == es.flicker_frame:
             img += 8.0
         for b in es.bubbles.get(cam, ()):
@@ -203,7 +205,9 @@ def render_camera(es: EventSpec, cam: int, background: np.ndarray, seed: int = 0
             yy, xx = np.mgrid[y0:y1, x0:x1]
             disc = (xx - b.cx) ** 2 + (yy - b.cy) ** 2 <= r * r
             img[y0:y1, x0:x1][disc] += b.amp
-        out[f] = np.clip(np.rint(img), 0, 255).astype(np.uint8)
+        np.rint(img, out=img)
+        np.clip(img, 0, 255, out=img)
+        out[f] = img                                                       # exact: integral values in [0, 255]
     return out
 
 
@@ -220,9 +224,14 @@ class SyntheticRun:
     bellows_templates: Optional[List[Optional[np.ndarray]]] = None   # cam<c>_bellows_template.png (bellows_object runs)
 
 
+def _render_job(job):
+    es, c, bg, seed, obj = job
+    return render_camera(es, c, bg, seed, obj)
+
+
 def make_run(n_events: int, classes: Optional[Sequence[str]] = None, rows: int = ROWS, cols: int = COLS,
              ncams: int = NCAMS, nframes: int = NFRAMES, seed: int = 0, run_id: str = RUN_ID,
-             bellows_object: bool = False) -> SyntheticRun:
+             bellows_object: bool = False, workers: int = 1, first_event: int = 0) -> SyntheticRun:
     """`classes[i]` = class of event i (cycled); default all "normal".  bellows_object=True puts the bellows of
     make_bellows_object into every frame of cameras 1 and 3 and provides their templates (BELLOWS_CLASSES move it)."""
     cam_masks, bellows = make_masks(rows, cols, ncams)
@@ -230,12 +239,22 @@ def make_run(n_events: int, classes: Optional[Sequence[str]] = None, rows: int =
     objs = [make_bellows_object(c, rows, cols) if bellows_object else None for c in range(ncams)]
     classes = list(classes) if classes else ["normal"]
     specs, events = [], []
-    for ev in range(n_events):
-        es = make_event_spec(ev, classes[ev % len(classes)], cam_masks, bellows, seed, nframes)
-        specs.append(es)
-        events.append([render_camera(es, c, bgs[c], seed, objs[c]) for c in range(ncams)])
+    for ev in range(first_event, first_event + n_events):
+        specs.append(make_event_spec(ev, classes[ev % len(classes)], cam_masks, bellows, seed, nframes))
+    if workers > 1 and n_events * ncams > 1:
+        # full-size frames cost about a second per camera to render: spread the cameras over processes (same pixels,
+        # every camera has its own generator keyed by (seed, event, camera))
+        import multiprocessing as mp
+        jobs = [(es, c, bgs[c], seed, objs[c]) for es in specs for c in range(ncams)]
+        with mp.get_context("fork").Pool(min(workers, len(jobs))) as pool:
+            flat = pool.map(_render_job, jobs, chunksize=1)
+        events = [flat[i * ncams:(i + 1) * ncams] for i in range(n_events)]
+    else:
+        for es in specs:
+            events.append([render_camera(es, c, bgs[c], seed, objs[c]) for c in range(ncams)])
     templates = [None if o is None else o[0] for o in objs] if bellows_object else None
-    return SyntheticRun(run_id, list(range(n_events)), specs, events, cam_masks, bellows, bgs, FRAME_OFFSET, templates)
+    return SyntheticRun(run_id, list(range(first_event, first_event + n_events)), specs, events, cam_masks, bellows, bgs, FRAME_OFFSET,
+                        templates)
 
 
 # ---------------------------------------------------------------------------------------

@@ -60,6 +60,14 @@ int  abub_sync(abub_ctx* ctx);                      /* cudaStreamSynchronize */
 /* cudaStream_t of the ctx as an opaque pointer (for event timing by the harness). */
 void* abub_stream(abub_ctx* ctx);
 
+/* Harness counters (nothing in the reference): kernels of this library launched so far by the ctx, and device time
+ * per kernel group.  abub_profile(ctx, 1) resets the table and records CUDA events around every group from then on
+ * (on the stream the group is launched on); abub_profile_read fills up to `cap` entries (names are static strings, ms =
+ * summed device time, calls = timed groups) and returns the number of groups.  Reading synchronises on the events. */
+long long abub_launch_count(const abub_ctx* ctx);
+int abub_profile(abub_ctx* ctx, int enable);
+int abub_profile_read(abub_ctx* ctx, int cap, const char** names, double* ms, long long* calls);
+
 /* ---- trained background (Trainer public fields, Trainer.hpp:35-54) ------------- */
 /* Installs TrainedAvgImage / TrainedSigmaImage / TrainingSetSize for one camera;
  * replaces the per-analyzer deep copy `new Trainer(**TrainedData)`
@@ -85,6 +93,10 @@ int abub_event_upload(abub_ctx* ctx, int slot, int cam, const uint8_t* frames, i
 int abub_event_submit_cam(abub_ctx* ctx, int slot, int cam, int nframes);
 /* Same for a single frame (its region of the staging buffer); the frame count of the camera is not changed. */
 int abub_event_upload_frame(abub_ctx* ctx, int slot, int cam, int frame);
+/* Frames [frame_first, frame_first + nframes) of one camera from the staging buffer (asynchronous; frame counts unchanged):
+ * what the localizer still needs after abub_trigger_stream stopped sending at the trigger -- the reference reads frames
+ * trig+1 .. trig+10 in CalculatePostTriggerFrameParams (L3Localizer.cpp:770). */
+int abub_event_submit_range(abub_ctx* ctx, int slot, int cam, int frame_first, int nframes);
 /* Device address of the slot's [cam][frame][rows*cols] stack (for producers that
  * already live on the device) and the matching frame counts. */
 int abub_event_device_ptr(abub_ctx* ctx, int slot, uint8_t** dev_ptr);

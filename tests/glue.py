@@ -116,3 +116,56 @@ def gpu_any_cam_analysis(ctx, slot, cam, nframes, tss, cam_mask, bellows_mask, e
                 return out
     except _Minus6:
         return o.CameraOutput(-6, 0, event_number)
+
+
+def host_recon_text(run, trained, tmp_path, tag, pinned, early_chunk, batch=None):
+    """Trains on the resident events through the C ABI, then runs the full recon through libabubhost.so."""
+    import os
+    from autobub3hs_b200 import capi, synth
+    nev = len(run.events)
+    mask_dir = str(tmp_path / ("masks_" + tag))
+    os.makedirs(mask_dir, exist_ok=True)
+    for c in range(4):
+        synth.write_bmp8(os.path.join(mask_dir, f"cam{c}_mask.bmp"), run.cam_masks[c])
+        synth.write_bmp8(os.path.join(mask_dir, f"cam{c}_bellows_mask.bmp"), run.bellows_masks[c])
+        if run.bellows_templates is not None and run.bellows_templates[c] is not None:
+            synth.write_png8(os.path.join(mask_dir, f"cam{c}_bellows_template.png"), run.bellows_templates[c])
+    out_dir = str(tmp_path / ("out_" + tag))
+    os.makedirs(out_dir, exist_ok=True)
+    rows, cols = run.cam_masks[0].shape
+    nfmax = max(len(st) for ev in run.events for st in ev)
+    with capi.HostRecon(rows, cols, 4, max(nfmax, 5), max_slots=nev, early_chunk=early_chunk) as hr:
+        ctx = hr.ctx
+        nframes = np.zeros((nev, 4), np.int32)
+        for ev in range(nev):
+            for c in range(4):
+                ctx.event_upload(ev, c, run.events[ev][c])
+                nframes[ev, c] = len(run.events[ev][c])
+        tss = []
+        for c in range(4):
+            ctx.train_begin(c)
+            ctx.train_add_slots(c, list(range(nev)))
+            mean, sigma, n, st = ctx.train_finish(c)
+            assert st == trained[c].status and n == trained[c].training_set_size
+            assert np.array_equal(mean, trained[c].avg) and np.array_equal(sigma, trained[c].sigma), f"trained planes of camera {c}"
+            ctx.set_background_from_training(c)
+            tss.append(n)
+        if pinned:
+            for ev in range(nev):
+                pin = ctx.pinned(ev)
+                for c in range(4):
+                    pin[c, :nframes[ev, c]] = run.events[ev][c]
+                # what is in HBM must not help: poison the slot so that only frames really sent can be used
+                for c in range(4):
+                    ctx.event_upload(ev, c, np.full_like(run.events[ev][c], 77))
+        path = hr.begin_run(run.run_id, out_dir, mask_dir, 30, tss)
+        b = batch or nev
+        for e0 in range(0, nev, b):
+            e1 = min(nev, e0 + b)
+            hr.recon(e0, run.event_numbers[e0:e1], nframes[e0:e1], pinned=pinned, chunk_frames=4)
+        stats = hr.read_stats()
+        hr.end_run()
+        text = open(path).read()
+    return text, stats
+
+

@@ -1,0 +1,153 @@
+"""GPU parity at the contract frame size (1050 x 1680).
+
+  * K1 on shapes whose rows are tiled by more than one strip of the TMA kernel (k1_trigger_tma.cu: strips of <= 350
+    output rows), with content on the strip seams and in both edge lanes;
+  * BASELINE.json configs[0]/[1] shape: 20 events x 4 cameras x 40 frames through the C ABI + host library
+    (libabubhost.so: trigger -> localizer -> tracking -> writer) and through the abub3hs binary from BMP files --
+    trained planes and the output text byte-identical to the oracle's;
+  * a slice of configs[4] (stress: >= 20 blobs per frame, noise sigma 6, late, no-trigger, 4- and 5-frame events,
+    flicker) at full size, 16 events, resident and streamed-from-pinned forms.
+The oracle (oracle/cv2_oracle.py) is the checker only."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+HOST = os.path.join(ROOT, "autobub3hs_b200", "host")
+ROWS, COLS = 1050, 1680
+
+
+def _workers():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def _oracle_hists(o, frames, sigma, tss):
+    n = len(frames)
+    H = np.zeros((n, 256), np.uint32)
+    d = 2 if tss >= 6 else 1
+    for j in range(1, n):
+        H[j] = o.hist256(o.process_frame(frames[j], frames[max(j - d, 0)], sigma)).astype(np.uint32)
+    return H
+
+
+@pytest.mark.parametrize("shape", [(1050, 1680), (704, 1680), (705, 1680), (355, 496), (1050, 1696)])
+def test_k1_multi_strip_seams_and_edge_lanes(shape):
+    """nstrips >= 2: strip s covers output rows 2 + s*th .. ; blobs are placed across every seam (rows seam-2 .. seam+2),
+    in columns 0..8 and cols-9..cols-1 (the reflecting edge lanes), and across the 240-column strip boundaries."""
+    from autobub3hs_b200 import capi
+    import oracle.cv2_oracle as o
+    rows, cols = shape
+    nmain = rows - 4
+    nstrips = (nmain + 349) // 350
+    th = (nmain + nstrips - 1) // nstrips
+    assert nstrips >= 2
+    rng = np.random.default_rng(rows * 13 + cols)
+    nfr = 5
+    with capi.Context(rows, cols, ncams=1, max_frames=nfr, max_slots=1) as ctx:
+        for tss in (12, 3):
+            sigma = rng.integers(0, 3, (rows, cols)).astype(np.uint8)
+            ctx.set_background(0, np.zeros_like(sigma), sigma, tss)
+            base = rng.integers(40, 200, (rows, cols)).astype(np.float32)
+            fr = np.clip(base[None] + rng.normal(0, 2.0, (nfr, rows, cols)), 0, 255).astype(np.uint8)
+            for s in range(1, nstrips):
+                seam = 2 + s * th
+                for k, x in enumerate((0, 3, 236, 238, 241, cols // 2, cols - 9, cols - 4)):
+                    y = seam - 2 + (k % 5)
+                    fr[2 + (k % 2):, y:y + 3, x:x + 5] = 250 - 10 * k          # appears in frame 2 or 3
+                fr[3:, seam - 3:seam + 3, 480 - 2:480 + 2] = 5                  # a dark blob on seam x strip corner
+            fr[2:, :4, :6] = 255                                                # corners: the four border rows + edge lanes
+            fr[2:, -4:, -6:] = 0
+            ctx.event_upload(0, 0, fr)
+            ctx.trigger_hist(0, 1)
+            H = ctx.trigger_hist_read(0, 0)
+            Href = _oracle_hists(o, fr, sigma, tss)
+            assert np.array_equal(H[:nfr], Href), (shape, tss)
+            assert int(Href[2:, 1:].sum()) > 100
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def abub3hs():
+    from autobub3hs_b200 import build
+    build.build()
+    subprocess.check_call(["make", "-s", "-C", HOST])
+    return os.path.join(HOST, "abub3hs")
+
+
+@pytest.fixture(scope="module")
+def config1():
+    """BASELINE.json configs[0]: 20 events x 4 cameras x 40 frames of 1050x1680, the event mix of the benchmark."""
+    from autobub3hs_b200 import synth
+    import oracle.cv2_oracle as o
+    classes = ["normal"] * 20
+    classes[7] = "multi"
+    classes[13] = "notrigger"
+    run = synth.make_run(20, classes, rows=ROWS, cols=COLS, seed=11, workers=_workers())
+    trained = o.train_all(run.events, 4)
+    text, recs = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks)
+    return run, trained, o.write_header() + text, recs
+
+
+from tests.glue import host_recon_text as _host_recon_text  # noqa: E402
+
+
+def test_config1_c_abi_resident(config1, tmp_path):
+    run, trained, want, _ = config1
+    text, _ = _host_recon_text(run, trained, tmp_path, "res", pinned=False, early_chunk=6)
+    assert text == want
+    text0, _ = _host_recon_text(run, trained, tmp_path, "res0", pinned=False, early_chunk=0, batch=7)
+    assert text0 == want
+
+
+def test_config1_c_abi_streamed_from_pinned(config1, tmp_path):
+    run, trained, want, recs = config1
+    text, stats = _host_recon_text(run, trained, tmp_path, "pin", pinned=True, early_chunk=6)
+    assert text == want
+    total = sum(len(st) for ev in run.events for st in ev)
+    assert 0 < stats["frames_sent"] < total          # the early exit kept frames off the link
+
+
+def test_config1_abub3hs_from_bmp_files(config1, abub3hs, tmp_path):
+    from autobub3hs_b200 import synth
+    run, _, want, _ = config1
+    synth.write_run(run, str(tmp_path / "data"), str(tmp_path / "masks"))
+    out = str(tmp_path / "out")
+    os.makedirs(out)
+    r = subprocess.run([abub3hs, "-D", "40l-19", "-d", str(tmp_path / "data"), "-r", run.run_id, "-o", out, "-c", str(tmp_path / "masks"),
+                        "--batch", "10"], capture_output=True, text=True, timeout=1200)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert open(os.path.join(out, f"abub3hs_{run.run_id}.txt")).read() == want
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def stress16():
+    """Slice of BASELINE.json configs[4] at full size: 16 events (E = 256 would take the oracle ~10 minutes)."""
+    from autobub3hs_b200 import synth
+    import oracle.cv2_oracle as o
+    classes = ["multi", "highnoise", "late", "notrigger", "short4", "short5", "flicker", "normal",
+               "multi", "highnoise", "late", "notrigger", "flicker", "multi", "highnoise", "normal"]
+    run = synth.make_run(16, classes, rows=ROWS, cols=COLS, seed=29, workers=_workers())
+    trained = o.train_all(run.events, 4)
+    text, recs = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks)
+    return run, trained, o.write_header() + text, recs
+
+
+def test_stress_slice_resident_and_streamed(stress16, tmp_path):
+    run, trained, want, recs = stress16
+    codes = {a.out.status for rr in recs for a in rr}
+    assert {-3, -9, -8} <= codes, codes                     # no-trigger, 4-frame and 5-frame events are in the slice
+    nblobs = max(len(a.out.bubbles) for rr in recs for a in rr)
+    assert nblobs >= 15, nblobs                              # the multi events keep many tracked bubbles
+    text, _ = _host_recon_text(run, trained, tmp_path, "res", pinned=False, early_chunk=6)
+    assert text == want
+    text, _ = _host_recon_text(run, trained, tmp_path, "pin", pinned=True, early_chunk=6, batch=5)
+    assert text == want

@@ -219,3 +219,36 @@ def test_bellows_run_with_and_without_template(abub3hs, tmp_path):
     want2, _ = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks, 30, None)
     assert want2 != want
     assert _run(abub3hs, str(tmp_path / "data"), str(tmp_path / "out2"), str(tmp_path / "masks")) == o.write_header() + want2
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_host_library_recon_in_memory(small_run, small_trained, tmp_path, pinned):
+    """libabubhost.so (include/abub_host.h): the abub3hs detect loop over events placed in HBM slots / pinned staging
+    buffers -- every event class at 264x420 (generic-pitch kernels), one batch and ragged batches."""
+    import oracle.cv2_oracle as o
+    from tests import glue
+    run, trained = small_run, small_trained
+    want, _ = o.run_detect(run.run_id, run.event_numbers, run.events, trained, run.cam_masks, run.bellows_masks)
+    want = o.write_header() + want
+    for batch, early in ((None, 6), (3, 0), (1, 4)):
+        text, stats = glue.host_recon_text(run, trained, tmp_path, f"b{batch}e{early}", pinned=pinned, early_chunk=early, batch=batch)
+        assert text == want, (batch, early)
+
+
+def test_host_library_recon_bellows_and_tma_pitch(tma_run, tmp_path):
+    import oracle.cv2_oracle as o
+    from autobub3hs_b200 import synth
+    from tests import glue
+    run, gold = tma_run
+    trained = o.train_all(run.events, 4)
+    for pinned in (False, True):
+        text, _ = glue.host_recon_text(run, trained, tmp_path, f"tma{int(pinned)}", pinned=pinned, early_chunk=6, batch=4)
+        assert text == gold
+    brun = synth.make_run(6, ["normal", "bellows", "bellows_bubble", "notrigger", "bellows", "normal"], rows=264, cols=420, seed=5,
+                          bellows_object=True)
+    btr = o.train_all(brun.events, 4)
+    want, recs = o.run_detect(brun.run_id, brun.event_numbers, brun.events, btr, brun.cam_masks, brun.bellows_masks, 30,
+                              brun.bellows_templates)
+    for pinned in (False, True):
+        text, _ = glue.host_recon_text(brun, btr, tmp_path, f"bel{int(pinned)}", pinned=pinned, early_chunk=6, batch=3)
+        assert text == o.write_header() + want
