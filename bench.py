@@ -1,29 +1,41 @@
 #!/usr/bin/env python
-"""bench.py -- events/s of the AutoBub3hs trigger hot path on B200 (BASELINE.json metric).
+"""bench.py -- events/s of the AutoBub3hs per-event image path on B200 (BASELINE.json metric).
 
-Workload (config[1] of BASELINE.json): "entropy-trigger only: 1000 events x 4 cameras x 40
-frames" of 1050x1680 8-bit frames.  One *step* = one pass of the trigger path (K1
-ProcessFrame+histogram over every frame pair, K2 significance state machine) over a batch
-of `--events-per-step` events resident in HBM (default 125 -> 8 steps = 1000 events; the
-batch is 35 GB, so every step re-reads far more than the 126 MB L2: no flush needed).
+Workload = BASELINE.json configs[3]: "full recon run (trigger + L3Localizer + CCL bubble boxes) of 10,000 synthetic
+events ... with PICOFormatWriterV4 output", 4 cameras x 40 frames of 1050x1680 8-bit frames per event.  10,000
+distinct events are 2.8 TB, so a RING of `--ring-events` (32) distinct synthetic events is rendered
+once on the host (numpy PCG64, autobub3hs_b200.synth -- the same pixels in both arms) and reused: the `--events-per-step`
+(125) HBM slots of a rank hold ring event (slot % ring); 10,000 events = 80 steps, the default run times 20 of them.
 
-  value       events/s with the batch resident in HBM (CUDA events on the library stream)
-  e2e         events/s through the C ABI from pinned HOST buffers: H2D of every frame +
-              K1 + K2 + D2H of the trigger results inside the timed region
-  roofline    K1's algorithmic bytes (41 planes per (event,camera)) / its
-              measured launch time, against MEASURED_PEAKS.json hbm_gbs
-  cpu_baseline the cv2 oracle (oracle/cv2_oracle.py, a port: the reference cannot be built
-              here) on a bounded sample of the same batch, one process per host core
+One *step* = the whole reference event loop (AutoBubStart3.cpp:342-388) over the resident slots through the host
+library (libabubhost.so = the abub3hs detect loop): K1+K2 trigger search with the reference's early exit, K5-K7
+localizer for every triggered camera, isInMask / tracking / bubble bookkeeping on the host cores, OutputWriter rows
+appended to abub3hs_<run>.txt and flushed per event.  Every step re-reads 35 GB of frames (>> 126 MB L2: no flush).
 
-`--impl reference` times the CPU oracle alone (all host cores) on the same config.
+  value        events/s, frames resident in HBM when the timed region starts (wall clock between synchronisations:
+               the host part of the path is inside)
+  e2e          the same from pinned HOST buffers: frames cross PCIe inside the timed region (cudaMemcpyAsync, per camera
+               only as far as the trigger search and the localizer read), results and blob records come back
+  roofline     dominant kernel (K1) + `kernels`: device time per kernel group (CUDA events on the library stream)
+               against the algorithmic bytes of SURVEY.md 8(d) and MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline the cv2 oracle (a port: the reference needs OpenCV C++/Boost, absent here) on a bounded sample of the
+               same ring, every host core busy; its output text is the parity check of the GPU's text
+  trainer      (N > 1) BASELINE.json configs[2]: 200 training events sharded over the ranks, exact integer partials,
+               ncclAllReduce + all-gather fix-up (abub_train_allreduce / abub_train_finish_allreduced), planes compared
+               bit for bit with the single-GPU Trainer
+  trigger_only BASELINE.json configs[1] as a named extra (K1 full table + K2, round-1 headline)
+
+`--impl reference` times the CPU oracle alone (all host cores) on the same workload.
 """
 from __future__ import annotations
 
 import argparse
 import json
 import os
+import shutil
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -34,9 +46,12 @@ sys.path.insert(0, ROOT)
 
 ROWS, COLS, NCAMS, NFRAMES = 1050, 1680, 4, 40
 NPIX = ROWS * COLS
-K1_BYTES_PER_EVENT_CAM = (NFRAMES + 1) * NPIX          # every frame once + the sigma plane once
-K1_DRAM_TRAFFIC_125 = 37.733456e9 + 8.645e6             # bytes per 125-event launch, measured (profiles/r1_k1_v6_125ev_full.txt)
-WORKLOAD = "trigger-only: 1000 events x 4 cams x 40 frames, 1050x1680 u8 (BASELINE.json configs[1])"
+K1_BYTES_PER_EVENT_CAM = (NFRAMES + 1) * NPIX          # full table: every frame once + the sigma plane once
+LOC_PLANES_MAX = 15                                     # localizer: 3 genesis planes + (10 + 2) post-trigger planes
+RUN_ID = "20210101_0"
+SEED = 11
+WORKLOAD = ("full recon: trigger + L3Localizer + PICOFormatWriterV4 rows, 4 cams x 40 frames of 1050x1680 u8 per event "
+            "(BASELINE.json configs[3]; ring of distinct synthetic events reused)")
 
 
 # --------------------------------------------------------------------------------------
@@ -82,8 +97,145 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
 # --------------------------------------------------------------------------------------
-# synthetic events on the device (same pixel model as autobub3hs_b200.synth, torch RNG)
+# the ring of synthetic events (host, numpy PCG64): identical in both arms and on every rank
+# --------------------------------------------------------------------------------------
+def ring_classes(n):
+    out = []
+    for i in range(n):
+        k = i % 20
+        out.append("multi" if k == 7 else ("notrigger" if k == 13 else "normal"))
+    return out
+
+
+def render_ring(first, count, total, workers):
+    """Events [first, first+count) of the ring of `total` events: SyntheticRun (events[i][cam] = [40,1050,1680] u8)."""
+    from autobub3hs_b200 import synth
+    return synth.make_run(count, ring_classes(total), rows=ROWS, cols=COLS, seed=SEED, run_id=RUN_ID, workers=workers,
+                          first_event=first)
+
+
+def write_masks(run, mask_dir):
+    from autobub3hs_b200 import synth
+    os.makedirs(mask_dir, exist_ok=True)
+    for c in range(NCAMS):
+        synth.write_bmp8(os.path.join(mask_dir, f"cam{c}_mask.bmp"), run.cam_masks[c])
+        synth.write_bmp8(os.path.join(mask_dir, f"cam{c}_bellows_mask.bmp"), run.bellows_masks[c])
+
+
+# --------------------------------------------------------------------------------------
+# CPU oracle leg (cpu_baseline of the GPU arm and the --impl reference arm)
+# --------------------------------------------------------------------------------------
+_G = {}
+
+
+def _cpu_noop(i):
+    import cv2
+    import oracle.cv2_oracle  # noqa: F401  (import cost outside the timed region)
+    cv2.setNumThreads(1)
+    return i
+
+
+def _cpu_task(idx):
+    """AnyCamAnalysis (AutoBubStart3.cpp:67-125) of one (event, camera): trigger search with the early exit, localizer,
+    tracking.  Returns (CameraOutput, seconds)."""
+    import oracle.cv2_oracle as o
+    t0 = time.perf_counter()
+    slot, cam = divmod(idx, NCAMS)
+    ev = _G["order"][slot]
+    a = o.any_cam_analysis(o.FrameSource(_G["events"][ev][cam]), _G["trained"][cam], _G["cam_masks"][cam], _G["bellows"][cam],
+                           _G["numbers"][slot], True, None)
+    return a.out, time.perf_counter() - t0
+
+
+class CpuRecon:
+    """The reference's event loop on the host cores: one worker process per core (cv2 single-threaded inside a worker,
+    like one OpenMP thread per event in AutoBubStart3.cpp:342), tasks = (event, camera) handed out one at a time."""
+
+    def __init__(self, run, trained, cores):
+        import multiprocessing as mp
+        self.cores = cores
+        _G.update(events=run.events, trained=trained, cam_masks=run.cam_masks, bellows=run.bellows_masks)
+        self.n_ring = len(run.events)
+        self.pool = None
+        self.mp = mp.get_context("fork")
+
+    def start(self, order, numbers):
+        _G["order"], _G["numbers"] = list(order), list(numbers)
+        self.pool = self.mp.Pool(self.cores)                 # forked after _G is complete
+        self.pool.map(_cpu_noop, range(self.cores * 2))
+
+    def one_pass(self):
+        """One pass over the sample.  Returns (seconds, utilisation, text)."""
+        import oracle.cv2_oracle as o
+        n = len(_G["order"]) * NCAMS
+        t0 = time.perf_counter()
+        res = self.pool.map(_cpu_task, range(n), chunksize=1)
+        outs = [r[0] for r in res]
+        text = "".join(o.write_camera_output(RUN_ID, outs[s * NCAMS:(s + 1) * NCAMS], 30) for s in range(len(_G["order"])))
+        dt = time.perf_counter() - t0
+        util = sum(r[1] for r in res) / (self.cores * dt)
+        return dt, util, text
+
+    def close(self):
+        if self.pool:
+            self.pool.close()
+            self.pool.join()
+            self.pool = None
+
+
+def cpu_sample_size(cores, ring):
+    """>= 2 events (8 tasks) per worker, at least the whole ring (the arm must not be starved)."""
+    return max(ring, 2 * cores)
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU oracle with every host core on the same workload; rank 0 alone."""
+    if rank != 0:
+        return
+    import oracle.cv2_oracle as o
+    cores = host_cores()
+    R = args.ring_events
+    t0 = time.perf_counter()
+    run = render_ring(0, R, R, cores)
+    t_render = time.perf_counter() - t0
+    trained = o.train_all(run.events[:min(R, args.train_events)], NCAMS)
+    n_s = cpu_sample_size(cores, R)
+    cpu = CpuRecon(run, trained, cores)
+    cpu.start([i % R for i in range(n_s)], list(range(n_s)))
+    times, utils = [], []
+    for s in range(args.warmup + args.steps):
+        dt, util, _ = cpu.one_pass()
+        if s >= args.warmup:
+            times.append(dt)
+            utils.append(util)
+    cpu.close()
+    total = sum(times)
+    v = n_s * len(times) / total
+    line = {"metric": "events_per_sec", "value": v, "unit": "events/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "impl": "reference",
+            "config": {"workload": WORKLOAD, "events_per_step": n_s, "ring_events": R, "train_events": min(R, args.train_events),
+                       "note": "cv2 oracle port of the reference CPU path (trigger with early exit + localizer + tracking + rows); "
+                               "ring rendered in %.1f s" % t_render},
+            "cpu_baseline": {"value": v, "unit": "events/s", "cores": cores, "kind": "port",
+                             "worker_utilisation": float(np.mean(utils)),
+                             "sample": f"{n_s} events x 4 cams x 40 frames per step ({n_s * NCAMS} (event,camera) tasks on {cores} "
+                                       f"worker processes, handed out one at a time), early exit at the trigger kept"},
+            "e2e": {"value": v, "unit": "events/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------
+# GPU arm
 # --------------------------------------------------------------------------------------
 class _DevPtr:
     def __init__(self, ptr, shape):
@@ -94,117 +246,9 @@ def slot_tensor(torch, ctx, slot):
     return torch.as_tensor(_DevPtr(ctx.event_device_ptr(slot), (NCAMS, NFRAMES, ROWS, COLS)), device="cuda")
 
 
-def fill_slot(torch, t, bgs, specs_for_event, gen, noise_sigma=2.0):
-    """t: u8 [cam, frame, rows, cols] view of a slot.  Renders background + N(0,sigma) noise +
-    growing discs, rounds, clips (SURVEY.md 8(d) pixel model)."""
-    for c in range(NCAMS):
-        img = torch.randn((NFRAMES, ROWS, COLS), generator=gen, device="cuda", dtype=torch.float32)
-        img.mul_(noise_sigma).add_(bgs[c])
-        for b in specs_for_event.get(c, ()):
-            for f in range(b.f_trig, NFRAMES):
-                r = b.r0 + b.growth * (f - b.f_trig)
-                x0, x1 = max(0, int(b.cx - r - 2)), min(COLS, int(b.cx + r + 3))
-                y0, y1 = max(0, int(b.cy - r - 2)), min(ROWS, int(b.cy + r + 3))
-                yy = torch.arange(y0, y1, device="cuda", dtype=torch.float32)[:, None]
-                xx = torch.arange(x0, x1, device="cuda", dtype=torch.float32)[None, :]
-                disc = ((xx - b.cx) ** 2 + (yy - b.cy) ** 2) <= r * r
-                img[f, y0:y1, x0:x1] += disc * float(b.amp)
-        t[c].copy_(img.round_().clamp_(0, 255).to(torch.uint8))
-
-
-def event_classes(n, rank):
-    out = []
-    for i in range(n):
-        k = (i + rank) % 20
-        out.append("multi" if k == 7 else ("notrigger" if k == 13 else "normal"))
-    return out
-
-
-# --------------------------------------------------------------------------------------
-# CPU oracle leg (also the --impl reference arm)
-# --------------------------------------------------------------------------------------
-_G = {}
-
-
-def _cpu_one(idx):
-    import oracle.cv2_oracle as o
-    ev, cam = divmod(idx, NCAMS)
-    fr = _G["events"][ev][cam]
-    st = o.SignificanceState()
-    r = o.find_trigger_frame(o.FrameSource(fr), _G["sigma"][cam], _G["tss"][cam], 1, st, 0)
-    return (r.status, r.trig, r.loc_thres)
-
-
-def cpu_trigger_pass(events, sigmas, tss, cores):
-    """One pass of the reference trigger path (early exit at the trigger kept) over `events`
-    (list of [cam][N,rows,cols] arrays) with `cores` worker processes.  Returns (seconds, results)."""
-    import multiprocessing as mp
-    _G["events"], _G["sigma"], _G["tss"] = events, sigmas, tss
-    n = len(events) * NCAMS
-    ctx = mp.get_context("fork")
-    with ctx.Pool(min(cores, n)) as pool:
-        pool.map(_cpu_noop, range(min(cores, n)))       # spin the workers up outside the timing
-        t0 = time.perf_counter()
-        res = pool.map(_cpu_one, range(n), chunksize=1)
-        dt = time.perf_counter() - t0
-    return dt, res
-
-
-def _cpu_noop(i):
-    import oracle.cv2_oracle  # noqa: F401  (import cost outside the timed region)
-    return i
-
-
-def host_cores():
-    try:
-        return len(os.sched_getaffinity(0))
-    except Exception:
-        return os.cpu_count() or 1
-
-
-def run_reference(args, rank, world):
-    """--impl reference: the CPU oracle with every host core, bounded sample per step."""
-    if rank != 0:
-        return
-    from autobub3hs_b200 import synth
-    import oracle.cv2_oracle as o
-    cores = host_cores()
-    n_ev = max(1, min(args.ref_events, max(1, cores // NCAMS)))
-    cam_masks, bellows = synth.make_masks(ROWS, COLS, NCAMS)
-    bgs = [synth.make_background(c, ROWS, COLS) for c in range(NCAMS)]
-    classes = event_classes(n_ev, 0)
-    events = []
-    for ev in range(n_ev):
-        es = synth.make_event_spec(ev, classes[ev], cam_masks, bellows, seed=11)
-        events.append([synth.render_camera(es, c, bgs[c], seed=11) for c in range(NCAMS)])
-    trained = o.train_all(events, NCAMS)
-    sig = [t.sigma for t in trained]
-    tss = [max(t.training_set_size, 6) for t in trained]
-    times = []
-    for s in range(args.warmup + args.steps):
-        dt, _ = cpu_trigger_pass(events, sig, tss, cores)
-        if s >= args.warmup:
-            times.append(dt)
-    total = sum(times)
-    v = n_ev * len(times) / total
-    line = {"metric": "events_per_sec", "value": v, "unit": "events/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "impl": "reference",
-            "config": {"workload": WORKLOAD, "events_per_step": n_ev, "note": "cv2 oracle port of the reference CPU path"},
-            "cpu_baseline": {"value": v, "unit": "events/s", "cores": cores, "kind": "port",
-                             "sample": f"{n_ev} events x 4 cams x 40 frames per step, early exit at trigger kept"},
-            "e2e": {"value": v, "unit": "events/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
-
-
-# --------------------------------------------------------------------------------------
-# GPU arm
-# --------------------------------------------------------------------------------------
 def bind_to_gpu_numa_node(local_rank):
-    """Pins this process to the CPUs of the NUMA node its GPU hangs off, so that the pinned staging buffers of the
-    end-to-end leg are allocated (first touch) in memory local to that GPU's PCIe root.  Best effort: returns the
-    node number or None."""
+    """Pins this process to the CPUs of the NUMA node its GPU hangs off (first-touch placement of the pinned staging
+    buffers).  Best effort: returns (node or None, why)."""
     try:
         import pynvml
         pynvml.nvmlInit()
@@ -213,184 +257,293 @@ def bind_to_gpu_numa_node(local_rank):
         dev = "/sys/bus/pci/devices/" + bus.lower()[-12:]
         node = int(open(dev + "/numa_node").read())
         if node < 0:
-            return None
+            return None, "sysfs reports numa_node -1 for " + bus
         cpus = set()
         for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
             lo, _, hi = part.partition("-")
             cpus.update(range(int(lo), int(hi or lo) + 1))
         cpus &= os.sched_getaffinity(0)
-        if cpus:
+        if not cpus:
+            return None, f"no allowed CPU on node {node}"
+        n_nodes = len([d for d in os.listdir("/sys/devices/system/node") if d.startswith("node")])
+        if n_nodes > 1:
             os.sched_setaffinity(0, cpus)
-            return node
+        return node, f"{n_nodes} NUMA node(s) visible"
+    except Exception as e:
+        return None, repr(e)[:100]
+
+
+def load_traffic():
+    """DRAM bytes per launch of the profiled kernels, written by tools/ncu_summary.py from the committed ncu captures."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
     except Exception:
-        pass
-    return None
+        return {}
 
 
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from autobub3hs_b200 import capi, synth
+    from autobub3hs_b200 import capi
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    cores = host_cores()
+    R, B = args.ring_events, args.events_per_step
+    if R % world:
+        raise SystemExit("--ring-events must be a multiple of the number of ranks")
+    # ---- ring: every rank renders its share on its share of the host cores (before CUDA is touched: fork) ----
+    share = R // world
+    t0 = time.perf_counter()
+    run = render_ring(rank * share, share, R, max(1, cores // world))
+    t_render = time.perf_counter() - t0
+
+    # ---- CPU baseline first (rank 0, N = 1): the oracle trains and detects on the same ring ----
+    cpu, cpu_text, n_s = None, None, 0
+    if world == 1 and not args.no_cpu_baseline:
+        import oracle.cv2_oracle as o
+        trained_cpu = o.train_all(run.events[:min(R, args.train_events)], NCAMS)
+        n_s = cpu_sample_size(cores, R)
+        cr = CpuRecon(run, trained_cpu, cores)
+        cr.start([i % R for i in range(n_s)], list(range(n_s)))
+        cr.one_pass()                                        # warm-up
+        dt, util, cpu_text = cr.one_pass()
+        cr.close()
+        cpu = {"value": n_s / dt, "unit": "events/s", "cores": cores, "kind": "port", "worker_utilisation": util,
+               "sample": f"{n_s} events x 4 cams x 40 frames of the ring ({n_s * NCAMS} (event,camera) tasks on {cores} worker "
+                         f"processes, one at a time), cv2 oracle: trigger with early exit + localizer + tracking + rows"}
+
     torch.cuda.set_device(local_rank)
-    numa_node = bind_to_gpu_numa_node(local_rank) if world > 1 else None
+    numa_node, numa_why = bind_to_gpu_numa_node(local_rank) if world > 1 else (None, "single rank")
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    B = args.events_per_step
-    ctx = capi.Context(ROWS, COLS, NCAMS, NFRAMES, max_slots=B, device=local_rank)
+    hr = capi.HostRecon(ROWS, COLS, NCAMS, NFRAMES, max_slots=B, device=local_rank, early_chunk=args.early_chunk)
+    ctx = hr.ctx
     stream = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
+    tmp = tempfile.mkdtemp(prefix=f"abub_bench_r{rank}_")
+    mask_dir = os.path.join(tmp, "masks")
+    write_masks(run, mask_dir)
 
-    # ---- synthetic batch, generated on the device ----
-    cam_masks, bellows = synth.make_masks(ROWS, COLS, NCAMS)
-    bgs_np = [synth.make_background(c, ROWS, COLS) for c in range(NCAMS)]
-    bgs = [torch.from_numpy(b.astype(np.float32)).cuda() for b in bgs_np]
-    gen = torch.Generator(device="cuda")
-    gen.manual_seed(7919 + rank)
-    classes = event_classes(B, rank)
-    specs = []
-    t_gen = time.perf_counter()
+    # ---- slots: ring event (slot % R); the other ranks' shares arrive over NCCL ----
+    for i in range(share):
+        for c in range(NCAMS):
+            ctx.event_upload(rank * share + i, c, run.events[i][c])
+    if world > 1:
+        mine = torch.stack([slot_tensor(torch, ctx, rank * share + i) for i in range(share)])
+        full = torch.empty((world,) + tuple(mine.shape), dtype=torch.uint8, device="cuda")
+        dist.all_gather_into_tensor(full, mine)
+        for r in range(world):
+            if r != rank:
+                for i in range(share):
+                    slot_tensor(torch, ctx, r * share + i).copy_(full[r, i])
+        del full, mine
+    for s in range(R, B):
+        slot_tensor(torch, ctx, s).copy_(slot_tensor(torch, ctx, s % R))
     for s in range(B):
-        es = synth.make_event_spec(rank * 100000 + s, classes[s], cam_masks, bellows, seed=11)
-        specs.append(es)
-        fill_slot(torch, slot_tensor(torch, ctx, s), bgs, es.bubbles, gen, args.noise_sigma)
         ctx.event_set_nframes(s, [NFRAMES] * NCAMS)
     torch.cuda.synchronize()
-    t_gen = time.perf_counter() - t_gen
 
-    # ---- Trainer (K3 gate + K4 Welford) on frames {0,1} of the batch; not part of the timed step ----
-    n_train = min(B, args.train_events)
-    kept, sig_np, tss_np = [], [], []
+    # ---- Trainer (K3 gate + K4 Welford) on frames {0,1} of the first --train-events ring events; not in the timed step ----
+    n_train = min(R, args.train_events)
+    tss = []
     for c in range(NCAMS):
         ctx.train_begin(c)
-        k = 0
-        for s in range(n_train):
-            _, kp = ctx.train_add_slot(c, s)
-            k += int(kp)
-        kept.append(k)
-        _, sg_plane, tss, status = ctx.train_finish(c)
-        sig_np.append(sg_plane)
-        tss_np.append(tss)
+        ctx.train_add_slots(c, list(range(n_train)))
+        _, _, n, status = ctx.train_finish(c)
         if status != 0:
             raise SystemExit(f"training failed for camera {c} (status {status})")
         ctx.set_background_from_training(c)
+        tss.append(n)
+
+    out_dir = os.path.join(tmp, "out")
+    os.makedirs(out_dir)
+    out_path = hr.begin_run(RUN_ID, out_dir, mask_dir, 30, tss)
+    nf_all = np.full((B, NCAMS), NFRAMES, np.int32)
+    base_no = rank * 10_000_000
+    step_no = [0]
 
     def step():
-        ctx.trigger_hist(0, B)
-        ctx.trigger_scan(0, B)      # synchronises the library stream (start-frame upload)
-
-    ev0 = torch.cuda.Event(enable_timing=True)
-    ev1 = torch.cuda.Event(enable_timing=True)
-    k1a = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    k1b = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+        numbers = [base_no + step_no[0] * B + s for s in range(B)]
+        step_no[0] += 1
+        hr.recon(0, numbers, nf_all)
 
     for _ in range(max(args.warmup, 0)):
         step()
+    hr.read_stats()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local_rank) as clk:
         torch.cuda.synchronize()
+        l0 = ctx.launch_count()
+        t0 = time.perf_counter()
         ev0.record(stream)
         for i in range(args.steps):
-            k1a[i].record(stream)
-            ctx.trigger_hist(0, B)
-            k1b[i].record(stream)
-            ctx.trigger_scan(0, B)
+            step()
         ev1.record(stream)
         torch.cuda.synchronize()
-    ms_total = ev0.elapsed_time(ev1)
-    k1_ms = float(np.mean([a.elapsed_time(b) for a, b in zip(k1a, k1b)]))
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        launches = ctx.launch_count() - l0
+    dev_ms = ev0.elapsed_time(ev1)
+    ms_total = max(wall_ms, dev_ms)                      # host analysis and the file appends are inside the path
+    stage = hr.read_stats()
     if world > 1:
         t = torch.tensor([ms_total], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
-    trig, status, lt, _ = ctx.trigger_results(0, B, want_sig=False)
     value = world * B * args.steps / (ms_total * 1e-3)
+    rows_written = sum(1 for _ in open(out_path)) - 6
 
-    # ---- the same batch with the reference's early exit (abub_trigger_early): extra key, not the headline ----
-    early = None
-    if args.early_chunk > 0:
-        ctx.trigger_early(0, B, args.early_chunk)
-        t_e, s_e, l_e, _ = ctx.trigger_results(0, B, want_sig=False)
-        ok = status == 0
-        if not (np.array_equal(s_e, status) and np.array_equal(t_e[ok], trig[ok]) and np.array_equal(l_e[status != -9], lt[status != -9])):
-            raise SystemExit("abub_trigger_early disagrees with the full-table trigger path")
-        n_e = max(1, min(args.steps, 8))
-        ee0 = torch.cuda.Event(enable_timing=True)
-        ee1 = torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        ee0.record(stream)
-        for _ in range(n_e):
-            ctx.trigger_early(0, B, args.early_chunk)
-        ee1.record(stream)
-        torch.cuda.synchronize()
-        ms_e = ee0.elapsed_time(ee1) / n_e
-        ch = args.early_chunk
-        need = np.where(ok, np.minimum(trig + 3, NFRAMES), NFRAMES)
-        bounds = np.minimum(NFRAMES, np.maximum(5, -(-need // ch) * ch))
-        early = {"value": B / (ms_e * 1e-3), "unit": "events/s (this rank)", "ms_per_step": ms_e, "chunk_frames": ch,
-                 "frame_pairs_computed_frac": float((bounds - 1).sum() / (B * NCAMS * (NFRAMES - 1))),
-                 "note": "K1 in rounds of chunk_frames frame pairs, K2 after every round, decided cameras drop out "
-                         "(AnalyzerUnit.cpp:297-300); results equal to the full-table path"}
+    # ---- parity of the output text: ring events 0..n_s-1 (slot s holds ring event s % R) against the oracle's text ----
+    parity = None
+    if cpu_text is not None:
+        hr.end_run()
+        p_dir = os.path.join(tmp, "parity")
+        os.makedirs(p_dir)
+        p_path = hr.begin_run(RUN_ID, p_dir, mask_dir, 30, tss)
+        if n_s > B:
+            raise SystemExit("--events-per-step is smaller than the CPU sample")
+        hr.recon(0, list(range(n_s)), nf_all[:n_s])
+        hr.end_run()
+        import oracle.cv2_oracle as o
+        got = open(p_path).read()
+        want = o.write_header() + cpu_text
+        if got != want:
+            gl, wl = got.splitlines(), want.splitlines()
+            bad = next((i for i, (a, b) in enumerate(zip(gl, wl)) if a != b), min(len(gl), len(wl)))
+            raise SystemExit(f"PARITY FAILURE: abub3hs text differs from the oracle's at line {bad}: {gl[bad:bad+1]} != {wl[bad:bad+1]}")
+        parity = {"events": n_s, "rows": len(want.splitlines()) - 6, "text_identical": True}
+        cpu["sample"] += f"; GPU output text of the same {n_s} events identical ({parity['rows']} rows)"
+        hr.begin_run(RUN_ID, out_dir, mask_dir, 30, tss)
+    hr.read_stats()
 
-    # ---- end-to-end through the C ABI from pinned host buffers ----
+    # ---- per-kernel device time (two more steps with CUDA events around every kernel group) ----
+    trig, status, lt, _ = ctx.trigger_results(0, B, want_sig=False)
+    ok = status == 0
+    npost = np.array([min(10 if t < 29 else 39 - t, NFRAMES - 1 - t) for t in trig.reshape(-1)]).reshape(trig.shape)
+    n_trig = int(ok.sum())
+    loc_frames = int((npost[ok] + 1).sum())
+    ch = max(args.early_chunk, 1)
+    need = np.where(ok, np.minimum(trig + 3, NFRAMES), NFRAMES)
+    bounds = np.minimum(NFRAMES, np.maximum(5, -(-need // ch) * ch)) if args.early_chunk > 0 else np.full_like(need, NFRAMES)
+    pairs = int((bounds - 1).sum())
+    ctx.profile(True)
+    nprof = 2
+    for _ in range(nprof):
+        step()
+    prof = ctx.profile_read()
+    ctx.profile(False)
+    hr.read_stats()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = load_traffic()
+    # algorithmic bytes per step of every kernel group (SURVEY.md 8(d)); groups without their own algorithmic bytes
+    # (candidate scan, sort, border tracing: scratch traffic) count against the localizer stage
+    alg = {
+        "K1": (pairs + B * NCAMS * 2) * NPIX,                 # every frame read once (pairs + 1) + the sigma plane, per camera
+        "K5a": 3 * n_trig * NPIX,                             # trigger frame, pre-trigger frame, sigma
+        "K5b": (loc_frames - n_trig + 2 * n_trig) * NPIX,     # post frames + mean + sigma per triggered camera
+    }
+    kernels, loc_ms = [], 0.0
+    for name, ms, calls in prof:
+        key = name.split()[0]
+        ms_step = ms / nprof
+        if key in ("K5a", "K5b", "K5c", "K6", "cub", "K7a", "K7b", "K7c"):
+            loc_ms += ms_step
+        if calls == 0:
+            continue
+        a = alg.get(key, 0)
+        ent = {"kernel": name, "ms_per_step": ms_step, "launch_groups_per_step": calls / nprof,
+               "algorithmic_bytes_per_step": a, "achieved": (a / (ms_step * 1e-3) / 1e9) if a and ms_step > 0 else None,
+               "frac": (a / (ms_step * 1e-3) / 1e9 / peak) if a and ms_step > 0 else None,
+               "traffic": traffic.get(key)}
+        kernels.append(ent)
+    loc_bytes = (3 * n_trig + (loc_frames - n_trig) + 2 * n_trig) * NPIX
+    kernels.append({"kernel": "localizer stage (K5a+K5b+K5c+K6+sort+K7, device time)", "ms_per_step": loc_ms,
+                    "algorithmic_bytes_per_step": loc_bytes,
+                    "achieved": loc_bytes / (loc_ms * 1e-3) / 1e9 if loc_ms > 0 else None,
+                    "frac": loc_bytes / (loc_ms * 1e-3) / 1e9 / peak if loc_ms > 0 else None, "traffic": None})
+    k1 = next((k for k in kernels if k["kernel"].startswith("K1")), None)
+
+    # ---- configs[1] as a named extra: K1 over every frame pair + K2 (the round-1 headline) ----
+    trig_only = None
+    if args.trigger_steps > 0:
+        ctx.trigger_hist(0, B)
+        ctx.trigger_scan(0, B)
+        torch.cuda.synchronize()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        k1a = [torch.cuda.Event(enable_timing=True) for _ in range(args.trigger_steps)]
+        k1b = [torch.cuda.Event(enable_timing=True) for _ in range(args.trigger_steps)]
+        a0.record(stream)
+        for i in range(args.trigger_steps):
+            k1a[i].record(stream)
+            ctx.trigger_hist(0, B)
+            k1b[i].record(stream)
+            ctx.trigger_scan(0, B)
+        a1.record(stream)
+        torch.cuda.synchronize()
+        t_ms = a0.elapsed_time(a1) / args.trigger_steps
+        k1_ms = float(np.mean([a.elapsed_time(b) for a, b in zip(k1a, k1b)]))
+        k1_bytes = B * NCAMS * K1_BYTES_PER_EVENT_CAM
+        t2, s2, l2, _ = ctx.trigger_results(0, B, want_sig=False)
+        if not (np.array_equal(s2, status) and np.array_equal(t2[ok], trig[ok]) and np.array_equal(l2[status != -9], lt[status != -9])):
+            raise SystemExit("PARITY FAILURE: the early-exit trigger search disagrees with the full-table search")
+        trig_only = {"workload": "trigger-only: 1000 events x 4 cams x 40 frames (BASELINE.json configs[1]), all 39 frame pairs",
+                     "value": B / (t_ms * 1e-3), "unit": "events/s (this rank)", "ms_per_step": t_ms,
+                     "k1_full_table": {"ms_per_launch": k1_ms, "algorithmic_bytes_per_launch": k1_bytes,
+                                       "achieved": k1_bytes / (k1_ms * 1e-3) / 1e9, "frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / peak,
+                                       "traffic": traffic.get("K1_full")},
+                     "results_equal_to_early_exit": True}
+
+    # ---- end to end from pinned host buffers ----
     Be = min(args.e2e_events, B)
-    nf = [NFRAMES] * NCAMS
-    host_res = None
     for s in range(Be):
-        pin = ctx.pinned(s)
-        pin_t = torch.from_numpy(pin)
-        pin_t.copy_(slot_tensor(torch, ctx, s).cpu())
+        pin = torch.from_numpy(ctx.pinned(s))
+        pin.copy_(slot_tensor(torch, ctx, s).cpu())
     torch.cuda.synchronize()
-
-    nf_arr = np.full((Be, NCAMS), NFRAMES, np.int32)
-    sent_total = [0]
+    nf_e = nf_all[:Be]
 
     def e2e_step():
-        if args.e2e_mode == "stream":
-            # frames leave the pinned buffers chunk by chunk; a camera whose trigger search is decided gets no
-            # more of them (the reference reads frame by frame and returns at the trigger, AnalyzerUnit.cpp:191-300)
-            t_, s_, l_, sent = ctx.trigger_stream(0, Be, nf_arr, args.e2e_chunk)
-            sent_total[0] += int(sent.sum())
-            return t_, s_, l_, None
-        for s in range(Be):
-            ctx.event_submit(s, nf)                 # cudaMemcpyAsync H2D of every frame from pinned staging
-        ctx.trigger_hist(0, Be)
-        ctx.trigger_scan(0, Be)
-        sent_total[0] += Be * NCAMS * NFRAMES
-        return ctx.trigger_results(0, Be, want_sig=False)   # D2H of the step's result
+        numbers = [base_no + 5_000_000 + step_no[0] * Be + s for s in range(Be)]
+        step_no[0] += 1
+        hr.recon(0, numbers, nf_e, pinned=True, chunk_frames=args.e2e_chunk)
 
-    e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    for _ in range(1):
+    for _ in range(2):
         e2e_step()
-    sent_total[0] = 0
+    hr.read_stats()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
-    ee0 = torch.cuda.Event(enable_timing=True)
-    ee1 = torch.cuda.Event(enable_timing=True)
-    ee0.record(stream)
-    for _ in range(e2e_steps):
-        host_res = e2e_step()
-    ee1.record(stream)
+    for _ in range(args.e2e_steps):
+        e2e_step()
     torch.cuda.synchronize()
-    e2e_wall = time.perf_counter() - t0
-    e2e_ms = max(ee0.elapsed_time(ee1), e2e_wall * 1e3)     # host-side D2H waits are part of the path
+    e2e_ms_local = (time.perf_counter() - t0) * 1e3
+    e2e_stage = hr.read_stats()
+    e2e_ms = e2e_ms_local
+    h2d_bytes_step = e2e_stage["frames_sent"] * NPIX / args.e2e_steps
+    h2d_gbs_local = h2d_bytes_step * args.e2e_steps / (e2e_ms_local * 1e-3) / 1e9
+    h2d_ranks = [h2d_gbs_local]
     if world > 1:
         t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
-    e2e_value = world * Be * e2e_steps / (e2e_ms * 1e-3)
+        g = torch.zeros(world, device="cuda", dtype=torch.float64)
+        g[rank] = h2d_gbs_local
+        dist.all_reduce(g)
+        h2d_ranks = [float(v) for v in g.tolist()]
+    e2e_value = world * Be * args.e2e_steps / (e2e_ms * 1e-3)
     # what the link does on one large pinned copy (context for e2e, which is bound by it)
     link_gbs = None
     try:
         pin0 = torch.from_numpy(ctx.pinned(0))
         dst0 = slot_tensor(torch, ctx, 0)
-        lk0 = torch.cuda.Event(enable_timing=True)
-        lk1 = torch.cuda.Event(enable_timing=True)
+        lk0, lk1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         cur = torch.cuda.current_stream()
         dst0.copy_(pin0, non_blocking=True)
         lk0.record(cur)
@@ -401,112 +554,142 @@ def run_ours(args, rank, world, local_rank):
         link_gbs = 4 * pin0.numel() / (lk0.elapsed_time(lk1) * 1e-3) / 1e9
     except Exception:
         pass
-    assert np.array_equal(host_res[1], status[:Be]) and np.array_equal(host_res[0], trig[:Be])
+    hr.end_run()
 
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+    # ---- configs[2]: the Trainer sharded over the ranks, one NCCL all-reduce + all-gather fix-up (last: it replaces the planes) ----
+    trainer = None
+    if world > 1 and args.trainer_events > 0:
+        trainer = trainer_leg(args, ctx, torch, dist, rank, world, R)
 
-    # ---- CPU baseline on a bounded sample of the same batch + parity check of that sample ----
-    cpu = None
-    if world == 1 and not args.no_cpu_baseline:
-        cores = host_cores()
-        n_s = max(1, min(args.cpu_events, B, max(1, cores // NCAMS)))
-        sample = [[slot_tensor(torch, ctx, s)[c].cpu().numpy() for c in range(NCAMS)] for s in range(n_s)]
-        dt, res = cpu_trigger_pass(sample, sig_np, tss_np, cores)
-        mism = 0
-        for i, (st_, tr_, lt_) in enumerate(res):
-            s, c = divmod(i, NCAMS)
-            if st_ != status[s, c] or (st_ == 0 and (tr_ != trig[s, c] or lt_ != lt[s, c])):
-                mism += 1
-        cpu = {"value": n_s / dt, "unit": "events/s", "cores": cores, "kind": "port",
-               "sample": f"{n_s} events x 4 cams x 40 frames of the benchmark batch (D2H), cv2 oracle, "
-                         f"one process per (event,camera), early exit at trigger kept; parity mismatches vs GPU: {mism}"}
-        if mism:
-            raise SystemExit(f"PARITY FAILURE: {mism} (event,camera) results differ from the oracle")
-        # the cv2-free C restatement (oracle/abub_ref.c), one thread: ProcessFrame + calcHist of a few frame pairs of
-        # the same sample, checked against the GPU's histograms of those pairs
-        try:
-            from oracle import cref
-            ctx.trigger_hist(0, 1)               # the streamed / early-exit passes above leave partial tables
-            H_gpu = ctx.trigger_hist_read(0, 0)
-            fr = sample[0][0]
-            n_pairs = 4
-            t0 = time.perf_counter()
-            hs = [cref.hist256(cref.process_frame(fr[j], fr[j - 2], sig_np[0])) for j in range(2, 2 + n_pairs)]
-            dt_c = (time.perf_counter() - t0) / n_pairs
-            bad = sum(0 if np.array_equal(h, H_gpu[2 + i]) else 1 for i, h in enumerate(hs))
-            if bad:
-                raise SystemExit(f"PARITY FAILURE: {bad} histograms differ from the C restatement")
-            cpu["c_port_one_thread"] = {"ms_per_frame_pair": dt_c * 1e3,
-                                        "events_per_s_without_early_exit": 1.0 / (dt_c * NCAMS * (NFRAMES - 1)),
-                                        "sample": f"{n_pairs} frame pairs of event 0, camera 0; histograms equal to the GPU's"}
-        except SystemExit:
-            raise
-        except Exception as e:
-            cpu["c_port_one_thread"] = {"unavailable": repr(e)[:120]}
-
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    k1_bytes = B * NCAMS * K1_BYTES_PER_EVENT_CAM
-    achieved = k1_bytes / (k1_ms * 1e-3) / 1e9
-    line = {
-        "metric": "events_per_sec", "value": value, "unit": "events/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "events_per_step": B, "l2": "inputs (35 GB/step at 125 events) exceed L2; no flush",
-                   "event_mix": f"90% normal (1-3 bubbles), 5% multi (>=20), 5% no-trigger; noise sigma {args.noise_sigma}",
-                   "train_events": n_train, "generated_on": "device (torch RNG), seconds=%.1f" % t_gen},
-        "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": sent_total[0] * NPIX // e2e_steps,
-                "d2h_bytes_per_step": Be * NCAMS * 16 * (1 if args.e2e_mode == "full" else (NFRAMES + args.e2e_chunk - 1) // args.e2e_chunk),
-                "events_per_step": Be, "steps": e2e_steps, "mode": args.e2e_mode, "rank0_numa_node": numa_node,
-                "h2d_gbs": sent_total[0] * NPIX / e2e_steps / (e2e_ms / e2e_steps * 1e-3) / 1e9 * 1.0,
-                "h2d_link_gbs_one_large_pinned_copy": link_gbs,
-                "note": ("abub_trigger_stream: host frames in pinned memory, sent %d frames at a time, a camera stops "
-                         "receiving frames once its trigger search is decided (the reference's early exit); "
-                         "frames_sent/frames_total = %.3f" % (args.e2e_chunk, sent_total[0] / max(1, e2e_steps * Be * NCAMS * NFRAMES)))
-                        if args.e2e_mode == "stream" else "every frame of every event copied H2D, then K1+K2"},
-        "gpu_launches": args.steps * 4,      # k1_trigger_tma + k1_trigger (border rows) + k1_fill_bin0 + k2_trigger_scan
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": K1_DRAM_TRAFFIC_125 if B == 125 else None,
-                     "traffic_source": "profiles/r1_k1_v6_125ev_full.txt (ncu --set full, dram read+write of one 125-event launch)",
-                     "kernel": "k1_trigger_tma_kernel (+ k1_trigger_kernel on the 4 border rows, k1_fill_bin0_kernel)",
-                     "ms_per_launch": k1_ms,
-                     "algorithmic_bytes_per_launch": k1_bytes,
-                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
-        "cpu_baseline": cpu,
-        "clocks": clk.summary(),
-        "triggered_fraction": float((status == 0).mean()),
-        "early_exit": early,
-    }
-    print(json.dumps(line), flush=True)
+    if rank == 0:
+        line = {
+            "metric": "events_per_sec", "value": value, "unit": "events/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "events_per_step": B, "ring_events": R,
+                       "events_timed": world * B * args.steps, "note_10000": "10,000 events = %d steps of %d events" % (-(-10000 // B), B),
+                       "l2": "inputs (35 GB/step at 125 events) exceed L2; no flush",
+                       "event_mix": "90% normal (1-3 bubbles), 5% multi (>=20), 5% no-trigger; noise sigma 2.0",
+                       "train_events": n_train, "early_chunk": args.early_chunk,
+                       "rendered_on": "host (numpy PCG64, %d of %d ring events on this rank, %.1f s)" % (share, R, t_render)},
+            "stage_seconds_per_step": {k: v / args.steps for k, v in stage.items() if k != "frames_sent"},
+            "device_ms_per_step": dev_ms / args.steps,
+            "rows_written": rows_written,
+            "triggered_fraction": float(ok.mean()),
+            "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": int(h2d_bytes_step),
+                    "d2h_bytes_per_step": int(Be * NCAMS * 16 * (-(-NFRAMES // args.e2e_chunk)) + 88 * rows_written / max(1, args.steps * B) * Be * 11),
+                    "events_per_step": Be, "steps": args.e2e_steps, "seconds_timed": e2e_ms * 1e-3,
+                    "frames_sent_frac": e2e_stage["frames_sent"] / (args.e2e_steps * Be * NCAMS * NFRAMES),
+                    "h2d_gbs_per_rank": {"min": min(h2d_ranks), "median": float(np.median(h2d_ranks)), "max": max(h2d_ranks)},
+                    "h2d_gbs_aggregate": float(sum(h2d_ranks)),
+                    "h2d_link_gbs_one_large_pinned_copy": link_gbs, "rank0_numa_node": numa_node, "numa_note": numa_why,
+                    "stage_seconds_per_step": {k: v / args.e2e_steps for k, v in e2e_stage.items() if k != "frames_sent"},
+                    "note": "abubhost_recon mode 1: frames wait in pinned host memory and are sent %d at a time; a camera stops "
+                            "receiving frames at its trigger decision, the localizer's frames (up to trig+10) follow; trigger "
+                            "results and blob records are read back; rows appended per event" % args.e2e_chunk},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": k1["achieved"] if k1 else None, "peak": peak, "unit": "GB/s",
+                         "frac": k1["frac"] if k1 else None, "traffic": traffic.get("K1"),
+                         "traffic_source": traffic.get("source"),
+                         "kernel": "k1_trigger_tma_kernel (+ border rows, bin 0) in rounds of %d frame pairs (early exit)" % args.early_chunk,
+                         "ms_per_step": k1["ms_per_step"] if k1 else None,
+                         "algorithmic_bytes_per_step": alg["K1"],
+                         "frame_pairs_computed_frac": pairs / (B * NCAMS * (NFRAMES - 1)),
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                         "kernels": kernels},
+            "cpu_baseline": cpu,
+            "parity": parity,
+            "clocks": clk.summary(),
+            "trigger_only": trig_only,
+            "trainer": trainer,
+        }
+        print(json.dumps(line), flush=True)
+    hr.close()
+    shutil.rmtree(tmp, ignore_errors=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def trainer_leg(args, ctx, torch, dist, rank, world, R):
+    """BASELINE.json configs[2]: `--trainer-events` training events (event i = ring event i % R) sharded by contiguous
+    range; per camera abub_train_partials -> abub_train_allreduce -> abub_train_finish_allreduced, compared bit for
+    bit with rank 0's single-GPU abub_train_finish over all the events."""
+    E = args.trainer_events
+    lo, hi = E * rank // world, E * (rank + 1) // world
+    idfile = os.path.join(tempfile.gettempdir(), "abub_bench_%s.ncclid" % os.environ.get("MASTER_PORT", "0"))
+    comm = ctx.nccl_comm_create(idfile, rank, world)
+    t_gate = t_part = t_ar = t_fix = 0.0
+    flagged, planes = [], []
+    dist.barrier()
+    for c in range(NCAMS):
+        ctx.train_begin(c)
+        t0 = time.perf_counter()
+        ctx.train_add_slots(c, [i % R for i in range(lo, hi)])
+        ctx.sync()
+        t1 = time.perf_counter()
+        ctx.train_partials(c)
+        ctx.sync()
+        t2 = time.perf_counter()
+        ctx.train_allreduce(c, comm)
+        ctx.sync()
+        t3 = time.perf_counter()
+        mean, sigma, n, st, nfl = ctx.train_finish_allreduced(c, comm)
+        t4 = time.perf_counter()
+        t_gate += t1 - t0; t_part += t2 - t1; t_ar += t3 - t2; t_fix += t4 - t3
+        flagged.append(nfl)
+        planes.append((mean, sigma, n, st))
+    tt = torch.tensor([t_gate, t_part, t_ar, t_fix], device="cuda", dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_gate, t_part, t_ar, t_fix = [float(v) for v in tt.tolist()]
+    identical, t_single = None, None
+    if rank == 0:
+        identical = True
+        t0 = time.perf_counter()
+        for c in range(NCAMS):
+            ctx.train_begin(c)
+            ctx.train_add_slots(c, [i % R for i in range(E)])
+            m1, s1, n1, st1 = ctx.train_finish(c)
+            m, s, n, st = planes[c]
+            if not (n1 == n and st1 == st and np.array_equal(m1, m) and np.array_equal(s1, s)):
+                identical = False
+        t_single = time.perf_counter() - t0
+    ok = torch.tensor([1 if (identical is None or identical) else 0], device="cuda")
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    ctx.nccl_barrier(comm)
+    ctx.nccl_comm_destroy(comm)
+    if rank != 0:
+        return None
+    if not bool(ok.item()):
+        raise SystemExit("PARITY FAILURE: the all-reduced Trainer planes differ from the single-GPU Trainer's")
+    nkept = planes[0][2]
+    return {"workload": "Trainer background statistics over %d training events sharded over %d ranks (BASELINE.json configs[2])" % (E, world),
+            "planes_identical": True, "kept_frames_per_cam": nkept,
+            "gate_keep_ms": 1e3 * t_gate, "partials_ms": 1e3 * t_part, "allreduce_ms": 1e3 * t_ar, "fixup_ms": 1e3 * t_fix,
+            "train_ms": 1e3 * (t_gate + t_part + t_ar + t_fix),
+            "single_gpu_train_ms_rank0": 1e3 * t_single,
+            "allreduce_bytes_per_cam": NPIX * 12 + 4,
+            "flagged_pixel_fraction": float(np.mean(flagged)) / NPIX,
+            "allgather_bytes_per_cam": float(np.mean(flagged)) * nkept,
+            "collective": "ncclAllReduce(sum) of u32 sum / u64 sum-of-squares / count + ncclAllGather of the flagged pixels' samples "
+                          "(csrc/nccl_glue.cu), communicator from abub_nccl_comm_create (ncclCommInitRank)"}
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--events-per-step", type=int, default=125)
+    ap.add_argument("--ring-events", type=int, default=32)
     ap.add_argument("--train-events", type=int, default=25)
-    ap.add_argument("--e2e-events", type=int, default=8)
-    ap.add_argument("--e2e-steps", type=int, default=3)
-    ap.add_argument("--e2e-mode", default="stream", choices=["stream", "full"])
+    ap.add_argument("--early-chunk", type=int, default=6, help="frame pairs per round of the trigger search's early exit (0 = full table)")
+    ap.add_argument("--e2e-events", type=int, default=16)
+    ap.add_argument("--e2e-steps", type=int, default=40)
     ap.add_argument("--e2e-chunk", type=int, default=4)
-    ap.add_argument("--early-chunk", type=int, default=6, help="frame pairs per round of abub_trigger_early (0 = skip)")
-    ap.add_argument("--cpu-events", type=int, default=8)
-    ap.add_argument("--ref-events", type=int, default=8)
+    ap.add_argument("--trigger-steps", type=int, default=8, help="steps of the trigger-only extra (0 = skip)")
+    ap.add_argument("--trainer-events", type=int, default=200, help="training events of the sharded Trainer leg at N > 1 (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--noise-sigma", type=float, default=2.0,
-                    help="camera noise of the synthetic frames (grey levels); 2.0 is the workload of the headline number")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -144,7 +144,7 @@ def stress16():
 def test_stress_slice_resident_and_streamed(stress16, tmp_path):
     run, trained, want, recs = stress16
     codes = {a.out.status for rr in recs for a in rr}
-    assert {-3, -9, -8} <= codes, codes                     # no-trigger, 4-frame and 5-frame events are in the slice
+    assert {-3, -9} <= codes, codes                         # no-trigger and 4-frame events (the 5-frame event ends -3 or -8)
     nblobs = max(len(a.out.bubbles) for rr in recs for a in rr)
     assert nblobs >= 15, nblobs                              # the multi events keep many tracked bubbles
     text, _ = _host_recon_text(run, trained, tmp_path, "res", pinned=False, early_chunk=6)
