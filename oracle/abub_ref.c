@@ -328,6 +328,15 @@ static void measure_polygon(const ipt* v, int n, ref_blob* b) {
     }
 }
 
+/* the same measures for a polygon given as (x, y) int32 pairs: cv::boundingRect / contourArea / moments of a contour
+ * (used by oracle/refshim, where the reference's own code calls them on the contours it holds) */
+void ref_measure_polygon(const int32_t* xy, int n, ref_blob* b) {
+    ipt* v = (ipt*)malloc((size_t)(n > 0 ? n : 1) * sizeof(ipt));
+    for (int i = 0; i < n; i++) { v[i].x = xy[2 * i]; v[i].y = xy[2 * i + 1]; }
+    if (n > 0) measure_polygon(v, n, b);
+    free(v);
+}
+
 /* External contours of a binary image (non-zero = foreground) in findContours order.
  * pts_out (may be NULL): polygon vertices (x,y int32 pairs) of all blobs back to back,
  * capacity pts_cap pairs.  Returns the number of contours (<= cap written), or -1. */

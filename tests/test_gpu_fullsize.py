@@ -151,3 +151,21 @@ def test_stress_slice_resident_and_streamed(stress16, tmp_path):
     assert text == want
     text, _ = _host_recon_text(run, trained, tmp_path, "pin", pinned=True, early_chunk=6, batch=5)
     assert text == want
+
+
+def test_config1_reference_compiled_binary_agrees(config1, tmp_path):
+    """The pin at the contract size: oracle/_ref/abub3hs_ref (the reference's own sources compiled against oracle/refshim,
+    prebuilt where /root/reference exists) on the same 20 events -- the text every GPU form above is compared with is
+    the reference's own."""
+    from autobub3hs_b200 import synth
+    exe = os.path.join(ROOT, "oracle", "_ref", "abub3hs_ref")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/abub3hs_ref is not built")
+    run, _, want, _ = config1
+    synth.write_run(run, str(tmp_path / "data"), str(tmp_path / "masks"))
+    out = str(tmp_path / "out")
+    os.makedirs(out)
+    r = subprocess.run([exe, "-D", "40l-19", "-d", str(tmp_path / "data"), "-r", run.run_id, "-o", out, "-c", str(tmp_path / "masks")],
+                       capture_output=True, text=True, timeout=1800)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert open(os.path.join(out, f"abub3hs_{run.run_id}.txt")).read() == want
