@@ -529,7 +529,8 @@ class Context:
 # points of host/ReconDriver.cpp -- the full recon of events produced in memory, through the abub3hs detect loop.
 # ---------------------------------------------------------------------------------------
 HOST_LIB_PATH = os.path.join(_HERE, "host", "libabubhost.so")
-HOST_EXPORTS = ["abubhost_open", "abubhost_begin_run", "abubhost_recon", "abubhost_end_run", "abubhost_close", "abubhost_last_error"]
+HOST_EXPORTS = ["abubhost_open", "abubhost_begin_run", "abubhost_recon", "abubhost_end_run", "abubhost_close", "abubhost_last_error",
+                "abubhost_drain", "abubhost_set_threads", "abubhost_stats"]
 _hostlib = None
 
 
@@ -546,6 +547,9 @@ def load_host() -> C.CDLL:
     lib.abubhost_begin_run.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, ip]
     lib.abubhost_recon.argtypes = [C.c_int, C.c_int, ip, ip, C.c_int, C.c_int, C.POINTER(C.c_double)]
     lib.abubhost_end_run.argtypes = []
+    lib.abubhost_drain.argtypes = []
+    lib.abubhost_set_threads.argtypes = [C.c_int, C.c_int]
+    lib.abubhost_stats.argtypes = [C.POINTER(C.c_double)]
     lib.abubhost_close.argtypes = []
     lib.abubhost_close.restype = None
     lib.abubhost_last_error.argtypes = []
@@ -587,8 +591,22 @@ class HostRecon:
         if rc != 0:
             raise AbubError("abubhost_recon: " + self.hl.abubhost_last_error().decode())
 
+    def set_threads(self, threads: int = 0, sub_batch: int = 32) -> None:
+        """Host threads of the event loop (0 = OpenMP default) and events per device->host hand-over; call before begin_run."""
+        self.hl.abubhost_set_threads(threads, sub_batch)
+
+    def drain(self) -> None:
+        """Returns when every submitted event has been analysed and its rows are in the file."""
+        if self.hl.abubhost_drain() != 0:
+            raise AbubError("abubhost_drain: " + self.hl.abubhost_last_error().decode())
+
     def read_stats(self, reset: bool = True) -> dict:
-        d = {k: float(self.stats[i]) for i, k in enumerate(self.STAT_KEYS)}
+        """Seconds per stage since the previous call (drains the pipeline first) + frames sent over PCIe."""
+        t = (C.c_double * 5)()
+        if self.hl.abubhost_stats(t) != 0:
+            raise AbubError("abubhost_stats: " + self.hl.abubhost_last_error().decode())
+        d = {k: float(t[i]) for i, k in enumerate(self.STAT_KEYS[:5])}
+        d["frames_sent"] = float(self.stats[5])
         if reset:
             for i in range(8):
                 self.stats[i] = 0.0

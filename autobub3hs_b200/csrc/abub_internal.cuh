@@ -19,6 +19,7 @@ struct abub_cam_state {
     uint32_t* d_k32 = nullptr;      // per pixel (255-t)|(765-t)<<16, t=min(6*sigma,255)  (K1 stage A)
     uint8_t*  d_t8 = nullptr;       // t = min(6*sigma,255)
     int16_t*  d_k16 = nullptr;      // per pixel -(255+t) as s16 (TMA trigger kernel stage A)
+    int16_t*  d_nt16 = nullptr;     // per pixel -t as s16 (localizer post-trigger kernel: relu(|a - avg| - t) in one VIADDMNMX)
     int training_set_size = 0;
     bool has_background = false;
     // training: kept frames live in device chunks until abub_train_finish
@@ -108,7 +109,10 @@ struct abub_ctx {
     void*     loc = nullptr;        // localizer arena (k5_localize.cu)
     void*     bel = nullptr;        // bellows-veto arena (k8_bellows.cu)
     void*     png = nullptr;        // on-device PNG decode arena (k9_png.cu)
-    void*     d_tmaps = nullptr;    // CUtensorMap[2*max_slots + 2*ncams] (k1_trigger_tma.cu); null = TMA path off
+    int*      d_post_list = nullptr; // indices of the post-trigger jobs of a localizer chunk (k5_post_tma.cu)
+    int       post_cap = 0;
+    void*     d_tmaps = nullptr;    // CUtensorMap[max_slots + 3*ncams]: frames of a slot, then per camera K16, TrainedAvgImage, -t
+                                    // (k1_trigger_tma.cu builds them; null = TMA paths off)
 };
 
 #define ABUB_L(ctx) ((void)++(ctx)->n_launches)
@@ -190,6 +194,7 @@ struct abub_loc_job {
     const uint8_t* b;        // genesis: pre-trigger frame ; post: TrainedAvgImage
     const uint32_t* k32;     // genesis: K32 plane of the camera
     const uint8_t* t8;       // post: min(6 sigma, 255)
+    const int16_t* nt16;     // post: -min(6 sigma, 255) as s16
     uint8_t* tz;             // out: TOZERO'd image (rows*cols)
     uint8_t* segflags;       // [rows][ceil(cols/240)] per 240-px row segment of tz: bit0 = holds a non-zero pixel now,
                              // bit1 = memory not known to be all zero (k5_localize.cu, sparse TOZERO frames)
@@ -198,8 +203,14 @@ struct abub_loc_job {
     int genesis;
     int k;                   // 0 = genesis frame, 1.. = post-trigger frame
     int item;                // index of the abub_loc_item this job belongs to
+    int slot, cam, zframe;   // post jobs on the TMA path: event slot, camera, cam * max_frames + frame of `a`
 };
 int abub_k1_launch_genesis_jobs(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs);
+// K5b TMA path (k5_post_tma.cu): post-trigger jobs of a chunk; false = shape not supported, use the streaming kernel
+bool abub_k5b_tma_supported(const abub_ctx* ctx);
+int abub_k5b_launch_tma(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs);
+const abub_loc_job* abub_loc_host_jobs(abub_ctx* ctx);      // host copy of the chunk's job table (k5_localize.cu)
+
 // K5-K7 (k5_localize.cu)
 int abub_loc_init(abub_ctx* ctx);
 void abub_loc_free(abub_ctx* ctx);

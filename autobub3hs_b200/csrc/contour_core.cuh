@@ -50,9 +50,23 @@ struct TraceResult {
     int minx, maxx, miny, maxy;
 };
 
+// The same predicate with a window of the binarised image held in fast memory (shared memory on the device): pixels inside
+// the window are answered from it, the rest from the image itself.  win[(y - wy0) * ww + (x - wx0)] != 0 <=> foreground.
+struct WinPix {
+    Pix g;
+    const uint8_t* win;
+    int wx0, wy0, ww, wh;
+    __host__ __device__ bool fg(int x, int y) const {
+        const unsigned dx = (unsigned)(x - wx0), dy = (unsigned)(y - wy0);
+        if (dx < (unsigned)ww && dy < (unsigned)wh) return win[dy * (unsigned)ww + dx] != 0;
+        return g.fg(x, y);
+    }
+};
+
 // Suzuki outer-border following from (px,py) whose W, NW, N, NE neighbours are background.
 // store == nullptr: measure only.  max_len guards against runaway loops.
-__host__ __device__ inline TraceResult trace_border(const Pix& im, int px, int py, ChainView* store, int max_len) {
+template <class PIX>
+__host__ __device__ inline TraceResult trace_border(const PIX& im, int px, int py, ChainView* store, int max_len) {
     TraceResult r;
     r.len = 0; r.accepted = 1; r.minx = r.maxx = px; r.miny = r.maxy = py;
     int s = 4;

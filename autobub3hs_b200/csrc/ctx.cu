@@ -32,6 +32,7 @@ extern "C" int abub_ctx_create(int device, int rows, int cols, int ncams, int ma
         ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_t8, n));
         ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_k32, n * sizeof(uint32_t)));
         ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_k16, n * sizeof(int16_t)));
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&cs.d_nt16, n * sizeof(int16_t)));
     }
     const size_t frames_per_slot = (size_t)ncams * max_frames;
     std::vector<uint8_t*> sp(max_slots);
@@ -79,7 +80,7 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     abub_png_free(ctx);
     for (int c = 0; c < ABUB_MAX_CAMS; c++) {
         abub_cam_state& cs = ctx->cam[c];
-        cudaFree(cs.d_mean); cudaFree(cs.d_sigma); cudaFree(cs.d_t8); cudaFree(cs.d_k32); cudaFree(cs.d_k16);
+        cudaFree(cs.d_mean); cudaFree(cs.d_sigma); cudaFree(cs.d_t8); cudaFree(cs.d_k32); cudaFree(cs.d_k16); cudaFree(cs.d_nt16);
         cudaFree(cs.d_sum); cudaFree(cs.d_sumsq); cudaFree(cs.d_count); cudaFree(cs.d_flag);
         cudaFree((void*)cs.d_table);
         cudaFree(cs.d_templ);
@@ -95,6 +96,7 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     cudaFree(ctx->d_hist_tmp);
     cudaFree((void*)ctx->d_gate_tab); cudaFree(ctx->d_gate_hist);
     cudaFree(ctx->d_tmaps);
+    cudaFree(ctx->d_post_list);
     if (ctx->h_raw) cudaFreeHost(ctx->h_raw);
     for (cudaEvent_t e : ctx->prof.pool) cudaEventDestroy(e);
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);

@@ -291,11 +291,12 @@ k1_trigger_tma_kernel(const CUtensorMap* __restrict__ slot_maps, const CUtensorM
 }
 
 // K16 = -(255 + t) as s16, t = min(6*sigma, 255)
-__global__ void k1_build_k16_kernel(const uint8_t* __restrict__ sigma, int16_t* __restrict__ k16, size_t n) {
+__global__ void k1_build_k16_kernel(const uint8_t* __restrict__ sigma, int16_t* __restrict__ k16, int16_t* __restrict__ nt16, size_t n) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int t = min(6 * (int)sigma[i], 255);
     k16[i] = (int16_t)(-(255 + t));
+    nt16[i] = (int16_t)(-t);
 }
 
 }  // namespace
@@ -329,7 +330,7 @@ int abub_k1_tma_init(abub_ctx* ctx) {
     if (!abub_k1_tma_supported(ctx)) return ABUB_OK;
     PFN_encodeTiled enc = get_encode();
     if (!enc) { ctx->err = "cuTensorMapEncodeTiled not available from the driver"; return ABUB_E_CUDA; }
-    const int nmaps = ctx->max_slots + ctx->ncams;
+    const int nmaps = ctx->max_slots + 3 * ctx->ncams;
     std::vector<CUtensorMap> maps(nmaps);
     const cuuint32_t ones[3] = {1, 1, 1};
     for (int s = 0; s < ctx->max_slots; s++) {
@@ -350,6 +351,21 @@ int abub_k1_tma_init(abub_ctx* ctx) {
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) { ctx->err = "cuTensorMapEncodeTiled(k16) failed: " + std::to_string((int)r); return ABUB_E_CUDA; }
     }
+    // localizer post-trigger kernel (k5_post_tma.cu): TrainedAvgImage as 2-byte elements, -t (s16) as 4-byte elements
+    for (int c = 0; c < ctx->ncams; c++) {
+        const cuuint64_t dims[2] = {(cuuint64_t)ctx->cols / 2, (cuuint64_t)ctx->rows};
+        const cuuint32_t box[2] = {(cuuint32_t)T_BW / 2, (cuuint32_t)T_R};
+        const cuuint64_t s16[1] = {(cuuint64_t)ctx->cols};
+        CUresult r = enc(&maps[ctx->max_slots + ctx->ncams + c], CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, ctx->cam[c].d_mean, dims, s16, box,
+                         ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { ctx->err = "cuTensorMapEncodeTiled(mean) failed: " + std::to_string((int)r); return ABUB_E_CUDA; }
+        const cuuint64_t s32[1] = {(cuuint64_t)ctx->cols * 2};
+        r = enc(&maps[ctx->max_slots + 2 * ctx->ncams + c], CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, ctx->cam[c].d_nt16, dims, s32, box,
+                ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { ctx->err = "cuTensorMapEncodeTiled(nt16) failed: " + std::to_string((int)r); return ABUB_E_CUDA; }
+    }
     ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_tmaps, (size_t)nmaps * sizeof(CUtensorMap)));
     ABUB_CHECK_CUDA(ctx, cudaMemcpy(ctx->d_tmaps, maps.data(), (size_t)nmaps * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
     return ABUB_OK;
@@ -358,7 +374,7 @@ int abub_k1_tma_init(abub_ctx* ctx) {
 int abub_k1_build_k16(abub_ctx* ctx, int cam) {
     abub_cam_state& c = ctx->cam[cam];
     const size_t n = ctx->npix;
-    ABUB_L(ctx), k1_build_k16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(c.d_sigma, c.d_k16, n);
+    ABUB_L(ctx), k1_build_k16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(c.d_sigma, c.d_k16, c.d_nt16, n);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
 }

@@ -110,20 +110,45 @@ k5_post_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols) {
 
 // Streaming form of K5b for pitches that allow 8-byte loads (cols % 8 == 0): one warp owns a strip of 240 output
 // columns (lane l holds the 8 pixels x0-8+8l.., lanes 0/31 are the halo) and walks down PS_TH rows.
-//   d   = sat_u8(|a - avg| - t8)                  VABSDIFF4 + byte-wise saturating subtract, 4 px per word
-//   3x3 = vertical sum of three rows in 16-bit lanes (two pixels per word), horizontal sum after taking the halo
-//         words from the neighbour lanes (SHFL) and one PRMT per word for the odd alignment
+//   d   = relu(|a - avg| - t)                     VABSDIFF4, widened to two pixels per word (PRMT), then ONE
+//                                                 VIADDMNMX.S16x2.RELU per word against the per-camera plane -t (s16)
+//   3x3 = vertical sum of three rows in 16-bit lanes, horizontal sum after taking the halo words from the neighbour
+//         lanes (SHFL) and one PRMT per word for the odd alignment
 //   v   = (sum + 4) / 9  (cv::blur rounding), THRESH_TOZERO -- only evaluated when some sum in the lane can exceed
 //         the threshold, which is rare: frames are almost empty after the 6-sigma cut
-// 3 bytes read + 1 byte written per pixel, no shared-memory tile.
+// After the 6-sigma cut against the TRAINED MEAN most 256-pixel rows hold nothing at all (unlike the trigger's frame
+// pairs, K1): one vote per row tells whether the warp's row is all zero, and when this row and the two before it are,
+// the 3x3 sums are zero without being formed -- the vertical / horizontal passes and the threshold test are skipped.
+// The frame rows are the only operand that comes from DRAM; at ~1 us of latency a warp must keep kilobytes of them in
+// flight, far more than a register prefetch holds: they go through a per-warp ring of PS_D rows in shared memory filled by
+// cp.async (each lane copies, and later reads, its own 8 bytes: no barrier, only cp.async.wait_group).  avg and -t come
+// from L2 and stay on a two-row register prefetch.
+// 3 bytes read (avg and -t from L2) + at most 1 byte written per pixel.
 constexpr int PS_TH = 64;
 constexpr int PS_WARPS = 4;
+constexpr int PS_D = 8;              // frame rows in flight per warp
+
+__device__ __forceinline__ void ps_cp_async8(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void ps_cp_async16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void ps_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void ps_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __device__ __forceinline__ uint2 ps_ld8(const uint8_t* p) { return __ldg(reinterpret_cast<const uint2*>(p)); }
+
+struct PsSlot {             // one frame row of one warp in the ring: what lane l needs of the three planes
+    uint2 a[32];            // frame[trig + k]
+    uint2 m[32];            // TrainedAvgImage
+    uint4 t[32];            // -min(6 sigma, 255), s16 per pixel
+};
 
 __global__ void __launch_bounds__(32 * PS_WARPS)
 k5_post_stream_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols, int nxw, int nstrips) {
     __shared__ uint32_t sh_hist[256];
+    __shared__ __align__(16) PsSlot sh_ring[PS_WARPS][PS_D];
     const abub_loc_job job = jobs[blockIdx.z];
     if (job.genesis) return;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -131,44 +156,68 @@ k5_post_stream_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols,
     __syncthreads();
     const int unit = blockIdx.x * PS_WARPS + warp;
     if (unit < nxw * nstrips) {
-        const int x0 = (unit % nxw) * 240, y0 = (unit / nxw) * PS_TH;
+        const int xw = unit % nxw;
+        const int x0 = xw * 240, y0 = (unit / nxw) * PS_TH;
         const int gx = x0 - 8 + lane * 8;
         const int gxl = min(max(gx, 0), cols - 8);
         const bool out_lane = lane >= 1 && lane <= 30 && gx < cols;
         const bool left_edge = (gx == 0), right_edge = (gx + 8 == cols);
         const int nout = min(PS_TH, rows - y0);
+        const int nrow = nout + 2;                                      // image rows y0-1 .. y0+nout
         const uint32_t lim = 9u * (uint32_t)job.tozero + 5u;            // (sum+4)/9 <= tozero  <=>  sum < lim
-        uint32_t r1[4] = {0, 0, 0, 0}, r2[4] = {0, 0, 0, 0};           // rows y-1 and y-2, widened (2 px per word)
-        // loads run two rows ahead of the arithmetic (the loop is otherwise bound by load latency)
-        struct RowIn { uint2 a, m, t; uint8_t prev; };
-        auto fetch = [&](int rl) {
-            int y = y0 - 1 + rl;                                        // BORDER_REFLECT_101
-            if (y < 0) y = -y;
-            if (y >= rows) y = 2 * (rows - 1) - y;
-            y = min(max(y, 0), rows - 1);
-            const size_t off = (size_t)y * cols + gxl;
-            RowIn r;
-            r.a = ps_ld8(job.a + off); r.m = ps_ld8(job.b + off); r.t = ps_ld8(job.t8 + off);
-            r.prev = job.segflags[(size_t)min(max(y0 + rl - 2, 0), rows - 1) * nxw + (unit % nxw)];   // same byte for every lane
-            return r;
+        // Rows are consecutive in memory except for BORDER_REFLECT_101 at the image's top (row -1 -> 1) and bottom
+        // (row `rows` -> rows-2): the three source pointers of the row being issued advance by one pitch, or step back.
+        const int yfirst = (y0 == 0) ? 1 : y0 - 1;
+        const uint8_t* pa = job.a + (size_t)yfirst * cols + gxl;
+        const uint8_t* pm = job.b + (size_t)yfirst * cols + gxl;
+        const int16_t* pt = job.nt16 + (size_t)yfirst * cols + gxl;
+        int yi = yfirst;                                                // image row the pointers stand on
+        int ri = 0;                                                     // rows issued so far
+        PsSlot* const ring = sh_ring[warp];
+        auto issue = [&]() {                                            // row ri -> ring slot ri % PS_D; one cp.async group per row
+            if (ri < nrow) {
+                PsSlot& sl = ring[ri & (PS_D - 1)];
+                ps_cp_async8(&sl.a[lane], pa);
+                ps_cp_async8(&sl.m[lane], pm);
+                ps_cp_async16(&sl.t[lane], pt);
+                // next image row: y0-1+ri+1, reflected
+                const int ynext = y0 + ri;
+                const int yn = (ynext >= rows) ? 2 * (rows - 1) - ynext : ynext;     // ynext >= 0 always (ri + 1 >= 1)
+                const ptrdiff_t step = (ptrdiff_t)(yn - yi) * cols;
+                pa += step; pm += step; pt += step;
+                yi = yn;
+            }
+            ps_cp_commit();
+            ri++;
         };
-        RowIn q0 = fetch(0), q1 = fetch(1);
-        for (int rl = 0; rl < nout + 2; rl++) {
-            const RowIn cur = q0;
-            q0 = q1;
-            if (rl + 2 < nout + 2) q1 = fetch(rl + 2);
-            const uint2 a = cur.a, m = cur.m, t = cur.t;
-            uint8_t* const flagp = job.segflags + (size_t)min(max(y0 + rl - 2, 0), rows - 1) * nxw + (unit % nxw);
-            const uint8_t prev = cur.prev;
-            const uint32_t d0 = __vsubus4(__vabsdiffu4(a.x, m.x), t.x);     // L3Localizer.cpp:779-782
-            const uint32_t d1 = __vsubus4(__vabsdiffu4(a.y, m.y), t.y);
-            uint32_t w[4];
-            w[0] = __byte_perm(d0, 0, 0x4140); w[1] = __byte_perm(d0, 0, 0x4342);
-            w[2] = __byte_perm(d1, 0, 0x4140); w[3] = __byte_perm(d1, 0, 0x4342);
-            if (rl >= 2) {
+#pragma unroll
+        for (int i = 0; i < PS_D; i++) issue();
+        uint8_t* flagp = job.segflags + (size_t)y0 * nxw + xw;          // flag of output row y0 + rl - 2
+        uint32_t zhist = 0;                                             // bit 0 / 1 / 2: this row / the one before / two before holds something (warp-uniform)
+        uint32_t wa[4] = {0, 0, 0, 0}, wb[4] = {0, 0, 0, 0}, wc[4];    // three consecutive rows, widened (2 px per word); roles rotate
+
+        // one image row: wn = this row, w1 = the row before, w2 = two rows before
+        auto do_row = [&](const int rl, uint32_t (&wn)[4], const uint32_t (&w1)[4], const uint32_t (&w2)[4]) {
+            ps_cp_wait<PS_D - 1>();                                     // the oldest group = row rl has landed
+            const PsSlot& sl = ring[rl & (PS_D - 1)];
+            const uint2 a = sl.a[lane], m = sl.m[lane];
+            const uint4 t = sl.t[lane];
+            issue();                                                    // the slot is free again
+            const uint32_t d0 = __vabsdiffu4(a.x, m.x), d1 = __vabsdiffu4(a.y, m.y);   // L3Localizer.cpp:779
+            wn[0] = __viaddmax_s16x2_relu(__byte_perm(d0, 0, 0x4140), t.x, t.x);        // :782  - 6 sigma, saturating
+            wn[1] = __viaddmax_s16x2_relu(__byte_perm(d0, 0, 0x4342), t.y, t.y);
+            wn[2] = __viaddmax_s16x2_relu(__byte_perm(d1, 0, 0x4140), t.z, t.z);
+            wn[3] = __viaddmax_s16x2_relu(__byte_perm(d1, 0, 0x4342), t.w, t.w);
+            const bool row_nz = __any_sync(0xffffffffu, (wn[0] | wn[1] | wn[2] | wn[3]) != 0u);
+            zhist = (zhist << 1) | (row_nz ? 1u : 0u);
+            if (rl < 2) return;
+            const uint8_t prev = *flagp;                                // same byte for every lane
+            uint2 o = make_uint2(0u, 0u);
+            bool nz = false;
+            if (zhist & 7u) {                                           // some pixel over the cut in these three rows
                 uint32_t W[6];
 #pragma unroll
-                for (int k = 0; k < 4; k++) W[k + 1] = w[k] + r1[k] + r2[k];
+                for (int k = 0; k < 4; k++) W[k + 1] = wn[k] + w1[k] + w2[k];
                 W[0] = __shfl_up_sync(0xffffffffu, W[4], 1);
                 W[5] = __shfl_down_sync(0xffffffffu, W[1], 1);
                 if (left_edge) W[0] = __byte_perm(W[1], 0, 0x3232);     // column -1 -> column 1 (hi lane is what is read)
@@ -176,12 +225,11 @@ k5_post_stream_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols,
                 uint32_t H[4], mx = 0;
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
-                    const uint32_t sl = __byte_perm(W[k], W[k + 1], 0x5432);      // (x-1, x) pairs
-                    const uint32_t sr = __byte_perm(W[k + 1], W[k + 2], 0x5432);  // (x+1, x+2) pairs
-                    H[k] = sl + W[k + 1] + sr;
+                    const uint32_t sl_ = __byte_perm(W[k], W[k + 1], 0x5432);     // (x-1, x) pairs
+                    const uint32_t sr_ = __byte_perm(W[k + 1], W[k + 2], 0x5432); // (x+1, x+2) pairs
+                    H[k] = sl_ + W[k + 1] + sr_;
                     mx = __vmaxu2(mx, H[k]);
                 }
-                uint2 o = make_uint2(0u, 0u);
                 if (out_lane && ((mx & 0xFFFFu) >= lim || (mx >> 16) >= lim)) {
                     uint32_t ob[8];
 #pragma unroll
@@ -197,15 +245,24 @@ k5_post_stream_kernel(const abub_loc_job* __restrict__ jobs, int rows, int cols,
                     o.x = ob[0] | (ob[1] << 8) | (ob[2] << 16) | (ob[3] << 24);
                     o.y = ob[4] | (ob[5] << 8) | (ob[6] << 16) | (ob[7] << 24);
                 }
-                // the segment is stored when it holds something, or when what the memory holds is not known to be zero
-                const bool nz = __any_sync(0xffffffffu, (o.x | o.y) != 0u);
-                if (out_lane && (nz || (prev & 2))) *reinterpret_cast<uint2*>(job.tz + (size_t)(y0 + rl - 2) * cols + gx) = o;
-                const uint8_t nf = nz ? 3 : 0;
-                if (lane == 0 && nf != prev) *flagp = nf;
+                nz = __any_sync(0xffffffffu, (o.x | o.y) != 0u);
             }
-#pragma unroll
-            for (int k = 0; k < 4; k++) { r2[k] = r1[k]; r1[k] = w[k]; }
+            // the segment is stored when it holds something, or when what the memory holds is not known to be zero
+            if (nz || (prev & 2)) {
+                if (out_lane) *reinterpret_cast<uint2*>(job.tz + (size_t)(y0 + rl - 2) * cols + gx) = o;
+            }
+            const uint8_t nf = nz ? 3 : 0;
+            if (lane == 0 && nf != prev) *flagp = nf;
+            flagp += nxw;
+        };
+        // three rows per trip: the roles (this row, the one before, two before) rotate without a register move
+#pragma unroll 1
+        for (int rl = 0; rl < nrow; rl += 3) {
+            do_row(rl, wc, wb, wa);
+            if (rl + 1 < nrow) do_row(rl + 1, wa, wc, wb);
+            if (rl + 2 < nrow) do_row(rl + 2, wb, wa, wc);
         }
+        ps_cp_wait<0>();
     }
     __syncthreads();
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -387,15 +444,40 @@ __device__ __forceinline__ void decode_key(unsigned long long key, int job0, int
     *px = (int)(0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull));
 }
 
-__global__ void k7_trace1_kernel(const unsigned long long* __restrict__ keys, int ncand, const abub_loc_job* __restrict__ jobs,
-                                 const int* __restrict__ thr, int rows, int cols, int job0, Cand* __restrict__ cand,
-                                 long long* __restrict__ sizes) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+// One WARP per candidate.  Border following is a chain of dependent pixel reads (up to eight probes per border pixel): from
+// global memory that is hundreds of cycles per probe and a kernel as long as its longest contour.  The warp therefore first
+// copies a window of the binarised image into shared memory (all lanes, coalesced), then lane 0 follows the border with the
+// window answering the probes (pixels outside it still come from the image).  Pass 2 also keeps the chain (points, codes and
+// the TC89 work arrays) in shared memory while it is approximated and measured, and the warp copies it to the arena at the
+// end (k7_external_kernel reads it for the hole test).
+constexpr int K7_WARPS = 4;
+constexpr int K7_W1W = 64, K7_W1H = 40;                  // pass 1 window: x in [px-32, px+32), y in [py-1, py+39)
+constexpr int K7_W2_BYTES = 6144;                         // pass 2 window: the bounding box + 1 (clipped to this many bytes)
+constexpr int K7_CHAIN_MAX = 255;                         // longest chain kept in shared memory (12 bytes per element)
+
+__device__ __forceinline__ void k7_load_window(const Pix& g, uint8_t* win, int wx0, int wy0, int ww, int wh, int lane) {
+    for (int idx = lane; idx < ww * wh; idx += 32) {
+        const int y = wy0 + idx / ww, x = wx0 + idx % ww;
+        win[idx] = g.fg(x, y) ? 1 : 0;
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(32 * K7_WARPS)
+k7_trace1_kernel(const unsigned long long* __restrict__ keys, int ncand, const abub_loc_job* __restrict__ jobs,
+                 const int* __restrict__ thr, int rows, int cols, int job0, Cand* __restrict__ cand,
+                 long long* __restrict__ sizes) {
+    __shared__ uint8_t sh_win[K7_WARPS][K7_W1W * K7_W1H];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * K7_WARPS + warp;
     if (i >= ncand) return;
     int jl, p;
     decode_key(keys[i], job0, &jl, &p);
-    const Pix im{jobs[jl].tz, thr[jl], rows, cols};
-    const TraceResult t = trace_border(im, p % cols, p / cols, nullptr, 4 * rows * cols);
+    const int px = p % cols, py = p / cols;
+    WinPix im{Pix{jobs[jl].tz, thr[jl], rows, cols}, sh_win[warp], px - K7_W1W / 2, py - 1, K7_W1W, K7_W1H};
+    k7_load_window(im.g, sh_win[warp], im.wx0, im.wy0, im.ww, im.wh, lane);
+    if (lane != 0) return;
+    const TraceResult t = trace_border(im, px, py, nullptr, 4 * rows * cols);
     Cand c;
     c.job = jl; c.first_px = p; c.len = t.len; c.accepted = t.accepted;
     c.minx = t.minx; c.maxx = t.maxx; c.miny = t.miny; c.maxy = t.maxy;
@@ -404,32 +486,51 @@ __global__ void k7_trace1_kernel(const unsigned long long* __restrict__ keys, in
     sizes[i] = t.accepted ? (long long)((ChainView::bytes(t.len) + 15) & ~(size_t)15) : 0;
 }
 
-__global__ void k7_trace2_kernel(int ncand, const abub_loc_job* __restrict__ jobs, const int* __restrict__ thr, int rows,
-                                 int cols, Cand* __restrict__ cand, const long long* __restrict__ offs,
-                                 uint8_t* __restrict__ arena, abub_blob* __restrict__ tmp) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(32 * K7_WARPS)
+k7_trace2_kernel(int ncand, const abub_loc_job* __restrict__ jobs, const int* __restrict__ thr, int rows,
+                 int cols, Cand* __restrict__ cand, const long long* __restrict__ offs,
+                 uint8_t* __restrict__ arena, abub_blob* __restrict__ tmp) {
+    __shared__ uint8_t sh_win[K7_WARPS][K7_W2_BYTES];
+    __shared__ __align__(16) uint8_t sh_chain[K7_WARPS][12 * (K7_CHAIN_MAX + 1)];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * K7_WARPS + warp;
     if (i >= ncand) return;
     Cand c = cand[i];
-    if (!c.accepted) return;
+    if (!c.accepted) return;                               // warp-uniform
     c.arena_off = offs[i];
-    cand[i].arena_off = c.arena_off;
-    const Pix im{jobs[c.job].tz, thr[c.job], rows, cols};
-    ChainView cv(arena + c.arena_off, c.len);
-    int L;
-    if (c.len == 0) {
-        cv.P[0] = make_short2((short)(c.first_px % cols), (short)(c.first_px / cols));
-        cv.removed[0] = 0;
-        L = 1;
-    } else {
-        trace_border(im, c.first_px % cols, c.first_px / cols, &cv, 4 * rows * cols);
-        L = approx_tc89_l1(cv, c.len);
+    const int px = c.first_px % cols, py = c.first_px / cols;
+    int ww = min(c.maxx - c.minx + 3, 128);
+    int wh = min(c.maxy - c.miny + 3, K7_W2_BYTES / ww);
+    WinPix im{Pix{jobs[c.job].tz, thr[c.job], rows, cols}, sh_win[warp], c.minx - 1, c.miny - 1, ww, wh};
+    if (c.len > 0) k7_load_window(im.g, sh_win[warp], im.wx0, im.wy0, ww, wh, lane);
+    const bool in_smem = c.len <= K7_CHAIN_MAX;
+    uint8_t* const chain_mem = in_smem ? sh_chain[warp] : arena + c.arena_off;
+    if (lane == 0) {
+        cand[i].arena_off = c.arena_off;
+        ChainView cv(chain_mem, c.len);
+        int L;
+        if (c.len == 0) {
+            cv.P[0] = make_short2((short)px, (short)py);
+            cv.removed[0] = 0;
+            L = 1;
+        } else {
+            trace_border(im, px, py, &cv, 4 * rows * cols);
+            L = approx_tc89_l1(cv, c.len);
+        }
+        const PolyMeasure m = measure_alive(cv, L);
+        abub_blob b;
+        b.k = jobs[c.job].k; b.x = m.x; b.y = m.y; b.w = m.w; b.h = m.h; b.npts = m.npts; b.first_px = c.first_px;
+        b.reserved = jobs[c.job].item; b.sum_x = m.sum_x; b.sum_y = m.sum_y;
+        b.area = m.area; b.m00 = m.m00; b.m10 = m.m10; b.m01 = m.m01;
+        tmp[i] = b;
     }
-    const PolyMeasure m = measure_alive(cv, L);
-    abub_blob b;
-    b.k = jobs[c.job].k; b.x = m.x; b.y = m.y; b.w = m.w; b.h = m.h; b.npts = m.npts; b.first_px = c.first_px;
-    b.reserved = jobs[c.job].item; b.sum_x = m.sum_x; b.sum_y = m.sum_y;
-    b.area = m.area; b.m00 = m.m00; b.m10 = m.m10; b.m01 = m.m01;
-    tmp[i] = b;
+    __syncwarp();
+    if (in_smem) {                                         // the chain goes to the arena (same layout), all lanes
+        const int nwords = (int)(ChainView::bytes(c.len) / 4);
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(sh_chain[warp]);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(arena + c.arena_off);
+        for (int w = lane; w < nwords; w += 32) dst[w] = src[w];
+    }
 }
 
 // RETR_EXTERNAL: drop components whose first pixel lies inside another component's outer border.
@@ -487,6 +588,8 @@ int grow(abub_ctx* ctx, T** p, size_t n_elems) {
 // host orchestration
 // ------------------------------------------------------------------------------------
 static LocArena* arena_of(abub_ctx* ctx) { return reinterpret_cast<LocArena*>(ctx->loc); }
+
+const abub_loc_job* abub_loc_host_jobs(abub_ctx* ctx) { return arena_of(ctx)->h_jobs; }
 
 int abub_loc_init(abub_ctx* ctx) {
     LocArena* a = new LocArena();
@@ -563,7 +666,10 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     if ((rc = abub_k1_launch_genesis_jobs(ctx, a->d_jobs, njobs))) return rc;
     {
     abub_prof_scope prof(ctx, ABUB_PROF_K5B);
-    if ((ctx->cols % 8) == 0 && ctx->cols >= 16) {
+    static const bool no_tma = getenv("ABUB_K5B_STREAM") != nullptr;       // A/B switch
+    if (!has_prepared && !no_tma && abub_k5b_tma_supported(ctx)) {
+        if ((rc = abub_k5b_launch_tma(ctx, a->d_jobs, njobs))) return rc;
+    } else if ((ctx->cols % 8) == 0 && ctx->cols >= 16) {
         const int nxw = (ctx->cols + 239) / 240, nstrips = (ctx->rows + PS_TH - 1) / PS_TH;
         dim3 grid((nxw * nstrips + PS_WARPS - 1) / PS_WARPS, 1, njobs);
         ABUB_L(ctx), k5_post_stream_kernel<<<grid, 32 * PS_WARPS, 0, st>>>(a->d_jobs, ctx->rows, ctx->cols, nxw, nstrips);
@@ -620,9 +726,10 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
         cub::DeviceRadixSort::SortKeys(a->d_cub_tmp, tmpb, a->d_keys, a->d_keys_alt, ncand, 0, 64, st);
     }
     const int tb = 64, nb = (ncand + tb - 1) / tb;
+    const int nbw = (ncand + K7_WARPS - 1) / K7_WARPS;          // the two tracing kernels run one warp per candidate
     {
     abub_prof_scope prof(ctx, ABUB_PROF_K7A);
-    ABUB_L(ctx), k7_trace1_kernel<<<nb, tb, 0, st>>>(a->d_keys_alt, ncand, a->d_jobs, a->d_thr, ctx->rows, ctx->cols, 0, a->d_cand,
+    ABUB_L(ctx), k7_trace1_kernel<<<nbw, 32 * K7_WARPS, 0, st>>>(a->d_keys_alt, ncand, a->d_jobs, a->d_thr, ctx->rows, ctx->cols, 0, a->d_cand,
                                         a->d_scan);
     }
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
@@ -642,7 +749,7 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     abub_blob* ordered = a->d_blobs + a->blob_cap;
     {
     abub_prof_scope prof(ctx, ABUB_PROF_K7B);
-    ABUB_L(ctx), k7_trace2_kernel<<<nb, tb, 0, st>>>(ncand, a->d_jobs, a->d_thr, ctx->rows, ctx->cols, a->d_cand, a->d_scan, a->d_chain, tmp);
+    ABUB_L(ctx), k7_trace2_kernel<<<nbw, 32 * K7_WARPS, 0, st>>>(ncand, a->d_jobs, a->d_thr, ctx->rows, ctx->cols, a->d_cand, a->d_scan, a->d_chain, tmp);
     }
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     int* flags = a->d_iscan;
@@ -705,8 +812,12 @@ extern "C" int abub_localize_batch(abub_ctx* ctx, const abub_loc_item* items, in
                 jb.genesis = (k == 0);
                 jb.k = k;
                 jb.item = i;
+                jb.slot = it.slot;
+                jb.cam = it.cam;
+                jb.zframe = it.cam * ctx->max_frames + it.trig + k;
                 jb.k32 = cs.d_k32;
                 jb.t8 = cs.d_t8;
+                jb.nt16 = cs.d_nt16;
                 jb.tz = a->d_tz + (size_t)j * npix;
                 jb.segflags = a->d_segflags + (size_t)j * ctx->rows * ((ctx->cols + 239) / 240);
                 jb.hist = a->d_hist + (size_t)j * 256;

@@ -66,7 +66,7 @@ bool AbubDevice::EnsureBellowsTemplate(int cam, const std::string& mask_dir) {
 }
 
 const Image8* AbubDevice::Mask(int cam, bool bellows, const std::string& mask_dir) {
-    std::lock_guard<std::recursive_mutex> g(mu_);
+    std::lock_guard<std::mutex> g(tab_mu_);
     const std::string key = mask_dir + "|" + std::to_string(cam) + (bellows ? "|b" : "|m");
     auto it = masks_.find(key);
     if (it == masks_.end()) {
@@ -90,7 +90,7 @@ void AbubDevice::Shutdown() {
 }
 
 int AbubDevice::AcquireSlot(const std::string& key) {
-    std::lock_guard<std::recursive_mutex> g(mu_);
+    std::lock_guard<std::mutex> g(tab_mu_);
     auto it = by_key_.find(key);
     if (it != by_key_.end()) { slots_[it->second].refs++; return it->second; }
     for (int s = 0; s < (int)slots_.size(); s++)
@@ -105,7 +105,7 @@ int AbubDevice::AcquireSlot(const std::string& key) {
 }
 
 int AbubDevice::BindSlot(const std::string& key, int slot) {
-    std::lock_guard<std::recursive_mutex> g(mu_);
+    std::lock_guard<std::mutex> g(tab_mu_);
     if (slot < 0 || slot >= (int)slots_.size()) throw AbubError("BindSlot: no such slot");
     auto it = by_key_.find(key);
     if (it != by_key_.end()) {
@@ -121,8 +121,13 @@ int AbubDevice::BindSlot(const std::string& key, int slot) {
     return slot;
 }
 
+bool AbubDevice::SlotInUse(int slot) {
+    std::lock_guard<std::mutex> g(tab_mu_);
+    return slot >= 0 && slot < (int)slots_.size() && slots_[slot].refs != 0;
+}
+
 void AbubDevice::ReleaseSlot(const std::string& key) {
-    std::lock_guard<std::recursive_mutex> g(mu_);
+    std::lock_guard<std::mutex> g(tab_mu_);
     auto it = by_key_.find(key);
     if (it == by_key_.end()) return;
     if (--slots_[it->second].refs <= 0) {
@@ -133,6 +138,7 @@ void AbubDevice::ReleaseSlot(const std::string& key) {
 
 void AbubDevice::LoadCamera(int slot, int cam, Parser* parser, const std::string& event_id,
                             const std::vector<std::string>& frames) {
+    if (slots_[slot].loaded[cam]) return;          // staged with its batch: nothing to do, and no need to wait for the device lock
     std::lock_guard<std::recursive_mutex> g(mu_);
     AbubSlot& st = slots_[slot];
     if (st.loaded[cam]) return;

@@ -10,12 +10,16 @@
 //   * PrefetchEvents() lets the driver loop stage a whole batch of events (decode on every host core,
 //     one K1 launch for the batch) before the per-camera objects are built; analyzers then find their
 //     frames and histograms resident.
-//   * The ctx is not internally locked (one CUDA stream): every C-ABI call goes through lock().
+//   * The ctx is not internally locked (one CUDA stream): every C-ABI call goes through lock().  The slot table and
+//     the mask cache have their own short lock, and an analyzer reads the results of its batch from the slot caches
+//     without any lock (they are complete before the batch is handed to the analyzers), so that the per-camera objects
+//     of one batch run on the host cores while the device works on the next batch.
 #ifndef ABUB_DEVICE_HPP
 #define ABUB_DEVICE_HPP
 
 #include <map>
 #include <mutex>
+#include <atomic>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -72,6 +76,7 @@ public:
     void ReleaseSlot(const std::string& key);
     // Binds an event key to a given slot (whose frames a producer has filled); the slot must be free.
     int BindSlot(const std::string& key, int slot);
+    bool SlotInUse(int slot);
     AbubSlot& slot(int s) { return slots_[s]; }
 
     // Decodes (in parallel over frames) and uploads the frames of one camera of an event into its slot;
@@ -119,7 +124,8 @@ private:
     AbubDevice() {}
     int device_ = 0, ncams_ = 0, max_frames_ = 0, max_slots_ = 0, rows_ = 0, cols_ = 0;
     abub_ctx* ctx_ = nullptr;
-    std::recursive_mutex mu_;
+    std::recursive_mutex mu_;         // the device: every C-ABI call on ctx_ (held for the whole of a batch's device work)
+    std::mutex tab_mu_;               // the slot table and the mask cache (short; may be taken while mu_ is held, never the other way round)
     std::vector<AbubSlot> slots_;
     // stages every camera of the given (slot, event) pairs: all frames are read on all cores; 8-bit grey PNG frames are
     // inflated and unfiltered on the device (abub_event_decode_png), anything else is decoded on the host

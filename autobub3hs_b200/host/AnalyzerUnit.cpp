@@ -56,12 +56,12 @@ void AnalyzerUnit::FindTriggerFrame(bool nonStopMode, int startframe) {
     int trig = 0, status = -3, lt = -1;
     std::vector<double> sig(dev.max_frames(), 0.0);
     {
-        std::lock_guard<std::recursive_mutex> g(dev.lock());
         AbubSlot& st = dev.slot(Slot);
-        if (startframe == 1 && st.trig_valid[CameraNumber]) {      // scanned with the rest of the batch (PrefetchEvents)
+        if (startframe == 1 && st.trig_valid[CameraNumber]) {      // scanned with the rest of the batch (AnalyzeBatch / StreamBatch)
             trig = st.trig[CameraNumber]; status = st.trig_status[CameraNumber]; lt = st.trig_loc_thres[CameraNumber];
             sig = st.sig[CameraNumber];
         } else {
+            std::lock_guard<std::recursive_mutex> g(dev.lock());
             dev.EnsureAllResident(Slot);                  // a streamed batch stopped sending frames at the first decision
             dev.Check(abub_trigger(dev.ctx(), Slot, CameraNumber, startframe, &trig, &status, &lt, sig.data()), "abub_trigger");
         }

@@ -27,7 +27,11 @@ bool L3Localizer::isInMask(RectI* r, bool bellows) {
     const int xpix = (int)(r->x + r->width / 2.);
     const int ypix = r->y + r->height / 2;
     if (MaskDir == "") return !bellows;                                   // silently skip the mask check
-    const Image8* mp = AbubDevice::Get().Mask(CameraNumber, bellows, MaskDir);
+    /* the analyzer keeps its masks once read (cam_mask / bellows_mask members of the reference, :983-984) */
+    const Image8*& cached = bellows ? bellows_mask_ : cam_mask_;
+    bool& looked = bellows ? bellows_mask_looked_ : cam_mask_looked_;
+    if (!looked) { cached = AbubDevice::Get().Mask(CameraNumber, bellows, MaskDir); looked = true; }
+    const Image8* mp = cached;
     if (!mp) {
         std::cout << "Mask image not loadable for event " << EventID << " camera " << CameraNumber
                   << "; skipping mask check" << std::endl;
@@ -181,7 +185,6 @@ void L3Localizer::LocalizeOMatic(std::string) {
     std::vector<abub_blob> blobs(1024);
     int npf[ABUB_MAX_TRACK + 1] = {0};
     {
-        std::lock_guard<std::recursive_mutex> g(dev.lock());
         AbubSlot& st = dev.slot(Slot);
         const int c = CameraNumber;
         if (st.loc_valid[c] && st.loc_trig[c] == MatTrigFrame && st.loc_pre[c] == preTrigNum && st.loc_thres[c] == loc_thres &&
@@ -189,6 +192,7 @@ void L3Localizer::LocalizeOMatic(std::string) {
             blobs = st.loc_blobs[c];
             for (int k = 0; k <= ABUB_MAX_TRACK; k++) npf[k] = st.loc_npf[c][k];
         } else {
+            std::lock_guard<std::recursive_mutex> g(dev.lock());
             dev.EnsureAllResident(Slot);
             for (;;) {
                 const int rc = abub_localize(dev.ctx(), Slot, CameraNumber, MatTrigFrame, preTrigNum, loc_thres, n_post,

@@ -14,6 +14,9 @@ private:
     bool nonStopMode;
 
     static BubbleImageFrame FrameFromBlob(const abub_blob& b, bool genesis);
+    const Image8* cam_mask_ = nullptr;
+    const Image8* bellows_mask_ = nullptr;
+    bool cam_mask_looked_ = false, bellows_mask_looked_ = false;
     int preTrigNumber = 0;                                           // frame used as preTrigFrame (:932-934)
     void GenesisFromBlobs(const abub_blob* blobs, int n);            // CalculateInitialBubbleParams bookkeeping
     bool BellowsVeto(std::vector<abub_blob>& again);                 // block :292-372; false = template not loadable

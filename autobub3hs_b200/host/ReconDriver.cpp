@@ -1,5 +1,6 @@
 #include "ReconDriver.hpp"
 
+#include <omp.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -61,7 +62,8 @@ void DetectStagedBatch(DetectRun& run, const std::vector<std::string>& chunk, co
     double t_write = 0;
     std::vector<Trainer*>& Trainers = *run.Trainers;
     /* events in parallel, cameras in series, rows committed in event order (AutoBubStart3.cpp:342, :360-365, :379-383) */
-#pragma omp parallel for ordered schedule(static, 1)
+    const int nthreads = run.threads > 0 ? run.threads : omp_get_max_threads();
+#pragma omp parallel for ordered schedule(dynamic, 1) num_threads(nthreads)
     for (int ci = 0; ci < n; ci++) {
         const std::string& ev = chunk[ci];
         OutputWriter* EventOutput = new OutputWriter(run.out_dir, run.run_number, run.frameOffset, run.numCams);
@@ -98,25 +100,98 @@ void DetectStagedBatch(DetectRun& run, const std::vector<std::string>& chunk, co
     run.T_analyze += wall() - t0 - t_write;
 }
 
-void MemParser::ParseAndSortFramesInFolder(std::string EventID, int Camera, std::vector<std::string>& Contents) {
-    Contents.clear();
-    for (size_t e = 0; e < events_.size(); e++) {
-        if (events_[e] != EventID) continue;
-        if (Camera < 0 || Camera >= (int)nframes_[e].size()) return;
-        char name[64];
-        for (int f = 0; f < nframes_[e][Camera]; f++) {
-            snprintf(name, sizeof(name), "cam%d_image%d.png", Camera, frame_offset_ + f);
-            Contents.push_back(name);
+void DetectPipeline::start(DetectRun* run, std::ofstream* out) {
+    stop();
+    run_ = run; out_ = out;
+    stop_ = false; inflight_ = 0; err_ = nullptr;
+    q_.clear();
+    th_ = std::thread(&DetectPipeline::loop, this);
+    started_ = true;
+}
+
+void DetectPipeline::loop() {
+    for (;;) {
+        Job job;
+        {
+            std::unique_lock<std::mutex> lk(m_);
+            cv_.wait(lk, [&] { return stop_ || !q_.empty(); });
+            if (q_.empty()) return;
+            job = std::move(q_.front());
+            q_.pop_front();
         }
-        return;
+        try {
+            DetectStagedBatch(*run_, job.chunk, job.keys, *out_);
+        } catch (...) {
+            std::lock_guard<std::mutex> lk(m_);
+            if (!err_) err_ = std::current_exception();
+        }
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            inflight_--;
+        }
+        cv_.notify_all();
     }
 }
 
-void MemParser::SetEvent(const std::string& event, const int* nframes, int ncams) {
-    for (size_t e = 0; e < events_.size(); e++)
-        if (events_[e] == event) { nframes_[e].assign(nframes, nframes + ncams); return; }
-    events_.push_back(event);
-    nframes_.emplace_back(nframes, nframes + ncams);
+void DetectPipeline::submit(std::vector<std::string> chunk, std::vector<std::string> keys) {
+    std::unique_lock<std::mutex> lk(m_);
+    cv_.wait(lk, [&] { return inflight_ == 0; });
+    if (err_) { std::exception_ptr e = err_; err_ = nullptr; std::rethrow_exception(e); }
+    q_.push_back(Job{std::move(chunk), std::move(keys)});
+    inflight_++;
+    lk.unlock();
+    cv_.notify_all();
+}
+
+void DetectPipeline::drain() {
+    std::unique_lock<std::mutex> lk(m_);
+    cv_.wait(lk, [&] { return inflight_ == 0; });
+    if (err_) { std::exception_ptr e = err_; err_ = nullptr; std::rethrow_exception(e); }
+}
+
+void DetectPipeline::stop() {
+    if (!started_) return;
+    {
+        std::unique_lock<std::mutex> lk(m_);
+        cv_.wait(lk, [&] { return inflight_ == 0; });
+        stop_ = true;
+    }
+    cv_.notify_all();
+    if (th_.joinable()) th_.join();
+    started_ = false;
+}
+
+void MemParser::ParseAndSortFramesInFolder(std::string EventID, int Camera, std::vector<std::string>& Contents) {
+    Contents.clear();
+    int n = 0;
+    {
+        std::lock_guard<std::mutex> g(tab_->mu);
+        auto it = tab_->nframes.find(EventID);
+        if (it == tab_->nframes.end() || Camera < 0 || Camera >= (int)it->second.size()) return;
+        n = it->second[Camera];
+    }
+    char name[64];
+    for (int f = 0; f < n; f++) {
+        snprintf(name, sizeof(name), "cam%d_image%d.png", Camera, frame_offset_ + f);
+        Contents.push_back(name);
+    }
+}
+
+void MemParser::GetEventDirLists(std::vector<std::string>& EventList) {
+    std::lock_guard<std::mutex> g(tab_->mu);
+    EventList.assign(tab_->order.begin(), tab_->order.end());
+}
+
+void MemParser::SetEvent(const std::string& event, const int* nframes, int ncams, size_t keep) {
+    std::lock_guard<std::mutex> g(tab_->mu);
+    auto it = tab_->nframes.find(event);
+    if (it != tab_->nframes.end()) { it->second.assign(nframes, nframes + ncams); return; }
+    tab_->nframes.emplace(event, std::vector<int>(nframes, nframes + ncams));
+    tab_->order.push_back(event);
+    while (tab_->order.size() > keep) {
+        tab_->nframes.erase(tab_->order.front());
+        tab_->order.pop_front();
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -131,7 +206,11 @@ struct HostRun {
     MemParser* parser = nullptr;
     std::ofstream out;
     std::string err;
+    DetectPipeline pipe;
+    int sub_batch = 32;
+    double base[5] = {0, 0, 0, 0, 0};           // counters at the last abubhost_stats call
 } g;
+int g_threads = 0;
 }  // namespace
 
 extern "C" {
@@ -158,11 +237,14 @@ int abubhost_open(int device, int rows, int cols, int ncams, int max_frames, int
 int abubhost_begin_run(const char* run_id, const char* out_dir, const char* mask_dir, int frame_offset, const int* training_set_sizes) {
     try {
         AbubDevice& dev = AbubDevice::Get();
+        g.pipe.stop();
         for (Trainer* t : g.trainers) delete t;
         g.trainers.clear();
         delete g.parser;
         DetectRun& r = g.run;
+        const double keepA = r.T_analyze, keepW = r.T_write;
         r = DetectRun();
+        r.T_analyze = keepA; r.T_write = keepW;
         r.run_number = run_id;
         r.out_dir = out_dir;
         if (!r.out_dir.empty() && r.out_dir.back() != '/') r.out_dir += "/";
@@ -182,9 +264,12 @@ int abubhost_begin_run(const char* run_id, const char* out_dir, const char* mask
         r.Trainers = &g.trainers;
         OutputWriter w(r.out_dir, r.run_number, r.frameOffset, r.numCams);
         w.writeHeader();
+        g.pipe.stop();
         if (g.out.is_open()) g.out.close();
         g.out.open(w.fileName(), std::fstream::out | std::fstream::app);
         if (!g.out) { g.err = "cannot open " + w.fileName(); return -1; }
+        r.threads = g_threads;
+        g.pipe.start(&g.run, &g.out);
         return 0;
     } catch (std::exception& e) {
         g.err = e.what();
@@ -202,28 +287,34 @@ int abubhost_recon(int slot_first, int nslots, const int* event_numbers, const i
         AbubDevice& dev = AbubDevice::Get();
         DetectRun& r = g.run;
         const int nc = r.numCams;
-        std::vector<std::string> chunk, keys;
-        std::vector<int> slots, tss;
-        g.parser->Clear();
-        for (int s = 0; s < nslots; s++) {
-            const std::string ev = std::to_string(event_numbers[s]);
-            chunk.push_back(ev);
-            keys.push_back(r.eventDir + ev + r.imageFolder + "|" + ev);
-            g.parser->SetEvent(ev, nframes + (size_t)s * nc, nc);
-            dev.BindSlot(keys.back(), slot_first + s);
-            dev.MarkResident(slot_first + s, nframes + (size_t)s * nc, mode == 0);
-            slots.push_back(slot_first + s);
-        }
+        std::vector<int> tss;
         for (int c = 0; c < nc; c++) tss.push_back(g.trainers[c]->TrainingSetSize);
-        const double a0 = dev.t_hist, a1 = dev.t_scan, a2 = dev.t_loc, a3 = r.T_analyze, a4 = r.T_write;
         long long sent = 0;
-        if (mode == 0) dev.AnalyzeBatch(slots, tss.data());
-        else sent = dev.StreamBatch(slots, tss.data(), chunk_frames);
-        DetectStagedBatch(r, chunk, keys, g.out);
-        if (stats) {
-            stats[0] += dev.t_hist - a0; stats[1] += dev.t_scan - a1; stats[2] += dev.t_loc - a2;
-            stats[3] += r.T_analyze - a3; stats[4] += r.T_write - a4; stats[5] += (double)sent;
+        /* sub-batches: while the per-camera objects of one run on the host cores (DetectPipeline), the device works on the next */
+        const int sub = g.sub_batch > 0 ? g.sub_batch : nslots;
+        for (int s0 = 0; s0 < nslots; s0 += sub) {
+            const int s1 = s0 + sub < nslots ? s0 + sub : nslots;
+            std::vector<std::string> chunk, keys;
+            std::vector<int> slots;
+            /* a slot whose previous event is still with the host stage: wait for it (a caller that alternates between
+             * two sets of slots never waits here) */
+            for (int s = s0; s < s1; s++)
+                if (dev.SlotInUse(slot_first + s)) { g.pipe.drain(); break; }
+            for (int s = s0; s < s1; s++) {
+                const std::string ev = std::to_string(event_numbers[s]);
+                chunk.push_back(ev);
+                keys.push_back(r.eventDir + ev + r.imageFolder + "|" + ev);
+                g.parser->SetEvent(ev, nframes + (size_t)s * nc, nc);
+                dev.BindSlot(keys.back(), slot_first + s);
+                dev.MarkResident(slot_first + s, nframes + (size_t)s * nc, mode == 0);
+                slots.push_back(slot_first + s);
+            }
+            if (mode == 0) dev.AnalyzeBatch(slots, tss.data());
+            else sent += dev.StreamBatch(slots, tss.data(), chunk_frames);
+            g.pipe.submit(std::move(chunk), std::move(keys));
         }
+        if (stats) stats[5] += (double)sent;
+        (void)stats;
         return 0;
     } catch (std::exception& e) {
         g.err = e.what();
@@ -231,9 +322,45 @@ int abubhost_recon(int slot_first, int nslots, const int* event_numbers, const i
     }
 }
 
-int abubhost_end_run() {
-    if (g.out.is_open()) g.out.close();
+/* Waits until every submitted event has been analysed and its rows are in the file. */
+int abubhost_drain() {
+    try {
+        g.pipe.drain();
+        return 0;
+    } catch (std::exception& e) {
+        g.err = e.what();
+        return -1;
+    }
+}
+
+/* Host threads of the event loop (0 = OpenMP's default) and events per sub-batch of abubhost_recon (the unit that is
+ * handed from the device stage to the host stage; 0 = the whole call).  Take effect at the next abubhost_begin_run. */
+int abubhost_set_threads(int threads, int sub_batch) {
+    g_threads = threads < 0 ? 0 : threads;
+    g.sub_batch = sub_batch < 0 ? 0 : sub_batch;
     return 0;
+}
+
+/* Seconds spent since the previous call of this function (after draining the pipeline): out[5] = {device trigger
+ * launches, trigger read-back (waits for K1/K2), localizer, host analysis, file writes}. */
+int abubhost_stats(double* out) {
+    if (abubhost_drain()) return -1;
+    AbubDevice& dev = AbubDevice::Get();
+    const double now[5] = {dev.t_hist, dev.t_scan, dev.t_loc, g.run.T_analyze, g.run.T_write};
+    for (int i = 0; i < 5; i++) { out[i] = now[i] - g.base[i]; g.base[i] = now[i]; }
+    return 0;
+}
+
+int abubhost_end_run() {
+    int rc = 0;
+    try {
+        g.pipe.stop();
+    } catch (std::exception& e) {
+        g.err = e.what();
+        rc = -1;
+    }
+    if (g.out.is_open()) g.out.close();
+    return rc;
 }
 
 void abubhost_close() {

@@ -177,7 +177,8 @@ int main(int argc, char** argv) {
     const int batch = std::max(1, opt.batch);
     void* nccl = nullptr;
     try {
-        AbubDevice::Get().Configure(opt.device >= 0 ? opt.device : opt.rank, numCams, max_frames, batch);
+        /* two batches of slots: one being analysed on the host cores while the next is staged and run on the device */
+        AbubDevice::Get().Configure(opt.device >= 0 ? opt.device : opt.rank, numCams, max_frames, 2 * batch);
         const int metric = opt.trigger_metric == "significance" ? ABUB_METRIC_SIGNIFICANCE
                          : opt.trigger_metric == "entropy" ? ABUB_METRIC_ENTROPY
                          : opt.trigger_metric == "entropy_significance" ? ABUB_METRIC_ENTROPY_SIGNIFICANCE : -1;
@@ -250,6 +251,8 @@ int main(int argc, char** argv) {
     drun.run_number = run_number; drun.out_dir = out_dir; drun.mask_dir = mask_dir; drun.eventDir = eventDir;
     drun.imageFolder = "/Images/"; drun.frameOffset = frameOffset; drun.numCams = numCams; drun.debug_mode = debug_mode;
     drun.nEvents = nEvents; drun.Trainers = &Trainers; drun.FileParser = FileParser;
+    DetectPipeline pipe;
+    pipe.start(&drun, &part_out);
     for (int b0 = ev_lo; b0 < ev_hi; b0 += batch) {
         const int b1 = std::min(b0 + batch, ev_hi);
         std::vector<std::string> chunk;
@@ -270,8 +273,10 @@ int main(int argc, char** argv) {
             std::cout << e.what() << std::endl;       /* the analyzers will meet the same problem and report -6 */
         }
         T_stage += wall() - ts0;
-        DetectStagedBatch(drun, chunk, keys, part_out);
+        /* the per-camera objects of this batch run on a worker thread while the next batch is staged */
+        pipe.submit(chunk, keys);
     }
+    pipe.stop();
     T_analyze = drun.T_analyze; T_write = drun.T_write;
     part_out.close();
     printf("run complete.\n");

@@ -357,6 +357,8 @@ def run_ours(args, rank, world, local_rank):
 
     out_dir = os.path.join(tmp, "out")
     os.makedirs(out_dir)
+    host_threads = args.host_threads or max(1, cores // world - 1)   # one core stays with the thread that drives the device
+    hr.set_threads(host_threads, args.sub_batch)                     # (torchrun exports OMP_NUM_THREADS=1)
     out_path = hr.begin_run(RUN_ID, out_dir, mask_dir, 30, tss)
     nf_all = np.full((B, NCAMS), NFRAMES, np.int32)
     base_no = rank * 10_000_000
@@ -381,6 +383,7 @@ def run_ours(args, rank, world, local_rank):
         ev0.record(stream)
         for i in range(args.steps):
             step()
+        hr.drain()                                        # the rows of the last events are in the file
         ev1.record(stream)
         torch.cuda.synchronize()
         wall_ms = (time.perf_counter() - t0) * 1e3
@@ -405,6 +408,7 @@ def run_ours(args, rank, world, local_rank):
         if n_s > B:
             raise SystemExit("--events-per-step is smaller than the CPU sample")
         hr.recon(0, list(range(n_s)), nf_all[:n_s])
+        hr.drain()
         hr.end_run()
         import oracle.cv2_oracle as o
         got = open(p_path).read()
@@ -507,6 +511,7 @@ def run_ours(args, rank, world, local_rank):
         pin.copy_(slot_tensor(torch, ctx, s).cpu())
     torch.cuda.synchronize()
     nf_e = nf_all[:Be]
+    hr.set_threads(host_threads, args.e2e_sub_batch)
 
     def e2e_step():
         numbers = [base_no + 5_000_000 + step_no[0] * Be + s for s in range(Be)]
@@ -522,6 +527,7 @@ def run_ours(args, rank, world, local_rank):
     t0 = time.perf_counter()
     for _ in range(args.e2e_steps):
         e2e_step()
+    hr.drain()
     torch.cuda.synchronize()
     e2e_ms_local = (time.perf_counter() - t0) * 1e3
     e2e_stage = hr.read_stats()
@@ -570,7 +576,7 @@ def run_ours(args, rank, world, local_rank):
                        "events_timed": world * B * args.steps, "note_10000": "10,000 events = %d steps of %d events" % (-(-10000 // B), B),
                        "l2": "inputs (35 GB/step at 125 events) exceed L2; no flush",
                        "event_mix": "90% normal (1-3 bubbles), 5% multi (>=20), 5% no-trigger; noise sigma 2.0",
-                       "train_events": n_train, "early_chunk": args.early_chunk,
+                       "train_events": n_train, "early_chunk": args.early_chunk, "sub_batch": args.sub_batch, "host_threads": host_threads,
                        "rendered_on": "host (numpy PCG64, %d of %d ring events on this rank, %.1f s)" % (share, R, t_render)},
             "stage_seconds_per_step": {k: v / args.steps for k, v in stage.items() if k != "frames_sent"},
             "device_ms_per_step": dev_ms / args.steps,
@@ -618,6 +624,7 @@ def trainer_leg(args, ctx, torch, dist, rank, world, R):
     lo, hi = E * rank // world, E * (rank + 1) // world
     idfile = os.path.join(tempfile.gettempdir(), "abub_bench_%s.ncclid" % os.environ.get("MASTER_PORT", "0"))
     comm = ctx.nccl_comm_create(idfile, rank, world)
+    ctx.nccl_barrier(comm)                     # first collective on the communicator: connection set-up, not timed
     t_gate = t_part = t_ar = t_fix = 0.0
     flagged, planes = [], []
     dist.barrier()
@@ -684,8 +691,11 @@ def main():
     ap.add_argument("--ring-events", type=int, default=32)
     ap.add_argument("--train-events", type=int, default=25)
     ap.add_argument("--early-chunk", type=int, default=6, help="frame pairs per round of the trigger search's early exit (0 = full table)")
-    ap.add_argument("--e2e-events", type=int, default=16)
-    ap.add_argument("--e2e-steps", type=int, default=40)
+    ap.add_argument("--host-threads", type=int, default=0, help="threads of the host event loop (0 = cores per rank - 1)")
+    ap.add_argument("--sub-batch", type=int, default=32, help="events handed from the device stage to the host stage at a time")
+    ap.add_argument("--e2e-events", type=int, default=32)
+    ap.add_argument("--e2e-sub-batch", type=int, default=16)
+    ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--e2e-chunk", type=int, default=4)
     ap.add_argument("--trigger-steps", type=int, default=8, help="steps of the trigger-only extra (0 = skip)")
     ap.add_argument("--trainer-events", type=int, default=200, help="training events of the sharded Trainer leg at N > 1 (0 = skip)")

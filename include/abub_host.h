@@ -41,12 +41,24 @@ int abubhost_begin_run(const char* run_id, const char* out_dir, const char* mask
  * time, per camera only as far as FindTriggerFrame reads (trig+2, AnalyzerUnit.cpp:191-300) and
  * CalculatePostTriggerFrameParams needs (trig+n_post, L3Localizer.cpp:770).
  * Per event: FindTriggerFrame -> LocalizeOMatic -> stageCameraOutput -> rows appended and flushed, in event order.
- * stats[8] (may be NULL) is incremented by {device trigger s, trigger read-back s, localizer s, host analysis s,
- * file write s, frames sent over PCIe, 0, 0}. */
+ * stats[8] (may be NULL): stats[5] is incremented by the frames sent over PCIe (the other entries are reserved; stage
+ * times come from abubhost_stats). */
 int abubhost_recon(int slot_first, int nslots, const int* event_numbers, const int* nframes, int mode, int chunk_frames,
                    double* stats);
 
-int abubhost_end_run(void);      /* closes the output file */
+/* abubhost_recon returns once the device work of its events is done; the per-camera objects of the last sub-batch may
+ * still be running on the host cores (they overlap the device work of the next call).  abubhost_drain returns when
+ * every submitted event has been analysed and its rows are in the file. */
+int abubhost_drain(void);
+/* Host threads of the event loop (0 = OpenMP's default; a launcher such as torchrun exports OMP_NUM_THREADS=1) and events
+ * per sub-batch, the unit handed from the device stage to the host stage (0 = a whole abubhost_recon call).  Take
+ * effect at the next abubhost_begin_run. */
+int abubhost_set_threads(int threads, int sub_batch);
+/* Seconds per stage since the previous call (drains first): out[5] = {trigger launches, trigger read-back incl. waiting
+ * for K1/K2, localizer, host analysis, file writes}. */
+int abubhost_stats(double* out);
+
+int abubhost_end_run(void);      /* drains and closes the output file */
 void abubhost_close(void);       /* end_run + destroys the context */
 
 #ifdef __cplusplus

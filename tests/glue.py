@@ -163,6 +163,7 @@ def host_recon_text(run, trained, tmp_path, tag, pinned, early_chunk, batch=None
         for e0 in range(0, nev, b):
             e1 = min(nev, e0 + b)
             hr.recon(e0, run.event_numbers[e0:e1], nframes[e0:e1], pinned=pinned, chunk_frames=4)
+        hr.drain()
         stats = hr.read_stats()
         hr.end_run()
         text = open(path).read()

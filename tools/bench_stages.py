@@ -19,6 +19,38 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench as B  # noqa: E402
 
+NCAMS, NFRAMES, ROWS, COLS = B.NCAMS, B.NFRAMES, B.ROWS, B.COLS
+
+
+# synthetic events rendered on the device (torch RNG; same pixel model as autobub3hs_b200.synth): fast set-up for stage timings
+def fill_slot(torch, t, bgs, specs_for_event, gen, noise_sigma=2.0):
+    """t: u8 [cam, frame, rows, cols] view of a slot.  Renders background + N(0,sigma) noise +
+    growing discs, rounds, clips (SURVEY.md 8(d) pixel model)."""
+    for c in range(NCAMS):
+        img = torch.randn((NFRAMES, ROWS, COLS), generator=gen, device="cuda", dtype=torch.float32)
+        img.mul_(noise_sigma).add_(bgs[c])
+        for b in specs_for_event.get(c, ()):
+            for f in range(b.f_trig, NFRAMES):
+                r = b.r0 + b.growth * (f - b.f_trig)
+                x0, x1 = max(0, int(b.cx - r - 2)), min(COLS, int(b.cx + r + 3))
+                y0, y1 = max(0, int(b.cy - r - 2)), min(ROWS, int(b.cy + r + 3))
+                yy = torch.arange(y0, y1, device="cuda", dtype=torch.float32)[:, None]
+                xx = torch.arange(x0, x1, device="cuda", dtype=torch.float32)[None, :]
+                disc = ((xx - b.cx) ** 2 + (yy - b.cy) ** 2) <= r * r
+                img[f, y0:y1, x0:x1] += disc * float(b.amp)
+        t[c].copy_(img.round_().clamp_(0, 255).to(torch.uint8))
+
+
+def event_classes(n, rank):
+    out = []
+    for i in range(n):
+        k = (i + rank) % 20
+        out.append("multi" if k == 7 else ("notrigger" if k == 13 else "normal"))
+    return out
+
+
+
+
 
 def main():
     ap = argparse.ArgumentParser()
@@ -27,6 +59,7 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--png-events", type=int, default=8, help="events of the PNG decode stage (0 = skip)")
     ap.add_argument("--only-png", action="store_true", help="only the PNG decode stage")
+    ap.add_argument("--kernels", action="store_true", help="device time per kernel group of one localizer pass and one trigger pass (abub_profile)")
     args = ap.parse_args()
     import torch
     from autobub3hs_b200 import capi, synth
@@ -38,10 +71,10 @@ def main():
     bgs = [torch.from_numpy(synth.make_background(c, B.ROWS, B.COLS).astype(np.float32)).cuda() for c in range(B.NCAMS)]
     gen = torch.Generator(device="cuda")
     gen.manual_seed(7919)
-    classes = B.event_classes(E, 0)
+    classes = event_classes(E, 0)
     for s in range(E):
         es = synth.make_event_spec(s, classes[s], cam_masks, bellows, seed=11)
-        B.fill_slot(torch, B.slot_tensor(torch, ctx, s), bgs, es.bubbles, gen)
+        fill_slot(torch, B.slot_tensor(torch, ctx, s), bgs, es.bubbles, gen)
         ctx.event_set_nframes(s, [B.NFRAMES] * B.NCAMS)
     torch.cuda.synchronize()
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0) if os.path.exists(
@@ -100,6 +133,16 @@ def main():
                           "seconds": best, "items_per_s": len(items) / best, "algorithmic_GB": byt / 1e9,
                           "GBps": byt / best / 1e9, "frac_of_peak": byt / best / 1e9 / peak}))
 
+        if args.kernels:
+            ctx.profile(True)
+            for _ in range(args.reps):
+                ctx.localize_batch_raw(items, cap=1 << 18, buffers=bufs)
+                ctx.trigger_hist(0, E)
+                ctx.trigger_scan(0, E)
+            prof = ctx.profile_read()
+            ctx.profile(False)
+            print(json.dumps({"stage": "kernel groups (device ms per pass)", "items": len(items), "frames": sum(it[5] + 1 for it in items),
+                              "kernels": {n: round(ms / args.reps, 4) for n, ms, c in prof if c}}))
         best = None
         for _ in range(args.reps):
             t0 = time.perf_counter()
