@@ -110,6 +110,8 @@ struct abub_ctx {
     void*     bel = nullptr;        // bellows-veto arena (k8_bellows.cu)
     void*     png = nullptr;        // on-device PNG decode arena (k9_png.cu)
     int*      d_post_list = nullptr; // indices of the post-trigger jobs of a localizer chunk (k5_post_tma.cu)
+    int*      h_post_list = nullptr; // its pinned staging copy; post_ev = the last upload from it
+    cudaEvent_t post_ev = nullptr;
     int       post_cap = 0;
     void*     d_tmaps = nullptr;    // CUtensorMap[max_slots + 3*ncams]: frames of a slot, then per camera K16, TrainedAvgImage, -t
                                     // (k1_trigger_tma.cu builds them; null = TMA paths off)

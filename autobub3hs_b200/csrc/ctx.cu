@@ -97,6 +97,8 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     cudaFree((void*)ctx->d_gate_tab); cudaFree(ctx->d_gate_hist);
     cudaFree(ctx->d_tmaps);
     cudaFree(ctx->d_post_list);
+    if (ctx->h_post_list) cudaFreeHost(ctx->h_post_list);
+    if (ctx->post_ev) cudaEventDestroy(ctx->post_ev);
     if (ctx->h_raw) cudaFreeHost(ctx->h_raw);
     for (cudaEvent_t e : ctx->prof.pool) cudaEventDestroy(e);
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
@@ -316,10 +318,7 @@ extern "C" int abub_event_set_nframes(abub_ctx* ctx, int slot, const int* nframe
         ABUB_REQUIRE(ctx, nframes[c] >= 0 && nframes[c] <= ctx->max_frames, "nframes out of range");
         ctx->slots[slot].nframes[c] = nframes[c];
     }
-    int rc = push_nframes(ctx, slot);
-    if (rc) return rc;
-    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return ABUB_OK;
+    return push_nframes(ctx, slot);                                  // counts travel as a kernel argument: nothing to wait for
 }
 
 // ---- trigger ------------------------------------------------------------------------

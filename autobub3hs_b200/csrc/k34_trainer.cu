@@ -164,8 +164,24 @@ __global__ void k4_partials_kernel(const uint8_t* const* __restrict__ frames, in
     sumsq[p] = q;
 }
 
-// mean/sigma from reduced integer partials in fp64; flags pixels whose truncation could
-// differ from the sequential float32 recurrence (value within eps of an integer boundary).
+// mean/sigma from reduced integer partials in fp64; flags every pixel whose truncated planes COULD differ from the
+// sequential float32 recurrence of K4 (Trainer.cpp:185-196).  The flag test is a worst-case bound of that recurrence's
+// rounding error, u = 2^-24, samples in [0, 255], k = 2 .. n (step 1 is exact: mean = x, m2 = 0):
+//   mean:  e_k = e_{k-1} (k-1)/k + l_k with |l_k| <= u' (2 |delta| / k + |mean_k|) <= 256 u' (2 / k + 1)
+//          => n |e_n| <= 256 u' sum_k (2 + k)   =>   |e_n| <= 256 u' (n / 2 + 5 / 2) =: e_mean   (increasing in n, so it
+//          also bounds every intermediate e_k)
+//   m2:    the exact terms P_k = delta_k (x_k - mean_k) = delta_k^2 (k-1)/k are >= 0 and sum to M2.  Computed terms
+//          differ by the three roundings (<= 3 u' P_k) and by the mean errors inside both factors
+//          (<= e_mean (|delta_k| + |x_k - mean_k|) + e_mean^2 <= 2 e_mean |delta_k| + e_mean^2); the n-1 additions
+//          each lose <= u' M2.  With sum |delta_k| <= sqrt(n sum delta_k^2) <= sqrt(2 n M2):
+//          |dM2| <= u' M2 (n + 3) + 2 e_mean sqrt(2 n M2) + n e_mean^2 =: bM,  bv = bM / (n-1)
+//   sigma: sqrt(var + bv) - sqrt(var) <= min(bv / (2 sigma), sqrt(bv))   (computed too large: matters just BELOW an integer)
+//          sqrt(var) - sqrt(var - bv) <= min(bv / sigma, sqrt(bv))       (computed too small: matters just ABOVE an integer)
+//          plus the division's and the square root's own roundings (<= 3 u' sigma).
+// u' = 1.01 u absorbs the second-order terms.  A flagged pixel is recomputed with the float32 recurrence itself
+// (k4_fixup_kernel), so a generous bound costs time, never exactness; an unflagged pixel provably needs no repair.
+// tests/test_gpu_train_localize.py::test_partials_flag_bound_covers_every_float32_difference attacks it (sparse 255
+// spikes, two-level and drifting data, n up to 2000).
 __global__ void k4_finish_partials_kernel(const uint32_t* __restrict__ sum, const uint64_t* __restrict__ sumsq, int n,
                                           uint8_t* __restrict__ mean_out, uint8_t* __restrict__ sigma_out,
                                           int* __restrict__ nflag, uint8_t* __restrict__ flag, size_t npix) {
@@ -173,12 +189,22 @@ __global__ void k4_finish_partials_kernel(const uint32_t* __restrict__ sum, cons
     if (p >= npix) return;
     const double s = (double)sum[p], q = (double)sumsq[p];
     const double mean = s / n;
-    double var = (n > 1) ? (q - s * s / n) / (n - 1) : 0.0;
-    if (var < 0) var = 0;
+    double M2 = (n > 1) ? (q - s * s / n) : 0.0;
+    if (M2 < 0) M2 = 0;
+    const double var = (n > 1) ? M2 / (n - 1) : 0.0;
     const double sg = sqrt(var);
-    const double eps = (double)n * 1.1920928955078125e-07 * 4.0 * (1.0 + mean);
+    const double u = 1.01 * 5.9604644775390625e-08;
+    const double e_mean = 256.0 * u * (0.5 * (double)n + 2.5);
+    const double bM = u * M2 * ((double)n + 3.0) + 2.0 * e_mean * sqrt(2.0 * (double)n * M2) + (double)n * e_mean * e_mean;
+    const double bv = bM / (double)(n > 1 ? n - 1 : 1) + 1e-9;       // + the fp64 cancellation in M2 (q, s*s/n < 2^38)
+    const double rb = sqrt(bv), tail = 3.0 * u * sg + 1e-12;
+    const double e_up = (sg > 0 ? fmin(bv / (2.0 * sg), rb) : rb) + tail;
+    const double e_dn = (sg > 0 ? fmin(bv / sg, rb) : rb) + tail;
     const double fm = mean - floor(mean), fs = sg - floor(sg);
-    const bool risky = (fm < eps) || (1.0 - fm < eps) || (fs < eps) || (1.0 - fs < eps) || n < 2;
+    // all samples equal (M2 == 0): the recurrence is exact (delta = 0 from step 2 on), nothing to repair
+    const bool risky_m = M2 > 0 && (fm < e_mean || 1.0 - fm < e_mean);
+    const bool risky_s = M2 > 0 && (fs < e_dn || 1.0 - fs < e_up);
+    const bool risky = risky_m || risky_s || n < 2;
     mean_out[p] = (uint8_t)mean;
     sigma_out[p] = (n > 1) ? (uint8_t)(int)sg : 0;
     flag[p] = risky ? 1 : 0;

@@ -240,21 +240,28 @@ bool abub_k5b_tma_supported(const abub_ctx* ctx) {
 
 int abub_k5b_launch_tma(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs) {
     // the post-trigger jobs of the chunk (genesis == 0 in the host copy of the job table): their indices go up as a table
-    std::vector<int> list;
     const abub_loc_job* hj = abub_loc_host_jobs(ctx);
-    for (int j = 0; j < njobs; j++)
-        if (hj[j].genesis == 0) list.push_back(j);
-    const int np = (int)list.size();
+    int np = 0;
+    for (int j = 0; j < njobs; j++) np += (hj[j].genesis == 0);
     if (np == 0) return ABUB_OK;
     if (np > ctx->post_cap) {
+        if (ctx->post_ev) ABUB_CHECK_CUDA(ctx, cudaEventSynchronize(ctx->post_ev));
         cudaFree(ctx->d_post_list);
+        if (ctx->h_post_list) cudaFreeHost(ctx->h_post_list);
         ctx->d_post_list = nullptr;
+        ctx->h_post_list = nullptr;
         ctx->post_cap = 0;
-        ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_post_list, (size_t)(np + np / 2 + 64) * sizeof(int)));
-        ctx->post_cap = np + np / 2 + 64;
+        const int cap = np + np / 2 + 64;
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_post_list, (size_t)cap * sizeof(int)));
+        ABUB_CHECK_CUDA(ctx, cudaHostAlloc(&ctx->h_post_list, (size_t)cap * sizeof(int), cudaHostAllocDefault));
+        ctx->post_cap = cap;
     }
-    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_post_list, list.data(), (size_t)np * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));          // `list` is a local
+    if (!ctx->post_ev) ABUB_CHECK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->post_ev, cudaEventDisableTiming));
+    else ABUB_CHECK_CUDA(ctx, cudaEventSynchronize(ctx->post_ev));     // the previous chunk's upload has left the staging copy
+    for (int j = 0, k = 0; j < njobs; j++)
+        if (hj[j].genesis == 0) ctx->h_post_list[k++] = j;
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(ctx->d_post_list, ctx->h_post_list, (size_t)np * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    ABUB_CHECK_CUDA(ctx, cudaEventRecord(ctx->post_ev, ctx->stream));
     const int nxg = (ctx->cols + P_OW - 1) / P_OW;
     const int nstrips = (ctx->rows + P_TH - 1) / P_TH;
     const int h0 = ctx->rows - P_TH * (nstrips - 1);

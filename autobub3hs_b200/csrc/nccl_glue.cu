@@ -37,13 +37,29 @@ __device__ __forceinline__ void wf_step(float x, float cnt, float& mean, float& 
     m2 = __fadd_rn(m2, __fmul_rn(delta, __fsub_rn(x, mean)));
 }
 
-// samples of the flagged pixels from this rank's kept frames: out[i*stride + f]
+// samples of the flagged pixels from this rank's kept frames: out[i*stride + f].  A block moves 32 pixels x 32 frames
+// through shared memory: the reads run along the (ascending) pixel list inside one frame, the writes along the frames
+// of one pixel, both contiguous.  grid.x = ceil(n_flagged / 32), block = (32, 8).
 __global__ void gather_flagged_kernel(const uint8_t* const* __restrict__ frames, int n_local, const int* __restrict__ idx,
                                       int n_flagged, int stride, uint8_t* __restrict__ out) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_flagged) return;
-    const int p = idx[i];
-    for (int f = 0; f < n_local; f++) out[(size_t)i * stride + f] = frames[f][p];
+    __shared__ uint8_t tile[32][33];
+    const int i0 = blockIdx.x * 32;
+    const int pi = i0 + threadIdx.x;
+    const int p = pi < n_flagged ? idx[pi] : -1;
+    for (int f0 = 0; f0 < n_local; f0 += 32) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int f = f0 + threadIdx.y + 8 * k;
+            tile[threadIdx.y + 8 * k][threadIdx.x] = (f < n_local && p >= 0) ? frames[f][p] : (uint8_t)0;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int i = i0 + threadIdx.y + 8 * k, f = f0 + threadIdx.x;
+            if (i < n_flagged && f < n_local) out[(size_t)i * stride + f] = tile[threadIdx.x][threadIdx.y + 8 * k];
+        }
+        __syncthreads();
+    }
 }
 
 // sequential float32 recurrence over the ranks' samples in rank order (= global push order)
@@ -171,14 +187,24 @@ extern "C" int abub_train_finish_allreduced(abub_ctx* ctx, int cam, void* comm, 
         cub::DeviceSelect::Flagged(nullptr, tmp_bytes, it, cs.d_flag, d_idx, d_nsel, (int)ctx->npix, ctx->stream);
         ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_tmp, tmp_bytes));
         cub::DeviceSelect::Flagged(d_tmp, tmp_bytes, it, cs.d_flag, d_idx, d_nsel, (int)ctx->npix, ctx->stream);
-        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_loc, (size_t)F * stride));
-        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_all, (size_t)world * F * stride));
-        ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_loc, 0, (size_t)F * stride, ctx->stream));
-        ABUB_L(ctx), gather_flagged_kernel<<<(F + 127) / 128, 128, 0, ctx->stream>>>(cs.d_table, n_local, d_idx, F, stride, d_loc);
-        nr = ag(d_loc, d_all, (size_t)F * stride, NCCL_U8, comm, ctx->stream);
-        if (!nr)
-            ABUB_L(ctx), fixup_gathered_kernel<<<(F + 127) / 128, 128, 0, ctx->stream>>>(d_all, d_counts, world, d_idx, F, stride, n,
-                                                                             cs.d_mean, cs.d_sigma);
+        // the flagged pixels go through the gather in tiles so that the gathered samples (world x tile x stride bytes on
+        // every rank) stay under ABUB_FIXUP_TILE_BYTES however many frames were kept and however many pixels are flagged;
+        // F, world and stride are the same on every rank, so every rank walks the same tiles
+        const size_t budget = (size_t)256 << 20;
+        size_t tile = budget / ((size_t)world * stride);
+        tile = tile < 1024 ? 1024 : tile;
+        if (tile > (size_t)F) tile = (size_t)F;
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_loc, tile * stride));
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_all, (size_t)world * tile * stride));
+        for (size_t t0 = 0; t0 < (size_t)F && !nr; t0 += tile) {
+            const int ft = (int)((size_t)F - t0 < tile ? (size_t)F - t0 : tile);
+            ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_loc, 0, (size_t)ft * stride, ctx->stream));
+            ABUB_L(ctx), gather_flagged_kernel<<<(ft + 31) / 32, dim3(32, 8), 0, ctx->stream>>>(cs.d_table, n_local, d_idx + t0, ft, stride, d_loc);
+            nr = ag(d_loc, d_all, (size_t)ft * stride, NCCL_U8, comm, ctx->stream);
+            if (!nr)
+                ABUB_L(ctx), fixup_gathered_kernel<<<(ft + 127) / 128, 128, 0, ctx->stream>>>(d_all, d_counts, world, d_idx + t0, ft, stride, n,
+                                                                                   cs.d_mean, cs.d_sigma);
+        }
         cudaError_t e = cudaStreamSynchronize(ctx->stream);
         cudaFree(d_idx); cudaFree(d_nsel); cudaFree(d_tmp); cudaFree(d_loc); cudaFree(d_all);
         if (nr) { cudaFree(d_counts); ctx->err = "ncclAllGather(samples) failed"; return ABUB_E_NCCL; }

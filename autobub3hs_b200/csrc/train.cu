@@ -4,6 +4,7 @@
 // statistics are one pass of K4 over that table at abub_train_finish.
 #include <dlfcn.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include "abub_internal.cuh"
 
@@ -152,26 +153,15 @@ extern "C" int abub_train_add_slots(abub_ctx* ctx, int cam, const int* slots, in
     std::vector<char> keep;
     int rc = gate_batch(ctx, pairs, n, e, keep);
     if (rc) return rc;
-    // park the kept pairs (frames 0 and 1 are adjacent in the slot: one copy per event), in event order
+    // the kept pairs stay where they are: K4 / the partial sums read them through the frame table in place (no parking
+    // copy, no wait) -- the caller keeps these slots untouched until abub_train_finish* / abub_train_partials has run
     for (int i = 0; i < n; i++) {
         if (entropy) entropy[i] = e[i];
         if (kept) kept[i] = keep[i];
         if (!keep[i]) continue;
-        if ((rc = ensure_room(ctx, cs, 2))) return rc;
-        uint8_t* f0 = store_ptr(ctx, cs, cs.n_stored);
-        uint8_t* f1 = store_ptr(ctx, cs, cs.n_stored + 1);
-        if (f1 == f0 + ctx->npix) {
-            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(f0, pairs[2 * i], 2 * ctx->npix, cudaMemcpyDeviceToDevice, ctx->stream));
-        } else {
-            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(f0, pairs[2 * i], ctx->npix, cudaMemcpyDeviceToDevice, ctx->stream));
-            ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(f1, pairs[2 * i + 1], ctx->npix, cudaMemcpyDeviceToDevice, ctx->stream));
-        }
-        cs.kept.push_back(f0);
-        cs.kept.push_back(f1);
-        cs.n_stored += 2;
+        cs.kept.push_back(pairs[2 * i]);
+        cs.kept.push_back(pairs[2 * i + 1]);
     }
-    // the slots may be overwritten as soon as this returns
-    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return ABUB_OK;
 }
 
@@ -350,8 +340,9 @@ extern "C" int abub_train_finish_partials(abub_ctx* ctx, int cam, uint8_t* mean,
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(cnt, cs.d_count, sizeof(cnt), cudaMemcpyDeviceToHost, ctx->stream));
     ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (n_flagged) *n_flagged = cnt[1];
-    // single-rank case: the full frame table is local, repair flagged pixels exactly
-    if ((int)cs.kept.size() == n) {
+    // single-rank case: the full frame table is local, repair flagged pixels exactly.  ABUB_TRAIN_NO_FIXUP (test hook)
+    // leaves the fp64 planes as they are so that a test can count what the repair had to change.
+    if ((int)cs.kept.size() == n && !getenv("ABUB_TRAIN_NO_FIXUP")) {
         rc = abub_k4_fixup(ctx, cs.d_table, n, cs.d_flag, cs.d_mean, cs.d_sigma);
         if (rc) return rc;
     }

@@ -692,7 +692,7 @@ def main():
     ap.add_argument("--train-events", type=int, default=25)
     ap.add_argument("--early-chunk", type=int, default=6, help="frame pairs per round of the trigger search's early exit (0 = full table)")
     ap.add_argument("--host-threads", type=int, default=0, help="threads of the host event loop (0 = cores per rank - 1)")
-    ap.add_argument("--sub-batch", type=int, default=32, help="events handed from the device stage to the host stage at a time")
+    ap.add_argument("--sub-batch", type=int, default=64, help="events handed from the device stage to the host stage at a time")
     ap.add_argument("--e2e-events", type=int, default=32)
     ap.add_argument("--e2e-sub-batch", type=int, default=16)
     ap.add_argument("--e2e-steps", type=int, default=20)

@@ -167,7 +167,10 @@ int abub_train_add_slot(abub_ctx* ctx, int cam, int slot, float* entropy, int* k
 /* Batched forms of the two calls above, for the event loop of Trainer.cpp:262-296 run over many events at
  * once: n events in the loop's order, one gate launch and one device->host read for all of them;
  * entropy[n] / kept[n] out (either may be NULL).  abub_train_add_events takes n consecutive
- * frame pairs (n * 2*rows*cols host bytes, pinned memory makes the upload asynchronous). */
+ * frame pairs (n * 2*rows*cols host bytes, pinned memory makes the upload asynchronous).
+ * abub_train_add_slots keeps no copy: the statistics read the kept frames where they lie in the slots, so the
+ * slots named here must stay untouched until abub_train_finish / abub_train_partials of this camera has run
+ * (a slot may be named more than once, e.g. a ring of resident events). */
 int abub_train_add_slots(abub_ctx* ctx, int cam, const int* slots, int n, float* entropy, int* kept);
 int abub_train_add_events(abub_ctx* ctx, int cam, const uint8_t* frames01, int n, float* entropy, int* kept);
 /* CalculateMeanSigmaImageVector (Trainer.cpp:144-216): exact sequential float32

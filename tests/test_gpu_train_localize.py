@@ -322,3 +322,69 @@ def test_train_add_events_with_rejected_pairs(capi):
     m_ref, s_ref = o.welford_mean_sigma(kept)
     assert (cnt, st) == (8, 0)
     assert np.array_equal(mean, m_ref) and np.array_equal(sigma, s_ref)
+
+
+def _adversarial_stack(kind, n, rows, cols, rng):
+    """n/2 distinct frames (each is pushed twice: an identical pair always passes the gate, Trainer.cpp:287)."""
+    h = n // 2
+    base = rng.integers(0, 250, (rows, cols))
+    if kind == "noise":
+        fr = base[None] + (rng.normal(0, 1, (h, rows, cols)) * rng.uniform(1, 6, (rows, cols))[None]).round()
+    elif kind == "spikes":              # sparse 255 spikes on a dark floor: sigma >> mean, the case the old threshold missed
+        fr = np.where(rng.random((h, rows, cols)) < 1.0 / 16, 255, (base % 8)[None] + rng.integers(0, 2, (h, rows, cols)))
+    elif kind == "two_level":           # exact .5 / integer means, sigma on exact values
+        lv = rng.integers(0, 128, (2, rows, cols))
+        fr = np.where((np.arange(h) % 2 == 0)[:, None, None], lv[0][None], (lv[0] + 2 * lv[1])[None])
+    elif kind == "drift":               # slow ramp: the recurrence's mean lags, order matters most
+        fr = base[None] * 0.5 + np.linspace(0, 120, h)[:, None, None] + rng.normal(0, 1.5, (h, rows, cols))
+    elif kind == "near_integer":        # mean = v + 2 j / n, -6 <= j <= 6: just above / just below an integer
+        fr = np.repeat(base[None] + 1, h, 0)
+        j = rng.integers(-6, 7, (rows, cols))
+        for t in range(6):
+            fr[t] += (j > t).astype(fr.dtype) - (-j > t).astype(fr.dtype)
+        fr = fr[rng.permutation(h)]
+    else:
+        raise ValueError(kind)
+    return np.clip(fr, 0, 255).astype(np.uint8)
+
+
+@pytest.mark.parametrize("n,kind", [(40, "noise"), (40, "spikes"), (400, "two_level"), (2000, "near_integer"), (2000, "noise"),
+                                    (2000, "spikes"), (2000, "drift")])
+def test_partials_flag_bound_covers_every_float32_difference(capi, monkeypatch, n, kind):
+    """Multi-GPU Trainer: planes from the exact integer sums (fp64) are truncated like the float32 recurrence's except
+    where rounding decides; those pixels must ALL be flagged (k4_finish_partials_kernel's error bound), because only
+    flagged pixels are repaired.  Single GPU, adversarial data: (1) K4 planes; (2) integer partials WITHOUT the repair
+    (test hook ABUB_TRAIN_NO_FIXUP): the pixels that differ from K4 are counted -- the data must produce some, or the
+    test has no teeth; (3) integer partials with the repair == K4 everywhere, i.e. every differing pixel was flagged."""
+    rows, cols = 48, 64
+    rng = np.random.default_rng(n * 7 + len(kind))
+    fr = _adversarial_stack(kind, n, rows, cols, rng)
+    pairs = np.stack([fr, fr], axis=1)                            # [n/2, 2, rows, cols]
+    with capi.Context(rows, cols, 1, 4, max_slots=1) as ctx:
+        def feed():
+            ctx.train_begin(0)
+            for i in range(0, len(pairs), 250):
+                _, k = ctx.train_add_events(0, pairs[i:i + 250])
+                assert k.all()
+        feed()
+        m4, s4, n4, st4 = ctx.train_finish(0)
+        assert (n4, st4) == (n, 0)
+        monkeypatch.setenv("ABUB_TRAIN_NO_FIXUP", "1")
+        feed()
+        ctx.train_partials(0)
+        m0, s0, n0, st0, nflag = ctx.train_finish_partials(0)
+        monkeypatch.delenv("ABUB_TRAIN_NO_FIXUP")
+        feed()
+        ctx.train_partials(0)
+        m1, s1, n1, st1, nflag1 = ctx.train_finish_partials(0)
+    assert (n0, st0, n1, st1) == (n, 0, n, 0) and nflag1 == nflag
+    assert np.array_equal(m1, m4) and np.array_equal(s1, s4), (kind, n)
+    ndiff = int(((m0 != m4) | (s0 != s4)).sum())
+    assert ndiff <= nflag
+    print(f"\n[flag bound] n={n} {kind}: {ndiff} pixels differ before the repair, {nflag} of {rows * cols} flagged")
+    if kind in ("two_level", "near_integer"):
+        assert ndiff > 0 or nflag > 0                              # means / sigmas sit on the boundaries by construction
+    if kind == "noise":
+        # generic data: exactly-integer means (a share ~ 1/n of the pixels at small n) plus the bound's width,
+        # 2 e_mean + e_up + e_dn ~ 0.5e-4 n at sigma ~ 3
+        assert nflag <= (0.06 + 1e-4 * n) * rows * cols, (nflag, n)

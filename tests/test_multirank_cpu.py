@@ -40,11 +40,19 @@ for cam in range(4):
         dist.all_reduce(t)                       # integer sums: associative, so the result is rank-independent
     N = int(n.item()); s = s.numpy().astype(F64); q = q.numpy().astype(F64)
     mean = s / N
-    var = np.maximum((q - s * s / N) / (N - 1), 0.0) if N > 1 else np.zeros_like(s)
+    M2 = np.maximum(q - s * s / N, 0.0) if N > 1 else np.zeros_like(s)
+    var = M2 / max(N - 1, 1)
     sg = np.sqrt(var)
-    eps = N * 1.1920928955078125e-07 * 4.0 * (1.0 + mean)
+    # the flag rule of k4_finish_partials_kernel (csrc/k34_trainer.cu): worst-case float32 error of the recurrence
+    u = 1.01 * 2.0 ** -24
+    e_mean = 256.0 * u * (0.5 * N + 2.5)
+    bv = (u * M2 * (N + 3.0) + 2.0 * e_mean * np.sqrt(2.0 * N * M2) + N * e_mean * e_mean) / max(N - 1, 1) + 1e-9
+    rb, tail = np.sqrt(bv), 3.0 * u * sg + 1e-12
+    with np.errstate(all="ignore"):
+        e_up = np.where(sg > 0, np.minimum(bv / (2.0 * sg), rb), rb) + tail
+        e_dn = np.where(sg > 0, np.minimum(bv / sg, rb), rb) + tail
     fm, fs = mean - np.floor(mean), sg - np.floor(sg)
-    flag = (fm < eps) | (1 - fm < eps) | (fs < eps) | (1 - fs < eps) | (N < 2)
+    flag = ((M2 > 0) & ((fm < e_mean) | (1 - fm < e_mean) | (fs < e_dn) | (1 - fs < e_up))) | (N < 2)
     mean8 = mean.astype(np.uint8); sig8 = sg.astype(np.int64).astype(np.uint8)
     idx = np.flatnonzero(flag.ravel())
     counts = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
