@@ -30,6 +30,7 @@ EXPORTS = [
     "abub_set_bellows_template", "abub_bellows_track", "abub_bellows_map", "abub_localize_bellows",
     "abub_localize", "abub_localize_batch", "abub_localize_binary", "abub_process_frame",
     "abub_event_submit_range", "abub_launch_count", "abub_profile", "abub_profile_read",
+    "abub_gate_entropy_static",
 ]
 
 
@@ -128,6 +129,7 @@ def load() -> C.CDLL:
     lib.abub_launch_count.argtypes = [vp]
     lib.abub_profile.argtypes = [vp, C.c_int]
     lib.abub_profile_read.argtypes = [vp, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
+    lib.abub_gate_entropy_static.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, C.c_char_p, C.c_int]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ("abub_ctx_destroy", "abub_last_error", "abub_stream", "abub_launch_count"):
@@ -135,6 +137,19 @@ def load() -> C.CDLL:
     lib.abub_launch_count.restype = C.c_longlong
     _lib = lib
     return lib
+
+
+ABUB_GATE_STATIC_MAX_PAIRS = 1024
+
+
+def gate_entropy_static(d_pairs: int, n_pairs: int, rows: int, cols: int, d_entropy: int, d_kept: int = 0, d_hist16: int = 0,
+                        stream: int = 0) -> Tuple[int, str]:
+    """abub_gate_entropy_static: every pointer is a raw DEVICE address (int); returns (return code, error text)."""
+    lib = load()
+    err = C.create_string_buffer(256)
+    rc = lib.abub_gate_entropy_static(C.c_void_p(d_pairs), n_pairs, rows, cols, C.c_void_p(d_entropy), C.c_void_p(d_kept or None),
+                                      C.c_void_p(d_hist16 or None), C.c_void_p(stream or None), err, len(err))
+    return rc, err.value.decode()
 
 
 def _p(a: Optional[np.ndarray]):

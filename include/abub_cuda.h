@@ -287,6 +287,26 @@ int abub_localize_binary(abub_ctx* ctx, int k, uint8_t* out);
 int abub_process_frame(abub_ctx* ctx, int cam, const uint8_t* work, const uint8_t* prev,
                        uint8_t* diff, uint32_t* hist);
 
+/* ---- allocation-free gate (no counterpart in the reference) ---------------------- */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The Trainer's entropy
+ * gate (the arithmetic of abub_train_add_events: 16-bin histogram of frame1 - frame0, entropy in float, kept when
+ * entropy <= 0.0005) for n_pairs frame pairs, with the per-pair bin-count scratch in a file-scope static __device__
+ * array of the library (csrc/gate_static.cu) instead of a context arena: the call needs no abub_ctx and calls no
+ * cudaMalloc / cudaFree / allocating routine, and it neither waits for the GPU nor copies to the host.
+ *   d_pairs    DEVICE in : n_pairs x 2 x rows*cols bytes, frame 0 then frame 1 of each pair, pairs back to back
+ *   d_entropy  DEVICE out: n_pairs floats          d_kept DEVICE out: n_pairs ints (may be NULL)
+ *   d_hist16   DEVICE out: n_pairs x 16 bin counts (may be NULL)
+ *   stream     cudaStream_t the work is queued on (NULL = the default stream); the device is the caller's current one
+ *   err        receives a message when the return value is not ABUB_OK (may be NULL)
+ * Limit: n_pairs <= ABUB_GATE_STATIC_MAX_PAIRS per call (the scratch is 16 counters per pair, 64 KiB per GPU, held from
+ * library load to process exit) -- more returns ABUB_E_CAPACITY; rows*cols < 2^31.
+ * All calls on a device share the one scratch array; each call clears the slice it uses on `stream` first.  Calls
+ * whose GPU work can overlap (two streams without an ordering, two host threads) race: serialise them. */
+#define ABUB_GATE_STATIC_MAX_PAIRS 1024
+int abub_gate_entropy_static(const uint8_t* d_pairs, int n_pairs, int rows, int cols, float* d_entropy, int* d_kept,
+                             uint32_t* d_hist16, void* stream, char* err, int err_cap);
+
 #ifdef __cplusplus
 }
 #endif
