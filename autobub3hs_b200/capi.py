@@ -372,9 +372,10 @@ class Context:
         self._ck(self.lib.abub_selftest_fdiv(self.h, steps, k_first, k_last, C.byref(n), ex), "abub_selftest_fdiv")
         return n.value, (ex[0], ex[1])
 
-    def train_finish(self, cam: int):
-        mean = np.zeros((self.rows, self.cols), np.uint8)
-        sigma = np.zeros((self.rows, self.cols), np.uint8)
+    def train_finish(self, cam: int, read: bool = True):
+        """read=False leaves the planes on the device (abub_set_background_from_training installs them from there)."""
+        mean = np.zeros((self.rows, self.cols), np.uint8) if read else None
+        sigma = np.zeros((self.rows, self.cols), np.uint8) if read else None
         n, st = C.c_int(), C.c_int()
         self._ck(self.lib.abub_train_finish(self.h, cam, _p(mean), _p(sigma), C.byref(n), C.byref(st)),
                  "abub_train_finish")

@@ -439,6 +439,16 @@ def run_ours(args, rank, world, local_rank):
     prof = ctx.profile_read()
     ctx.profile(False)
     hr.read_stats()
+    if args.profile_step:
+        # one more step between cudaProfilerStart / Stop: `ncu --profile-from-start off` sees exactly one step's launches
+        # (tools/round_profile.sh -> tools/ncu_traffic.py -> profiles/r2_traffic.json)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        step()
+        hr.drain()
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        hr.read_stats()
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -700,7 +710,9 @@ def main():
     ap.add_argument("--trigger-steps", type=int, default=8, help="steps of the trigger-only extra (0 = skip)")
     ap.add_argument("--trainer-events", type=int, default=200, help="training events of the sharded Trainer leg at N > 1 (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-step", action="store_true", help="run one extra step between cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     args = ap.parse_args()
+    args.e2e_steps = max(1, args.e2e_steps)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -13,8 +13,11 @@ def main():
     rd = csv.reader(lines)
     hdr = next(rd)
     ki, vi, ui = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Metric Unit")
+    mi = hdr.index("Metric Name")
     agg = OrderedDict()
     for r in rd:
+        if r[mi] != "gpu__time_duration.sum":
+            continue
         name = re.sub(r"\(.*", "", r[ki]).replace("void ", "").replace("<unnamed>::", "")
         name = re.sub(r"cub::CUB_\d+_\w+?::", "cub::", name)[:90]
         v = float(r[vi].replace(",", ""))

@@ -1,32 +1,39 @@
 #!/bin/bash
-# One GPU-box pass that produces the evidence kept under profiles/: bench lines (own arm + reference arm), a launch
-# list of the bench and of the per-stage tool (own kernels only), and one ncu --set full capture per kernel family.
-# Run with:  gpurun --timeout 1500 -- 'bash tools/round_profile.sh'
+# One GPU-box pass that produces the evidence kept under profiles/ (round 2): the bench line, a launch list of the
+# bench, DRAM traffic per kernel group of one bench step (-> profiles/r2_traffic.json, which bench.py reads), and one
+# `ncu --set full` capture per kernel family.  Every profiled command first runs to exit code 0 without ncu.
+#   gpurun --timeout 2400 -- 'bash tools/round_profile.sh'
+# then here:  bash tools/round_profile_collect.sh   (summaries -> profiles/r2_*)
 set -u
 O=gpurun_out
 mkdir -p $O
-python bench.py --steps 16 --warmup 3 > $O/bench_n1.json 2> $O/bench_n1.err || echo "bench failed"
-python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err || echo "ref bench failed"
-python tools/bench_stages.py --events 32 --train-events 200 --reps 3 > $O/stages.json 2> $O/stages.err || echo "stages failed"
+B="python bench.py --steps 2 --warmup 1 --no-cpu-baseline --trigger-steps 0 --e2e-steps 1 --e2e-events 16"
+python bench.py > $O/r2_bench_n1.json 2> $O/r2_bench_n1.err || echo "bench failed"
+$B --profile-step > $O/r2_bench_short.json 2> $O/r2_bench_short.err || { echo "short bench failed"; tail -5 $O/r2_bench_short.err; }
 K='regex:k[1-9]_|DeviceRadixSort|DeviceScan|DeviceSelect'
-ncu --metrics gpu__time_duration.sum --clock-control none -k "$K" --csv --log-file $O/launches_bench.csv \
-    python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $O/ncu_lb.log 2>&1
-ncu --metrics gpu__time_duration.sum --clock-control none -k "$K" --csv --log-file $O/launches_stages.csv \
-    python tools/bench_stages.py --events 32 --train-events 32 --reps 1 > $O/ncu_ls.log 2>&1
-python tools/bench_decode.py --events 12 --batch 12 > $O/decode_bmp.json 2> $O/decode_bmp.err || echo "decode bmp failed"
-python tools/bench_decode.py --events 24 --batch 24 --format png > $O/decode_png.json 2> $O/decode_png.err || echo "decode png failed"
-ncu --set full --clock-control none --import-source on -k regex:k9_inflate -c 1 -o $O/r1f_k9 -f \
-    python tools/bench_stages.py --events 8 --png-events 8 --only-png --reps 1 > $O/ncu_k9.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k9_unfilter -c 1 -o $O/r1f_k9u -f \
-    python tools/bench_stages.py --events 8 --png-events 8 --only-png --reps 1 > $O/ncu_k9u.log 2>&1
-for spec in "k1_trigger_tma:k1_tma:1" "k5_post_stream:k5b:1" "k6_candidates:k6:1" "k7_trace2:k7:1" "k8_ncc:k8:1" "k4_welford16:k4:1" "k3_gate_batch:k3:1"; do
-    IFS=: read -r kern tag cnt <<< "$spec"
-    if [ "$kern" = "k1_trigger_tma" ]; then
-        ncu --set full --clock-control none --import-source on -k regex:$kern -s 1 -c $cnt -o $O/r1f_$tag -f \
-            python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $O/ncu_$tag.log 2>&1
-    else
-        ncu --set full --clock-control none --import-source on -k regex:$kern -c $cnt -o $O/r1f_$tag -f \
-            python tools/bench_stages.py --events 32 --train-events 64 --reps 1 > $O/ncu_$tag.log 2>&1
-    fi
+# launch list of a whole short bench run (own kernels + the CUB kernels they call)
+ncu --metrics gpu__time_duration.sum --clock-control none -k "$K" --csv --log-file $O/r2_launches_bench.csv \
+    $B > $O/ncu_lb.log 2>&1
+# one step, with DRAM bytes: early-exit form (the headline) and the full-table form
+ncu --profile-from-start off --clock-control none --csv --log-file $O/r2_step.csv \
+    --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum \
+    $B --profile-step > $O/ncu_step.log 2>&1
+ncu --profile-from-start off --clock-control none --csv --log-file $O/r2_step_full.csv \
+    --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum \
+    $B --profile-step --early-chunk 0 > $O/ncu_step_full.log 2>&1
+# --set full, one launch per kernel family, inside the profiled step
+for spec in "k1_trigger_tma:k1_early:0" "k5_post_tma:k5b:0" "k1_genesis|k5_genesis:k5a:0" "k7_trace2:k7b:0"; do
+    IFS=: read -r kern tag skip <<< "$spec"
+    ncu --profile-from-start off --set full --clock-control none --import-source on -k "regex:$kern" -s $skip -c 1 -o $O/r2_$tag -f \
+        $B --profile-step > $O/ncu_$tag.log 2>&1
 done
-ls -la $O | tail -30
+ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:k1_trigger_tma -c 1 -o $O/r2_k1_full -f \
+    $B --profile-step --early-chunk 0 > $O/ncu_k1_full.log 2>&1
+# Trainer kernels (K3, K4) and the stage numbers of tools/bench_stages.py
+python tools/bench_stages.py --events 32 --train-events 200 --reps 3 > $O/r2_stages.json 2> $O/r2_stages.err || echo "stages failed"
+for spec in "k4_welford16:k4" "k3_gate_batch:k3"; do
+    IFS=: read -r kern tag <<< "$spec"
+    ncu --set full --clock-control none --import-source on -k regex:$kern -c 1 -o $O/r2_$tag -f \
+        python tools/bench_stages.py --events 32 --train-events 64 --reps 1 > $O/ncu_$tag.log 2>&1
+done
+ls -la $O | tail -40
