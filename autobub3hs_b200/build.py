@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libabub_cuda.so")
-SOURCES = ["ctx.cu", "train.cu", "k1_processframe.cu", "k1_trigger_tma.cu", "k2_trigger_scan.cu", "k34_trainer.cu", "k5_localize.cu", "k5_post_tma.cu", "nccl_glue.cu", "k8_bellows.cu", "k9_png.cu", "gate_static.cu"]
+SOURCES = ["ctx.cu", "train.cu", "k1_processframe.cu", "k1_trigger_tma.cu", "k2_trigger_scan.cu", "k34_trainer.cu", "k5_localize.cu", "k5_post_tma.cu", "k5_genesis_tma.cu", "nccl_glue.cu", "k8_bellows.cu", "k9_png.cu", "gate_static.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--fmad=false"]
 

@@ -30,7 +30,7 @@ EXPORTS = [
     "abub_set_bellows_template", "abub_bellows_track", "abub_bellows_map", "abub_localize_bellows",
     "abub_localize", "abub_localize_batch", "abub_localize_binary", "abub_process_frame",
     "abub_event_submit_range", "abub_launch_count", "abub_profile", "abub_profile_read",
-    "abub_gate_entropy_static",
+    "abub_gate_entropy_static", "abub_event_set_nframes_range",
 ]
 
 
@@ -129,6 +129,7 @@ def load() -> C.CDLL:
     lib.abub_launch_count.argtypes = [vp]
     lib.abub_profile.argtypes = [vp, C.c_int]
     lib.abub_profile_read.argtypes = [vp, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
+    lib.abub_event_set_nframes_range.argtypes = [vp, C.c_int, C.c_int, ip]
     lib.abub_gate_entropy_static.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, C.c_char_p, C.c_int]
     for name in EXPORTS:
         fn = getattr(lib, name)

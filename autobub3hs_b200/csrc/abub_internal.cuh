@@ -53,8 +53,8 @@ struct abub_slot_state {
 enum {
     ABUB_PROF_K1 = 0,   // k1_trigger_tma_kernel + k1_trigger_kernel (border rows) + k1_fill_bin0_kernel
     ABUB_PROF_K2,       // k2_trigger_scan_kernel (+ k2_next_avail_kernel)
-    ABUB_PROF_K5A,      // localizer genesis frames (ProcessFrame in store mode + TOZERO + histogram)
-    ABUB_PROF_K5B,      // localizer post-trigger frames (k5_post_stream_kernel)
+    ABUB_PROF_K5A,      // localizer genesis frames: k5_genesis_tma_kernel + k1_genesis_border_kernel (or k1_genesis_jobs_kernel)
+    ABUB_PROF_K5B,      // localizer post-trigger frames: k5_post_tma_kernel (or k5_post_stream_kernel / k5_post_kernel)
     ABUB_PROF_K5C,      // k5_otsu_kernel + flag fill
     ABUB_PROF_K6,       // k6_candidates_*_kernel
     ABUB_PROF_SORT,     // cub radix sort / scans (library kernels)
@@ -112,6 +112,10 @@ struct abub_ctx {
     int*      d_post_list = nullptr; // indices of the post-trigger jobs of a localizer chunk (k5_post_tma.cu)
     int*      h_post_list = nullptr; // its pinned staging copy; post_ev = the last upload from it
     cudaEvent_t post_ev = nullptr;
+    int*      d_gen_list = nullptr;  // the same for the genesis jobs (k5_genesis_tma.cu)
+    int*      h_gen_list = nullptr;
+    cudaEvent_t gen_ev = nullptr;
+    int       gen_cap = 0;
     int       post_cap = 0;
     void*     d_tmaps = nullptr;    // CUtensorMap[max_slots + 3*ncams]: frames of a slot, then per camera K16, TrainedAvgImage, -t
                                     // (k1_trigger_tma.cu builds them; null = TMA paths off)
@@ -205,9 +209,14 @@ struct abub_loc_job {
     int genesis;
     int k;                   // 0 = genesis frame, 1.. = post-trigger frame
     int item;                // index of the abub_loc_item this job belongs to
-    int slot, cam, zframe;   // post jobs on the TMA path: event slot, camera, cam * max_frames + frame of `a`
+    int slot, cam, zframe;   // jobs on the TMA paths: event slot, camera, cam * max_frames + frame of `a`
+    int zb;                  // genesis jobs on the TMA path: cam * max_frames + the comparison (pre-trigger) frame
 };
 int abub_k1_launch_genesis_jobs(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs);
+// K5a TMA path (k5_genesis_tma.cu): rows [2, rows-2) of the chunk's genesis jobs, sparse store + segment flags; builds
+// ctx->d_gen_list (indices of the genesis jobs) and returns their number
+bool abub_k5a_tma_supported(const abub_ctx* ctx);
+int abub_k5a_launch_tma(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs, int* n_genesis);
 // K5b TMA path (k5_post_tma.cu): post-trigger jobs of a chunk; false = shape not supported, use the streaming kernel
 bool abub_k5b_tma_supported(const abub_ctx* ctx);
 int abub_k5b_launch_tma(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs);

@@ -99,6 +99,9 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     cudaFree(ctx->d_post_list);
     if (ctx->h_post_list) cudaFreeHost(ctx->h_post_list);
     if (ctx->post_ev) cudaEventDestroy(ctx->post_ev);
+    cudaFree(ctx->d_gen_list);
+    if (ctx->h_gen_list) cudaFreeHost(ctx->h_gen_list);
+    if (ctx->gen_ev) cudaEventDestroy(ctx->gen_ev);
     if (ctx->h_raw) cudaFreeHost(ctx->h_raw);
     for (cudaEvent_t e : ctx->prof.pool) cudaEventDestroy(e);
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
@@ -118,8 +121,8 @@ extern "C" void* abub_stream(abub_ctx* ctx) { return ctx ? (void*)ctx->stream : 
 extern "C" long long abub_launch_count(const abub_ctx* ctx) { return ctx ? ctx->n_launches : 0; }
 
 static const char* const kProfNames[ABUB_PROF_N] = {
-    "K1 k1_trigger_tma_kernel + border rows + bin0", "K2 k2_trigger_scan_kernel", "K5a genesis ProcessFrame (store mode)",
-    "K5b k5_post_stream_kernel", "K5c k5_otsu_kernel + flags", "K6 k6_candidates_seg_kernel", "cub sort/scan (library)",
+    "K1 k1_trigger_tma_kernel + border rows + bin0", "K2 k2_trigger_scan_kernel", "K5a k5_genesis_tma_kernel + border rows (generic pitch: k1_genesis_jobs_kernel)",
+    "K5b k5_post_tma_kernel (generic pitch: k5_post_stream_kernel)", "K5c k5_otsu_kernel + flags", "K6 k6_candidates_seg_kernel", "cub sort/scan (library)",
     "K7a k7_trace1_kernel", "K7b k7_trace2_kernel", "K7c k7_external_kernel + k7_emit_kernel", "K3 k3_gate_batch_kernel",
     "K4 k4_welford16_kernel"};
 
@@ -208,6 +211,34 @@ static int push_nframes(abub_ctx* ctx, int slot) {
     ABUB_L(ctx), set_nframes_kernel<<<1, 32, 0, ctx->stream>>>(ctx->d_nframes + (size_t)slot * ctx->ncams, a, ctx->ncams);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     ctx->slots[slot].hist_valid = false;
+    return ABUB_OK;
+}
+
+// the same for a range of slots: up to 64 slots' counts per launch
+struct NframesRangeArg { int n[64 * ABUB_MAX_CAMS]; };
+__global__ void set_nframes_range_kernel(int* __restrict__ dst, const NframesRangeArg a, int count) {
+    for (int i = threadIdx.x; i < count; i += blockDim.x) dst[i] = a.n[i];
+}
+
+extern "C" int abub_event_set_nframes_range(abub_ctx* ctx, int slot_first, int nslots, const int* nframes) {
+    if (!ctx) return ABUB_E_INVALID;
+    ABUB_REQUIRE(ctx, slot_first >= 0 && nslots >= 1 && slot_first + nslots <= ctx->max_slots && nframes, "abub_event_set_nframes_range");
+    cudaSetDevice(ctx->device);
+    for (int i = 0; i < nslots * ctx->ncams; i++)
+        ABUB_REQUIRE(ctx, nframes[i] >= 0 && nframes[i] <= ctx->max_frames, "nframes out of range");
+    const int per = (64 * ABUB_MAX_CAMS) / ctx->ncams;               // slots per launch
+    for (int s0 = 0; s0 < nslots; s0 += per) {
+        const int ns = nslots - s0 < per ? nslots - s0 : per;
+        NframesRangeArg a;
+        for (int s = 0; s < ns; s++) {
+            abub_slot_state& st = ctx->slots[slot_first + s0 + s];
+            for (int c = 0; c < ctx->ncams; c++) a.n[s * ctx->ncams + c] = st.nframes[c] = nframes[(size_t)(s0 + s) * ctx->ncams + c];
+            st.hist_valid = false;
+        }
+        ABUB_L(ctx), set_nframes_range_kernel<<<1, 256, 0, ctx->stream>>>(ctx->d_nframes + (size_t)(slot_first + s0) * ctx->ncams, a,
+                                                                         ns * ctx->ncams);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
     return ABUB_OK;
 }
 

@@ -431,6 +431,31 @@ __global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_genesis_jobs_kernel(cons
     }
 }
 
+// the four border rows (0, 1, rows-2, rows-1) of the genesis jobs listed in gen_list, for the TMA genesis kernel
+// (k5_genesis_tma.cu) that covers rows [2, rows-2): two strips of two rows with reflected vertical taps, written densely;
+// the rows' 240-pixel segments are flagged "holds something / memory not known to be zero" (3).
+__global__ void __launch_bounds__(K1_MAX_THREADS, 2) k1_genesis_border_kernel(const abub_loc_job* __restrict__ jobs, const int* __restrict__ gen_list,
+                                                                              int rows, int cols, int nxg) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    const abub_loc_job job = jobs[gen_list[blockIdx.y]];
+    uint32_t* sh_hist = smem;
+    const int warp = threadIdx.x >> 5;
+    uint32_t* xch = smem + 256 + warp * K1_WARP_WORDS;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) sh_hist[i] = 0;
+    __syncthreads();
+    const int y0 = (blockIdx.x / nxg) == 0 ? 0 : rows - 2;
+    const int x0 = ((blockIdx.x % nxg) * (blockDim.x >> 5) + warp) * ABUB_K1_TILE_W;
+    if (x0 < cols)
+        k1_strip_any<1>(job.a, job.b, job.k32, rows, cols, y0, 2, x0, sh_hist, xch, job.tz, job.tozero);
+    const int nxw = (cols + 239) / 240;
+    if ((blockIdx.x % nxg) == 0 && (int)threadIdx.x < 2 * nxw) job.segflags[(size_t)(y0 + (int)threadIdx.x / nxw) * nxw + (int)threadIdx.x % nxw] = 3;
+    __syncthreads();
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        const uint32_t c = sh_hist[i];
+        if (c && i) atomicAdd(&job.hist[i], c);
+    }
+}
+
 __global__ void k1_fill_bin0_single(uint32_t* hist, uint32_t npix) {
     const int lane = threadIdx.x;
     uint32_t s = 0;
@@ -541,8 +566,30 @@ int abub_k1_launch_single(abub_ctx* ctx, const uint8_t* d_a, const uint8_t* d_b,
     return ABUB_OK;
 }
 
+int abub_k1_launch_genesis_border(abub_ctx* ctx, const abub_loc_job* d_jobs, const int* d_gen_list, int ngen) {
+    const int threads = k1_block_threads(ctx->cols);
+    if (int rc = k1_allow_smem(ctx, k1_genesis_border_kernel, k1_smem_bytes(threads))) return rc;
+    const int nxg = k1_xgroups(ctx->cols);
+    for (int j0 = 0; j0 < ngen; j0 += 65535) {
+        const int nj = (ngen - j0 < 65535) ? ngen - j0 : 65535;
+        ABUB_L(ctx), k1_genesis_border_kernel<<<dim3(2 * nxg, nj), threads, k1_smem_bytes(threads), ctx->stream>>>(
+            d_jobs, d_gen_list + j0, ctx->rows, ctx->cols, nxg);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
+    return ABUB_OK;
+}
+
 int abub_k1_launch_genesis_jobs(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs) {
     abub_prof_scope prof(ctx, ABUB_PROF_K5A);
+    // cols % 16 == 0: the TMA-fed kernel (k5_genesis_tma.cu) on rows [2, rows-2), sparse store; the four border rows here.
+    // A/B switch for profiling: ABUB_K5A_LEGACY
+    static const bool legacy = getenv("ABUB_K5A_LEGACY") != nullptr;
+    if (!legacy && abub_k5a_tma_supported(ctx)) {
+        int ngen = 0;
+        if (int rc = abub_k5a_launch_tma(ctx, d_jobs, njobs, &ngen)) return rc;
+        if (ngen == 0) return ABUB_OK;
+        return abub_k1_launch_genesis_border(ctx, d_jobs, ctx->d_gen_list, ngen);
+    }
     const int threads = k1_block_threads(ctx->cols);
     int nstrips, th;
     k1_strips(ctx->rows, &nstrips, &th);

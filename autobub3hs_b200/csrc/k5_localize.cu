@@ -688,8 +688,12 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     const bool stream_k5b = (ctx->cols % 8) == 0 && ctx->cols >= 16;
     {
     abub_prof_scope prof(ctx, ABUB_PROF_K5C);
-    ABUB_L(ctx), k5_flag_fill_kernel<<<dim3(4, njobs), 256, 0, st>>>(a->d_jobs, (size_t)ctx->rows * nxw_f, stream_k5b ? 0 : 1);
-    ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    // frames written in full have every segment flagged; the TMA genesis kernel keeps the flags itself
+    static const bool k5a_legacy = getenv("ABUB_K5A_LEGACY") != nullptr;
+    if (has_prepared || !stream_k5b || k5a_legacy || !abub_k5a_tma_supported(ctx)) {
+        ABUB_L(ctx), k5_flag_fill_kernel<<<dim3(4, njobs), 256, 0, st>>>(a->d_jobs, (size_t)ctx->rows * nxw_f, stream_k5b ? 0 : 1);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+    }
     ABUB_L(ctx), k5_otsu_kernel<<<(njobs + 63) / 64, 64, 0, st>>>(a->d_jobs, a->d_thr, njobs, (uint32_t)npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
@@ -815,6 +819,7 @@ extern "C" int abub_localize_batch(abub_ctx* ctx, const abub_loc_item* items, in
                 jb.slot = it.slot;
                 jb.cam = it.cam;
                 jb.zframe = it.cam * ctx->max_frames + it.trig + k;
+                jb.zb = it.cam * ctx->max_frames + it.pre_trig;
                 jb.k32 = cs.d_k32;
                 jb.t8 = cs.d_t8;
                 jb.nt16 = cs.d_nt16;

@@ -168,9 +168,12 @@ void AbubDevice::LoadCamera(int slot, int cam, Parser* parser, const std::string
     // frame; ZipParser: positional reads on the shared descriptor)
 #pragma omp parallel for schedule(dynamic, 1)
     for (int i = 0; i < n; i++) {
-        std::vector<uint8_t> enc;
-        bool good = parser->GetImageBytes(event_id, frames[i], enc) != parser->FailureCode() && !enc.empty();
-        if (good) good = abubcodec::decode_into(enc.data(), enc.size(), base + (size_t)i * npix, rows_, cols_);
+        bool good = false;
+        try {                                   // nothing may leave the parallel region: a frame that throws is a bad frame
+            std::vector<uint8_t> enc;
+            good = parser->GetImageBytes(event_id, frames[i], enc) != parser->FailureCode() && !enc.empty();
+            if (good) good = abubcodec::decode_into(enc.data(), enc.size(), base + (size_t)i * npix, rows_, cols_);
+        } catch (...) { good = false; }
         if (!good) memset(base + (size_t)i * npix, 0, npix);
         ok[i] = good;
     }
@@ -240,6 +243,7 @@ void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const
         for (long i = (long)i0; i < (long)i1; i++) {
             Item& it = items[i];
             uint8_t* region = pin[it.slot] + ((size_t)it.cam * max_frames_ + it.frame) * npix;
+            try {                               // nothing may leave the parallel region: a frame that throws is a bad frame
             if (device_flip) {
                 bool bottom_up = false;
                 if (parser->ReadGray8BmpPixels(*it.event, it.name, rows_, cols_, region, &bottom_up)) { it.state = bottom_up ? 3 : 1; continue; }
@@ -252,6 +256,7 @@ void AbubDevice::StageBatch(Parser* parser, const std::vector<int>& slots, const
             }
             if (abubcodec::decode_into(enc.data(), enc.size(), region, rows_, cols_)) it.state = 1;
             else memset(region, 0, npix);
+            } catch (...) { it.state = 0; memset(region, 0, npix); }
         }
         const double tb = now();
         bool host_cam[8] = {false};
@@ -338,7 +343,7 @@ std::vector<int> AbubDevice::PrefetchEvents(Parser* parser, const std::vector<st
 
 static inline double wall_now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
-void AbubDevice::MarkResident(int slot, const int* nframes, bool in_hbm) {
+void AbubDevice::MarkResident(int slot, const int* nframes, bool in_hbm, bool push) {
     std::lock_guard<std::recursive_mutex> g(mu_);
     AbubSlot& st = slots_[slot];
     for (int c = 0; c < ncams_; c++) {
@@ -348,7 +353,13 @@ void AbubDevice::MarkResident(int slot, const int* nframes, bool in_hbm) {
         st.resident_upto[c] = in_hbm ? nframes[c] : 0;
         st.trig_valid[c] = st.loc_valid[c] = false;
     }
-    if (in_hbm) Check(abub_event_set_nframes(ctx_, slot, nframes), "abub_event_set_nframes");
+    if (in_hbm && push) Check(abub_event_set_nframes(ctx_, slot, nframes), "abub_event_set_nframes");
+}
+
+// consecutive slots whose frames are in HBM: the device's frame counts in one launch (after MarkResident(..., true, false))
+void AbubDevice::PushFrameCounts(int slot_first, int nslots, const int* nframes) {
+    std::lock_guard<std::recursive_mutex> g(mu_);
+    Check(abub_event_set_nframes_range(ctx_, slot_first, nslots, nframes), "abub_event_set_nframes_range");
 }
 
 void AbubDevice::EnsureAllResident(int slot) {

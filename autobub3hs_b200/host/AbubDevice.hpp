@@ -99,7 +99,8 @@ public:
     long long StreamBatch(const std::vector<int>& slots, const int* training_set_sizes, int chunk_frames);
     // Declares the frames of a slot present: in_hbm = a producer wrote them to abub_event_device_ptr; otherwise they are
     // in the pinned staging buffer (abub_pinned_acquire) and StreamBatch / EnsureAllResident send them.
-    void MarkResident(int slot, const int* nframes, bool in_hbm);
+    void MarkResident(int slot, const int* nframes, bool in_hbm, bool push = true);
+    void PushFrameCounts(int slot_first, int nslots, const int* nframes);
     void EnsureAllResident(int slot);
     // frame pairs per round of the resident early exit (abub_trigger_early); 0 = full histogram table
     void SetEarlyChunk(int chunk) { early_chunk_ = chunk; }

@@ -306,9 +306,10 @@ int abubhost_recon(int slot_first, int nslots, const int* event_numbers, const i
                 keys.push_back(r.eventDir + ev + r.imageFolder + "|" + ev);
                 g.parser->SetEvent(ev, nframes + (size_t)s * nc, nc);
                 dev.BindSlot(keys.back(), slot_first + s);
-                dev.MarkResident(slot_first + s, nframes + (size_t)s * nc, mode == 0);
+                dev.MarkResident(slot_first + s, nframes + (size_t)s * nc, mode == 0, false);
                 slots.push_back(slot_first + s);
             }
+            if (mode == 0) dev.PushFrameCounts(slot_first + s0, s1 - s0, nframes + (size_t)s0 * nc);   /* one launch, not one per slot */
             if (mode == 0) dev.AnalyzeBatch(slots, tss.data());
             else sent += dev.StreamBatch(slots, tss.data(), chunk_frames);
             g.pipe.submit(std::move(chunk), std::move(keys));

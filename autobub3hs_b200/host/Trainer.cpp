@@ -84,7 +84,8 @@ void Trainer::MakeAvgSigmaImage(bool PerformLBPOnImages) {
         for (int i = 0; i < 2 * nev; i++) {
             const int e = i / 2;
             if (names[i].empty()) continue;
-            const int err = FileParser->GetImageBytes(EventList[c0 + e], names[i], enc[i]);
+            int err = failure;
+            try { err = FileParser->GetImageBytes(EventList[c0 + e], names[i], enc[i]); } catch (...) { err = failure; enc[i].clear(); }
             if (err == failure || enc[i].empty()) {
 #pragma omp critical
                 { std::cout << "Skipping corrupted image for training.\n"; good[e] = 0; }
@@ -104,7 +105,9 @@ void Trainer::MakeAvgSigmaImage(bool PerformLBPOnImages) {
         for (int i = 0; i < 2 * nev; i++) {
             const int e = i / 2;
             if (!good[e]) continue;
-            if (!abubcodec::decode_into(enc[i].data(), enc[i].size(), px.data() + (size_t)i * npix, dev.rows(), dev.cols())) {
+            bool dec = false;
+            try { dec = abubcodec::decode_into(enc[i].data(), enc[i].size(), px.data() + (size_t)i * npix, dev.rows(), dev.cols()); } catch (...) {}
+            if (!dec) {
 #pragma omp critical
                 { std::cout << "Skipping corrupted image for training.\n"; good[e] = 0; }
             }

@@ -73,6 +73,12 @@ void ZipParser::BuildFileList() {
         if (!read_at(fp, e64, rec, 56) || r32(rec) != 0x06064b50u) throw -10;
         n_entries = r64(rec + 32); cd_size = r64(rec + 40); cd_off = r64(rec + 48);
     }
+    // sizes come from the archive: they must lie inside the file before anything is allocated from them
+    if (cd_off > fsize || cd_size > fsize - cd_off || n_entries > cd_size / 46 + 1) {
+        std::cout << "Error when creating file list; cannot continue." << std::endl;
+        throw -10;
+    }
+    idx->archive_size = fsize;
     std::vector<uint8_t> cd(cd_size);
     if (cd_size && !read_at(fp, cd_off, cd.data(), cd_size)) throw -10;
     const std::regex re("^.*/(\\d+)/.*/?(cam\\d.*image\\s*\\d+.*(png|bmp))");
@@ -117,6 +123,12 @@ bool ZipParser::ReadEntry(const ZipEntryLoc& loc, std::vector<uint8_t>& out) {
     uint8_t lh[30];
     if (!read_at(fp, loc.local_off, lh, 30) || r32(lh) != 0x04034b50u) return false;
     const uint64_t data = loc.local_off + 30 + r16(lh + 26) + r16(lh + 28);
+    // a corrupt central directory must end as "frame does not decode" (-9 / -6 for the camera), not as bad_alloc inside
+    // a parallel region: the compressed bytes must lie inside the archive, and one frame never inflates past kMaxEntry
+    constexpr uint64_t kMaxEntry = (uint64_t)256 << 20;
+    if (data > idx->archive_size || loc.comp_size > idx->archive_size - data || loc.uncomp_size > kMaxEntry ||
+        (loc.method == 0 && loc.comp_size > kMaxEntry))
+        return false;
     std::vector<uint8_t> comp(loc.comp_size);
     if (loc.comp_size && !read_at(fp, data, comp.data(), loc.comp_size)) return false;
     if (loc.method == 0) { out.swap(comp); return true; }

@@ -40,6 +40,7 @@ private:
         std::vector<std::string> FileContents;                                  // every entry name
         std::map<std::string, std::map<std::string, std::string>> ImageNames;   // [event][frame] -> entry name
         std::map<std::string, std::map<std::string, ZipEntryLoc>> ImageLocs;    // [event][frame] -> location
+        uint64_t archive_size = 0;                                              // bytes of the archive file (entry sizes are checked against it)
     };
     FILE* fp = nullptr;
     std::shared_ptr<Index> idx = std::make_shared<Index>();

@@ -24,11 +24,58 @@
 #include "RawParser.hpp"
 #include "ReconDriver.hpp"
 #include <chrono>
+#include <time.h>
 
 #include "Trainer.hpp"
 #include "ZipParser.hpp"
 
 static bool eventNameOrderSort(std::string a, std::string b) { return std::stoi(a) < std::stoi(b); }
+
+/* Multi-rank runs: the ranks agree on a status word before every phase that ends in a collective, so that a rank which
+ * failed (no readable frame in its range, a CUDA error, a failed training) cannot leave its peers blocked inside
+ * ncclCommInitRank / ncclAllReduce.  File rendezvous next to the output file: rank r publishes
+ * <base>.<phase>.<r> = "<start time> <status>" (written whole, then renamed) and waits -- ABUB_RANK_TIMEOUT seconds,
+ * default 300 -- for the other ranks' files of the same phase.  Files older than this rank's start minus two minutes are
+ * leftovers of an earlier run and are ignored.  Returns the minimum status over the ranks, or -1 when a rank did not
+ * show up in time.  A rank removes its own file of a phase once the next phase (or the final barrier) has passed. */
+struct RankSync {
+    std::string base;
+    int rank = 0, world = 1;
+    long long t_start = 0;
+    std::vector<std::string> mine;
+    double timeout() const { const char* e = getenv("ABUB_RANK_TIMEOUT"); const double t = e ? atof(e) : 0; return t > 0 ? t : 300.0; }
+    int agree(const char* phase, int status) {
+        if (world <= 1) return status;
+        const std::string me = base + "." + phase + "." + std::to_string(rank);
+        {
+            std::ofstream f(me + ".tmp");
+            f << t_start << " " << status << "\n";
+        }
+        rename((me + ".tmp").c_str(), me.c_str());
+        mine.push_back(me);
+        const auto t0 = std::chrono::steady_clock::now();
+        int lo = status;
+        for (int r = 0; r < world; r++) {
+            if (r == rank) continue;
+            const std::string fn = base + "." + phase + "." + std::to_string(r);
+            for (;;) {
+                long long ts = 0;
+                int st = 0;
+                std::ifstream f(fn);
+                if (f && (f >> ts >> st) && ts >= t_start - 120) { lo = std::min(lo, st); break; }
+                if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > timeout()) {
+                    std::cout << "rank " << rank << ": rank " << r << " did not reach phase '" << phase << "' in time\n";
+                    return -1;
+                }
+                usleep(20000);
+            }
+        }
+        return lo;
+    }
+    void forget(size_t keep_last) {
+        while (mine.size() > keep_last) { unlink(mine.front().c_str()); mine.erase(mine.begin()); }
+    }
+};
 
 static std::string usage() {
     return "Usage: abub3hs [-hzme] [-D data_series] [-c cam_mask_dir] [--debug code] -d data_dir -r run_ID -o out_dir\n"
@@ -201,6 +248,10 @@ int main(int argc, char** argv) {
     for (int icam = 0; icam < numCams; icam++)
         Trainers.push_back(new Trainer(icam, EventList, eventDir, imageFormat, imageFolder, FileParser->clone(), debug_mode / 100));
     bool succeeded = true;
+    RankSync sync;
+    sync.base = out_dir + ".abub3hs_" + run_number + ".status";
+    sync.rank = opt.rank; sync.world = opt.world; sync.t_start = (long long)time(nullptr);
+    const std::string part_path = out_dir + "abub3hs_" + run_number + ".txt" + (opt.world > 1 ? ".rank" + std::to_string(opt.rank) : "");
     try {
         if (opt.world > 1) {
             /* ranks train on their own events and all-reduce exact integer partials; needs a context first */
@@ -214,7 +265,10 @@ int main(int argc, char** argv) {
                 if (!fr.empty() && FileParser->GetImage(EventList[evi], fr[0], im) != FileParser->FailureCode() && !im.empty())
                     AbubDevice::Get().Context(im.rows, im.cols);
             }
-            if (!AbubDevice::Get().ctx()) throw AbubError("no readable frame in this rank's event range");
+            /* every rank must have a context before any of them enters ncclCommInitRank */
+            const bool have_ctx = AbubDevice::Get().ctx() != nullptr;
+            if (!have_ctx) std::cout << "rank " << opt.rank << ": no readable frame in this rank's event range\n";
+            if (sync.agree("context", have_ctx ? 0 : -1) < 0) throw AbubError("a rank cannot take part in the training: no communicator is created");
             AbubDevice::Get().Check(abub_nccl_comm_create(AbubDevice::Get().ctx(), idfile.c_str(), opt.rank, opt.world, &nccl),
                                     "abub_nccl_comm_create");
             for (int icam = 0; icam < numCams; icam++) Trainers[icam]->NcclComm = nccl;
@@ -226,6 +280,8 @@ int main(int argc, char** argv) {
     }
     for (int icam = 0; icam < numCams; icam++)
         if (Trainers[icam]->StatusCode) succeeded = false;
+    /* the ranks take the -7 path together or not at all */
+    if (opt.world > 1 && sync.agree("trained", succeeded ? 0 : -1) < 0) succeeded = false;
 
     if (!succeeded) {
         /* -7 for every camera of every event (AutoBubStart3.cpp:315-325) */
@@ -236,6 +292,14 @@ int main(int argc, char** argv) {
                 for (int icam = 0; icam < numCams; icam++) PICO60Output->stageCameraOutputError(icam, -7, actualEventNumber);
                 PICO60Output->writeCameraOutput();
             }
+        if (opt.world > 1) {
+            /* nothing of a failed multi-rank run stays behind: part file, status files, the NCCL id file */
+            unlink(part_path.c_str());
+            usleep(300000);                       /* the peers have read this rank's status by now */
+            sync.forget(0);
+            if (lead) unlink((opt.nccl_id != "" ? opt.nccl_id : out_dir + ".abub3hs_" + run_number + ".ncclid").c_str());
+            if (nccl) abub_nccl_comm_destroy(nccl);
+        }
         return -7;
     }
     printf("***Training complete. AutoBub is now in detect mode***\n");
@@ -289,8 +353,16 @@ int main(int argc, char** argv) {
     }
 
     if (opt.world > 1) {
-        /* every rank has flushed its part; rank 0 concatenates in rank order = event order (omp ordered, :380) */
+        /* every rank has flushed its part; rank 0 concatenates in rank order = event order (omp ordered, :380).  The
+         * ranks meet through the status files first: a rank that died in detect mode must not hang the barrier. */
+        const int all_done = sync.agree("detected", 0);
+        if (all_done < 0) {
+            std::cout << "A rank did not finish its events: the part files are left in place, no merged output.\n";
+            sync.forget(0);
+            return -6;
+        }
         AbubDevice::Get().Check(abub_nccl_barrier(AbubDevice::Get().ctx(), nccl), "abub_nccl_barrier");
+        sync.forget(0);
         if (lead) {
             std::ofstream out(out_dir + "abub3hs_" + run_number + ".txt", std::fstream::out | std::fstream::app);
             for (int r = 0; r < opt.world; r++) {

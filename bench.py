@@ -231,7 +231,43 @@ def run_reference(args, rank, world):
                                        f"worker processes, handed out one at a time), early exit at the trigger kept"},
             "e2e": {"value": v, "unit": "events/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    rb = reference_binary_leg(run, cores, args.ref_binary_events)
+    if rb:
+        line["reference_binary_from_files"] = rb
     print(json.dumps(line), flush=True)
+
+
+def reference_binary_leg(run, cores, n):
+    """The reference's own compiled code from image FILES: oracle/_ref/abub3hs_ref (the unmodified first-party sources
+    built -O0 -fopenmp as CMakeLists.txt:35 does, against oracle/refshim) on the first n ring events written as 8-bit BMP:
+    file read + decode + training pass + detect loop + output file, OMP_NUM_THREADS = the host cores.  The pixel routines
+    behind its cv:: calls are the plain C of oracle/abub_ref.c, not OpenCV's SIMD code, which is why this figure is far
+    below the cv2 port above and is reported beside it, not as the baseline."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "abub3hs_ref")
+    if n <= 0 or not os.path.exists(exe):
+        return None
+    import dataclasses
+    from autobub3hs_b200 import synth
+    n = min(n, len(run.events))
+    sub = dataclasses.replace(run, events=run.events[:n], event_numbers=run.event_numbers[:n], specs=run.specs[:n])
+    tmp = tempfile.mkdtemp(prefix="abub_refbin_")
+    try:
+        synth.write_run(sub, os.path.join(tmp, "data"), os.path.join(tmp, "masks"))
+        os.makedirs(os.path.join(tmp, "out"))
+        nbytes = sum(os.path.getsize(os.path.join(dp, f)) for dp, _, fs in os.walk(os.path.join(tmp, "data")) for f in fs)
+        t0 = time.perf_counter()
+        r = subprocess.run([exe, "-D", "40l-19", "-d", os.path.join(tmp, "data"), "-r", run.run_id, "-o", os.path.join(tmp, "out"),
+                            "-c", os.path.join(tmp, "masks")], capture_output=True, text=True, timeout=1200,
+                           env=dict(os.environ, OMP_NUM_THREADS=str(cores)))
+        dt = time.perf_counter() - t0
+        if r.returncode != 0:
+            return {"error": (r.stdout + r.stderr)[-300:]}
+        rows = sum(1 for _ in open(os.path.join(tmp, "out", f"abub3hs_{run.run_id}.txt"))) - 6
+        return {"value": n / dt, "unit": "events/s", "events": n, "seconds": dt, "cores": cores, "kind": "reference",
+                "rows_written": rows, "bytes_read": nbytes,
+                "what": "oracle/_ref/abub3hs_ref from 8-bit BMP files: read + decode + Trainer pass + detect loop + output file"}
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
 
 
 # --------------------------------------------------------------------------------------
@@ -709,6 +745,7 @@ def main():
     ap.add_argument("--e2e-chunk", type=int, default=4)
     ap.add_argument("--trigger-steps", type=int, default=8, help="steps of the trigger-only extra (0 = skip)")
     ap.add_argument("--trainer-events", type=int, default=200, help="training events of the sharded Trainer leg at N > 1 (0 = skip)")
+    ap.add_argument("--ref-binary-events", type=int, default=8, help="--impl reference: events the compiled reference binary runs from BMP files (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-step", action="store_true", help="run one extra step between cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     args = ap.parse_args()

@@ -101,6 +101,8 @@ int abub_event_submit_range(abub_ctx* ctx, int slot, int cam, int frame_first, i
  * already live on the device) and the matching frame counts. */
 int abub_event_device_ptr(abub_ctx* ctx, int slot, uint8_t** dev_ptr);
 int abub_event_set_nframes(abub_ctx* ctx, int slot, const int* nframes);
+/* The same for slots [slot_first, slot_first+nslots): nframes[nslots*ncams], one launch per 64 slots' worth of counts. */
+int abub_event_set_nframes_range(abub_ctx* ctx, int slot_first, int nslots, const int* nframes);
 
 /* ---- trigger: AnalyzerUnit::FindTriggerFrame (AnalyzerUnit.cpp:119-324) --------- */
 /* K1: for every (slot, cam, j>=1) computes the 256-bin histogram of

@@ -201,6 +201,41 @@ def test_two_ranks_same_text(abub3hs, tma_run, tmp_path):
     assert not [f for f in os.listdir(out) if "rank" in f or "ncclid" in f]
 
 
+def test_two_ranks_one_cannot_train_both_end_minus7(abub3hs, tmp_path):
+    """Multi-rank failure path (both processes on GPU 0: no communicator is ever created): rank 1's event range holds no
+    readable frame, so it cannot take part in the training.  The ranks agree on that through the status files BEFORE
+    anyone enters ncclCommInitRank: both end with -7, rank 0 writes the -7 rows of every event (AutoBubStart3.cpp:315-325),
+    nobody blocks, and no part / status / id file is left behind."""
+    from autobub3hs_b200 import synth
+    import oracle.cv2_oracle as o
+    rng = np.random.default_rng(1)
+    data = tmp_path / "data"
+    quiet = rng.integers(60, 120, (48, 64)).astype(np.uint8)
+    for ev in range(2):
+        d = data / "20210101_0" / str(ev) / "Images"
+        d.mkdir(parents=True)
+        if ev == 1:
+            continue                                     # rank 1's only event: the folder is there, the frames are not
+        for c in range(4):
+            for f in range(6):
+                synth.write_bmp8(str(d / f"cam{c}_image{30 + f}.bmp"), quiet)
+    out = tmp_path / "out"
+    out.mkdir()
+    procs = []
+    for r in range(2):
+        cmd = [abub3hs, "-D", "40l-19", "-d", str(data), "-r", "20210101_0", "-o", str(out), "--rank", str(r), "--world", "2",
+               "--device", "0"]
+        procs.append(subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                                      env=dict(os.environ, ABUB_RANK_TIMEOUT="120")))
+    logs = [p.communicate(timeout=300)[0] for p in procs]
+    assert [p.returncode for p in procs] == [(-7) % 256] * 2, "\n".join(l[-1500:] for l in logs)
+    exp = o.write_header()
+    for ev in range(2):
+        exp += o.write_camera_output("20210101_0", [o.CameraOutput(-7, 0, ev) for _ in range(4)], 30)
+    assert open(out / "abub3hs_20210101_0.txt").read() == exp
+    assert sorted(os.listdir(out)) == ["abub3hs_20210101_0.txt"], os.listdir(out)
+
+
 def test_bellows_run_with_and_without_template(abub3hs, tmp_path):
     """Cameras 1 and 3 show a moving bellows: every genesis contour lies in the bellows mask and the veto branch
     (L3Localizer.cpp:292-390) runs -- with the template PNG in the mask directory, and with it missing."""
