@@ -112,6 +112,8 @@ struct abub_ctx {
     int*      d_post_list = nullptr; // indices of the post-trigger jobs of a localizer chunk (k5_post_tma.cu)
     int*      h_post_list = nullptr; // its pinned staging copy; post_ev = the last upload from it
     cudaEvent_t post_ev = nullptr;
+    void*     fix_buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // grow-only scratch of the multi-GPU fix-up (nccl_glue.cu)
+    size_t    fix_cap[6] = {0, 0, 0, 0, 0, 0};
     int*      d_gen_list = nullptr;  // the same for the genesis jobs (k5_genesis_tma.cu)
     int*      h_gen_list = nullptr;
     cudaEvent_t gen_ev = nullptr;
@@ -189,7 +191,7 @@ int abub_k2_next_avail(abub_ctx* ctx, int slot_first, int nslots, int next, bool
 int abub_k3_gate_hist16(abub_ctx* ctx, const uint8_t* d_f0, const uint8_t* d_f1, uint32_t* d_hist16);
 int abub_k3_gate_batch(abub_ctx* ctx, const uint8_t* const* d_pairs, int n, uint32_t* d_hist16);
 int abub_k4_welford(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint8_t* d_mean, uint8_t* d_sigma);
-int abub_k4_partials(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint32_t* d_sum, uint64_t* d_sumsq);
+int abub_k4_partials(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint32_t* d_sum, uint64_t* d_sumsq, bool aligned16);
 int abub_k4_finish_from_partials(abub_ctx* ctx, const uint32_t* d_sum, const uint64_t* d_sumsq, int n, uint8_t* d_mean,
                                  uint8_t* d_sigma, int* d_nflag, uint8_t* d_flag);
 int abub_k4_fixup(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, const uint8_t* d_flag, uint8_t* d_mean,

@@ -100,6 +100,7 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
     if (ctx->h_post_list) cudaFreeHost(ctx->h_post_list);
     if (ctx->post_ev) cudaEventDestroy(ctx->post_ev);
     cudaFree(ctx->d_gen_list);
+    for (void* b : ctx->fix_buf) cudaFree(b);
     if (ctx->h_gen_list) cudaFreeHost(ctx->h_gen_list);
     if (ctx->gen_ev) cudaEventDestroy(ctx->gen_ev);
     if (ctx->h_raw) cudaFreeHost(ctx->h_raw);

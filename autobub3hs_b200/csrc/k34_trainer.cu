@@ -164,6 +164,43 @@ __global__ void k4_partials_kernel(const uint8_t* const* __restrict__ frames, in
     sumsq[p] = q;
 }
 
+// the same, 16 pixels per thread (one 16-byte load per frame, four frames in flight) with 32-bit sums of squares:
+// 255^2 * n < 2^32 for n <= 66051 frames; the launcher uses this kernel up to 60000 frames and 16-byte aligned planes
+__global__ void __launch_bounds__(128) k4_partials16_kernel(const uint8_t* const* __restrict__ frames, int n, uint32_t* __restrict__ sum,
+                                                            uint64_t* __restrict__ sumsq, size_t nvec) {
+    const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= nvec) return;
+    uint32_t s[16], q[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) s[i] = q[i] = 0;
+    auto add = [&](const uint4 v) {
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const uint32_t x = (w[k] >> (8 * c)) & 0xFFu;
+                s[4 * k + c] += x;
+                q[4 * k + c] += x * x;
+            }
+    };
+    int f = 0;
+    for (; f + 4 <= n; f += 4) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) v[u] = __ldg(reinterpret_cast<const uint4*>(frames[f + u]) + g);
+#pragma unroll
+        for (int u = 0; u < 4; u++) add(v[u]);
+    }
+    for (; f < n; f++) add(__ldg(reinterpret_cast<const uint4*>(frames[f]) + g));
+    uint4* so = reinterpret_cast<uint4*>(sum) + 4 * g;
+#pragma unroll
+    for (int k = 0; k < 4; k++) so[k] = make_uint4(s[4 * k], s[4 * k + 1], s[4 * k + 2], s[4 * k + 3]);
+    ulonglong2* qo = reinterpret_cast<ulonglong2*>(sumsq) + 8 * g;
+#pragma unroll
+    for (int k = 0; k < 8; k++) qo[k] = make_ulonglong2((unsigned long long)q[2 * k], (unsigned long long)q[2 * k + 1]);
+}
+
 // mean/sigma from reduced integer partials in fp64; flags every pixel whose truncated planes COULD differ from the
 // sequential float32 recurrence of K4 (Trainer.cpp:185-196).  The flag test is a worst-case bound of that recurrence's
 // rounding error, u = 2^-24, samples in [0, 255], k = 2 .. n (step 1 is exact: mean = x, m2 = 0):
@@ -411,7 +448,14 @@ int abub_k4_welford(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, u
     return ABUB_OK;
 }
 
-int abub_k4_partials(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint32_t* d_sum, uint64_t* d_sumsq) {
+int abub_k4_partials(abub_ctx* ctx, const uint8_t* const* d_frame_table, int n, uint32_t* d_sum, uint64_t* d_sumsq, bool aligned16) {
+    abub_prof_scope prof(ctx, ABUB_PROF_K4);
+    if (aligned16 && n <= 60000 && ctx->npix % 16 == 0 && !getenv("ABUB_K4_GENERIC")) {
+        const size_t nvec = ctx->npix / 16;
+        ABUB_L(ctx), k4_partials16_kernel<<<(unsigned)((nvec + 127) / 128), 128, 0, ctx->stream>>>(d_frame_table, n, d_sum, d_sumsq, nvec);
+        ABUB_CHECK_CUDA(ctx, cudaGetLastError());
+        return ABUB_OK;
+    }
     ABUB_L(ctx), k4_partials_kernel<<<(unsigned)((ctx->npix + 255) / 256), 256, 0, ctx->stream>>>(d_frame_table, n, d_sum, d_sumsq,
                                                                                      ctx->npix);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());

@@ -165,37 +165,51 @@ extern "C" int abub_train_finish_allreduced(abub_ctx* ctx, int cam, void* comm, 
     ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const int F = cnt[1];                      // identical on every rank: flags derive from the reduced partials
     if (n_flagged) *n_flagged = F;
+    // scratch kept from call to call (one camera after the other reuses it): [0] counts, [1] flagged indices, [2] count of
+    // selected, [3] cub temp, [4] this rank's samples, [5] every rank's samples
+    auto need = [&](int i, size_t bytes) -> int {
+        if (bytes <= ctx->fix_cap[i]) return ABUB_OK;
+        cudaFree(ctx->fix_buf[i]);
+        ctx->fix_buf[i] = nullptr;
+        ctx->fix_cap[i] = 0;
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->fix_buf[i], bytes + bytes / 4));
+        ctx->fix_cap[i] = bytes + bytes / 4;
+        return ABUB_OK;
+    };
     // kept-frame counts of every rank
     const int n_local = (int)cs.kept.size();
-    int* d_counts = nullptr;
-    ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_counts, (size_t)(world + 1) * sizeof(int)));
+    if (int rc2 = need(0, (size_t)(world + 1) * sizeof(int))) return rc2;
+    int* d_counts = (int*)ctx->fix_buf[0];
+    // 4 bytes from the stack: a pageable source is staged by the runtime before cudaMemcpyAsync returns
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(d_counts + world, &n_local, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     int nr = ag(d_counts + world, d_counts, 1, NCCL_I32, comm, ctx->stream);
     std::vector<int> counts(world);
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(counts.data(), d_counts, world * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (nr) { cudaFree(d_counts); ctx->err = "ncclAllGather(counts) failed"; return ABUB_E_NCCL; }
+    if (nr) { ctx->err = "ncclAllGather(counts) failed"; return ABUB_E_NCCL; }
     if (F > 0) {
         int stride = 1;
         for (int c : counts) stride = c > stride ? c : stride;
         stride = (stride + 15) & ~15;
-        int* d_idx = nullptr; int* d_nsel = nullptr; void* d_tmp = nullptr; uint8_t* d_loc = nullptr; uint8_t* d_all = nullptr;
         size_t tmp_bytes = 0;
-        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_idx, (size_t)F * sizeof(int)));
-        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_nsel, sizeof(int)));
         cub::CountingInputIterator<int> it(0);
-        cub::DeviceSelect::Flagged(nullptr, tmp_bytes, it, cs.d_flag, d_idx, d_nsel, (int)ctx->npix, ctx->stream);
-        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_tmp, tmp_bytes));
-        cub::DeviceSelect::Flagged(d_tmp, tmp_bytes, it, cs.d_flag, d_idx, d_nsel, (int)ctx->npix, ctx->stream);
+        cub::DeviceSelect::Flagged(nullptr, tmp_bytes, it, cs.d_flag, (int*)nullptr, (int*)nullptr, (int)ctx->npix, ctx->stream);
         // the flagged pixels go through the gather in tiles so that the gathered samples (world x tile x stride bytes on
-        // every rank) stay under ABUB_FIXUP_TILE_BYTES however many frames were kept and however many pixels are flagged;
-        // F, world and stride are the same on every rank, so every rank walks the same tiles
+        // every rank) stay under 256 MB however many frames were kept and however many pixels are flagged; F, world and
+        // stride are the same on every rank, so every rank walks the same tiles
         const size_t budget = (size_t)256 << 20;
         size_t tile = budget / ((size_t)world * stride);
         tile = tile < 1024 ? 1024 : tile;
         if (tile > (size_t)F) tile = (size_t)F;
-        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_loc, tile * stride));
-        ABUB_CHECK_CUDA(ctx, cudaMalloc(&d_all, (size_t)world * tile * stride));
+        int rc2;
+        if ((rc2 = need(1, (size_t)F * sizeof(int))) || (rc2 = need(2, sizeof(int))) || (rc2 = need(3, tmp_bytes)) ||
+            (rc2 = need(4, tile * stride)) || (rc2 = need(5, (size_t)world * tile * stride)))
+            return rc2;
+        int* d_idx = (int*)ctx->fix_buf[1];
+        int* d_nsel = (int*)ctx->fix_buf[2];
+        uint8_t* d_loc = (uint8_t*)ctx->fix_buf[4];
+        uint8_t* d_all = (uint8_t*)ctx->fix_buf[5];
+        cub::DeviceSelect::Flagged(ctx->fix_buf[3], tmp_bytes, it, cs.d_flag, d_idx, d_nsel, (int)ctx->npix, ctx->stream);
         for (size_t t0 = 0; t0 < (size_t)F && !nr; t0 += tile) {
             const int ft = (int)((size_t)F - t0 < tile ? (size_t)F - t0 : tile);
             ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(d_loc, 0, (size_t)ft * stride, ctx->stream));
@@ -205,12 +219,8 @@ extern "C" int abub_train_finish_allreduced(abub_ctx* ctx, int cam, void* comm, 
                 ABUB_L(ctx), fixup_gathered_kernel<<<(ft + 127) / 128, 128, 0, ctx->stream>>>(d_all, d_counts, world, d_idx + t0, ft, stride, n,
                                                                                    cs.d_mean, cs.d_sigma);
         }
-        cudaError_t e = cudaStreamSynchronize(ctx->stream);
-        cudaFree(d_idx); cudaFree(d_nsel); cudaFree(d_tmp); cudaFree(d_loc); cudaFree(d_all);
-        if (nr) { cudaFree(d_counts); ctx->err = "ncclAllGather(samples) failed"; return ABUB_E_NCCL; }
-        ABUB_CHECK_CUDA(ctx, e);
+        if (nr) { cudaStreamSynchronize(ctx->stream); ctx->err = "ncclAllGather(samples) failed"; return ABUB_E_NCCL; }
     }
-    cudaFree(d_counts);
     cs.training_set_size = n;
     cs.has_background = true;
     if (status) *status = 0;

@@ -273,7 +273,9 @@ extern "C" int abub_train_partials(abub_ctx* ctx, int cam, uint32_t** d_sum, uin
     rc = upload_table(ctx, cs);
     if (rc) return rc;
     const int n = (int)cs.kept.size();
-    rc = abub_k4_partials(ctx, cs.d_table, n, cs.d_sum, cs.d_sumsq);
+    bool aligned16 = true;
+    for (const uint8_t* f : cs.kept) aligned16 = aligned16 && (((uintptr_t)f) & 15) == 0;
+    rc = abub_k4_partials(ctx, cs.d_table, n, cs.d_sum, cs.d_sumsq, aligned16);
     if (rc) return rc;
     const int cnt[4] = {n, 0, 0, 0};
     ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(cs.d_count, cnt, sizeof(cnt), cudaMemcpyHostToDevice, ctx->stream));

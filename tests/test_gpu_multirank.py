@@ -56,8 +56,10 @@ def test_trainer_two_ranks_exact(tmp_path, npairs, cut):
         f1 = f0.copy()                               # identical pair: passes the entropy gate
         frames += [f0, f1]
     frames = np.stack(frames)
-    frames[:, :8] = 77                               # constant pixels: mean exactly on an integer boundary -> flagged
-    frames[:, 8:16] = (np.arange(len(frames)) % 2 * 3 + 10).astype(np.uint8)[:, None, None]
+    frames[:, :8] = 77                               # constant pixels: the recurrence is exact there, nothing to repair
+    # every frame 10 but one pair at 10 + npairs: the mean is exactly 11 with a non-zero spread -> on an integer boundary, flagged
+    frames[:, 8:16] = 10
+    frames[:2, 8:16] = 10 + npairs
     data = str(tmp_path / "data.npz")
     np.savez(data, frames=frames, cuts=np.array([0, 2 * cut, 2 * npairs]))
     wfile = str(tmp_path / "worker.py")
