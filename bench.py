@@ -606,6 +606,25 @@ def run_ours(args, rank, world, local_rank):
         link_gbs = 4 * pin0.numel() / (lk0.elapsed_time(lk1) * 1e-3) / 1e9
     except Exception:
         pass
+    # the same copy by every rank at once: what the box's host memory system gives N GPUs together (the ceiling of e2e)
+    link_all = None
+    if world > 1 and link_gbs is not None:
+        try:
+            dist.barrier()
+            torch.cuda.synchronize()
+            lk0.record(cur)
+            for _ in range(8):
+                dst0.copy_(pin0, non_blocking=True)
+            lk1.record(cur)
+            torch.cuda.synchronize()
+            g = torch.zeros(world, device="cuda", dtype=torch.float64)
+            g[rank] = 8 * pin0.numel() / (lk0.elapsed_time(lk1) * 1e-3) / 1e9
+            dist.all_reduce(g)
+            per = [float(v) for v in g.tolist()]
+            link_all = {"per_rank_min": min(per), "per_rank_max": max(per), "aggregate": float(sum(per)),
+                        "what": "every rank copies one 282 MB pinned event buffer to its GPU 8 times, all ranks at once"}
+        except Exception:
+            pass
     hr.end_run()
 
     # ---- configs[2]: the Trainer sharded over the ranks, one NCCL all-reduce + all-gather fix-up (last: it replaces the planes) ----
@@ -634,7 +653,7 @@ def run_ours(args, rank, world, local_rank):
                     "frames_sent_frac": e2e_stage["frames_sent"] / (args.e2e_steps * Be * NCAMS * NFRAMES),
                     "h2d_gbs_per_rank": {"min": min(h2d_ranks), "median": float(np.median(h2d_ranks)), "max": max(h2d_ranks)},
                     "h2d_gbs_aggregate": float(sum(h2d_ranks)),
-                    "h2d_link_gbs_one_large_pinned_copy": link_gbs, "rank0_numa_node": numa_node, "numa_note": numa_why,
+                    "h2d_link_gbs_one_large_pinned_copy": link_gbs, "h2d_all_ranks_copying_at_once_gbs": link_all, "rank0_numa_node": numa_node, "numa_note": numa_why,
                     "stage_seconds_per_step": {k: v / args.e2e_steps for k, v in e2e_stage.items() if k != "frames_sent"},
                     "note": "abubhost_recon mode 1: frames wait in pinned host memory and are sent %d at a time; a camera stops "
                             "receiving frames at its trigger decision, the localizer's frames (up to trig+10) follow; trigger "
