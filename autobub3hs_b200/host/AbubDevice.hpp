@@ -133,7 +133,7 @@ private:
     void StageBatch(Parser* parser, const std::vector<int>& slots, const std::vector<std::string>& events);
     void LocalizeBatch(const std::vector<int>& slots, const int* training_set_sizes);
     std::vector<abub_blob> loc_blobs_;
-    int early_chunk_ = 6;
+    int early_chunk_ = 5;
     int trigger_metric_ = 0;
     float trigger_threshold_ = 0.f;
     std::map<std::string, int> by_key_;

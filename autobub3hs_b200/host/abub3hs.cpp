@@ -95,7 +95,7 @@ static std::string usage() {
            "GPU arguments (not in the reference):\n"
            "  --device = Int\t\tCUDA device ordinal (default 0, or the rank with --world)\n"
            "  --batch = Int\t\t\tevents staged on the GPU at once (default 8; 282 MB of HBM each at 4x40 frames of 1680x1050)\n"
-           "  --early_chunk = Int\t\tframe pairs per round of the trigger search's early exit (default 6; 0 = all pairs at once)\n"
+           "  --early_chunk = Int\t\tframe pairs per round of the trigger search's early exit (default 5; 0 = all pairs at once)\n"
            "  --max_frames = Int\t\tframes per camera a slot can hold (default: what the first events hold, at least 40)\n"
            "  --trigger_metric = Str	significance (default) | entropy | entropy_significance: which of the three lines of\n"
            "\t\t\t\tAnalyzerUnit.cpp:226-228 is the live one; --trigger_threshold = Float overrides its entropyThreshold\n"
@@ -105,7 +105,7 @@ static std::string usage() {
 
 struct Options {
     std::string dataLoc, run_number, out_dir, mask_dir, data_series, nccl_id, trigger_metric = "significance", trigger_threshold = "0";
-    int event_user = -1, debug_mode = 0, device = -1, batch = 8, early_chunk = 6, max_frames = 0, rank = 0, world = 1;
+    int event_user = -1, debug_mode = 0, device = -1, batch = 8, early_chunk = 5, max_frames = 0, rank = 0, world = 1;
     bool zipped = false, mask_check = false, help = false;
 };
 

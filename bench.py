@@ -353,7 +353,10 @@ def run_ours(args, rank, world, local_rank):
     numa_node, numa_why = bind_to_gpu_numa_node(local_rank) if world > 1 else (None, "single rank")
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    hr = capi.HostRecon(ROWS, COLS, NCAMS, NFRAMES, max_slots=B, device=local_rank, early_chunk=args.early_chunk)
+    # --slot-sets sets of B slots: step i works on set i % sets, so the host stage of one step's last sub-batch never holds
+    # the slots the next step needs (abub3hs does the same: 2 x batch slots)
+    SETS = max(1, args.slot_sets)
+    hr = capi.HostRecon(ROWS, COLS, NCAMS, NFRAMES, max_slots=SETS * B, device=local_rank, early_chunk=args.early_chunk)
     ctx = hr.ctx
     stream = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
     tmp = tempfile.mkdtemp(prefix=f"abub_bench_r{rank}_")
@@ -373,9 +376,9 @@ def run_ours(args, rank, world, local_rank):
                 for i in range(share):
                     slot_tensor(torch, ctx, r * share + i).copy_(full[r, i])
         del full, mine
-    for s in range(R, B):
-        slot_tensor(torch, ctx, s).copy_(slot_tensor(torch, ctx, s % R))
-    for s in range(B):
+    for s in range(R, SETS * B):
+        slot_tensor(torch, ctx, s).copy_(slot_tensor(torch, ctx, (s % B) % R))
+    for s in range(SETS * B):
         ctx.event_set_nframes(s, [NFRAMES] * NCAMS)
     torch.cuda.synchronize()
 
@@ -402,8 +405,9 @@ def run_ours(args, rank, world, local_rank):
 
     def step():
         numbers = [base_no + step_no[0] * B + s for s in range(B)]
+        first = (step_no[0] % SETS) * B
         step_no[0] += 1
-        hr.recon(0, numbers, nf_all)
+        hr.recon(first, numbers, nf_all)
 
     for _ in range(max(args.warmup, 0)):
         step()
@@ -641,7 +645,7 @@ def run_ours(args, rank, world, local_rank):
                        "events_timed": world * B * args.steps, "note_10000": "10,000 events = %d steps of %d events" % (-(-10000 // B), B),
                        "l2": "inputs (35 GB/step at 125 events) exceed L2; no flush",
                        "event_mix": "90% normal (1-3 bubbles), 5% multi (>=20), 5% no-trigger; noise sigma 2.0",
-                       "train_events": n_train, "early_chunk": args.early_chunk, "sub_batch": args.sub_batch, "host_threads": host_threads,
+                       "train_events": n_train, "early_chunk": args.early_chunk, "sub_batch": args.sub_batch, "slot_sets": SETS, "host_threads": host_threads,
                        "rendered_on": "host (numpy PCG64, %d of %d ring events on this rank, %.1f s)" % (share, R, t_render)},
             "stage_seconds_per_step": {k: v / args.steps for k, v in stage.items() if k != "frames_sent"},
             "device_ms_per_step": dev_ms / args.steps,
@@ -758,9 +762,10 @@ def main():
     ap.add_argument("--events-per-step", type=int, default=125)
     ap.add_argument("--ring-events", type=int, default=32)
     ap.add_argument("--train-events", type=int, default=25)
-    ap.add_argument("--early-chunk", type=int, default=6, help="frame pairs per round of the trigger search's early exit (0 = full table)")
+    ap.add_argument("--early-chunk", type=int, default=5, help="frame pairs per round of the trigger search's early exit (0 = full table)")
     ap.add_argument("--host-threads", type=int, default=0, help="threads of the host event loop (0 = cores per rank - 1)")
-    ap.add_argument("--sub-batch", type=int, default=64, help="events handed from the device stage to the host stage at a time")
+    ap.add_argument("--slot-sets", type=int, default=2, help="sets of --events-per-step slots the steps alternate between")
+    ap.add_argument("--sub-batch", type=int, default=125, help="events handed from the device stage to the host stage at a time")
     ap.add_argument("--e2e-events", type=int, default=32)
     ap.add_argument("--e2e-sub-batch", type=int, default=16)
     ap.add_argument("--e2e-steps", type=int, default=20)

@@ -1,9 +1,13 @@
 #!/bin/bash
-# bench.py headline over early-exit chunk sizes and sub-batch sizes (one ring render per run; ~40 s each)
-for sb in 64 125; do for ec in 4 5 6 8; do
-  python bench.py --no-cpu-baseline --trigger-steps 0 --e2e-steps 1 --e2e-events 16 --early-chunk $ec --sub-batch $sb --steps 12 2>/dev/null | python -c "
+# bench.py headline over localizer scratch sizes (chunks per sub-batch), slot sets, sub-batch and early-exit chunk sizes
+run() {
+  python bench.py --no-cpu-baseline --trigger-steps 0 --e2e-steps 1 --e2e-events 16 --steps 12 "$@" 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.read().strip().splitlines()[-1])
 k={x['kernel'].split()[0]:x['ms_per_step'] for x in d['roofline']['kernels']}
-print('sub_batch $sb early_chunk $ec value %.1f ms %.2f K1 %.2f K2 %.2f pairs %.3f launches %d'%(d['value'], d['ms_per_step'], k.get('K1',0), k.get('K2',0), d['roofline']['frame_pairs_computed_frac'], d['gpu_launches']))"
-done; done
+loc=[x for x in d['roofline']['kernels'] if x['kernel'].startswith('localizer')][0]
+print('$LABEL $* value %.1f ms %.2f K1 %.2f K2 %.2f loc %.2f (K5b %.2f K7b %.2f) host %.2f launches %d'%(d['value'], d['ms_per_step'], k.get('K1',0), k.get('K2',0), loc['ms_per_step'], k.get('K5b',0), k.get('K7b',0), 1e3*d['stage_seconds_per_step']['host_analysis_s'], d['gpu_launches']))"
+}
+LABEL="scratch 4GB(default)" run
+for mb in 8000 16000; do LABEL="scratch ${mb}MB" ABUB_LOC_SCRATCH_MB=$mb run; done
+LABEL="scratch 16000MB" ABUB_LOC_SCRATCH_MB=16000 run --early-chunk 6
