@@ -292,6 +292,12 @@ class Context:
         nf = (C.c_int * self.ncams)(*nframes)
         self._ck(self.lib.abub_event_set_nframes(self.h, slot, nf), "abub_event_set_nframes")
 
+    def event_set_nframes_range(self, slot_first: int, nframes) -> None:
+        """nframes: [nslots, ncams] frame counts of slots slot_first ... (frames placed in HBM by a producer)."""
+        nf = np.ascontiguousarray(nframes, dtype=np.int32).reshape(-1, self.ncams)
+        self._ck(self.lib.abub_event_set_nframes_range(self.h, slot_first, len(nf), nf.ctypes.data_as(C.POINTER(C.c_int))),
+                 "abub_event_set_nframes_range")
+
     # ---- trigger ----
     def trigger_hist(self, slot_first: int = 0, nslots: int = 1) -> None:
         self._ck(self.lib.abub_trigger_hist(self.h, slot_first, nslots), "abub_trigger_hist")

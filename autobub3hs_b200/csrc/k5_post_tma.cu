@@ -22,6 +22,8 @@
 // k5_localize.cu): a row segment is written only when it holds something or may still hold something older.
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "abub_internal.cuh"
 
 namespace {
@@ -38,6 +40,9 @@ namespace {
 #ifndef ABUB_K5T_SKIP
 #define ABUB_K5T_SKIP 0
 #endif
+#ifndef ABUB_K5T_FMA
+#define ABUB_K5T_FMA 1      // 1: the adds of the 3x3 window go through IMAD (a * one + b with a run-time 1): the ALU pipe, which
+#endif                      // carries PRMT / VIADDMNMX / VIMNMX / VABSDIFF4 / IADD3 / LOP3 and bounds this kernel, is relieved
 constexpr int P_R = 4;                    // rows per TMA box
 constexpr int P_S = ABUB_K5T_S;           // ring stages per warp
 constexpr int P_OW = 240;                 // output columns per warp
@@ -83,7 +88,7 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
 __global__ void __launch_bounds__(32, P_MINCTA)
 k5_post_tma_kernel(const abub_loc_job* __restrict__ jobs, const int* __restrict__ post_list, const CUtensorMap* __restrict__ slot_maps,
                    const CUtensorMap* __restrict__ mean_maps, const CUtensorMap* __restrict__ nt_maps, int rows, int cols, int nxg,
-                   int nstrips, int h0) {
+                   int nstrips, int h0, uint32_t one) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     const int lane = threadIdx.x;
     const abub_loc_job job = jobs[post_list[blockIdx.y]];
@@ -165,6 +170,10 @@ k5_post_tma_kernel(const abub_loc_job* __restrict__ jobs, const int* __restrict_
         mbar_wait(bars + stage * 8, parity);
         const uint8_t* const st = smem_raw + stage * P_STAGE_BYTES;
         uint32_t newfl = fl;
+        // CHK = the stage may hold rows without an output (the priming box, the rows past the strip): interior stages
+        // run the copy of the row body without the per-row test
+        auto do_rows = [&](auto chk) {
+        constexpr bool CHK = decltype(chk)::value;
 #pragma unroll
         for (int r = 0; r < P_R; r++) {
             const uint2 a = *reinterpret_cast<const uint2*>(st + P_A_OFF + r * P_BW + 8 + lane * 8);
@@ -180,13 +189,13 @@ k5_post_tma_kernel(const abub_loc_job* __restrict__ jobs, const int* __restrict_
             zhist = (zhist << 1) | (row_nz ? 1u : 0u);
             const int yo = yo0 + r;                                     // output row completed by this row
             const uint32_t prev = __shfl_sync(0xffffffffu, fl, r);      // its segment flag
-            if (yo >= y0 && yo < y0 + nout) {                           // warp-uniform
+            if (!CHK || (yo >= y0 && yo < y0 + nout)) {                 // warp-uniform
                 uint2 o = make_uint2(0u, 0u);
                 bool nz = false;
                 if (!ABUB_K5T_SKIP || (zhist & 7u)) {                   // some pixel over the cut in these three rows
                     uint32_t W[6];
 #pragma unroll
-                    for (int k = 0; k < 4; k++) W[k + 1] = w[k] + pp[k];
+                    for (int k = 0; k < 4; k++) W[k + 1] = ABUB_K5T_FMA ? w[k] * one + pp[k] : w[k] + pp[k];
                     W[0] = __shfl_up_sync(0xffffffffu, W[4], 1);
                     W[5] = __shfl_down_sync(0xffffffffu, W[1], 1);
                     if (left_edge) W[0] = __byte_perm(W[1], 0, 0x3232);     // column -1 -> column 1
@@ -196,7 +205,7 @@ k5_post_tma_kernel(const abub_loc_job* __restrict__ jobs, const int* __restrict_
                     for (int k = 0; k < 4; k++) {
                         const uint32_t sl = __byte_perm(W[k], W[k + 1], 0x5432);      // (x-1, x) pairs
                         const uint32_t sr = __byte_perm(W[k + 1], W[k + 2], 0x5432);  // (x+1, x+2) pairs
-                        H[k] = sl + W[k + 1] + sr;
+                        H[k] = ABUB_K5T_FMA ? (sl * one + W[k + 1]) + sr : sl + W[k + 1] + sr;
                         mx = __vmaxu2(mx, H[k]);
                     }
                     if (out_lane && ((mx & 0xFFFFu) >= lim || (mx >> 16) >= lim)) {
@@ -225,6 +234,9 @@ k5_post_tma_kernel(const abub_loc_job* __restrict__ jobs, const int* __restrict_
 #pragma unroll
             for (int k = 0; k < 4; k++) { pp[k] = pr[k] + w[k]; pr[k] = w[k]; }
         }
+        };
+        if (yo0 >= y0 && yo0 + P_R <= y0 + nout) do_rows(std::false_type{});
+        else do_rows(std::true_type{});
         if (lane < 4 && frow && newfl != fl) flags[(size_t)yf * nxw] = (uint8_t)newfl;
         __syncwarp();                                                   // every lane is done with the stage
         if (lane == 0 && s + P_S < nst) issue(s + P_S, stage);
@@ -272,7 +284,7 @@ int abub_k5b_launch_tma(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs) {
         const int n = np - p0 < 65535 ? np - p0 : 65535;
         ABUB_L(ctx), k5_post_tma_kernel<<<dim3(nstrips * nxg, n), 32, smem, ctx->stream>>>(
             d_jobs, ctx->d_post_list + p0, maps, maps + ctx->max_slots + ctx->ncams, maps + ctx->max_slots + 2 * ctx->ncams, ctx->rows, ctx->cols,
-            nxg, nstrips, h0);
+            nxg, nstrips, h0, 1u);
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     }
     return ABUB_OK;

@@ -228,6 +228,51 @@ def test_trigger_stream_equals_batch(capi, small_run, small_trained, chunk):
         assert np.array_equal(s3, status) and np.array_equal(t3[ok], trig[ok])
 
 
+def test_set_nframes_range_equals_per_slot_calls(capi, small_run, small_trained):
+    """abub_event_set_nframes_range (one launch for a range of slots) leaves the device with the same frame counts as one
+    abub_event_set_nframes per slot: frames are placed through the device pointer, the counts -- shortened for some
+    cameras, which changes status and trigger frame -- go in both ways, and the trigger results must agree."""
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    nev = len(run.events)
+    rng = np.random.default_rng(3)
+    counts = np.array([[len(run.events[ev][c]) for c in range(4)] for ev in range(nev)], np.int32)
+    cut = counts.copy()
+    for ev in range(nev):
+        c = int(rng.integers(0, 4))
+        cut[ev, c] = max(0, int(cut[ev, c]) - int(rng.integers(1, 30)))
+    with capi.Context(rows, cols, ncams=4, max_frames=40, max_slots=nev) as ctx:
+        for c in range(4):
+            ctx.set_background(c, trained[c].avg, trained[c].sigma, trained[c].training_set_size)
+        for ev in range(nev):
+            for c in range(4):
+                ctx.event_upload(ev, c, run.events[ev][c])
+        res = []
+        for form in ("per_slot", "range", "range_tail"):
+            if form == "per_slot":
+                for ev in range(nev):
+                    ctx.event_set_nframes(ev, cut[ev])
+            elif form == "range":
+                ctx.event_set_nframes_range(0, cut)
+            else:                                            # a range that starts in the middle, after resetting everything
+                ctx.event_set_nframes_range(0, counts)
+                ctx.event_set_nframes_range(0, cut[:2])
+                ctx.event_set_nframes_range(2, cut[2:])
+            ctx.trigger_hist(0, nev)
+            ctx.trigger_scan(0, nev)
+            res.append(ctx.trigger_results(0, nev, want_sig=False)[:3])
+        for other in res[1:]:
+            for a, b in zip(res[0], other):
+                assert np.array_equal(a, b)
+        ctx.event_set_nframes_range(0, counts)
+        ctx.trigger_hist(0, nev)
+        ctx.trigger_scan(0, nev)
+        full = ctx.trigger_results(0, nev, want_sig=False)[:3]
+        assert not all(np.array_equal(a, b) for a, b in zip(res[0], full))      # the shortened counts did matter
+        with pytest.raises(capi.AbubError):
+            ctx.event_set_nframes_range(nev - 1, cut[:2])                       # runs past the last slot
+
+
 @pytest.mark.parametrize("chunk", [1, 4, 6, 40])
 def test_trigger_early_equals_batch(capi, small_run, small_trained, chunk):
     """abub_trigger_early (resident frames, K1 in rounds of `chunk` frame pairs, decided cameras drop out of the later
