@@ -119,6 +119,7 @@ k5_post_tma_kernel(const abub_loc_job* __restrict__ jobs, const int* __restrict_
     const int za = job.zframe;
     const uint32_t lim = 9u * (uint32_t)job.tozero + 5u;                // (sum+4)/9 <= tozero  <=>  sum < lim
     const int tozero = job.tozero;
+    const uint32_t nlim2 = ((0x10000u - (lim - 1u)) & 0xFFFFu) * 0x00010001u;           // -(lim - 1) in both s16 lanes
     // stages: 0 = priming box (rows y0-4 .. y0-1; the top strip: -2 .. 1), 1 .. nreg = boxes from y0 on (covering at least one
     // row below the strip), then for the bottom strip one box at rows-2.  ybox(s) = first image row of stage s.
     const int nreg = bottom ? nout / P_R : (nout + 1 + P_R - 1) / P_R;
@@ -208,7 +209,8 @@ k5_post_tma_kernel(const abub_loc_job* __restrict__ jobs, const int* __restrict_
                         H[k] = ABUB_K5T_FMA ? (sl * one + W[k + 1]) + sr : sl + W[k + 1] + sr;
                         mx = __vmaxu2(mx, H[k]);
                     }
-                    if (out_lane && ((mx & 0xFFFFu) >= lim || (mx >> 16) >= lim)) {
+                    // some 16-bit sum of the lane reaches lim: relu(mx - (lim - 1)) per s16 lane, one VIADDMNMX (sums <= 2295)
+                    if (out_lane && __viaddmax_s16x2_relu(mx, nlim2, nlim2) != 0u) {
                         uint32_t ob[8];
 #pragma unroll
                         for (int k = 0; k < 4; k++) {
