@@ -21,14 +21,19 @@ ncu --profile-from-start off --clock-control none --csv --log-file $O/r2_step.cs
 ncu --profile-from-start off --clock-control none --csv --log-file $O/r2_step_full.csv \
     --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum \
     $B --profile-step --early-chunk 0 > $O/ncu_step_full.log 2>&1
-# --set full, one launch per kernel family, inside the profiled step
-for spec in "k1_trigger_tma:k1_early:0" "k5_post_tma:k5b:0" "k1_genesis|k5_genesis:k5a:0" "k7_trace2:k7b:0"; do
+# --set full, one launch per kernel family, inside the profiled step (ONLY="k5b k5a": just these tags)
+SPECS="k1_trigger_tma:k1_early:0 k5_post_tma:k5b:0 k5_genesis_tma:k5a:0 k7_trace2:k7b:0"
+for spec in $SPECS; do
     IFS=: read -r kern tag skip <<< "$spec"
+    if [ -n "${ONLY:-}" ] && ! echo " $ONLY " | grep -q " $tag "; then continue; fi
     ncu --profile-from-start off --set full --clock-control none --import-source on -k "regex:$kern" -s $skip -c 1 -o $O/r2_$tag -f \
         $B --profile-step > $O/ncu_$tag.log 2>&1
 done
+if [ -z "${ONLY:-}" ]; then
 ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:k1_trigger_tma -c 1 -o $O/r2_k1_full -f \
     $B --profile-step --early-chunk 0 > $O/ncu_k1_full.log 2>&1
+fi
+[ -n "${ONLY:-}" ] && { ls -la $O | tail -20; exit 0; }
 # Trainer kernels (K3, K4) and the stage numbers of tools/bench_stages.py
 python tools/bench_stages.py --events 32 --train-events 200 --reps 3 > $O/r2_stages.json 2> $O/r2_stages.err || echo "stages failed"
 for spec in "k4_welford16:k4" "k3_gate_batch:k3"; do
