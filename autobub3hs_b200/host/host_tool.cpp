@@ -4,6 +4,8 @@
 //   host_tool raw-events <run_dir/>                               RawParser::GetEventDirLists
 //   host_tool zip-list <run.zip> <event> <cam> | zip-events <run.zip> | zip-get <run.zip> <event> <frame> <out.raw>
 //   host_tool writer-selftest <out_dir/>         fixed bubble lists through OutputWriter (header + rows)
+#include "RankSync.hpp"
+#include <time.h>
 #include <chrono>
 #include <cstring>
 #include <cstdint>
@@ -43,6 +45,25 @@ int main(int argc, char** argv) {
     if (argc < 2) return 1;
     const std::string cmd = argv[1];
     try {
+        if (cmd == "rank-sync" && argc >= 7) {
+            /* rank-sync <base> <rank> <world> <start time or 0> <phase>=<status> ... : the status rendezvous of abub3hs
+             * --world N, one phase after the other; prints the agreed value of every phase */
+            RankSync rs;
+            rs.base = argv[2]; rs.rank = atoi(argv[3]); rs.world = atoi(argv[4]);
+            rs.t_start = atoll(argv[5]) ? atoll(argv[5]) : (long long)time(nullptr);
+            for (int i = 6; i < argc; i++) {
+                const std::string a = argv[i];
+                const size_t eq = a.find('=');
+                if (eq == std::string::npos) return 1;
+                const int got = rs.agree(a.substr(0, eq).c_str(), atoi(a.substr(eq + 1).c_str()));
+                printf("%s %d\n", a.substr(0, eq).c_str(), got);
+                fflush(stdout);
+                if (got < 0) break;
+            }
+            usleep(300000);
+            rs.forget(0);
+            return 0;
+        }
         if (cmd == "decode" && argc == 4) {
             std::vector<uint8_t> b;
             Image8 im;

@@ -163,3 +163,75 @@ def test_output_writer_matches_oracle(tool, tmp_path):
     exp = o.write_header() + o.write_camera_output("20210101_0", cams, 30)
     exp += o.write_camera_output("20210101_0", [o.CameraOutput(-7, 0, 4) for _ in range(4)], 30)
     assert text == exp
+
+
+def test_zip_parser_rejects_sizes_a_corrupt_directory_claims(tool, tmp_path):
+    """Entry sizes come from the archive's central directory; a corrupt one must end as "frame does not decode" (the
+    per-camera -9 / -6 row), not as a bad_alloc inside a parallel region.  The compressed / uncompressed sizes of one
+    entry are overwritten in the central directory with values far beyond the file: that frame reads as MISSING, its
+    neighbours still decode, and a directory whose own size field points outside the file throws -10 like an unreadable
+    archive (ZipParser.cpp:66-70)."""
+    import struct
+    run, names = _make_tree(tmp_path)
+    zp = str(tmp_path / "20210101_0.zip")
+    with zipfile.ZipFile(zp, "w", zipfile.ZIP_DEFLATED) as z:
+        for ev in (0, 2):
+            d = run / str(ev) / "Images"
+            for fn in sorted(os.listdir(d)):
+                z.write(str(d / fn), f"20210101_0/{ev}/Images/{fn}")
+    raw = bytearray(open(zp, "rb").read())
+    target = b"20210101_0/2/Images/cam1_image100.bmp"
+    pos, hits = 0, []
+    while True:
+        pos = raw.find(b"PK\x01\x02", pos)
+        if pos < 0:
+            break
+        nlen = struct.unpack_from("<H", raw, pos + 28)[0]
+        if bytes(raw[pos + 46:pos + 46 + nlen]) == target:
+            hits.append(pos)
+        pos += 4
+    assert len(hits) == 1
+    out = str(tmp_path / "z.raw")
+    for comp, uncomp in ((0xFFFFFFF0, 0x1000), (0x20, 0xFFFFFFF0)):       # compressed bytes past the file / a 4 GB frame
+        bad = bytearray(raw)
+        struct.pack_into("<II", bad, hits[0] + 20, comp, uncomp)
+        zb = str(tmp_path / "bad" / "20210101_0.zip")
+        os.makedirs(os.path.dirname(zb), exist_ok=True)
+        open(zb, "wb").write(bad)
+        r = subprocess.run([tool, "zip-get", zb, "2", "cam1_image100.bmp", out], capture_output=True, text=True)
+        assert r.returncode == 0 and r.stdout.strip() == "MISSING", (r.returncode, r.stdout, r.stderr[-300:])
+        r = subprocess.run([tool, "zip-get", zb, "2", "cam1_image31.bmp", out], capture_output=True, text=True)
+        assert r.stdout.split() == ["8", "12"]
+    eocd = raw.rfind(b"PK\x05\x06")
+    bad = bytearray(raw)
+    struct.pack_into("<I", bad, eocd + 12, 0x7FFFFFF0)                     # central directory "larger than the file"
+    open(zb, "wb").write(bad)
+    assert subprocess.run([tool, "zip-events", zb], capture_output=True, text=True).stdout.split()[-2:] == ["THROW", "-10"]
+
+
+def test_rank_status_rendezvous(tool, tmp_path):
+    """RankSync (host/RankSync.hpp), the status exchange `abub3hs --world N` makes before every phase that ends in a
+    collective: every rank sees the minimum status, a failing rank takes everybody out of the next phase, a rank that
+    never shows up costs a bounded wait instead of a hang, and leftovers of an earlier run are ignored."""
+    import time
+    base = str(tmp_path / ".abub3hs_run.status")
+
+    def launch(rank, world, phases, start=0, timeout="30"):
+        return subprocess.Popen([tool, "rank-sync", base, str(rank), str(world), str(start)] + phases, stdout=subprocess.PIPE, text=True,
+                                env=dict(os.environ, ABUB_RANK_TIMEOUT=timeout))
+
+    # all fine through two phases
+    ps = [launch(r, 3, ["context=0", "trained=0"]) for r in range(3)]
+    outs = [p.communicate(timeout=60)[0].split() for p in ps]
+    assert outs == [["context", "0", "trained", "0"]] * 3
+    assert not [f for f in os.listdir(tmp_path) if "status" in f]              # every rank removed its own files
+    # rank 1 fails in the first phase: everybody stops there
+    ps = [launch(r, 3, [f"context={-1 if r == 1 else 0}", "trained=0"]) for r in range(3)]
+    outs = [p.communicate(timeout=60)[0].split() for p in ps]
+    assert outs == [["context", "-1"]] * 3
+    # rank 2 never arrives: bounded wait, -1; a status file left by a run of an hour ago does not count as its arrival
+    open(base + ".context.2", "w").write(f"{int(time.time()) - 3600} 0\n")
+    t0 = time.time()
+    ps = [launch(r, 3, ["context=0", "trained=0"], timeout="2") for r in range(2)]
+    outs = [p.communicate(timeout=60)[0].split() for p in ps]
+    assert outs == [["context", "-1"]] * 2 and time.time() - t0 < 20
