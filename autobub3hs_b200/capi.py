@@ -30,7 +30,7 @@ EXPORTS = [
     "abub_set_bellows_template", "abub_bellows_track", "abub_bellows_map", "abub_localize_bellows",
     "abub_localize", "abub_localize_batch", "abub_localize_binary", "abub_process_frame",
     "abub_event_submit_range", "abub_launch_count", "abub_profile", "abub_profile_read",
-    "abub_gate_entropy_static", "abub_event_set_nframes_range",
+    "abub_gate_entropy_static", "abub_event_set_nframes_range", "abub_trigger_early_deferred", "abub_trigger_deferred_flush",
 ]
 
 
@@ -130,6 +130,8 @@ def load() -> C.CDLL:
     lib.abub_profile.argtypes = [vp, C.c_int]
     lib.abub_profile_read.argtypes = [vp, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
     lib.abub_event_set_nframes_range.argtypes = [vp, C.c_int, C.c_int, ip]
+    lib.abub_trigger_early_deferred.argtypes = [vp, C.c_int, C.c_int, C.c_int]
+    lib.abub_trigger_deferred_flush.argtypes = [vp]
     lib.abub_gate_entropy_static.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, C.c_char_p, C.c_int]
     for name in EXPORTS:
         fn = getattr(lib, name)
@@ -553,7 +555,7 @@ class Context:
 # ---------------------------------------------------------------------------------------
 HOST_LIB_PATH = os.path.join(_HERE, "host", "libabubhost.so")
 HOST_EXPORTS = ["abubhost_open", "abubhost_begin_run", "abubhost_recon", "abubhost_end_run", "abubhost_close", "abubhost_last_error",
-                "abubhost_drain", "abubhost_set_threads", "abubhost_stats"]
+                "abubhost_drain", "abubhost_set_threads", "abubhost_stats", "abubhost_recon_hint"]
 _hostlib = None
 
 
@@ -569,6 +571,7 @@ def load_host() -> C.CDLL:
     lib.abubhost_open.argtypes = [C.c_int] * 7 + [C.POINTER(C.c_void_p)]
     lib.abubhost_begin_run.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, ip]
     lib.abubhost_recon.argtypes = [C.c_int, C.c_int, ip, ip, C.c_int, C.c_int, C.POINTER(C.c_double)]
+    lib.abubhost_recon_hint.argtypes = [C.c_int, C.c_int, ip]
     lib.abubhost_end_run.argtypes = []
     lib.abubhost_drain.argtypes = []
     lib.abubhost_set_threads.argtypes = [C.c_int, C.c_int]
@@ -613,6 +616,12 @@ class HostRecon:
                                     self.stats)
         if rc != 0:
             raise AbubError("abubhost_recon: " + self.hl.abubhost_last_error().decode())
+
+    def recon_hint(self, slot_first: int, nslots: int, nframes) -> None:
+        """Announces the next recon call (resident form): its trigger search is queued inside the current call's localizer."""
+        nf = np.ascontiguousarray(nframes, dtype=np.int32).reshape(nslots * self.ncams)
+        if self.hl.abubhost_recon_hint(slot_first, nslots, nf.ctypes.data_as(C.POINTER(C.c_int))) != 0:
+            raise AbubError("abubhost_recon_hint: bad arguments")
 
     def set_threads(self, threads: int = 0, sub_batch: int = 32) -> None:
         """Host threads of the event loop (0 = OpenMP default) and events per device->host hand-over; call before begin_run."""

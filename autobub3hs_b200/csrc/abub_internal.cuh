@@ -75,6 +75,9 @@ struct abub_prof_state {
     long long calls[ABUB_PROF_N] = {0};
 };
 
+// a trigger search registered with abub_trigger_early_deferred (ctx.cu)
+struct abub_deferred_trigger { int first, n, chunk; int lo = -1, hi = 0, nf_max = 0; bool done = false; };
+
 struct abub_ctx {
     long long n_launches = 0;           // kernels of this library launched so far (ABUB_L at every launch site)
     abub_prof_state prof;
@@ -112,6 +115,7 @@ struct abub_ctx {
     int*      d_post_list = nullptr; // indices of the post-trigger jobs of a localizer chunk (k5_post_tma.cu)
     int*      h_post_list = nullptr; // its pinned staging copy; post_ev = the last upload from it
     cudaEvent_t post_ev = nullptr;
+    std::vector<abub_deferred_trigger> deferred;   // pending deferred trigger searches
     void*     fix_buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // grow-only scratch of the multi-GPU fix-up (nccl_glue.cu)
     size_t    fix_cap[6] = {0, 0, 0, 0, 0, 0};
     int*      d_gen_list = nullptr;  // the same for the genesis jobs (k5_genesis_tma.cu)
@@ -225,6 +229,7 @@ int abub_k5b_launch_tma(abub_ctx* ctx, const abub_loc_job* d_jobs, int njobs);
 const abub_loc_job* abub_loc_host_jobs(abub_ctx* ctx);      // host copy of the chunk's job table (k5_localize.cu)
 
 // K5-K7 (k5_localize.cu)
+int abub_run_deferred(abub_ctx* ctx, int phase);           // ctx.cu: launches pending deferred trigger searches (phase 0 / 1)
 int abub_loc_init(abub_ctx* ctx);
 void abub_loc_free(abub_ctx* ctx);
 int abub_loc_run_prepared(abub_ctx* ctx, const uint8_t* d_over, int tozero, abub_blob* out, int cap, int* n_out);

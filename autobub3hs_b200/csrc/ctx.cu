@@ -594,32 +594,84 @@ extern "C" int abub_trigger_stream(abub_ctx* ctx, int slot_first, int nslots, co
 // stops computing ProcessFrame at the trigger (AnalyzerUnit.cpp:297-300) and so does this call: K1 runs on
 // chunk_frames frame pairs at a time, K2 after every round, and a (slot,cam) whose search is decided drops out of the
 // following rounds.  No host round trip between the rounds: the per-camera frame limits are updated on the device.
-extern "C" int abub_trigger_early(abub_ctx* ctx, int slot_first, int nslots, int chunk_frames) {
-    if (!ctx) return ABUB_E_INVALID;
+// One search of abub_trigger_early, resumable between rounds: rounds are launched until the frame limit `upto` is reached
+// (or the search is through).  d.lo < 0 = not started.
+static int trigger_early_rounds(abub_ctx* ctx, abub_deferred_trigger& d, int upto) {
+    int rc;
+    if (d.lo < 0) {
+        d.nf_max = 0;
+        for (int s = d.first; s < d.first + d.n; s++) {
+            for (int c = 0; c < ctx->ncams; c++) d.nf_max = ctx->slots[s].nframes[c] > d.nf_max ? ctx->slots[s].nframes[c] : d.nf_max;
+            ctx->slots[s].hist_valid = false;                         // the tables stop where the searches stopped
+        }
+        if (d.nf_max == 0) { d.done = true; return abub_k2_launch(ctx, d.first, d.n); }      // status -9 everywhere
+        // nothing can be decided on fewer than 5 frames (candidate at i >= 2 plus two look-ahead frames)
+        d.lo = 0;
+        d.hi = d.chunk < 5 ? 5 : d.chunk;
+    }
+    while (!d.done && d.lo < upto) {
+        if (d.hi > d.nf_max) d.hi = d.nf_max;
+        const bool first = d.lo == 0;
+        if ((rc = abub_k2_next_avail(ctx, d.first, d.n, d.hi, first))) return rc;
+        if ((rc = abub_k1_launch_trigger_range(ctx, d.first, d.n, d.lo, d.hi, ctx->d_avail, first))) return rc;
+        if ((rc = abub_k2_launch_avail(ctx, d.first, d.n, ctx->d_avail))) return rc;
+        d.lo = d.hi;
+        d.hi += d.chunk;
+        if (d.lo >= d.nf_max) d.done = true;
+    }
+    return ABUB_OK;
+}
+
+static int trigger_early_check(abub_ctx* ctx, int slot_first, int nslots, int chunk_frames) {
     ABUB_REQUIRE(ctx, slot_first >= 0 && nslots >= 1 && slot_first + nslots <= ctx->max_slots, "slot range");
     ABUB_REQUIRE(ctx, chunk_frames >= 1, "chunk_frames");
-    int rc = require_backgrounds(ctx);
+    return require_backgrounds(ctx);
+}
+
+extern "C" int abub_trigger_early(abub_ctx* ctx, int slot_first, int nslots, int chunk_frames) {
+    if (!ctx) return ABUB_E_INVALID;
+    int rc = trigger_early_check(ctx, slot_first, nslots, chunk_frames);
     if (rc) return rc;
     cudaSetDevice(ctx->device);
-    int nf_max = 0;
-    for (int s = slot_first; s < slot_first + nslots; s++) {
-        for (int c = 0; c < ctx->ncams; c++) nf_max = ctx->slots[s].nframes[c] > nf_max ? ctx->slots[s].nframes[c] : nf_max;
-        ctx->slots[s].hist_valid = false;                         // the tables stop where the searches stopped
-    }
-    // nothing can be decided on fewer than 5 frames (candidate at i >= 2 plus two look-ahead frames)
-    int lo = 0, hi = chunk_frames < 5 ? 5 : chunk_frames;
-    bool first = true;
-    do {
-        if (hi > nf_max) hi = nf_max;
-        if ((rc = abub_k2_next_avail(ctx, slot_first, nslots, hi, first))) return rc;
-        if ((rc = abub_k1_launch_trigger_range(ctx, slot_first, nslots, lo, hi, ctx->d_avail, first))) return rc;
-        if ((rc = abub_k2_launch_avail(ctx, slot_first, nslots, ctx->d_avail))) return rc;
-        first = false;
-        lo = hi;
-        hi += chunk_frames;
-    } while (lo < nf_max);
-    if (nf_max == 0) return abub_k2_launch(ctx, slot_first, nslots);      // status -9 everywhere
+    abub_deferred_trigger d{slot_first, nslots, chunk_frames};
+    return trigger_early_rounds(ctx, d, 1 << 30);
+}
+
+// The same search, registered now and LAUNCHED by the next abub_localize_batch between its own stages (half of the rounds
+// once its front-end kernels are queued, the rest behind its last kernel): the host round trips of that localizer call and
+// whatever the caller does before it asks for these results are then covered by device work instead of an idle GPU.
+// abub_trigger_deferred_flush launches what is still pending (a caller that ends up not calling the localizer).
+extern "C" int abub_trigger_early_deferred(abub_ctx* ctx, int slot_first, int nslots, int chunk_frames) {
+    if (!ctx) return ABUB_E_INVALID;
+    int rc = trigger_early_check(ctx, slot_first, nslots, chunk_frames);
+    if (rc) return rc;
+    ctx->deferred.push_back(abub_deferred_trigger{slot_first, nslots, chunk_frames});
     return ABUB_OK;
+}
+
+// phase 0: rounds up to the middle of the longest event; phase 1: everything that is left
+int abub_run_deferred(abub_ctx* ctx, int phase) {
+    int rc = ABUB_OK;
+    for (abub_deferred_trigger& d : ctx->deferred) {
+        if (d.done) continue;
+        int upto = 1 << 30;
+        if (phase == 0) {
+            int nf = 0;
+            for (int s = d.first; s < d.first + d.n; s++)
+                for (int c = 0; c < ctx->ncams; c++) nf = ctx->slots[s].nframes[c] > nf ? ctx->slots[s].nframes[c] : nf;
+            upto = nf / 2;
+        }
+        const int r = trigger_early_rounds(ctx, d, upto);
+        if (r && !rc) rc = r;
+    }
+    if (phase != 0) ctx->deferred.clear();
+    return rc;
+}
+
+extern "C" int abub_trigger_deferred_flush(abub_ctx* ctx) {
+    if (!ctx) return ABUB_E_INVALID;
+    cudaSetDevice(ctx->device);
+    return abub_run_deferred(ctx, 1);
 }
 
 // ---- single-frame parity tap --------------------------------------------------------

@@ -61,6 +61,10 @@ struct LocArena {
     int* d_npf = nullptr;            // per job count of emitted blobs
     // parity tap of the last call
     int last_njobs = 0;
+    // pinned read-back words (counters[8], then the chain total as two ints) and the event the host waits on: waiting for an
+    // event instead of the stream lets work queued BEHIND the read-back (a deferred trigger search, ctx.cu) keep the GPU busy
+    int* h_ctr = nullptr;
+    cudaEvent_t ev = nullptr;
 };
 
 
@@ -596,6 +600,8 @@ int abub_loc_init(abub_ctx* ctx) {
     LocArena* a = new LocArena();
     ctx->loc = a;
     ABUB_CHECK_CUDA(ctx, cudaMalloc(&a->d_counters, 8 * sizeof(int)));
+    ABUB_CHECK_CUDA(ctx, cudaHostAlloc(&a->h_ctr, 16 * sizeof(int), cudaHostAllocDefault));
+    ABUB_CHECK_CUDA(ctx, cudaEventCreateWithFlags(&a->ev, cudaEventDisableTiming));
     return ABUB_OK;
 }
 
@@ -607,6 +613,8 @@ void abub_loc_free(abub_ctx* ctx) {
     cudaFree(a->d_scan); cudaFree(a->d_iscan); cudaFree(a->d_cub_tmp); cudaFree(a->d_chain);
     cudaFree(a->d_blobs); cudaFree(a->d_npf);
     free(a->h_jobs);
+    if (a->h_ctr) cudaFreeHost(a->h_ctr);
+    if (a->ev) cudaEventDestroy(a->ev);
     delete a;
     ctx->loc = nullptr;
 }
@@ -720,8 +728,12 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
         }
         }
         ABUB_CHECK_CUDA(ctx, cudaGetLastError());
-        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(counters, a->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
-        ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(st));
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(a->h_ctr, a->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
+        ABUB_CHECK_CUDA(ctx, cudaEventRecord(a->ev, st));
+        // the front-end kernels of this chunk are queued: the first half of a deferred trigger search goes behind them
+        if ((rc = abub_run_deferred(ctx, 0))) return rc;
+        ABUB_CHECK_CUDA(ctx, cudaEventSynchronize(a->ev));
+        memcpy(counters, a->h_ctr, sizeof(counters));
         if (counters[0] <= a->cand_cap) break;
         if ((rc = ensure_cands(ctx, a, counters[0] + counters[0] / 4 + 1024))) return rc;
     }
@@ -746,8 +758,10 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     tmpb = a->cub_tmp_bytes;
     cub::DeviceScan::ExclusiveSum(a->d_cub_tmp, tmpb, a->d_scan, a->d_scan, ncand + 1, st);
     long long total = 0;
-    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(&total, a->d_scan + ncand, sizeof(long long), cudaMemcpyDeviceToHost, st));
-    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(st));
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(a->h_ctr + 8, a->d_scan + ncand, sizeof(long long), cudaMemcpyDeviceToHost, st));
+    ABUB_CHECK_CUDA(ctx, cudaEventRecord(a->ev, st));
+    ABUB_CHECK_CUDA(ctx, cudaEventSynchronize(a->ev));
+    memcpy(&total, a->h_ctr + 8, sizeof(long long));
     if ((size_t)total + 64 > a->chain_cap) {
         const size_t want = (size_t)total + (size_t)total / 2 + (1 << 20);
         if ((rc = grow(ctx, &a->d_chain, want))) return rc;
@@ -771,14 +785,19 @@ static int run_chunk(abub_ctx* ctx, LocArena* a, int njobs, std::vector<abub_blo
     ABUB_L(ctx), k7_emit_kernel<<<nb, tb, 0, st>>>(ncand, a->d_cand, flags, pos, tmp, ordered, a->blob_cap, a->d_npf, a->d_counters);
     }
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
-    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(counters, a->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
-    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(npf_out.data(), a->d_npf, njobs * sizeof(int), cudaMemcpyDeviceToHost, st));
-    ABUB_CHECK_CUDA(ctx, cudaStreamSynchronize(st));
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(a->h_ctr, a->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
+    ABUB_CHECK_CUDA(ctx, cudaEventRecord(a->ev, st));
+    ABUB_CHECK_CUDA(ctx, cudaEventSynchronize(a->ev));
+    memcpy(counters, a->h_ctr, sizeof(counters));
     const int nblob = counters[2];
     const size_t base = blobs_out.size();
     blobs_out.resize(base + nblob);
+    // results leave on the stream BEFORE the rest of a deferred trigger search is queued behind them
+    ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(npf_out.data(), a->d_npf, njobs * sizeof(int), cudaMemcpyDeviceToHost, st));
     if (nblob)
-        ABUB_CHECK_CUDA(ctx, cudaMemcpy(blobs_out.data() + base, ordered, sizeof(abub_blob) * nblob, cudaMemcpyDeviceToHost));
+        ABUB_CHECK_CUDA(ctx, cudaMemcpyAsync(blobs_out.data() + base, ordered, sizeof(abub_blob) * nblob, cudaMemcpyDeviceToHost, st));
+    ABUB_CHECK_CUDA(ctx, cudaEventRecord(a->ev, st));
+    ABUB_CHECK_CUDA(ctx, cudaEventSynchronize(a->ev));
     return ABUB_OK;
 }
 
@@ -854,6 +873,9 @@ extern "C" int abub_localize_batch(abub_ctx* ctx, const abub_loc_item* items, in
         }
         blobs.clear();
         if ((rc = run_chunk(ctx, a, njobs, blobs, npf))) return rc;
+        // last chunk: its results are on the host; what is left of a deferred trigger search is queued now, so that the
+        // GPU works through the host-side tail of this call and the caller's next steps
+        if (i1 == n_items && (rc = abub_run_deferred(ctx, 1))) return rc;
         j = 0;
         for (int i = i0; i < i1; i++)
             for (int k = 0; k <= ABUB_MAX_TRACK; k++)

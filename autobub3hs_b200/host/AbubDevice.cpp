@@ -114,7 +114,13 @@ int AbubDevice::BindSlot(const std::string& key, int slot) {
         return slot;
     }
     if (slots_[slot].refs != 0) throw AbubError("BindSlot: slot " + std::to_string(slot) + " is in use");
+    // a trigger search started ahead of time for the frames this event is about to claim survives the reset
+    const bool pre = slots_[slot].trig_prelaunched;
+    int pre_nf[8];
+    for (int c = 0; c < 8; c++) pre_nf[c] = slots_[slot].pre_nframes[c];
     slots_[slot] = AbubSlot();
+    slots_[slot].trig_prelaunched = pre;
+    for (int c = 0; c < 8; c++) slots_[slot].pre_nframes[c] = pre_nf[c];
     slots_[slot].key = key;
     slots_[slot].refs = 1;
     by_key_[key] = slot;
@@ -353,6 +359,7 @@ void AbubDevice::MarkResident(int slot, const int* nframes, bool in_hbm, bool pu
         st.resident_upto[c] = in_hbm ? nframes[c] : 0;
         st.trig_valid[c] = st.loc_valid[c] = false;
     }
+    if (!in_hbm) st.trig_prelaunched = false;        // the frames come from the staging buffer: nothing started ahead counts
     if (in_hbm && push) Check(abub_event_set_nframes(ctx_, slot, nframes), "abub_event_set_nframes");
 }
 
@@ -373,12 +380,38 @@ void AbubDevice::EnsureAllResident(int slot) {
 }
 
 // FindTriggerFrame(startframe = 1) of every (event, camera) of the slots, then LocalizeOMatic of every triggered one.
-void AbubDevice::AnalyzeBatch(const std::vector<int>& out, const int* training_set_sizes) {
+// Registers the early-exit trigger search of slots [slot_first, slot_first + nslots) -- frames resident, `nframes` per camera --
+// to be launched inside the next localizer call.  False (nothing registered) when the full-table form is configured or a slot
+// is still held by an analyzer.
+bool AbubDevice::PrefetchTrigger(int slot_first, int nslots, const int* nframes) {
+    std::lock_guard<std::recursive_mutex> g(mu_);
+    if (!ctx_ || early_chunk_ <= 0 || slot_first < 0 || nslots < 1 || slot_first + nslots > max_slots_) return false;
+    {
+        std::lock_guard<std::mutex> t(tab_mu_);
+        for (int s = slot_first; s < slot_first + nslots; s++)
+            if (slots_[s].refs > 0) return false;
+    }
+    Check(abub_event_set_nframes_range(ctx_, slot_first, nslots, nframes), "abub_event_set_nframes_range");
+    Check(abub_trigger_early_deferred(ctx_, slot_first, nslots, early_chunk_), "abub_trigger_early_deferred");
+    for (int s = 0; s < nslots; s++) {
+        AbubSlot& st = slots_[slot_first + s];
+        st.trig_prelaunched = true;
+        for (int c = 0; c < ncams_; c++) st.pre_nframes[c] = nframes[(size_t)s * ncams_ + c];
+    }
+    return true;
+}
+
+void AbubDevice::AnalyzeBatch(const std::vector<int>& out, const int* training_set_sizes, int next_first, int next_n,
+                              const int* next_nframes) {
     std::lock_guard<std::recursive_mutex> g(mu_);
     if (!ctx_) return;
     std::vector<int> sorted(out);
     std::sort(sorted.begin(), sorted.end());
     const double h0 = wall_now();
+    // searches started ahead of time (PrefetchTrigger) must be launched in full before their results are read
+    bool any_pre = false;
+    for (int s : sorted) any_pre = any_pre || slots_[s].trig_prelaunched;
+    if (any_pre) Check(abub_trigger_deferred_flush(ctx_), "abub_trigger_deferred_flush");
     // The trigger search of a contiguous slot range.  Default: the resident early exit (abub_trigger_early) -- K1 over
     // early_chunk_ frame pairs at a time, K2 after every round, decided cameras drop out, as the reference stops calling
     // ProcessFrame at the trigger (AnalyzerUnit.cpp:297-300).  early_chunk_ = 0: the full table (one K1 launch over all
@@ -387,7 +420,15 @@ void AbubDevice::AnalyzeBatch(const std::vector<int>& out, const int* training_s
         size_t j = i + 1;
         while (j < sorted.size() && sorted[j] == sorted[j - 1] + 1) j++;
         const int first = sorted[i], ns = (int)(j - i);
-        if (early_chunk_ > 0) {
+        bool pre = true;
+        for (int s = first; s < first + ns; s++) {
+            pre = pre && slots_[s].trig_prelaunched;
+            for (int c = 0; c < ncams_ && pre; c++) pre = slots_[s].pre_nframes[c] == slots_[s].nframes[c];
+        }
+        for (int s = first; s < first + ns; s++) slots_[s].trig_prelaunched = false;
+        if (pre) {
+            // started inside the previous batch's localizer call: nothing to launch
+        } else if (early_chunk_ > 0) {
             Check(abub_trigger_early(ctx_, first, ns, early_chunk_), "abub_trigger_early");
         } else {
             Check(abub_trigger_hist(ctx_, first, ns), "abub_trigger_hist");
@@ -417,7 +458,9 @@ void AbubDevice::AnalyzeBatch(const std::vector<int>& out, const int* training_s
     }
     const double h2 = wall_now();
     t_scan += h2 - h1;
+    if (next_first >= 0 && next_n > 0 && next_nframes) PrefetchTrigger(next_first, next_n, next_nframes);
     if (training_set_sizes) LocalizeBatch(out, training_set_sizes);
+    Check(abub_trigger_deferred_flush(ctx_), "abub_trigger_deferred_flush");     // no-op when the localizer call launched it
     t_loc += wall_now() - h2;
 }
 

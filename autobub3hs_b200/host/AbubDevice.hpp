@@ -47,6 +47,9 @@ struct AbubSlot {
     int loc_trig[8] = {0}, loc_pre[8] = {0}, loc_thres[8] = {0}, loc_npost[8] = {0};
     int loc_npf[8][ABUB_MAX_TRACK + 1] = {{0}};
     std::vector<abub_blob> loc_blobs[8];
+    // the trigger search of this slot's CURRENT frames was started ahead of time (AbubDevice::PrefetchTrigger) for these counts
+    bool trig_prelaunched = false;
+    int pre_nframes[8] = {0};
 };
 
 class AbubDevice {
@@ -93,7 +96,12 @@ public:
 
     // The device work of a batch whose frames are resident: FindTriggerFrame(1) of every (event, camera), LocalizeOMatic
     // of every triggered one (when training_set_sizes is given); results land in the slots' caches.
-    void AnalyzeBatch(const std::vector<int>& slots, const int* training_set_sizes);
+    // next_first / next_n / next_nframes (optional): the slots of the batch that will be analysed after this one, frames already
+    // in HBM: their trigger search is queued inside this batch's localizer call (abub_trigger_early_deferred), so the GPU has
+    // work while the host goes through the localizer's round trips and the bookkeeping between two batches
+    void AnalyzeBatch(const std::vector<int>& slots, const int* training_set_sizes, int next_first = -1, int next_n = 0,
+                      const int* next_nframes = nullptr);
+    bool PrefetchTrigger(int slot_first, int nslots, const int* nframes);
     // Same for slots whose frames wait in the pinned staging buffers: frames cross PCIe chunk_frames at a time and only as
     // far as the search and the localizer need them.  Returns the number of frames sent.
     long long StreamBatch(const std::vector<int>& slots, const int* training_set_sizes, int chunk_frames);

@@ -209,6 +209,8 @@ struct HostRun {
     DetectPipeline pipe;
     int sub_batch = 32;
     double base[5] = {0, 0, 0, 0, 0};           // counters at the last abubhost_stats call
+    int hint_first = -1, hint_n = 0;            // abubhost_recon_hint: the slots of the next call ...
+    std::vector<int> hint_nframes;              // ... and their frame counts
 } g;
 int g_threads = 0;
 }  // namespace
@@ -310,8 +312,22 @@ int abubhost_recon(int slot_first, int nslots, const int* event_numbers, const i
                 slots.push_back(slot_first + s);
             }
             if (mode == 0) dev.PushFrameCounts(slot_first + s0, s1 - s0, nframes + (size_t)s0 * nc);   /* one launch, not one per slot */
-            if (mode == 0) dev.AnalyzeBatch(slots, tss.data());
-            else sent += dev.StreamBatch(slots, tss.data(), chunk_frames);
+            if (mode == 0) {
+                /* what the device will be asked for next -- the following sub-batch of this call, or the batch announced
+                 * with abubhost_recon_hint -- has its trigger search queued inside this sub-batch's localizer call */
+                if (s1 < nslots) {
+                    const int n1 = (s1 + sub < nslots ? s1 + sub : nslots) - s1;
+                    dev.AnalyzeBatch(slots, tss.data(), slot_first + s1, n1, nframes + (size_t)s1 * nc);
+                } else if (g.hint_first >= 0 && (int)g.hint_nframes.size() == g.hint_n * nc) {
+                    const int hf = g.hint_first, hn = g.hint_n;
+                    g.hint_first = -1;
+                    dev.AnalyzeBatch(slots, tss.data(), hf, hn, g.hint_nframes.data());
+                } else {
+                    dev.AnalyzeBatch(slots, tss.data());
+                }
+            } else {
+                sent += dev.StreamBatch(slots, tss.data(), chunk_frames);
+            }
             g.pipe.submit(std::move(chunk), std::move(keys));
         }
         if (stats) stats[5] += (double)sent;
@@ -321,6 +337,19 @@ int abubhost_recon(int slot_first, int nslots, const int* event_numbers, const i
         g.err = e.what();
         return -1;
     }
+}
+
+/* Optional: the NEXT abubhost_recon call (mode 0) will be for exactly these slots with these frame counts, and their frames
+ * are already in HBM.  The current call then queues that batch's trigger search inside its own localizer call
+ * (abub_trigger_early_deferred), and the next call finds it running or done.  A hint that does not come true costs one
+ * trigger search; a next call that differs from the hint simply starts its own. */
+int abubhost_recon_hint(int slot_first, int nslots, const int* nframes) {
+    const int nc = g.run.numCams;
+    if (slot_first < 0 || nslots < 1 || !nframes || nc < 1) { g.hint_first = -1; return -1; }
+    g.hint_first = slot_first;
+    g.hint_n = nslots;
+    g.hint_nframes.assign(nframes, nframes + (size_t)nslots * nc);
+    return 0;
 }
 
 /* Waits until every submitted event has been analysed and its rows are in the file. */

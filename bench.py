@@ -407,6 +407,11 @@ def run_ours(args, rank, world, local_rank):
         numbers = [base_no + step_no[0] * B + s for s in range(B)]
         first = (step_no[0] % SETS) * B
         step_no[0] += 1
+        if SETS > 1 and not args.no_hint:
+            # the set the NEXT step works on: its trigger search is queued inside this step's localizer call, so the GPU has work
+            # during the localizer's host round trips and between two steps (every timed step launches exactly one such
+            # search -- the next step's -- and finds its own already launched by the step before)
+            hr.recon_hint((step_no[0] % SETS) * B, B, nf_all)
         hr.recon(first, numbers, nf_all)
 
     for _ in range(max(args.warmup, 0)):
@@ -773,6 +778,7 @@ def main():
     ap.add_argument("--trigger-steps", type=int, default=8, help="steps of the trigger-only extra (0 = skip)")
     ap.add_argument("--trainer-events", type=int, default=200, help="training events of the sharded Trainer leg at N > 1 (0 = skip)")
     ap.add_argument("--ref-binary-events", type=int, default=8, help="--impl reference: events the compiled reference binary runs from BMP files (0 = skip)")
+    ap.add_argument("--no-hint", action="store_true", help="do not announce the next step's slots (abubhost_recon_hint)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-step", action="store_true", help="run one extra step between cudaProfilerStart/Stop (for ncu --profile-from-start off)")
     args = ap.parse_args()

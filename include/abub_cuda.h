@@ -157,6 +157,15 @@ int abub_trigger_stream(abub_ctx* ctx, int slot_first, int nslots, const int* nf
  * frames that were evaluated).  The histogram tables of the range are left partial: abub_trigger / abub_trigger_hist
  * rebuild them when a later call needs them (a re-trigger from start_frame > 1). */
 int abub_trigger_early(abub_ctx* ctx, int slot_first, int nslots, int chunk_frames);
+/* The same search for ANOTHER slot range, registered now and launched by the next abub_localize_batch between its own
+ * stages (half of the rounds once its front-end kernels are queued, the rest behind its last kernel), on the same
+ * stream: the localizer's host round trips, and whatever the caller does before it asks for these results, are covered by
+ * device work instead of an idle GPU.  The frame counts of the range must be set before this call and its frames must be
+ * resident before the localizer call.  abub_trigger_deferred_flush launches whatever is still pending (for a caller that
+ * ends up not calling the localizer); abub_trigger_results then reads the results as after abub_trigger_early.
+ * (The reference has one thread per event and no such overlap; AutoBubStart3.cpp:342.) */
+int abub_trigger_early_deferred(abub_ctx* ctx, int slot_first, int nslots, int chunk_frames);
+int abub_trigger_deferred_flush(abub_ctx* ctx);
 
 /* ---- training: Trainer::MakeAvgSigmaImage (Trainer.cpp:221-331) ----------------- */
 int abub_train_begin(abub_ctx* ctx, int cam);

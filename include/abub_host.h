@@ -46,6 +46,12 @@ int abubhost_begin_run(const char* run_id, const char* out_dir, const char* mask
 int abubhost_recon(int slot_first, int nslots, const int* event_numbers, const int* nframes, int mode, int chunk_frames,
                    double* stats);
 
+/* Optional.  Announces the NEXT abubhost_recon call (mode 0): exactly these slots, these frame counts, frames already in
+ * HBM.  The current call then queues that batch's trigger search inside its own localizer call, so that the GPU has work
+ * during the localizer's host round trips and the bookkeeping between two calls (a caller that alternates between two sets
+ * of slots announces the other set before each call).  A hint that does not come true costs one trigger search. */
+int abubhost_recon_hint(int slot_first, int nslots, const int* nframes);
+
 /* abubhost_recon returns once the device work of its events is done; the per-camera objects of the last sub-batch may
  * still be running on the host cores (they overlap the device work of the next call).  abubhost_drain returns when
  * every submitted event has been analysed and its rows are in the file. */

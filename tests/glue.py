@@ -118,7 +118,7 @@ def gpu_any_cam_analysis(ctx, slot, cam, nframes, tss, cam_mask, bellows_mask, e
         return o.CameraOutput(-6, 0, event_number)
 
 
-def host_recon_text(run, trained, tmp_path, tag, pinned, early_chunk, batch=None):
+def host_recon_text(run, trained, tmp_path, tag, pinned, early_chunk, batch=None, sub_batch=None, hint=False):
     """Trains on the resident events through the C ABI, then runs the full recon through libabubhost.so."""
     import os
     from autobub3hs_b200 import capi, synth
@@ -158,10 +158,16 @@ def host_recon_text(run, trained, tmp_path, tag, pinned, early_chunk, batch=None
                 # what is in HBM must not help: poison the slot so that only frames really sent can be used
                 for c in range(4):
                     ctx.event_upload(ev, c, np.full_like(run.events[ev][c], 77))
+        if sub_batch:
+            hr.set_threads(0, sub_batch)       # several sub-batches per call: the next one's trigger search is queued ahead
         path = hr.begin_run(run.run_id, out_dir, mask_dir, 30, tss)
         b = batch or nev
         for e0 in range(0, nev, b):
             e1 = min(nev, e0 + b)
+            if hint and e1 < nev:              # announce the next call's slots (abubhost_recon_hint)
+                e2 = min(nev, e1 + b)
+                # hint == "wrong": the announcement names fewer frames than the call will bring -- the call must not use it
+                hr.recon_hint(e1, e2 - e1, nframes[e1:e2] if hint is True else np.maximum(nframes[e1:e2] - 7, 0))
             hr.recon(e0, run.event_numbers[e0:e1], nframes[e0:e1], pinned=pinned, chunk_frames=4)
         hr.drain()
         stats = hr.read_stats()

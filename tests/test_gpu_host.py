@@ -268,6 +268,12 @@ def test_host_library_recon_in_memory(small_run, small_trained, tmp_path, pinned
     for batch, early in ((None, 6), (3, 0), (1, 4)):
         text, stats = glue.host_recon_text(run, trained, tmp_path, f"b{batch}e{early}", pinned=pinned, early_chunk=early, batch=batch)
         assert text == want, (batch, early)
+    # trigger searches queued ahead of time (abub_trigger_early_deferred): the next sub-batch of a call, the announced
+    # next call (abubhost_recon_hint), and a hint that is wrong about the next call
+    for tag, kw in (("sub3", dict(sub_batch=3)), ("hint3", dict(batch=3, hint=True)), ("hint2sub1", dict(batch=2, sub_batch=1, hint=True)),
+                    ("wronghint", dict(batch=3, hint="wrong"))):
+        text, stats = glue.host_recon_text(run, trained, tmp_path, tag, pinned=pinned, early_chunk=5, **kw)
+        assert text == want, tag
 
 
 def test_host_library_recon_bellows_and_tma_pitch(tma_run, tmp_path):
