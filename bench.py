@@ -5,7 +5,9 @@ Workload = BASELINE.json configs[3]: "full recon run (trigger + L3Localizer + CC
 events ... with PICOFormatWriterV4 output", 4 cameras x 40 frames of 1050x1680 8-bit frames per event.  10,000
 distinct events are 2.8 TB, so a RING of `--ring-events` (32) distinct synthetic events is rendered
 once on the host (numpy PCG64, autobub3hs_b200.synth -- the same pixels in both arms) and reused: the `--events-per-step`
-(125) HBM slots of a rank hold ring event (slot % ring); 10,000 events = 80 steps, the default run times 20 of them.
+(125) HBM slots of a set hold ring event (slot % ring), two such sets are used in turn (--slot-sets), and each step
+announces the other set so that its trigger search is queued inside the current step's localizer call
+(abubhost_recon_hint); 10,000 events = 80 steps, the default run times 20 of them.
 
 One *step* = the whole reference event loop (AutoBubStart3.cpp:342-388) over the resident slots through the host
 library (libabubhost.so = the abub3hs detect loop): K1+K2 trigger search with the reference's early exit, K5-K7
@@ -18,14 +20,16 @@ appended to abub3hs_<run>.txt and flushed per event.  Every step re-reads 35 GB 
                only as far as the trigger search and the localizer read), results and blob records come back
   roofline     dominant kernel (K1) + `kernels`: device time per kernel group (CUDA events on the library stream)
                against the algorithmic bytes of SURVEY.md 8(d) and MEASURED_PEAKS.json hbm_gbs
-  cpu_baseline the cv2 oracle (a port: the reference needs OpenCV C++/Boost, absent here) on a bounded sample of the
-               same ring, every host core busy; its output text is the parity check of the GPU's text
+  cpu_baseline the cv2 oracle (a port; the reference's own sources compiled against API stand-ins, oracle/_ref, are much
+               slower and are timed from files in the reference arm) on a bounded sample of the same ring, every host core
+               busy; its output text is the parity check of the GPU's text
   trainer      (N > 1) BASELINE.json configs[2]: 200 training events sharded over the ranks, exact integer partials,
                ncclAllReduce + all-gather fix-up (abub_train_allreduce / abub_train_finish_allreduced), planes compared
                bit for bit with the single-GPU Trainer
   trigger_only BASELINE.json configs[1] as a named extra (K1 full table + K2, round-1 headline)
 
-`--impl reference` times the CPU oracle alone (all host cores) on the same workload.
+`--impl reference` times the CPU oracle alone (all host cores) on the same workload, plus oracle/_ref/abub3hs_ref from
+BMP files (reference_binary_from_files).
 """
 from __future__ import annotations
 
