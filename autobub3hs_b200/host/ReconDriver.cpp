@@ -292,6 +292,7 @@ int abubhost_recon(int slot_first, int nslots, const int* event_numbers, const i
         std::vector<int> tss;
         for (int c = 0; c < nc; c++) tss.push_back(g.trainers[c]->TrainingSetSize);
         long long sent = 0;
+        if (mode != 0) g.hint_first = -1;          /* an announcement only holds for a resident-form call that follows it directly */
         /* sub-batches: while the per-camera objects of one run on the host cores (DetectPipeline), the device works on the next */
         const int sub = g.sub_batch > 0 ? g.sub_batch : nslots;
         for (int s0 = 0; s0 < nslots; s0 += sub) {
@@ -390,6 +391,7 @@ int abubhost_end_run() {
         rc = -1;
     }
     if (g.out.is_open()) g.out.close();
+    g.hint_first = -1;
     return rc;
 }
 
