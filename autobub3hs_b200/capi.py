@@ -30,7 +30,7 @@ EXPORTS = [
     "abub_set_bellows_template", "abub_bellows_track", "abub_bellows_map", "abub_localize_bellows",
     "abub_localize", "abub_localize_batch", "abub_localize_binary", "abub_process_frame",
     "abub_event_submit_range", "abub_launch_count", "abub_profile", "abub_profile_read",
-    "abub_gate_entropy_static", "abub_event_set_nframes_range", "abub_trigger_early_deferred", "abub_trigger_deferred_flush",
+    "abub_gate_entropy_static", "abub_event_set_nframes_range", "abub_trigger_early_deferred", "abub_trigger_deferred_flush", "abub_trigger_deferred_start",
 ]
 
 
@@ -132,6 +132,7 @@ def load() -> C.CDLL:
     lib.abub_event_set_nframes_range.argtypes = [vp, C.c_int, C.c_int, ip]
     lib.abub_trigger_early_deferred.argtypes = [vp, C.c_int, C.c_int, C.c_int]
     lib.abub_trigger_deferred_flush.argtypes = [vp]
+    lib.abub_trigger_deferred_start.argtypes = [vp]
     lib.abub_gate_entropy_static.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, C.c_char_p, C.c_int]
     for name in EXPORTS:
         fn = getattr(lib, name)

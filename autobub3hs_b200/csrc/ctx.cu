@@ -649,13 +649,16 @@ extern "C" int abub_trigger_early_deferred(abub_ctx* ctx, int slot_first, int ns
     return ABUB_OK;
 }
 
-// phase 0: rounds up to the middle of the longest event; phase 1: everything that is left
+// phase -1: the first round only (abub_trigger_deferred_start); phase 0: rounds up to the middle of the longest event;
+// phase 1: everything that is left
 int abub_run_deferred(abub_ctx* ctx, int phase) {
     int rc = ABUB_OK;
     for (abub_deferred_trigger& d : ctx->deferred) {
         if (d.done) continue;
         int upto = 1 << 30;
-        if (phase == 0) {
+        if (phase < 0) {
+            upto = 1;                                                    // rounds run while lo < upto: exactly the first
+        } else if (phase == 0) {
             int nf = 0;
             for (int s = d.first; s < d.first + d.n; s++)
                 for (int c = 0; c < ctx->ncams; c++) nf = ctx->slots[s].nframes[c] > nf ? ctx->slots[s].nframes[c] : nf;
@@ -664,8 +667,16 @@ int abub_run_deferred(abub_ctx* ctx, int phase) {
         const int r = trigger_early_rounds(ctx, d, upto);
         if (r && !rc) rc = r;
     }
-    if (phase != 0) ctx->deferred.clear();
+    if (phase > 0) ctx->deferred.clear();
     return rc;
+}
+
+// Launches the first round of every registered search at once: device work for the time the caller spends preparing its
+// localizer call (item and job tables).
+extern "C" int abub_trigger_deferred_start(abub_ctx* ctx) {
+    if (!ctx) return ABUB_E_INVALID;
+    cudaSetDevice(ctx->device);
+    return abub_run_deferred(ctx, -1);
 }
 
 extern "C" int abub_trigger_deferred_flush(abub_ctx* ctx) {

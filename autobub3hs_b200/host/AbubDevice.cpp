@@ -458,7 +458,10 @@ void AbubDevice::AnalyzeBatch(const std::vector<int>& out, const int* training_s
     }
     const double h2 = wall_now();
     t_scan += h2 - h1;
-    if (next_first >= 0 && next_n > 0 && next_nframes) PrefetchTrigger(next_first, next_n, next_nframes);
+    // the next batch's search: registered, its first round launched now (device work while the item and job tables of this
+    // batch's localizer call are built), the rest by the localizer call itself
+    if (next_first >= 0 && next_n > 0 && next_nframes && PrefetchTrigger(next_first, next_n, next_nframes))
+        Check(abub_trigger_deferred_start(ctx_), "abub_trigger_deferred_start");
     if (training_set_sizes) LocalizeBatch(out, training_set_sizes);
     Check(abub_trigger_deferred_flush(ctx_), "abub_trigger_deferred_flush");     // no-op when the localizer call launched it
     t_loc += wall_now() - h2;

@@ -195,6 +195,36 @@ class CpuRecon:
             self.pool = None
 
 
+def check_timed_rows(out_path, cpu_text, B, R, base_no):
+    """Every row the warm-up and timed steps wrote, against the oracle's rows: the event with number base_no + step*B + s was
+    read from slot s of a set = ring event s % R, and the oracle's sample event i (i < R) is ring event i -- so apart from
+    the event number a step's rows must be the oracle's rows of that ring event, in order.  Returns (events, rows) checked."""
+    exp = {}
+    for line in cpu_text.splitlines():
+        p = line.split(None, 2)
+        if len(p) == 3 and int(p[1]) < R:
+            exp.setdefault(int(p[1]), []).append(p[2])
+    got, order = {}, []
+    with open(out_path) as f:
+        for k, line in enumerate(f):
+            if k < 6:
+                continue
+            p = line.rstrip("\n").split(None, 2)
+            ev = int(p[1])
+            if ev not in got:
+                got[ev] = []
+                order.append(ev)
+            got[ev].append(p[2])
+    if order != sorted(order):
+        raise SystemExit("PARITY FAILURE: the rows of the timed steps are not in event order")
+    for ev in order:
+        ring = ((ev - base_no) % B) % R
+        if ring in exp and got[ev] != exp[ring]:
+            raise SystemExit(f"PARITY FAILURE: rows of timed event {ev} (ring event {ring}) differ from the oracle's: "
+                             f"{got[ev][:1]} != {exp[ring][:1]} ({len(got[ev])} vs {len(exp[ring])} rows)")
+    return len(order), sum(len(v) for v in got.values())
+
+
 def cpu_sample_size(cores, ring):
     """>= 2 events (8 tasks) per worker, at least the whole ring (the arm must not be starved)."""
     return max(ring, 2 * cores)
@@ -467,6 +497,10 @@ def run_ours(args, rank, world, local_rank):
             bad = next((i for i, (a, b) in enumerate(zip(gl, wl)) if a != b), min(len(gl), len(wl)))
             raise SystemExit(f"PARITY FAILURE: abub3hs text differs from the oracle's at line {bad}: {gl[bad:bad+1]} != {wl[bad:bad+1]}")
         parity = {"events": n_s, "rows": len(want.splitlines()) - 6, "text_identical": True}
+        # ... and every row of the warm-up and timed steps themselves (the path with the trigger searches queued ahead)
+        ev_chk, rows_chk = check_timed_rows(out_path, cpu_text, B, R, base_no)
+        parity["timed_steps_events_checked"] = ev_chk
+        parity["timed_steps_rows_checked"] = rows_chk
         cpu["sample"] += f"; GPU output text of the same {n_s} events identical ({parity['rows']} rows)"
         hr.begin_run(RUN_ID, out_dir, mask_dir, 30, tss)
     hr.read_stats()

@@ -166,6 +166,8 @@ int abub_trigger_early(abub_ctx* ctx, int slot_first, int nslots, int chunk_fram
  * (The reference has one thread per event and no such overlap; AutoBubStart3.cpp:342.) */
 int abub_trigger_early_deferred(abub_ctx* ctx, int slot_first, int nslots, int chunk_frames);
 int abub_trigger_deferred_flush(abub_ctx* ctx);
+/* Launches the FIRST round of every registered search right away (device work while the caller prepares its localizer call). */
+int abub_trigger_deferred_start(abub_ctx* ctx);
 
 /* ---- training: Trainer::MakeAvgSigmaImage (Trainer.cpp:221-331) ----------------- */
 int abub_train_begin(abub_ctx* ctx, int cam);
