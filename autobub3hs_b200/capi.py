@@ -414,6 +414,16 @@ class Context:
                  "abub_trigger_stream")
         return tuple(out)
 
+    def trigger_early_deferred(self, slot_first: int, nslots: int, chunk_frames: int = 6) -> None:
+        """Registers the same search for another slot range; the next localize_batch launches it between its stages."""
+        self._ck(self.lib.abub_trigger_early_deferred(self.h, slot_first, nslots, chunk_frames), "abub_trigger_early_deferred")
+
+    def trigger_deferred_start(self) -> None:
+        self._ck(self.lib.abub_trigger_deferred_start(self.h), "abub_trigger_deferred_start")
+
+    def trigger_deferred_flush(self) -> None:
+        self._ck(self.lib.abub_trigger_deferred_flush(self.h), "abub_trigger_deferred_flush")
+
     def trigger_early(self, slot_first: int, nslots: int, chunk_frames: int = 6) -> None:
         """Resident FindTriggerFrame with the reference's early exit (K1 in rounds of chunk_frames frame pairs, decided
         cameras drop out); asynchronous, results through trigger_results."""

@@ -273,6 +273,63 @@ def test_set_nframes_range_equals_per_slot_calls(capi, small_run, small_trained)
             ctx.event_set_nframes_range(nev - 1, cut[:2])                       # runs past the last slot
 
 
+@pytest.mark.parametrize("start_now", [False, True])
+def test_trigger_early_deferred_equals_direct(capi, small_run, small_trained, start_now):
+    """abub_trigger_early_deferred: the search of a SECOND slot range is registered, launched by the localizer call of the
+    first range between its own stages (optionally its first round at once, abub_trigger_deferred_start), and gives what
+    abub_trigger_early gives when called directly; so does a registration that is only flushed (no localizer call), and
+    the localizer's own results are not disturbed by the launches in its middle."""
+    from tests import glue
+    run, trained = small_run, small_trained
+    rows, cols = run.cam_masks[0].shape
+    nev = len(run.events)
+    half = nev // 2
+
+    def same(got, want, lo, hi):
+        t, s, l, sg = got
+        tw, sw, lw, sgw = (a[lo:hi] for a in want)
+        assert np.array_equal(s, sw)
+        ok = sw == 0
+        assert np.array_equal(t[ok], tw[ok])
+        live = sw != -9
+        assert np.array_equal(l[live], lw[live])
+        for e in range(hi - lo):
+            for c in range(4):
+                upto = tw[e, c] + 1 if sw[e, c] == 0 else (len(run.events[lo + e][c]) if sw[e, c] == -3 else 0)
+                assert np.array_equal(sg[e, c, :upto], sgw[e, c, :upto], equal_nan=True), (e, c)
+
+    with capi.Context(rows, cols, ncams=4, max_frames=40, max_slots=nev) as ctx:
+        for c in range(4):
+            ctx.set_background(c, trained[c].avg, trained[c].sigma, trained[c].training_set_size)
+        for ev in range(nev):
+            for c in range(4):
+                ctx.event_upload(ev, c, run.events[ev][c])
+        ctx.trigger_early(0, nev, 5)
+        want = ctx.trigger_results(0, nev)
+        tw, sw, lw, _ = want
+        items = [(ev, c, int(tw[ev, c]), max(0, int(tw[ev, c]) - 2), int(lw[ev, c]), glue.n_post_frames(int(tw[ev, c]), len(run.events[ev][c])))
+                 for ev in range(half) for c in range(4) if sw[ev, c] == 0]
+        assert items
+        ref_blobs = ctx.localize_batch(items)
+        # first range searched directly, second range registered and launched inside the first range's localizer call
+        ctx.trigger_early(0, half, 5)
+        same(ctx.trigger_results(0, half), want, 0, half)
+        ctx.trigger_early_deferred(half, nev - half, 5)
+        if start_now:
+            ctx.trigger_deferred_start()
+        blobs = ctx.localize_batch(items)
+        ctx.trigger_deferred_flush()                                   # nothing left to launch
+        same(ctx.trigger_results(half, nev - half), want, half, nev)
+        assert [[[(b.x, b.y, b.w, b.h, b.npts, b.area) for b in fr] for fr in it] for it in blobs] == \
+               [[[(b.x, b.y, b.w, b.h, b.npts, b.area) for b in fr] for fr in it] for it in ref_blobs]
+        # a registration that never meets a localizer call: the flush launches all of it
+        ctx.trigger_early_deferred(0, nev, 6)
+        if start_now:
+            ctx.trigger_deferred_start()
+        ctx.trigger_deferred_flush()
+        same(ctx.trigger_results(0, nev), want, 0, nev)
+
+
 @pytest.mark.parametrize("chunk", [1, 4, 6, 40])
 def test_trigger_early_equals_batch(capi, small_run, small_trained, chunk):
     """abub_trigger_early (resident frames, K1 in rounds of `chunk` frame pairs, decided cameras drop out of the later
