@@ -3,6 +3,9 @@
 import ctypes
 import os
 import re
+import subprocess
+
+import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -38,3 +41,25 @@ def test_host_library_exports_every_declared_symbol():
     assert declared == set(capi.HOST_EXPORTS)
     for name in sorted(declared):
         assert hasattr(hl, name), f"{name} declared in abub_host.h but not exported"
+
+
+def test_tma_kernels_issue_tma_and_packed_simd_instructions():
+    """The three TMA-fed kernels really are: their sm_100a SASS holds UTMALDG (cp.async.bulk.tensor), SYNCS (mbarrier) and
+    the VIADDMNMX stage A; no cp.async (LDGSTS) fallback hides in them.  cuobjdump reads the objects build() just compiled."""
+    import shutil
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    from autobub3hs_b200 import build
+    build.build()
+    csrc = os.path.join(ROOT, "autobub3hs_b200", "csrc")
+    for obj, kernel in (("k1_trigger_tma.o", "k1_trigger_tma_kernel"), ("k5_post_tma.o", "k5_post_tma_kernel"),
+                        ("k5_genesis_tma.o", "k5_genesis_tma_kernel")):
+        txt = subprocess.run(["cuobjdump", "-sass", os.path.join(csrc, obj)], capture_output=True, text=True, check=True).stdout
+        assert "arch = sm_100a" in txt
+        body = txt[txt.index(kernel):]
+        nxt = body.find("Function :", 10)
+        body = body[:nxt] if nxt > 0 else body
+        ops = re.findall(r"^\s+/\*[0-9a-f]{4,}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_]+)", body, re.M)
+        assert ops.count("UTMALDG") >= 6, (kernel, ops.count("UTMALDG"))         # 3 planes x (prologue + re-arm)
+        assert ops.count("SYNCS") >= 4 and ops.count("VIADDMNMX") >= 8, kernel
+        assert "LDGSTS" not in ops, kernel
