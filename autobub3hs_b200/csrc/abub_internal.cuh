@@ -98,6 +98,7 @@ struct abub_ctx {
     int*      d_avail = nullptr;    // [slot][cam] frames resident so far (abub_trigger_stream)
     int*      d_trig = nullptr;     // [slot][cam] x {trig,status,loc_thres,scanned}
     double*   d_sig = nullptr;      // [slot][cam][frame]
+    void*     d_k2_state = nullptr; // [slot][cam] K2State: searches of abub_trigger_early that wait for the next round (k2_trigger_scan.cu)
     int       trig_metric = 0;      // ABUB_METRIC_* used by K2 (abub_set_trigger_metric)
     float     trig_thr = 3.5f;      // entropyThreshold before the TrainingSetSize < 6 scaling (AnalyzerUnit.cpp:140-142)
     int*      d_tss = nullptr;      // [cam] TrainingSetSize
@@ -187,7 +188,7 @@ int abub_k1_launch_trigger_tma(abub_ctx* ctx, int slot_first, int nslots, int j_
 int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots);
 // streamed form: d_avail[slot*ncams+cam] frames are resident; a search that needs a frame beyond them reports
 // ABUB_STATUS_PENDING
-int abub_k2_launch_avail(abub_ctx* ctx, int slot_first, int nslots, const int* d_avail);
+int abub_k2_launch_avail(abub_ctx* ctx, int slot_first, int nslots, const int* d_avail, bool keep_state = false, bool resume = false);
 #define ABUB_STATUS_PENDING (-100)
 // abub_trigger_early: d_avail (and d_start on the first round) of the range for the next round of frames
 int abub_k2_next_avail(abub_ctx* ctx, int slot_first, int nslots, int next, bool first_round);

@@ -91,7 +91,7 @@ extern "C" void abub_ctx_destroy(abub_ctx* ctx) {
         if (s.h_pinned) cudaFreeHost(s.h_pinned);
     }
     cudaFree(ctx->d_hist); cudaFree(ctx->d_nframes); cudaFree(ctx->d_start); cudaFree(ctx->d_avail); cudaFree(ctx->d_trig);
-    cudaFree(ctx->d_sig); cudaFree(ctx->d_tss); cudaFree(ctx->d_k32_ptrs); cudaFree(ctx->d_slot_ptrs);
+    cudaFree(ctx->d_sig); cudaFree(ctx->d_k2_state); cudaFree(ctx->d_tss); cudaFree(ctx->d_k32_ptrs); cudaFree(ctx->d_slot_ptrs);
     for (int i = 0; i < 4; i++) cudaFree(ctx->d_tmp8[i]);
     cudaFree(ctx->d_hist_tmp);
     cudaFree((void*)ctx->d_gate_tab); cudaFree(ctx->d_gate_hist);
@@ -614,7 +614,7 @@ static int trigger_early_rounds(abub_ctx* ctx, abub_deferred_trigger& d, int upt
         const bool first = d.lo == 0;
         if ((rc = abub_k2_next_avail(ctx, d.first, d.n, d.hi, first))) return rc;
         if ((rc = abub_k1_launch_trigger_range(ctx, d.first, d.n, d.lo, d.hi, ctx->d_avail, first))) return rc;
-        if ((rc = abub_k2_launch_avail(ctx, d.first, d.n, ctx->d_avail))) return rc;
+        if ((rc = abub_k2_launch_avail(ctx, d.first, d.n, ctx->d_avail, true, !first))) return rc;
         d.lo = d.hi;
         d.hi += d.chunk;
         if (d.lo >= d.nf_max) d.done = true;

@@ -25,6 +25,16 @@ struct WarpScratch {
 
 __device__ __forceinline__ double wrapsq(uint32_t c) { return (double)(int32_t)(c * c); }
 
+// A search that stopped for want of frames (ABUB_STATUS_PENDING in the early-exit rounds of abub_trigger_early), kept so that
+// the next round continues where it stopped instead of replaying frames 1..i: the history sums exactly as the replay would
+// leave them (same additions in the same order), the frame to go on with, and whether that frame is already in the sums
+// (the search stopped inside its look-ahead).  next_i == 0: nothing kept.
+struct K2State {
+    double s1[256];
+    double s2[256];
+    int next_i, added, scanned, loc_thres;
+};
+
 // Evaluates one histogram row against the current history.  Returns the significance on
 // all lanes; first_over / max_adc as the reference tracks them (:483-485).
 __device__ double significance(const uint32_t* __restrict__ Hrow, WarpScratch* ws, int n, int lane,
@@ -111,7 +121,8 @@ __global__ void __launch_bounds__(32 * K2_WARPS)
 k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict__ nframes,
                        const int* __restrict__ start, const int* __restrict__ tss_cam,
                        int* __restrict__ result, double* __restrict__ sig_out, int slot_first, int nslots,
-                       int ncams, int max_frames, const int* __restrict__ avail, int metric, float thr0, float inv_npix) {
+                       int ncams, int max_frames, const int* __restrict__ avail, int metric, float thr0, float inv_npix,
+                       K2State* __restrict__ state, int resume) {
     __shared__ WarpScratch scratch[K2_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int item = blockIdx.x * K2_WARPS + warp;
@@ -128,10 +139,15 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
     const int av = avail ? min(avail[sc], nf) : nf;
     if (avail && avail[sc] <= 0) return;                          // finished earlier (or nothing resident): leave its results
     const int tss = tss_cam[cam];
-    for (int f = lane; f < max_frames; f += 32) so[f] = 0.0;
+    // the significance searches of abub_trigger_early keep their state between rounds (`state`); `resume`: this is a later round
+    K2State* const stp = (state && metric == ABUB_METRIC_SIGNIFICANCE) ? state + sc : nullptr;
+    const bool resumed = stp && resume && stp->next_i > 0;
+    if (!resumed)
+        for (int f = lane; f < max_frames; f += 32) so[f] = 0.0;
 
     if (nf < 5) {                                                 // :122-126
         if (lane == 0) { res[0] = 0; res[1] = -9; res[2] = -1; res[3] = 0; }
+        if (stp && lane == 0) stp->next_i = 0;
         return;
     }
     int s = start[sc];
@@ -142,32 +158,49 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
     EntropyHistory eh;
     if (metric == ABUB_METRIC_ENTROPY_SIGNIFICANCE)
         for (int f = 1; f < s && f < nf; f++) eh.push((double)entropy128(H + (size_t)f * 256, ws, inv_npix, lane));
+    int status = -3, trig = 0, loc_thres = -1, scanned = 0;      // :180
+    int i_first = s, i_added = -1;                                // i_added: this frame is already in the sums
+    if (resumed) {
 #pragma unroll
-    for (int q = 0; q < 8; q++) {
-        const int b = q * 32 + lane;
-        double a1 = 0.0, a2 = 0.0;
-        for (int f = 1; f < s && f < nf; f++) {
-            const uint32_t c = H[(size_t)f * 256 + b];
-            a1 += (double)c;
-            a2 += wrapsq(c);
+        for (int q = 0; q < 8; q++) {
+            const int b = q * 32 + lane;
+            ws->s1[b] = stp->s1[b];
+            ws->s2[b] = stp->s2[b];
         }
-        ws->s1[b] = a1;
-        ws->s2[b] = a2;
+        i_first = stp->next_i;
+        if (stp->added) i_added = i_first;
+        scanned = stp->scanned;
+        loc_thres = stp->loc_thres;
+    } else {
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const int b = q * 32 + lane;
+            double a1 = 0.0, a2 = 0.0;
+            for (int f = 1; f < s && f < nf; f++) {
+                const uint32_t c = H[(size_t)f * 256 + b];
+                a1 += (double)c;
+                a2 += wrapsq(c);
+            }
+            ws->s1[b] = a1;
+            ws->s2[b] = a2;
+        }
     }
     __syncwarp();
 
-    int status = -3, trig = 0, loc_thres = -1, scanned = 0;      // :180
-    for (int i = s; i < nf; i++) {                                // :191
-        if (i >= av) { status = ABUB_STATUS_PENDING; break; }
+    int keep_i = 0, keep_added = 0;                               // where a PENDING search goes on
+    for (int i = i_first; i < nf; i++) {                          // :191
+        if (i >= av) { status = ABUB_STATUS_PENDING; keep_i = i; keep_added = 0; break; }
         const uint32_t* Hi = H + (size_t)i * 256;
         double sg;
         if (metric == ABUB_METRIC_SIGNIFICANCE) {
+            if (i != i_added) {
 #pragma unroll
-            for (int q = 0; q < 8; q++) {                         // store = true (:461)
-                const int b = q * 32 + lane;
-                const uint32_t c = Hi[b];
-                ws->s1[b] += (double)c;
-                ws->s2[b] += wrapsq(c);
+                for (int q = 0; q < 8; q++) {                     // store = true (:461)
+                    const int b = q * 32 + lane;
+                    const uint32_t c = Hi[b];
+                    ws->s1[b] += (double)c;
+                    ws->s2[b] += wrapsq(c);
+                }
             }
             __syncwarp();
             int fo, madc;
@@ -182,14 +215,14 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
             else sg = e;
             loc_thres = 3;                                        // never updated on these paths (:29)
         }
-        scanned++;
+        if (i != i_added) scanned++;                              // a frame met again after a stop in its look-ahead counts once
         if (lane == 0) so[i] = sg;
         float single = (float)sg;
         if (single > thr && i >= 2) {                             // :254
             if (i != nf - 1) {                                    // :261
                 double max_so_far = (double)single;              // :280
                 for (int ii = 1; ii <= 2 && ii + i < nf; ii++) {  // :282
-                    if (i + ii >= av) { status = ABUB_STATUS_PENDING; break; }
+                    if (i + ii >= av) { status = ABUB_STATUS_PENDING; keep_i = i; keep_added = 1; break; }
                     int fo2, madc2;
                     double s2v;                                   // :290-292  (store = false)
                     if (metric == ABUB_METRIC_SIGNIFICANCE) {
@@ -210,6 +243,20 @@ k2_trigger_scan_kernel(const uint32_t* __restrict__ hist, const int* __restrict_
         }
     }
     if (lane == 0) { res[0] = trig; res[1] = status; res[2] = loc_thres; res[3] = scanned; }
+    if (stp) {
+        if (status == ABUB_STATUS_PENDING) {
+            __syncwarp();
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                const int b = q * 32 + lane;
+                stp->s1[b] = ws->s1[b];
+                stp->s2[b] = ws->s2[b];
+            }
+            if (lane == 0) { stp->next_i = keep_i; stp->added = keep_added; stp->scanned = scanned; stp->loc_thres = loc_thres; }
+        } else if (lane == 0) {
+            stp->next_i = 0;
+        }
+    }
 }
 
 // Resident early exit (abub_trigger_early): frames a camera may look at in the next round -- none once its search is
@@ -239,12 +286,20 @@ int abub_k2_next_avail(abub_ctx* ctx, int slot_first, int nslots, int next, bool
 
 int abub_k2_launch(abub_ctx* ctx, int slot_first, int nslots) { return abub_k2_launch_avail(ctx, slot_first, nslots, nullptr); }
 
-int abub_k2_launch_avail(abub_ctx* ctx, int slot_first, int nslots, const int* d_avail) {
+// keep_state: the rounds of abub_trigger_early -- a search that stops for want of frames leaves its history sums in
+// ctx->d_k2_state; resume: this is a later round of the same searches (the first round passes false and starts afresh)
+int abub_k2_launch_avail(abub_ctx* ctx, int slot_first, int nslots, const int* d_avail, bool keep_state, bool resume) {
     const int items = nslots * ctx->ncams;
+    if (keep_state && !ctx->d_k2_state) {
+        const size_t n = (size_t)ctx->max_slots * ctx->ncams;
+        ABUB_CHECK_CUDA(ctx, cudaMalloc(&ctx->d_k2_state, n * sizeof(K2State)));
+        ABUB_CHECK_CUDA(ctx, cudaMemsetAsync(ctx->d_k2_state, 0, n * sizeof(K2State), ctx->stream));
+    }
     abub_prof_scope prof(ctx, ABUB_PROF_K2);
     ABUB_L(ctx), k2_trigger_scan_kernel<<<(items + K2_WARPS - 1) / K2_WARPS, 32 * K2_WARPS, 0, ctx->stream>>>(
         ctx->d_hist, ctx->d_nframes, ctx->d_start, ctx->d_tss, ctx->d_trig, ctx->d_sig, slot_first, nslots,
-        ctx->ncams, ctx->max_frames, d_avail, ctx->trig_metric, ctx->trig_thr, (float)(1.0 / (double)ctx->npix));
+        ctx->ncams, ctx->max_frames, d_avail, ctx->trig_metric, ctx->trig_thr, (float)(1.0 / (double)ctx->npix),
+        keep_state ? reinterpret_cast<K2State*>(ctx->d_k2_state) : nullptr, resume ? 1 : 0);
     ABUB_CHECK_CUDA(ctx, cudaGetLastError());
     return ABUB_OK;
 }
